@@ -1,0 +1,247 @@
+/*
+ * t4c.h -- C ABI of the B200-native collision-query engine ("tesseract_b200").
+ *
+ * This is the drop-in boundary for ONE hot path of ros-industrial-consortium/tesseract
+ * (v0.5.0): batched discrete and continuous (cast-hull) contact tests of a kinematic
+ * robot against itself and its environment.  Everything here is plain C: pointers,
+ * sizes, PODs.  No torch / Eigen / Bullet types.  The C++ classes in
+ * tesseract_b200/csrc/b200_contact_managers.h (DiscreteContactManager /
+ * ContinuousContactManager implementations) and the Python test tooling both sit on
+ * top of exactly these entry points.
+ *
+ * Reference interfaces each entry replaces (paths relative to the reference checkout):
+ *   t4c_scene_create / _clone / _destroy
+ *       DiscreteContactManager::addCollisionObject / clone
+ *       tesseract_collision/include/tesseract_collision/core/discrete_contact_manager.h:65-110
+ *       (shape conversion rules: tesseract_collision/src/bullet/bullet_utils.cpp:59-365)
+ *   t4c_scene_set_active / _set_enabled / _set_acm / _set_margins / _set_link_pose
+ *       setActiveCollisionObjects / enable|disableCollisionObject / setIsContactAllowedFn /
+ *       setCollisionMarginData / setCollisionObjectsTransform (static links)
+ *       discrete_contact_manager.h:112-200, continuous_contact_manager.h:112-250
+ *   t4c_fk_model_create, t4c_fk
+ *       StateSolver::getState (tesseract_environment/src/kdl/kdl_state_solver.cpp:144-161,232-258)
+ *       ForwardKinematics::calcFwdKinAll (tesseract_kinematics/src/kdl/kdl_fwd_kin_chain.cpp:71-106)
+ *   t4c_check_discrete / t4c_check_link_poses_discrete
+ *       checkTrajectoryState + DiscreteContactManager::contactTest
+ *       (tesseract_environment/include/tesseract_environment/core/utils.h:129-160;
+ *        tesseract_collision/src/bullet/bullet_discrete_bvh_manager.cpp:267-283)
+ *   t4c_check_cast / t4c_check_link_poses_cast / t4c_check_trajectories_cast
+ *       checkTrajectorySegment / checkTrajectory(LVS_CONTINUOUS) + ContinuousContactManager::contactTest
+ *       (core/utils.h:87-119,172-297; tesseract_collision/src/bullet/bullet_cast_bvh_manager.cpp:260-332,446-462)
+ *   t4c_check_trajectories_discrete
+ *       checkTrajectory(LVS_DISCRETE) (core/utils.h:309-428)
+ *
+ * Threading: one t4c_scene per host thread (the reference's "clone per thread" rule,
+ * discrete_contact_manager.h:59-65).  All calls are synchronous unless a stream is given.
+ * There is NO CPU fallback: every compute entry fails with T4C_ERR_CUDA when no device
+ * is usable.
+ */
+#ifndef T4C_H_
+#define T4C_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define T4C_ABI_VERSION 1
+
+typedef int32_t t4c_status;
+enum {
+  T4C_OK = 0,
+  T4C_ERR_INVALID = -1,     /* bad argument / inconsistent description */
+  T4C_ERR_CUDA = -2,        /* CUDA runtime error or no device; see t4c_last_error() */
+  T4C_ERR_CAPACITY = -3,    /* contact buffer too small: n_contacts holds the required count */
+  T4C_ERR_UNSUPPORTED = -4, /* e.g. cast check of a non-convex leaf (reference throws runtime_error) */
+  T4C_ERR_NOMEM = -5
+};
+
+/* Shape kinds after the reference's conversion rules (bullet_utils.cpp:59-243):
+ * Mesh -> one T4C_TRIANGLE per face, Octree -> one BOX / SPHERE per occupied leaf. */
+enum {
+  T4C_SPHERE = 0,   /* params[0] = r (core is a point, margin r) */
+  T4C_BOX = 1,      /* params = half extents */
+  T4C_CYLINDER = 2, /* Z axis; params[0] = r, params[1] = half length */
+  T4C_CONE = 3,     /* Z axis, origin at mid height; params[0] = r, params[1] = height */
+  T4C_CAPSULE = 4,  /* Z axis; params[0] = r, params[1] = half length of the core segment */
+  T4C_HULL = 5,     /* convex vertex cloud: vertex_offset / vertex_count */
+  T4C_TRIANGLE = 6  /* 3 vertices at vertex_offset */
+};
+
+typedef struct t4c_shape {
+  int32_t type;
+  int32_t link;          /* owning link */
+  int32_t shape_id;      /* ContactResult::shape_id  (index in the link's geometry list) */
+  int32_t subshape_id;   /* ContactResult::subshape_id (triangle / voxel index) or -1 */
+  double params[3];
+  int32_t vertex_offset; /* into t4c_scene_desc::vertices (HULL, TRIANGLE) */
+  int32_t vertex_count;
+  double pose[12];       /* shape pose in the link frame, 3x4 row-major [R|p] */
+} t4c_shape;
+
+typedef struct t4c_link {
+  const char* name; /* used only for diagnostics; pair keys are built by the caller */
+  int32_t type_id;  /* user mask id (ContactResult::type_id) */
+  int32_t enabled;
+  int32_t active;   /* 1: kinematic (pose given per state); 0: static */
+  double pose[12];  /* world pose (static links; start pose for active links) */
+} t4c_link;
+
+typedef struct t4c_scene_desc {
+  int32_t n_links;
+  const t4c_link* links;
+  int32_t n_shapes;
+  const t4c_shape* shapes;
+  int32_t n_vertices;
+  const double* vertices;         /* xyz triples */
+  int32_t n_acm_pairs;
+  const int32_t* acm_pairs;       /* 2*n link indices: contact allowed => pair never tested */
+  double default_margin;          /* CollisionMarginData default */
+  int32_t n_margin_pairs;
+  const int32_t* margin_pairs;    /* 2*n link indices */
+  const double* margin_values;    /* n per-pair margins */
+} t4c_scene_desc;
+
+enum { T4C_JOINT_FIXED = 0, T4C_JOINT_REVOLUTE = 1, T4C_JOINT_PRISMATIC = 2 };
+
+typedef struct t4c_joint {
+  int32_t type;
+  int32_t parent_link;
+  int32_t child_link;
+  int32_t q_index;   /* column of the joint vector, -1 for fixed joints */
+  double origin[12]; /* parent_to_joint_origin_transform, 3x4 row-major */
+  double axis[3];
+} t4c_joint;
+
+/* Joints must be ordered parent-before-child.  Links that no joint reaches keep their
+ * scene pose.  root_link's pose is taken from the scene (t4c_link::pose). */
+typedef struct t4c_fk_model_desc {
+  int32_t n_links;
+  int32_t n_joints;
+  const t4c_joint* joints;
+  int32_t n_q;
+  int32_t root_link;
+} t4c_fk_model_desc;
+
+enum { T4C_TEST_FIRST = 0, T4C_TEST_CLOSEST = 1, T4C_TEST_ALL = 2 };
+
+typedef struct t4c_request {
+  int32_t type;                  /* ContactTestType */
+  int32_t calculate_penetration; /* ContactRequest::calculate_penetration */
+  int32_t calculate_distance;    /* ContactRequest::calculate_distance */
+} t4c_request;
+
+enum { T4C_CC_NONE = 0, T4C_CC_TIME0 = 1, T4C_CC_TIME1 = 2, T4C_CC_BETWEEN = 3 };
+
+/* One contact, 80 bytes, 16-byte aligned (five 128-bit stores on the device). */
+typedef struct t4c_contact {
+  int32_t state;          /* state index (discrete) or sub-segment index (cast) */
+  int32_t link[2];
+  int32_t subshape_id[2];
+  int16_t shape_id[2];
+  float distance;
+  float point[2][3];      /* nearest points on link[0], link[1]; world frame */
+  float normal[3];        /* from link[0] towards link[1] */
+  float cc_time[2];       /* cast only, else -1 */
+  uint8_t cc_type[2];     /* T4C_CC_* */
+  uint8_t reserved[2];
+  uint32_t flags;         /* bit 0: produced by the penetration (EPA) pass */
+} t4c_contact;
+
+typedef struct t4c_stats {
+  uint64_t states;          /* states / sub-segments processed */
+  uint64_t bvh_nodes;       /* wide-BVH node visits */
+  uint64_t candidates;      /* (shape, shape) pairs passing the AABB + filter tests */
+  uint64_t culled;          /* candidates rejected by the bounding-sphere pretest */
+  uint64_t gjk_pairs;       /* pairs entering GJK */
+  uint64_t gjk_iterations;  /* support-pair evaluations in GJK */
+  uint64_t epa_pairs;       /* pairs entering EPA */
+  uint64_t epa_iterations;
+  uint64_t contacts;        /* records emitted */
+  uint64_t colliding_states;
+} t4c_stats;
+
+typedef struct t4c_scene t4c_scene;
+typedef struct t4c_fk_model t4c_fk_model;
+
+/* Host-buffer result view (caller owns all memory). */
+typedef struct t4c_result {
+  uint8_t* hit;          /* optional, n bytes: 1 if the state has >=1 accepted contact */
+  t4c_contact* contacts; /* optional, capacity records */
+  int64_t capacity;
+  int64_t n_contacts;    /* out */
+  t4c_stats stats;       /* out */
+} t4c_result;
+
+/* Device-buffer variant: every pointer is a device pointer on the scene's device. */
+enum { T4C_Q_F32_SOA = 0, T4C_Q_F64_ROWMAJOR = 1, T4C_Q_F32_ROWMAJOR = 2 };
+typedef struct t4c_device_io {
+  const void* q;          /* joint states, layout per q_layout; SoA: q[j*n + i] */
+  int32_t q_layout;
+  uint8_t* hit;           /* optional */
+  t4c_contact* contacts;  /* optional */
+  int64_t capacity;
+  uint64_t* counters;     /* device t4c_stats (10 x u64), zeroed by the call */
+  void* stream;           /* cudaStream_t or NULL */
+} t4c_device_io;
+
+const char* t4c_last_error(void);
+int32_t t4c_abi_version(void);
+int32_t t4c_device_count(void);
+
+t4c_status t4c_scene_create(const t4c_scene_desc* desc, int32_t device, t4c_scene** out);
+t4c_status t4c_scene_clone(const t4c_scene* scene, t4c_scene** out);
+void t4c_scene_destroy(t4c_scene* scene);
+t4c_status t4c_scene_set_active(t4c_scene* scene, const int32_t* active_flags /* n_links */);
+t4c_status t4c_scene_set_enabled(t4c_scene* scene, int32_t link, int32_t enabled);
+t4c_status t4c_scene_set_acm(t4c_scene* scene, int32_t n_pairs, const int32_t* pairs);
+t4c_status t4c_scene_set_margins(t4c_scene* scene, double default_margin, int32_t n_pairs,
+                                 const int32_t* pairs, const double* values);
+t4c_status t4c_scene_set_link_pose(t4c_scene* scene, int32_t link, const double* pose12);
+int32_t t4c_scene_num_active(const t4c_scene* scene); /* kinematic links, ascending link index */
+
+t4c_status t4c_fk_model_create(const t4c_fk_model_desc* desc, const t4c_scene* scene, t4c_fk_model** out);
+void t4c_fk_model_destroy(t4c_fk_model* model);
+
+/* Batched forward kinematics: q is n x n_q row-major doubles (host); out is n x n_links x 12 doubles. */
+t4c_status t4c_fk(const t4c_fk_model* model, const double* q, int64_t n, double* link_poses);
+
+/* Discrete batched check: FK + self + environment test of n joint vectors (host buffers). */
+t4c_status t4c_check_discrete(t4c_scene* scene, const t4c_fk_model* model, const double* q, int64_t n,
+                              const t4c_request* request, t4c_result* result);
+/* Same, FK bypassed: poses = n x n_active x 12 doubles (active links in ascending link index). */
+t4c_status t4c_check_link_poses_discrete(t4c_scene* scene, const double* poses, int64_t n,
+                                         const t4c_request* request, t4c_result* result);
+/* Cast check of n independent segments q0[i] -> q1[i] (each n x n_q row-major). */
+t4c_status t4c_check_cast(t4c_scene* scene, const t4c_fk_model* model, const double* q0, const double* q1,
+                          int64_t n, const t4c_request* request, t4c_result* result);
+t4c_status t4c_check_link_poses_cast(t4c_scene* scene, const double* poses0, const double* poses1, int64_t n,
+                                     const t4c_request* request, t4c_result* result);
+/* LVS trajectory checks (core/utils.h:172-428): traj is n_traj x n_wp x n_q row-major doubles.
+ * Work items are LVS sub-states (discrete) / sub-segments (cast); result contact.state is the
+ * flat work-item index; item_traj / item_step (optional, capacity n_items_cap) map items back to
+ * (trajectory, waypoint step).  n_items receives the item count. */
+t4c_status t4c_check_trajectories_discrete(t4c_scene* scene, const t4c_fk_model* model, const double* traj,
+                                           int64_t n_traj, int32_t n_wp, double lvs, const t4c_request* request,
+                                           t4c_result* result, int64_t* n_items);
+t4c_status t4c_check_trajectories_cast(t4c_scene* scene, const t4c_fk_model* model, const double* traj,
+                                       int64_t n_traj, int32_t n_wp, double lvs, const t4c_request* request,
+                                       t4c_result* result, int64_t* n_items);
+
+/* Device-resident entries (inputs already in HBM; used by bench.py "value" and by multi-GPU
+ * callers that gather with NCCL themselves). */
+t4c_status t4c_check_discrete_device(t4c_scene* scene, const t4c_fk_model* model, int64_t n,
+                                     const t4c_request* request, const t4c_device_io* io);
+t4c_status t4c_check_cast_device(t4c_scene* scene, const t4c_fk_model* model, int64_t n /* segments */,
+                                 const void* q1, const t4c_request* request, const t4c_device_io* io);
+/* number of this library's kernel launches since load (bench.py "gpu_launches") */
+uint64_t t4c_kernel_launch_count(void);
+/* measured-peak helper: runs an FP32 FMA loop on every SM, returns TFLOP/s (roofline denominator) */
+t4c_status t4c_measure_fp32_peak(int32_t device, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* T4C_H_ */
