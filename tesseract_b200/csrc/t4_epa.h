@@ -1,0 +1,374 @@
+/*
+ * t4_epa.h -- penetration depth (minimum translation) of two intersecting convex cores by polytope expansion.
+ *
+ * Computes what btGjkEpaPenetrationDepthSolver::calcPenDepth / btGjkEpaSolver2::Penetration converge to
+ * (called at tesseract_collision/src/bullet/tesseract_gjk_pair_detector.cpp:1024-1032; Bullet itself is an
+ * un-vendored dependency): the face of the Minkowski difference A-B closest to the origin.
+ * Differences from a literal port, all result-preserving at convergence:
+ *   - margins (sphere / capsule radii, also of cast shapes) are NOT put into the support: the penetration depth of
+ *     two ball-inflated cores is depth(cores) + rA + rB along the same normal, so the polytope stays finite and the
+ *     expansion terminates exactly for sphere / capsule / box / hull / triangle pairs;
+ *   - iterative visible-set marking with an explicit horizon instead of Bullet's recursive silhouette walk
+ *     (no device recursion, bounded stack);
+ *   - fixed-capacity vertex / face pools in thread-local memory with slot reuse.
+ */
+#ifndef T4_EPA_H_
+#define T4_EPA_H_
+
+#include "t4_gjk.h"
+
+namespace t4
+{
+template <class T>
+struct EpaResult
+{
+  V3<T> normal;  // outward normal of the closest face of A-B (unit)
+  T depth;       // distance of that face from the origin (>= 0)
+  V3<T> pA;      // witness on core A (world frame of the inputs)
+  int iterations;
+  bool converged;
+};
+
+template <class T, int MAXV = 80, int MAXF = 160>
+struct Epa
+{
+  struct Face
+  {
+    V3<T> n;
+    T d;
+    int16_t v[3];
+    int16_t adj[3];
+    int16_t mark;
+    int16_t alive;
+  };
+  V3<T> W[MAXV], P[MAXV];
+  Face F[MAXF];
+  int nv, nf_hi;         // vertices used; high-water mark of face slots
+  int16_t free_list[MAXF];
+  int n_free;
+  int16_t stack[MAXF], visible[MAXF];
+  int16_t hz_a[MAXF], hz_b[MAXF], hz_g[MAXF];
+
+  const ShapeW<T>* A;
+  const ShapeW<T>* B;
+
+  T4_HD void support(const V3<T>& d, V3<T>& w, V3<T>& p) const
+  {
+    p = supportW(*A, d, false);
+    w = p - supportW(*B, -d, false);
+  }
+  T4_HD static T det3(const V3<T>& a, const V3<T>& b, const V3<T>& c) { return a.dot(b.cross(c)); }
+
+  T4_HD bool pushSupport(const V3<T>& d)
+  {
+    if (nv >= MAXV)
+      return false;
+    support(d, W[nv], P[nv]);
+    ++nv;
+    return true;
+  }
+  // btGjkEpaSolver2 GJK::EncloseOrigin: grow the simplex (W[0..nv)) to a non-degenerate tetrahedron
+  T4_HD bool enclose4() const { return t4abs(det3(W[0] - W[3], W[1] - W[3], W[2] - W[3])) > T(0); }
+  T4_HD bool enclose3()
+  {
+    const V3<T> n = (W[1] - W[0]).cross(W[2] - W[0]);
+    if (n.len2() > T(0))
+    {
+      pushSupport(n);
+      if (enclose4())
+        return true;
+      --nv;
+      pushSupport(-n);
+      if (enclose4())
+        return true;
+      --nv;
+    }
+    return false;
+  }
+  T4_HD bool enclose2()
+  {
+    const V3<T> d = W[1] - W[0];
+    for (int i = 0; i < 3; ++i)
+    {
+      V3<T> axis(0, 0, 0);
+      axis.set(i, 1);
+      const V3<T> p = d.cross(axis);
+      if (p.len2() > T(0))
+      {
+        pushSupport(p);
+        if (enclose3())
+          return true;
+        --nv;
+        pushSupport(-p);
+        if (enclose3())
+          return true;
+        --nv;
+      }
+    }
+    return false;
+  }
+  T4_HD bool enclose1()
+  {
+    for (int i = 0; i < 3; ++i)
+    {
+      V3<T> axis(0, 0, 0);
+      axis.set(i, 1);
+      pushSupport(axis);
+      if (enclose2())
+        return true;
+      --nv;
+      pushSupport(-axis);
+      if (enclose2())
+        return true;
+      --nv;
+    }
+    return false;
+  }
+
+  T4_HD bool makeFace(int a, int b, int c, Face& f) const
+  {
+    f.v[0] = (int16_t)a, f.v[1] = (int16_t)b, f.v[2] = (int16_t)c;
+    f.adj[0] = f.adj[1] = f.adj[2] = -1;
+    const V3<T> n = (W[b] - W[a]).cross(W[c] - W[a]);
+    const T l = n.len();
+    if (!(l > T(1e-20)))
+      return false;
+    f.n = n * (T(1) / l);
+    f.d = f.n.dot(W[a]);
+    f.alive = 1;
+    f.mark = 0;
+    return true;
+  }
+  T4_HD int allocFace()
+  {
+    if (n_free > 0)
+      return free_list[--n_free];
+    if (nf_hi < MAXF)
+      return nf_hi++;
+    return -1;
+  }
+  T4_HD static int edgeIndex(const Face& g, int from, int to)
+  {
+    for (int e = 0; e < 3; ++e)
+      if (g.v[e] == from && g.v[(e + 1) % 3] == to)
+        return e;
+    return -1;
+  }
+
+  // simplex: up to 4 points of A-B (and their A witnesses) around the origin, from the GJK that found the overlap
+  T4_HD bool run(const ShapeW<T>& a, const ShapeW<T>& b, const V3<T>* sw, const V3<T>* sp, int rank, int max_iter,
+                 T tol, EpaResult<T>& res)
+  {
+    A = &a;
+    B = &b;
+    nv = 0;
+    for (int i = 0; i < rank && i < 4; ++i)
+    {
+      W[i] = sw[i];
+      P[i] = sp[i];
+      ++nv;
+    }
+    res.converged = false;
+    res.iterations = 0;
+    bool ok = false;
+    if (nv == 0)
+    {
+      pushSupport(V3<T>(1, 0, 0));
+    }
+    if (nv == 1)
+      ok = enclose1();
+    else if (nv == 2)
+      ok = enclose2();
+    else if (nv == 3)
+      ok = enclose3();
+    else
+      ok = enclose4();
+    if (!ok || nv != 4)
+      return false;
+    if (det3(W[0] - W[3], W[1] - W[3], W[2] - W[3]) < T(0))
+    {
+      V3<T> t = W[0];
+      W[0] = W[1];
+      W[1] = t;
+      t = P[0];
+      P[0] = P[1];
+      P[1] = t;
+    }
+    nf_hi = 0;
+    n_free = 0;
+    const int tet[4][3] = { { 0, 1, 2 }, { 1, 0, 3 }, { 2, 1, 3 }, { 0, 2, 3 } };
+    for (int i = 0; i < 4; ++i)
+    {
+      if (!makeFace(tet[i][0], tet[i][1], tet[i][2], F[i]))
+        return false;
+      ++nf_hi;
+    }
+    for (int i = 0; i < 4; ++i)
+      for (int e = 0; e < 3; ++e)
+        for (int j = 0; j < 4; ++j)
+          if (j != i && edgeIndex(F[j], F[i].v[(e + 1) % 3], F[i].v[e]) >= 0)
+            F[i].adj[e] = (int16_t)j;
+    int mark = 0;
+    int best = -1;
+    int it = 0;
+    for (; it < max_iter; ++it)
+    {
+      best = -1;
+      for (int i = 0; i < nf_hi; ++i)
+        if (F[i].alive && (best < 0 || F[i].d < F[best].d))
+          best = i;
+      if (best < 0)
+        return false;
+      if (nv >= MAXV)
+        break;
+      V3<T> w, p;
+      support(F[best].n, w, p);
+      const T wdist = F[best].n.dot(w) - F[best].d;
+      if (wdist <= tol)
+      {
+        res.converged = true;
+        break;
+      }
+      const int wi = nv;
+      W[nv] = w;
+      P[nv] = p;
+      ++nv;
+      // visible set: flood fill from the closest face
+      ++mark;
+      int sp_ = 0, nvis = 0;
+      stack[sp_++] = (int16_t)best;
+      F[best].mark = (int16_t)mark;
+      while (sp_ > 0)
+      {
+        const int f = stack[--sp_];
+        visible[nvis++] = (int16_t)f;
+        for (int e = 0; e < 3; ++e)
+        {
+          const int g = F[f].adj[e];
+          if (g < 0 || F[g].mark == mark)
+            continue;
+          if (F[g].n.dot(w) - F[g].d > T(1e-14))
+          {
+            F[g].mark = (int16_t)mark;
+            stack[sp_++] = (int16_t)g;
+          }
+        }
+      }
+      // horizon; absorb outside neighbours that would give a zero-area new face
+      int nh = 0;
+      for (int guard = 0; guard < 64; ++guard)
+      {
+        nh = 0;
+        bool grew = false;
+        for (int k = 0; k < nvis && !grew; ++k)
+        {
+          const int f = visible[k];
+          for (int e = 0; e < 3 && !grew; ++e)
+          {
+            const int g = F[f].adj[e];
+            if (g >= 0 && F[g].mark == mark)
+              continue;
+            const int va = F[f].v[e], vb = F[f].v[(e + 1) % 3];
+            const V3<T> n = (W[vb] - W[va]).cross(w - W[va]);
+            if (g >= 0 && n.len() < T(1e-14) * (T(1) + w.len2()) && nvis < MAXF)
+            {
+              F[g].mark = (int16_t)mark;
+              visible[nvis++] = (int16_t)g;
+              grew = true;
+              break;
+            }
+            if (nh < MAXF)
+            {
+              hz_a[nh] = (int16_t)va;
+              hz_b[nh] = (int16_t)vb;
+              hz_g[nh] = (int16_t)g;
+              ++nh;
+            }
+          }
+        }
+        if (!grew)
+          break;
+      }
+      if (nh < 3)
+      {
+        --nv;
+        break;
+      }
+      // capacity check before touching the hull
+      if (nh > (MAXF - nf_hi) + n_free + nvis)
+      {
+        --nv;
+        break;
+      }
+      for (int k = 0; k < nvis; ++k)
+      {
+        F[visible[k]].alive = 0;
+        free_list[n_free++] = visible[k];
+      }
+      // new faces (a, b, w): edge0 = horizon edge, edge1 = (b,w), edge2 = (w,a)
+      bool bad = false;
+      int first_new = -1;
+      // remember the slots of the new faces in `stack` (free again at this point)
+      int nnew = 0;
+      for (int k = 0; k < nh; ++k)
+      {
+        const int slot = allocFace();
+        Face nf;
+        if (slot < 0 || !makeFace(hz_a[k], hz_b[k], wi, nf))
+        {
+          bad = true;
+          break;
+        }
+        nf.adj[0] = hz_g[k];
+        nf.mark = 0;
+        F[slot] = nf;
+        stack[nnew++] = (int16_t)slot;
+        if (first_new < 0)
+          first_new = slot;
+        const int g = hz_g[k];
+        if (g >= 0)
+        {
+          const int ge = edgeIndex(F[g], hz_b[k], hz_a[k]);
+          if (ge >= 0)
+            F[g].adj[ge] = (int16_t)slot;
+        }
+      }
+      if (bad)
+        break;
+      for (int i = 0; i < nnew; ++i)
+        for (int j = 0; j < nnew; ++j)
+        {
+          Face& fi = F[stack[i]];
+          const Face& fj = F[stack[j]];
+          if (fj.v[0] == fi.v[1])
+            fi.adj[1] = stack[j];
+          if (fj.v[1] == fi.v[0])
+            fi.adj[2] = stack[j];
+        }
+    }
+    res.iterations = it;
+    // closest ALIVE face (after a break the stored `best` may have been freed)
+    best = -1;
+    for (int i = 0; i < nf_hi; ++i)
+      if (F[i].alive && (best < 0 || F[i].d < F[best].d))
+        best = i;
+    if (best < 0)
+      return false;
+    const Face& o = F[best];
+    res.normal = o.n;
+    res.depth = o.d;
+    const V3<T> proj = o.n * o.d;
+    T b0 = (W[o.v[1]] - proj).cross(W[o.v[2]] - proj).len();
+    T b1 = (W[o.v[2]] - proj).cross(W[o.v[0]] - proj).len();
+    T b2 = (W[o.v[0]] - proj).cross(W[o.v[1]] - proj).len();
+    const T sum = b0 + b1 + b2;
+    if (!(sum > T(0)))
+      return false;
+    b0 /= sum, b1 /= sum, b2 /= sum;
+    res.pA = P[o.v[0]] * b0 + P[o.v[1]] * b1 + P[o.v[2]] * b2;
+    return true;
+  }
+};
+
+}  // namespace t4
+#endif

@@ -1,0 +1,444 @@
+/*
+ * t4_kernels.h -- per-work-item bodies of every kernel of the batched collision pipeline.
+ *
+ *   fkBody           joint vector -> world poses of the kinematic links          (StateSolver::getState,
+ *                    tesseract_environment/src/kdl/kdl_state_solver.cpp:144-161,232-258; rule ofkt_nodes.cpp:200-289)
+ *   broadStaticBody  (state, active shape) x static-environment BVH -> candidate pairs
+ *                    (btDbvtBroadphase pair set + TesseractOverlapFilterCallback, bullet_utils.h:864-881,170-177)
+ *   broadActiveBody  (state, active-active shape pair) AABB test -> candidate pairs
+ *   cullBody         FP32 GJK lower bound vs. the contact cut-off -> survivors (+ early accept for boolean queries)
+ *   exactBody        FP64 narrowphase + result bridging / processResult
+ *                    (bullet_utils.h:388-441,527-611,757-802 ; core/common.h:114-167)
+ *   closestInsert / closestEmit   ContactTestType::CLOSEST reduction per (state, link pair) key
+ *
+ * The bodies are plain functions of (item index, KParams); t4c.cu wraps them in __global__ kernels for sm_100a.
+ */
+#ifndef T4_KERNELS_H_
+#define T4_KERNELS_H_
+
+#include "../../include/t4c.h"
+#include "t4_pair.h"
+
+namespace t4
+{
+enum
+{
+  ST_STATES = 0,
+  ST_BVH_NODES,
+  ST_CANDIDATES,
+  ST_CULLED,
+  ST_GJK_PAIRS,
+  ST_GJK_ITERS,
+  ST_EPA_PAIRS,
+  ST_EPA_ITERS,
+  ST_CONTACTS,
+  ST_COLLIDING,
+  ST_COUNT
+};
+
+// work-queue counters (u32, device)
+enum
+{
+  Q_CAND = 0,   // candidate pairs appended by the broadphase
+  Q_SURV,       // survivors of the FP32 cull
+  Q_RAW,        // raw contacts (CLOSEST staging) or final contacts (ALL / FIRST)
+  Q_OUT,        // final contacts emitted by the CLOSEST reduction
+  Q_COUNT
+};
+
+#define T4_MAX_JOINTS 64
+
+struct alignas(16) DJoint
+{
+  double origin[12];
+  double axis[3];  // normalised
+  int32_t type, parent_joint, q_index, pad;
+  double pre[12];  // world pose of the parent link when parent_joint < 0
+};
+
+struct KParams
+{
+  // ---- scene (read only)
+  const DShape* shapes;
+  const DStaticW* statics;  // indexed by shape index (valid for static shapes)
+  const f4* verts;
+  const DBvhNode* bvh;
+  int32_t n_bvh_nodes;
+  const int32_t* active_shapes;
+  int32_t n_active_shapes;
+  const int32_t* aa_pairs;
+  int32_t n_aa_pairs;
+  const uint32_t* acm_bits;  // [n_alinks][acm_words]
+  int32_t acm_words;
+  const float* pair_margin;  // [n_alinks][n_links] or null
+  int32_t n_links, n_alinks;
+  float default_margin, max_margin;
+  // ---- FK model
+  const DJoint* joints;
+  int32_t n_joints, n_q;
+  const int32_t* alink_joint;   // [n_alinks] joint index driving the link or -1
+  const double* alink_static;   // [n_alinks][12]
+  const int32_t* link_joint;    // [n_links] (t4c_fk full output) or null
+  const double* link_static;    // [n_links][12]
+  // ---- batch
+  int64_t n;  // states / segments in this chunk
+  int64_t state_base;
+  const void* q0;
+  const void* q1;
+  int32_t q_layout;
+  int64_t q_stride_n;  // total n of the SoA array (SoA layout only)
+  float* poses0;       // [n][n_alinks][12]
+  float* poses1;
+  const double* poses_in0;  // FK bypass input (device, double)
+  const double* poses_in1;
+  double* fk_out;  // t4c_fk
+  int32_t cast;
+  // ---- request
+  int32_t test_type, calc_pen, calc_dist, hit_only;
+  // ---- queues / outputs
+  uint32_t* cand_state;
+  uint32_t* cand_a;
+  uint32_t* cand_b;
+  uint32_t cand_cap;
+  uint32_t* surv;
+  float* surv_axis;
+  uint32_t surv_cap;
+  uint32_t* qcount;       // [Q_COUNT]
+  unsigned long long* stats;  // [ST_COUNT]
+  uint8_t* hit;           // [n] (chunk-relative) or null
+  uint32_t* first_claim;  // [n] FIRST: 0 free / 1 claimed
+  t4c_contact* raw;       // staging (CLOSEST) or final buffer
+  float* raw_local;       // cast: nearest_points_local [cap][6] or null
+  uint32_t raw_cap;
+  t4c_contact* out;       // CLOSEST final
+  float* out_local;
+  uint32_t out_cap;
+  int32_t* ht_rep;        // CLOSEST hash table: representative raw index per slot (-1 empty)
+  unsigned long long* ht_best;
+  uint32_t ht_size;       // power of two
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// device / host-simulator primitives
+// ---------------------------------------------------------------------------------------------------------------
+#ifdef T4_DEVICE_BUILD
+__device__ __forceinline__ uint32_t qAppend(uint32_t* ctr)
+{
+  const unsigned m = __activemask();
+  const int lane = threadIdx.x & 31;
+  const int leader = __ffs(m) - 1;
+  uint32_t base = 0;
+  if (lane == leader)
+    base = atomicAdd(ctr, (uint32_t)__popc(m));
+  base = __shfl_sync(m, base, leader);
+  return base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+}
+__device__ __forceinline__ void statAdd(unsigned long long* stats, int k, uint32_t v)
+{
+  const unsigned m = __activemask();
+  const uint32_t s = __reduce_add_sync(m, v);
+  if ((threadIdx.x & 31) == __ffs(m) - 1 && s)
+    atomicAdd(&stats[k], (unsigned long long)s);
+}
+__device__ __forceinline__ uint32_t casU32(uint32_t* p, uint32_t cmp, uint32_t val) { return atomicCAS(p, cmp, val); }
+__device__ __forceinline__ int32_t casI32(int32_t* p, int32_t cmp, int32_t val) { return atomicCAS(p, cmp, val); }
+__device__ __forceinline__ void minU64(unsigned long long* p, unsigned long long v) { atomicMin(p, v); }
+#else
+inline uint32_t qAppend(uint32_t* ctr) { return (*ctr)++; }
+inline void statAdd(unsigned long long* stats, int k, uint32_t v) { stats[k] += v; }
+inline uint32_t casU32(uint32_t* p, uint32_t cmp, uint32_t val)
+{
+  uint32_t o = *p;
+  if (o == cmp)
+    *p = val;
+  return o;
+}
+inline int32_t casI32(int32_t* p, int32_t cmp, int32_t val)
+{
+  int32_t o = *p;
+  if (o == cmp)
+    *p = val;
+  return o;
+}
+inline void minU64(unsigned long long* p, unsigned long long v)
+{
+  if (v < *p)
+    *p = v;
+}
+#endif
+
+template <class T>
+T4_HD Xf<T> loadPose(const float* p)
+{
+  Xf<T> x;
+  const f4* q = reinterpret_cast<const f4*>(p);
+  const f4 a = q[0], b = q[1], c = q[2];
+  x.r[0] = (T)a.x, x.r[1] = (T)a.y, x.r[2] = (T)a.z, x.p.x = (T)a.w;
+  x.r[3] = (T)b.x, x.r[4] = (T)b.y, x.r[5] = (T)b.z, x.p.y = (T)b.w;
+  x.r[6] = (T)c.x, x.r[7] = (T)c.y, x.r[8] = (T)c.z, x.p.z = (T)c.w;
+  return x;
+}
+
+// world pose(s) of shape `sh` in state s
+template <class T>
+T4_HD void shapePose(const KParams& P, const DShape& S, int sh, int64_t s, Xf<T>& x0, Xf<T>& x1)
+{
+  if (S.alink < 0)
+  {
+    x0 = loadPose<T>(P.statics[sh].pose);
+    x1 = x0;
+    return;
+  }
+  const size_t off = ((size_t)s * (size_t)P.n_alinks + (size_t)S.alink) * 12;
+  x0 = loadPose<T>(P.poses0 + off);
+  if (P.cast)
+    x1 = loadPose<T>(P.poses1 + off);
+  if (!S.identity_lpose)
+  {
+    const Xf<T> l = loadPose<T>(S.lpose);
+    x0 = x0 * l;
+    if (P.cast)
+      x1 = x1 * l;
+  }
+  if (!P.cast)
+    x1 = x0;
+}
+
+T4_HD bool acmAllowed(const KParams& P, int alink, int linkB)
+{
+  return (P.acm_bits[(size_t)alink * P.acm_words + (linkB >> 5)] >> (linkB & 31)) & 1u;
+}
+
+T4_HD float pairMargin(const KParams& P, int alink, int linkB)
+{
+  return P.pair_margin ? P.pair_margin[(size_t)alink * P.n_links + linkB] : P.default_margin;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// FK
+// ---------------------------------------------------------------------------------------------------------------
+T4_HD double loadQ(const KParams& P, const void* q, int64_t s, int j)
+{
+  if (P.q_layout == T4C_Q_F32_SOA)
+    return (double)((const float*)q)[(size_t)j * (size_t)P.q_stride_n + (size_t)s];
+  if (P.q_layout == T4C_Q_F64_ROWMAJOR)
+    return ((const double*)q)[(size_t)s * P.n_q + j];
+  return (double)((const float*)q)[(size_t)s * P.n_q + j];
+}
+
+T4_HD void fkOne(const KParams& P, const void* q, int64_t s, Xf<double>* Tj)
+{
+  for (int j = 0; j < P.n_joints; ++j)
+  {
+    const DJoint& J = P.joints[j];
+    Xf<double> local = Xf<double>::from12(J.origin);
+    if (J.type == T4C_JOINT_REVOLUTE)
+    {
+      // Eigen::AngleAxisd(q, axis.normalized()) (ofkt_nodes.cpp:200,217-219)
+      const double a = loadQ(P, q, s, J.q_index);
+      double sn, cs;
+      sincos(a, &sn, &cs);
+      const double t = 1.0 - cs, x = J.axis[0], y = J.axis[1], z = J.axis[2];
+      Xf<double> rot;
+      rot.r[0] = t * x * x + cs, rot.r[1] = t * x * y - sn * z, rot.r[2] = t * x * z + sn * y;
+      rot.r[3] = t * x * y + sn * z, rot.r[4] = t * y * y + cs, rot.r[5] = t * y * z - sn * x;
+      rot.r[6] = t * x * z - sn * y, rot.r[7] = t * y * z + sn * x, rot.r[8] = t * z * z + cs;
+      local = local * rot;
+    }
+    else if (J.type == T4C_JOINT_PRISMATIC)
+    {
+      // T_origin * Translation(q * axis.normalized()) (ofkt_nodes.cpp:272,287-289)
+      const double a = loadQ(P, q, s, J.q_index);
+      Xf<double> tr;
+      tr.p = V3<double>(J.axis[0] * a, J.axis[1] * a, J.axis[2] * a);
+      local = local * tr;
+    }
+    const Xf<double> parent = J.parent_joint >= 0 ? Tj[J.parent_joint] : Xf<double>::from12(J.pre);
+    Tj[j] = parent * local;
+  }
+}
+
+T4_HD void storePoseF(float* dst, const Xf<double>& x)
+{
+  f4* d = reinterpret_cast<f4*>(dst);
+  f4 a, b, c;
+  a.x = (float)x.r[0], a.y = (float)x.r[1], a.z = (float)x.r[2], a.w = (float)x.p.x;
+  b.x = (float)x.r[3], b.y = (float)x.r[4], b.z = (float)x.r[5], b.w = (float)x.p.y;
+  c.x = (float)x.r[6], c.y = (float)x.r[7], c.z = (float)x.r[8], c.w = (float)x.p.z;
+  d[0] = a, d[1] = b, d[2] = c;
+}
+
+// item = state.  Writes poses0 (and poses1 for cast) of the kinematic links, or fk_out (all links, FP64).
+T4_HD void fkBody(int64_t s, const KParams& P)
+{
+  Xf<double> Tj[T4_MAX_JOINTS];
+  for (int pass = 0; pass < (P.cast ? 2 : 1); ++pass)
+  {
+    fkOne(P, pass ? P.q1 : P.q0, s, Tj);
+    if (P.fk_out)
+    {
+      for (int l = 0; l < P.n_links; ++l)
+      {
+        const int j = P.link_joint[l];
+        const Xf<double> x = j >= 0 ? Tj[j] : Xf<double>::from12(P.link_static + (size_t)l * 12);
+        x.to12(P.fk_out + ((size_t)s * P.n_links + l) * 12);
+      }
+      return;
+    }
+    float* dst = pass ? P.poses1 : P.poses0;
+    for (int a = 0; a < P.n_alinks; ++a)
+    {
+      const int j = P.alink_joint[a];
+      const Xf<double> x = j >= 0 ? Tj[j] : Xf<double>::from12(P.alink_static + (size_t)a * 12);
+      storePoseF(dst + ((size_t)s * P.n_alinks + a) * 12, x);
+    }
+  }
+}
+
+// item = (state, active link): FK bypass, FP64 host poses -> FP32 device poses
+T4_HD void convertPosesBody(int64_t i, const KParams& P)
+{
+  const double* src0 = P.poses_in0 + (size_t)i * 12;
+  storePoseF(P.poses0 + (size_t)i * 12, Xf<double>::from12(src0));
+  if (P.cast)
+    storePoseF(P.poses1 + (size_t)i * 12, Xf<double>::from12(P.poses_in1 + (size_t)i * 12));
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// broadphase
+// ---------------------------------------------------------------------------------------------------------------
+T4_HD bool boxesOverlap(const V3<float>& mn, const V3<float>& mx, const float* bmn, const float* bmx)
+{
+  return !(mn.x > bmx[0] || mx.x < bmn[0] || mn.y > bmx[1] || mx.y < bmn[1] || mn.z > bmx[2] || mx.z < bmn[2]);
+}
+
+T4_HD void shapeWorldBox(const KParams& P, const DShape& S, const Xf<float>& x0, const Xf<float>& x1, V3<float>& mn,
+                         V3<float>& mx)
+{
+  const V3<float> c(S.bc[0], S.bc[1], S.bc[2]), h(S.bh[0], S.bh[1], S.bh[2]);
+  boxAabb(x0, c, h, mn, mx);
+  if (P.cast && S.alink >= 0)
+  {
+    V3<float> mn1, mx1;
+    boxAabb(x1, c, h, mn1, mx1);
+    mn = V3<float>(t4min(mn.x, mn1.x), t4min(mn.y, mn1.y), t4min(mn.z, mn1.z));
+    mx = V3<float>(t4max(mx.x, mx1.x), t4max(mx.y, mx1.y), t4max(mx.z, mx1.z));
+  }
+}
+
+T4_HD void pushCandidate(const KParams& P, int64_t s, int a, int b)
+{
+  const uint32_t k = qAppend(&P.qcount[Q_CAND]);
+  if (k < P.cand_cap)
+  {
+    P.cand_state[k] = (uint32_t)s;
+    P.cand_a[k] = (uint32_t)a;
+    P.cand_b[k] = (uint32_t)b;
+  }
+}
+
+// conservative slack (metres) absorbing FP32 rounding of poses / boxes in every cull
+#define T4_CULL_SLACK 2e-5f
+
+// item = a_ord * n + s  (shape-major, so that a warp works on 32 states of the SAME robot shape)
+T4_HD void broadStaticBody(int64_t item, const KParams& P)
+{
+  const int a_ord = (int)(item / P.n);
+  const int64_t s = item - (int64_t)a_ord * P.n;
+  const int sh = P.active_shapes[a_ord];
+  const DShape& S = P.shapes[sh];
+  Xf<float> x0, x1;
+  shapePose<float>(P, S, sh, s, x0, x1);
+  V3<float> mn, mx;
+  shapeWorldBox(P, S, x0, x1, mn, mx);
+  const float grow = P.max_margin + T4_CULL_SLACK;
+  mn = mn - V3<float>(grow, grow, grow);
+  mx = mx + V3<float>(grow, grow, grow);
+  const V3<float> bc(S.bc[0], S.bc[1], S.bc[2]), bh(S.bh[0], S.bh[1], S.bh[2]);
+  const V3<float> cw = x0(bc);
+  const float ra = S.bc[3];
+  uint32_t nodes = 0, culled = 0, cands = 0;
+  int stack[64];
+  int sp = 0;
+  stack[sp++] = 0;
+  while (sp > 0)
+  {
+    const int ni = stack[--sp];
+    const DBvhNode& N = P.bvh[ni];
+    ++nodes;
+    for (int side = 0; side < 2; ++side)
+    {
+      const float* bmn = side ? N.rmn : N.lmn;
+      const float* bmx = side ? N.rmx : N.lmx;
+      if (!boxesOverlap(mn, mx, bmn, bmx))
+        continue;
+      const int child = side ? N.right : N.left;
+      if (child >= 0)
+      {
+        if (sp < 64)
+          stack[sp++] = child;
+        continue;
+      }
+      const int b = ~child;
+      const DShape& Sb = P.shapes[b];
+      if (Sb.link == S.link || acmAllowed(P, S.alink, Sb.link))
+        continue;
+      if (!P.cast)
+      {
+        // bounding-sphere and link-frame box culls (exact tests follow in the narrowphase)
+        const DStaticW& W = P.statics[b];
+        const V3<float> cb(W.bs[0], W.bs[1], W.bs[2]);
+        const float reach = W.bs[3] + grow;
+        const V3<float> d = cb - cw;
+        const float rr = ra + reach;
+        if (d.len2() > rr * rr)
+        {
+          ++culled;
+          continue;
+        }
+        const V3<float> pl = x0.invApply(cb) - bc;
+        const V3<float> e(t4max(t4abs(pl.x) - bh.x, 0.f), t4max(t4abs(pl.y) - bh.y, 0.f),
+                          t4max(t4abs(pl.z) - bh.z, 0.f));
+        if (e.len2() > reach * reach)
+        {
+          ++culled;
+          continue;
+        }
+      }
+      ++cands;
+      pushCandidate(P, s, sh, b);
+    }
+  }
+  statAdd(P.stats, ST_BVH_NODES, nodes);
+  statAdd(P.stats, ST_CULLED, culled);
+  statAdd(P.stats, ST_CANDIDATES, cands + culled);
+}
+
+// item = pair * n + s ; pairs are (active shape, active shape) of two different links, ACM-filtered on the host
+T4_HD void broadActiveBody(int64_t item, const KParams& P)
+{
+  const int pr = (int)(item / P.n);
+  const int64_t s = item - (int64_t)pr * P.n;
+  const int a = P.aa_pairs[2 * pr], b = P.aa_pairs[2 * pr + 1];
+  const DShape& Sa = P.shapes[a];
+  const DShape& Sb = P.shapes[b];
+  Xf<float> a0, a1, b0, b1;
+  shapePose<float>(P, Sa, a, s, a0, a1);
+  shapePose<float>(P, Sb, b, s, b0, b1);
+  V3<float> amn, amx, bmn, bmx;
+  shapeWorldBox(P, Sa, a0, a1, amn, amx);
+  shapeWorldBox(P, Sb, b0, b1, bmn, bmx);
+  const float grow = P.max_margin + T4_CULL_SLACK;
+  amn = amn - V3<float>(grow, grow, grow);
+  amx = amx + V3<float>(grow, grow, grow);
+  uint32_t cands = 0;
+  if (!(amn.x > bmx.x || amx.x < bmn.x || amn.y > bmx.y || amx.y < bmn.y || amn.z > bmx.z || amx.z < bmn.z))
+  {
+    cands = 1;
+    pushCandidate(P, s, a, b);
+  }
+  statAdd(P.stats, ST_CANDIDATES, cands);
+}
+
+}  // namespace t4
+#endif

@@ -1,0 +1,292 @@
+/*
+ * t4_kernels2.h -- narrowphase kernel bodies: FP32 cull, FP64 exact query + result bridging, CLOSEST reduction.
+ * See t4_kernels.h for the pipeline overview and reference citations.
+ */
+#ifndef T4_KERNELS2_H_
+#define T4_KERNELS2_H_
+
+#include "t4_kernels.h"
+
+namespace t4
+{
+template <class T>
+T4_HD void loadPairShapes(const KParams& P, int64_t s, int a, int b, ShapeW<T>& A, ShapeW<T>& B)
+{
+  const DShape& Sa = P.shapes[a];
+  const DShape& Sb = P.shapes[b];
+  Xf<T> a0, a1, b0, b1;
+  shapePose<T>(P, Sa, a, s, a0, a1);
+  shapePose<T>(P, Sb, b, s, b0, b1);
+  A = makeShapeW<T>(Sa, P.verts, a0, a1, P.cast && Sa.alink >= 0);
+  B = makeShapeW<T>(Sb, P.verts, b0, b1, P.cast && Sb.alink >= 0);
+}
+
+T4_HD bool analyticPair(int ta, int tb)
+{
+  if (ta == SH_SPHERE && (tb == SH_SPHERE || tb == SH_TRIANGLE || tb == SH_CAPSULE))
+    return true;
+  if (ta == SH_TRIANGLE && tb == SH_SPHERE)
+    return true;
+  if (ta == SH_CAPSULE && (tb == SH_CAPSULE || tb == SH_SPHERE))
+    return true;
+  return false;
+}
+
+T4_HD void pushSurvivor(const KParams& P, uint32_t c, const V3<float>& axis)
+{
+  const uint32_t k = qAppend(&P.qcount[Q_SURV]);
+  if (k < P.surv_cap)
+  {
+    P.surv[k] = c;
+    P.surv_axis[3 * (size_t)k + 0] = axis.x;
+    P.surv_axis[3 * (size_t)k + 1] = axis.y;
+    P.surv_axis[3 * (size_t)k + 2] = axis.z;
+  }
+}
+
+// item = candidate index.  FP32 GJK used ONLY to discard pairs that are provably farther apart than the contact
+// cut-off (and, for boolean FIRST queries without contact output, to accept pairs that are provably inside it).
+// Everything that is reported goes through exactBody.
+T4_HD void cullBody(int64_t c, const KParams& P)
+{
+  const int64_t s = P.cand_state[c];
+  // FIRST (or flags-only output): the state already has its contact (ContactTestData::done, core/common.h:129-133)
+  if ((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit && P.hit[s])
+    return;
+  const int a = (int)P.cand_a[c], b = (int)P.cand_b[c];
+  ShapeW<float> A, B;
+  loadPairShapes<float>(P, s, a, b, A, B);
+  const V3<float> axis0 = A.x0.p - B.x0.p;
+  if (!A.cast && !B.cast && analyticPair(A.type, B.type))
+  {
+    pushSurvivor(P, (uint32_t)c, axis0);
+    return;
+  }
+  const V3<float> offset = (A.x0.p + B.x0.p) * 0.5f;
+  A.x0.p -= offset;
+  A.x1.p -= offset;
+  B.x0.p -= offset;
+  B.x1.p -= offset;
+  const float msum = A.innerMargin() + B.innerMargin();
+  const float cutoff = msum + P.max_margin + T4_CULL_SLACK;
+  float accept = cutoff;  // anything within the cut-off is decided by the exact pass
+  bool bool_mode = false;
+  if (P.hit_only && P.calc_dist)
+  {
+    const float pm = t4min(pairMargin(P, P.shapes[a].alink, P.shapes[b].link), P.max_margin);
+    accept = msum + pm - T4_CULL_SLACK;
+    bool_mode = accept > 0.f;
+    if (!bool_mode)
+      accept = cutoff;
+  }
+  if (!P.calc_dist)
+    accept = -1.f;  // separated cores are never reported (tesseract_gjk_pair_detector.cpp:830-834)
+  GjkOut<float, false> g;
+  const int st = gjkDistance<float, false>(A, B, axis0, false, cutoff, accept, g, 48);
+  statAdd(P.stats, ST_GJK_PAIRS, 1);
+  statAdd(P.stats, ST_GJK_ITERS, (uint32_t)g.iters);
+  if (st == GJK_FAR)
+    return;
+  if (st == GJK_SEPARATED && !P.calc_dist)
+    return;
+  if (P.hit_only)
+  {
+    // simplex encloses the origin (cores overlap), or |v| <= margins + pair margin - slack: certainly a contact
+    if ((st == GJK_INTERSECT && (g.v.len2() == 0.f || bool_mode)) || (st == GJK_NEAR && bool_mode))
+    {
+      P.hit[s] = 1;
+      return;
+    }
+  }
+  pushSurvivor(P, (uint32_t)c, g.v);
+}
+
+T4_HD uint32_t orderedBits(float f)
+{
+  uint32_t u;
+#ifdef T4_DEVICE_BUILD
+  u = __float_as_uint(f);
+#else
+  union
+  {
+    float f;
+    uint32_t u;
+  } cv;
+  cv.f = f;
+  u = cv.u;
+#endif
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+// item = survivor index: the exact (FP64) query and the reference's result bridging.
+template <class EPA_T>
+T4_HD void exactBody(int64_t k, const KParams& P, EPA_T& epa)
+{
+  const uint32_t c = P.surv[k];
+  const int64_t s = P.cand_state[c];
+  const bool first = P.test_type == T4C_TEST_FIRST;
+  if ((first || P.hit_only) && P.hit && P.hit[s])
+    return;
+  const int a = (int)P.cand_a[c], b = (int)P.cand_b[c];
+  ShapeW<double> A, B;
+  loadPairShapes<double>(P, s, a, b, A, B);
+  const V3<double> axis0((double)P.surv_axis[3 * (size_t)k], (double)P.surv_axis[3 * (size_t)k + 1],
+                         (double)P.surv_axis[3 * (size_t)k + 2]);
+  PairResult<double> pr;
+  exactPair<double>(A, B, (double)P.max_margin, P.calc_pen != 0, P.calc_dist != 0, axis0, pr, epa);
+  statAdd(P.stats, ST_GJK_ITERS, (uint32_t)pr.gjk_iters);
+  statAdd(P.stats, ST_EPA_PAIRS, pr.used_epa ? 1u : 0u);
+  statAdd(P.stats, ST_EPA_ITERS, (uint32_t)pr.epa_iters);
+  if (!pr.has)
+    return;
+  // TesseractBroadphaseBridgedManifoldResult::addContactPoint / addSingleResult: reject beyond the max margin
+  if (pr.distance > (double)P.max_margin)
+    return;
+  const DShape& Sa = P.shapes[a];
+  const DShape& Sb = P.shapes[b];
+  // processResult (core/common.h:114-167): per-pair margin unless both calculate_* flags are off
+  if ((P.calc_dist || P.calc_pen) && pr.distance > (double)pairMargin(P, Sa.alink, Sb.link))
+    return;
+  if (P.hit)
+    P.hit[s] = 1;
+  if (P.hit_only || !P.raw)
+    return;
+  if (first && casU32(&P.first_claim[s], 0u, 1u) != 0u)
+    return;
+  const uint32_t slot = qAppend(&P.qcount[Q_RAW]);
+  if (slot >= P.raw_cap)
+    return;
+  const V3<double> pointA = pr.pointOnB + pr.normalOnB * pr.distance;
+  t4c_contact ct;
+  ct.state = (int32_t)(s + P.state_base);
+  ct.flags = pr.used_epa ? 1u : 0u;
+  ct.distance = (float)pr.distance;
+  ct.cc_time[0] = ct.cc_time[1] = -1.f;
+  ct.cc_type[0] = ct.cc_type[1] = T4C_CC_NONE;
+  ct.reserved[0] = ct.reserved[1] = 0;
+  double local[2][3] = { { 0, 0, 0 }, { 0, 0, 0 } };
+  bool swap = false;
+  if (P.cast)
+  {
+    // addCastSingleResult (bullet_utils.h:527-611): continuous data per cast side; a single cast side is reported as
+    // index 1 (:595-607)
+    const size_t offA = ((size_t)s * (size_t)P.n_alinks + (size_t)Sa.alink) * 12;
+    const Xf<double> linkA0 = loadPose<double>(P.poses0 + offA);
+    ShapeW<double> Au = A;
+    Au.cast = false;
+    double t;
+    int ty;
+    V3<double> pl = linkA0.invApply(pointA);
+    if (Sb.alink >= 0)
+    {
+      continuousData(Au, linkA0, pointA, -pr.normalOnB, t, ty, pl);
+      ct.cc_time[0] = (float)t, ct.cc_type[0] = (uint8_t)ty;
+      local[0][0] = pl.x, local[0][1] = pl.y, local[0][2] = pl.z;
+      const size_t offB = ((size_t)s * (size_t)P.n_alinks + (size_t)Sb.alink) * 12;
+      const Xf<double> linkB0 = loadPose<double>(P.poses0 + offB);
+      ShapeW<double> Bu = B;
+      Bu.cast = false;
+      V3<double> plb = linkB0.invApply(pr.pointOnB);
+      continuousData(Bu, linkB0, pr.pointOnB, pr.normalOnB, t, ty, plb);
+      ct.cc_time[1] = (float)t, ct.cc_type[1] = (uint8_t)ty;
+      local[1][0] = plb.x, local[1][1] = plb.y, local[1][2] = plb.z;
+    }
+    else
+    {
+      swap = true;
+      continuousData(Au, linkA0, pointA, -pr.normalOnB, t, ty, pl);
+      ct.cc_time[1] = (float)t, ct.cc_type[1] = (uint8_t)ty;
+      local[1][0] = pl.x, local[1][1] = pl.y, local[1][2] = pl.z;
+    }
+  }
+  const int i0 = swap ? 1 : 0, i1 = swap ? 0 : 1;
+  const double sg = swap ? 1.0 : -1.0;
+  ct.link[i0] = Sa.link, ct.link[i1] = Sb.link;
+  ct.shape_id[i0] = (int16_t)Sa.shape_id, ct.shape_id[i1] = (int16_t)Sb.shape_id;
+  ct.subshape_id[i0] = Sa.subshape_id, ct.subshape_id[i1] = Sb.subshape_id;
+  ct.point[i0][0] = (float)pointA.x, ct.point[i0][1] = (float)pointA.y, ct.point[i0][2] = (float)pointA.z;
+  ct.point[i1][0] = (float)pr.pointOnB.x, ct.point[i1][1] = (float)pr.pointOnB.y, ct.point[i1][2] = (float)pr.pointOnB.z;
+  ct.normal[0] = (float)(sg * pr.normalOnB.x), ct.normal[1] = (float)(sg * pr.normalOnB.y);
+  ct.normal[2] = (float)(sg * pr.normalOnB.z);
+  P.raw[slot] = ct;
+  if (P.raw_local)
+  {
+    float* L = P.raw_local + (size_t)slot * 6;
+    for (int j = 0; j < 2; ++j)
+      for (int q = 0; q < 3; ++q)
+        L[3 * j + q] = (float)local[j][q];
+  }
+}
+
+T4_HD unsigned long long mix64(unsigned long long x)
+{
+  x ^= x >> 33;
+  x *= 0xff51afd7ed558ccdULL;
+  x ^= x >> 33;
+  x *= 0xc4ceb9fe1a85ec53ULL;
+  x ^= x >> 33;
+  return x;
+}
+
+T4_HD bool sameKey(const t4c_contact& x, const t4c_contact& y)
+{
+  if (x.state != y.state)
+    return false;
+  return (x.link[0] == y.link[0] && x.link[1] == y.link[1]) || (x.link[0] == y.link[1] && x.link[1] == y.link[0]);
+}
+
+// ContactTestType::CLOSEST (core/common.h:151-157): keep the minimum-distance contact per (state, link pair).
+// item = raw contact index.  Pass 1 finds / claims the hash slot of the key and atomically minimises
+// (ordered distance bits, raw index); pass 2 lets every winner copy itself to the output.
+T4_HD uint32_t closestSlot(const KParams& P, uint32_t i, bool insert)
+{
+  const t4c_contact& c = P.raw[i];
+  const unsigned lo = (unsigned)(c.link[0] < c.link[1] ? c.link[0] : c.link[1]);
+  const unsigned hi = (unsigned)(c.link[0] < c.link[1] ? c.link[1] : c.link[0]);
+  uint32_t h = (uint32_t)mix64(((unsigned long long)(unsigned)c.state << 32) ^ ((unsigned long long)lo << 21) ^ hi) &
+               (P.ht_size - 1);
+  for (uint32_t probe = 0; probe < P.ht_size; ++probe)
+  {
+    int32_t rep = P.ht_rep[h];
+    if (rep < 0 && insert)
+    {
+      rep = casI32(&P.ht_rep[h], -1, (int32_t)i);
+      if (rep < 0)
+        return h;
+    }
+    if (rep >= 0 && sameKey(P.raw[rep], c))
+      return h;
+    if (rep < 0 && !insert)
+      return 0xffffffffu;
+    h = (h + 1) & (P.ht_size - 1);
+  }
+  return 0xffffffffu;
+}
+
+T4_HD void closestInsertBody(int64_t i, const KParams& P)
+{
+  const uint32_t h = closestSlot(P, (uint32_t)i, true);
+  if (h == 0xffffffffu)
+    return;
+  const unsigned long long key = ((unsigned long long)orderedBits(P.raw[i].distance) << 32) | (uint32_t)i;
+  minU64(&P.ht_best[h], key);
+}
+
+T4_HD void closestEmitBody(int64_t i, const KParams& P)
+{
+  const uint32_t h = closestSlot(P, (uint32_t)i, false);
+  if (h == 0xffffffffu)
+    return;
+  if ((uint32_t)(P.ht_best[h] & 0xffffffffu) != (uint32_t)i)
+    return;
+  const uint32_t slot = qAppend(&P.qcount[Q_OUT]);
+  if (slot >= P.out_cap)
+    return;
+  P.out[slot] = P.raw[i];
+  if (P.out_local && P.raw_local)
+    for (int q = 0; q < 6; ++q)
+      P.out_local[(size_t)slot * 6 + q] = P.raw_local[(size_t)i * 6 + q];
+}
+
+}  // namespace t4
+#endif
