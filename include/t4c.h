@@ -32,7 +32,7 @@
  *       checkTrajectory(LVS_DISCRETE) (core/utils.h:309-428)
  *
  * Threading: one t4c_scene per host thread (the reference's "clone per thread" rule,
- * discrete_contact_manager.h:59-65).  All calls are synchronous unless a stream is given.
+ * discrete_contact_manager.h:59-65).  All calls are synchronous with respect to the caller.
  * There is NO CPU fallback: every compute entry fails with T4C_ERR_CUDA when no device
  * is usable.
  */
@@ -173,6 +173,9 @@ typedef struct t4c_result {
   int64_t capacity;
   int64_t n_contacts;    /* out */
   t4c_stats stats;       /* out */
+  float* cc_local;       /* optional, cast checks only: 6 floats per contact = ContactResult::nearest_points_local
+                            of the cast side(s) (bullet_utils.h:452-525; the "Between" case moves it to the
+                            mid-point of the two supports); rows of non-cast sides are zero */
 } t4c_result;
 
 /* Device-buffer variant: every pointer is a device pointer on the scene's device. */
@@ -183,8 +186,9 @@ typedef struct t4c_device_io {
   uint8_t* hit;           /* optional */
   t4c_contact* contacts;  /* optional */
   int64_t capacity;
-  uint64_t* counters;     /* device t4c_stats (10 x u64), zeroed by the call */
-  void* stream;           /* cudaStream_t or NULL */
+  float* cc_local;        /* optional (cast): see t4c_result::cc_local */
+  int64_t n_contacts;     /* out (host value) */
+  t4c_stats stats;        /* out (host value) */
 } t4c_device_io;
 
 const char* t4c_last_error(void);
@@ -205,8 +209,9 @@ int32_t t4c_scene_num_active(const t4c_scene* scene); /* kinematic links, ascend
 t4c_status t4c_fk_model_create(const t4c_fk_model_desc* desc, const t4c_scene* scene, t4c_fk_model** out);
 void t4c_fk_model_destroy(t4c_fk_model* model);
 
-/* Batched forward kinematics: q is n x n_q row-major doubles (host); out is n x n_links x 12 doubles. */
-t4c_status t4c_fk(const t4c_fk_model* model, const double* q, int64_t n, double* link_poses);
+/* Batched forward kinematics: q is n x n_q row-major doubles (host); out is n x n_links x 12 doubles
+ * (every scene link; links no joint reaches keep their scene pose). */
+t4c_status t4c_fk(const t4c_fk_model* model, const t4c_scene* scene, const double* q, int64_t n, double* link_poses);
 
 /* Discrete batched check: FK + self + environment test of n joint vectors (host buffers). */
 t4c_status t4c_check_discrete(t4c_scene* scene, const t4c_fk_model* model, const double* q, int64_t n,
@@ -230,12 +235,16 @@ t4c_status t4c_check_trajectories_cast(t4c_scene* scene, const t4c_fk_model* mod
                                        int64_t n_traj, int32_t n_wp, double lvs, const t4c_request* request,
                                        t4c_result* result, int64_t* n_items);
 
+/* number of LVS work items checkTrajectory would visit (core/utils.h:189-205,328-347); no device work */
+t4c_status t4c_lvs_count(const double* traj, int64_t n_traj, int32_t n_wp, int32_t n_q, double lvs, int32_t cast,
+                         int64_t* n_items);
+
 /* Device-resident entries (inputs already in HBM; used by bench.py "value" and by multi-GPU
  * callers that gather with NCCL themselves). */
 t4c_status t4c_check_discrete_device(t4c_scene* scene, const t4c_fk_model* model, int64_t n,
-                                     const t4c_request* request, const t4c_device_io* io);
+                                     const t4c_request* request, t4c_device_io* io);
 t4c_status t4c_check_cast_device(t4c_scene* scene, const t4c_fk_model* model, int64_t n /* segments */,
-                                 const void* q1, const t4c_request* request, const t4c_device_io* io);
+                                 const void* q1, const t4c_request* request, t4c_device_io* io);
 /* number of this library's kernel launches since load (bench.py "gpu_launches") */
 uint64_t t4c_kernel_launch_count(void);
 /* measured-peak helper: runs an FP32 FMA loop on every SM, returns TFLOP/s (roofline denominator) */

@@ -65,12 +65,12 @@ class Stats(C.Structure):
 
 class Result(C.Structure):
     _fields_ = [("hit", C.POINTER(C.c_uint8)), ("contacts", C.c_void_p), ("capacity", C.c_int64),
-                ("n_contacts", C.c_int64), ("stats", Stats)]
+                ("n_contacts", C.c_int64), ("stats", Stats), ("cc_local", C.POINTER(C.c_float))]
 
 
 class DeviceIO(C.Structure):
     _fields_ = [("q", C.c_void_p), ("q_layout", C.c_int32), ("hit", C.c_void_p), ("contacts", C.c_void_p),
-                ("capacity", C.c_int64), ("counters", C.c_void_p), ("stream", C.c_void_p)]
+                ("capacity", C.c_int64), ("cc_local", C.c_void_p), ("n_contacts", C.c_int64), ("stats", Stats)]
 
 
 # numpy view of t4c_contact (80 bytes)
@@ -109,7 +109,8 @@ def load_library(path=None):
     lib.t4c_fk_model_create.argtypes = [C.POINTER(FkModelDesc), VP, C.POINTER(VP)]
     lib.t4c_fk_model_destroy.argtypes = [VP]
     lib.t4c_fk_model_destroy.restype = None
-    lib.t4c_fk.argtypes = [VP, DP, I64, DP]
+    lib.t4c_fk.argtypes = [VP, VP, DP, I64, DP]
+    lib.t4c_lvs_count.argtypes = [DP, I64, I32, I32, C.c_double, I32, C.POINTER(I64)]
     lib.t4c_check_discrete.argtypes = [VP, VP, DP, I64, C.POINTER(Request), C.POINTER(Result)]
     lib.t4c_check_link_poses_discrete.argtypes = [VP, DP, I64, C.POINTER(Request), C.POINTER(Result)]
     lib.t4c_check_cast.argtypes = [VP, VP, DP, DP, I64, C.POINTER(Request), C.POINTER(Result)]
@@ -127,7 +128,7 @@ def load_library(path=None):
                  "t4c_fk_model_create", "t4c_fk", "t4c_check_discrete", "t4c_check_link_poses_discrete",
                  "t4c_check_cast", "t4c_check_link_poses_cast", "t4c_check_trajectories_discrete",
                  "t4c_check_trajectories_cast", "t4c_check_discrete_device", "t4c_check_cast_device",
-                 "t4c_measure_fp32_peak"):
+                 "t4c_measure_fp32_peak", "t4c_lvs_count"):
         getattr(lib, name).restype = I32
     if path is None:
         _lib = lib

@@ -354,17 +354,43 @@ struct Epa
         best = i;
     if (best < 0)
       return false;
-    const Face& o = F[best];
+    // A flat face of A-B is usually split into several coplanar triangles with the same plane distance: take the one
+    // that actually contains the foot point of the origin (signed barycentric coordinates), otherwise the witness
+    // blend below would extrapolate.
+    const T dband = F[best].d + T(1e-9) * (T(1) + t4abs(F[best].d));
+    T b0 = 0, b1 = 0, b2 = 0, best_min = -Eps<T>::large();
+    int pick = best;
+    for (int i = 0; i < nf_hi; ++i)
+    {
+      if (!F[i].alive || F[i].d > dband)
+        continue;
+      const Face& f = F[i];
+      const V3<T> pr = f.n * f.d;
+      const T c0 = f.n.dot((W[f.v[1]] - pr).cross(W[f.v[2]] - pr));
+      const T c1 = f.n.dot((W[f.v[2]] - pr).cross(W[f.v[0]] - pr));
+      const T c2 = f.n.dot((W[f.v[0]] - pr).cross(W[f.v[1]] - pr));
+      const T sum = c0 + c1 + c2;
+      if (!(sum > T(0)))
+        continue;
+      const T m = t4min(c0, t4min(c1, c2)) / sum;
+      if (m > best_min)
+      {
+        best_min = m;
+        pick = i;
+        b0 = c0 / sum, b1 = c1 / sum, b2 = c2 / sum;
+      }
+    }
+    if (best_min == -Eps<T>::large())
+      return false;
+    // clamp tiny negative weights (foot point on an edge) and renormalise
+    b0 = t4max(b0, T(0)), b1 = t4max(b1, T(0)), b2 = t4max(b2, T(0));
+    {
+      const T sum = b0 + b1 + b2;
+      b0 /= sum, b1 /= sum, b2 /= sum;
+    }
+    const Face& o = F[pick];
     res.normal = o.n;
     res.depth = o.d;
-    const V3<T> proj = o.n * o.d;
-    T b0 = (W[o.v[1]] - proj).cross(W[o.v[2]] - proj).len();
-    T b1 = (W[o.v[2]] - proj).cross(W[o.v[0]] - proj).len();
-    T b2 = (W[o.v[0]] - proj).cross(W[o.v[1]] - proj).len();
-    const T sum = b0 + b1 + b2;
-    if (!(sum > T(0)))
-      return false;
-    b0 /= sum, b1 /= sum, b2 /= sum;
     res.pA = P[o.v[0]] * b0 + P[o.v[1]] * b1 + P[o.v[2]] * b2;
     return true;
   }

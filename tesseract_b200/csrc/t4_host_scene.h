@@ -1,0 +1,397 @@
+/*
+ * t4_host_scene.h -- host-side scene compiler: t4c_scene_desc -> flat device records.
+ *
+ * Mirrors what the reference does once per manager (cold path):
+ *   createShapePrimitive family              tesseract_collision/src/bullet/bullet_utils.cpp:59-365
+ *   updateCollisionObjectFilters             bullet_utils.h:900-917 (active = kinematic, static x static never tested)
+ *   needsCollisionCheck / isContactAllowed   bullet_utils.h:381-386 ; core/common.h:79-104
+ *   CollisionMarginData (default + pairs)    tesseract_common/collision_margin_data.h:66-270
+ * and replaces btDbvtBroadphase's static tree by a linear BVH (Morton order, split at the highest differing bit)
+ * over the world boxes of all STATIC convex shapes, built once per scene revision and uploaded to the GPU.
+ */
+#ifndef T4_HOST_SCENE_H_
+#define T4_HOST_SCENE_H_
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#include <unordered_set>
+#include <vector>
+
+#include "t4_kernels.h"
+
+namespace t4
+{
+struct HostLink
+{
+  std::string name;
+  int type_id = 0;
+  bool enabled = true;
+  bool active = false;
+  double pose[12];
+};
+
+inline uint64_t hostPairKey(int a, int b)
+{
+  if (a > b)
+    std::swap(a, b);
+  return ((uint64_t)(uint32_t)a << 32) | (uint32_t)b;
+}
+
+struct CompiledScene
+{
+  std::vector<DShape> shapes;
+  std::vector<DStaticW> statics;
+  std::vector<f4> verts;
+  std::vector<DBvhNode> bvh;
+  std::vector<int32_t> active_shapes;
+  std::vector<int32_t> aa_pairs;
+  std::vector<uint32_t> acm_bits;
+  int acm_words = 0;
+  std::vector<float> pair_margin;  // empty: default only
+  std::vector<int32_t> alinks;     // link index of every active link, ascending
+  std::vector<int32_t> link_alink; // per link: active ordinal or -1
+  float default_margin = 0, max_margin = 0;
+  bool cast_unsupported = false;
+};
+
+struct HostScene
+{
+  std::vector<HostLink> links;
+  std::vector<t4c_shape> shapes;
+  std::vector<double> vertices;
+  std::unordered_set<uint64_t> acm;
+  double default_margin = 0;
+  std::unordered_map<uint64_t, double> pair_margins;
+
+  double maxMargin() const
+  {
+    double m = default_margin;
+    for (auto& kv : pair_margins)
+      m = std::max(m, kv.second);
+    return m;
+  }
+};
+
+inline uint32_t expandBits10(uint32_t v)
+{
+  v = (v * 0x00010001u) & 0xFF0000FFu;
+  v = (v * 0x00000101u) & 0x0F00F00Fu;
+  v = (v * 0x00000011u) & 0xC30C30C3u;
+  v = (v * 0x00000005u) & 0x49249249u;
+  return v;
+}
+
+struct LbvhBuilder
+{
+  struct Box
+  {
+    float mn[3], mx[3];
+  };
+  const std::vector<Box>& boxes;  // per leaf (sorted order)
+  const std::vector<uint32_t>& codes;
+  const std::vector<int32_t>& leaf_shape;
+  std::vector<DBvhNode>& nodes;
+
+  // returns child reference (>=0 node, <0 leaf) and its box
+  int32_t build(int lo, int hi, Box& out)
+  {
+    if (hi - lo == 1)
+    {
+      out = boxes[lo];
+      return ~leaf_shape[lo];
+    }
+    // split at the highest differing Morton bit (Karras 2012 hierarchy), middle when all codes are equal
+    int split = (lo + hi) / 2;
+    const uint32_t first = codes[lo], last = codes[hi - 1];
+    if (first != last)
+    {
+      const int prefix = __builtin_clz(first ^ last);
+      int s = lo, step = hi - 1 - lo;
+      do
+      {
+        step = (step + 1) >> 1;
+        const int ns = s + step;
+        if (ns < hi - 1 && __builtin_clz(first ^ codes[ns]) > prefix)
+          s = ns;
+      } while (step > 1);
+      split = s + 1;
+    }
+    const int idx = (int)nodes.size();
+    nodes.emplace_back();
+    Box l, r;
+    const int32_t lc = build(lo, split, l);
+    const int32_t rc = build(split, hi, r);
+    DBvhNode& n = nodes[idx];
+    for (int k = 0; k < 3; ++k)
+    {
+      n.lmn[k] = l.mn[k], n.lmx[k] = l.mx[k], n.rmn[k] = r.mn[k], n.rmx[k] = r.mx[k];
+      out.mn[k] = std::min(l.mn[k], r.mn[k]);
+      out.mx[k] = std::max(l.mx[k], r.mx[k]);
+    }
+    n.left = lc, n.right = rc;
+    n.pad[0] = n.pad[1] = 0;
+    return idx;
+  }
+};
+
+inline float roundDown(double x) { return std::nextafter((float)x, -INFINITY); }
+inline float roundUp(double x) { return std::nextafter((float)x, INFINITY); }
+
+// shape-frame bounding box (centre, half extents incl. margins) of one convex shape
+inline void shapeLocalBox(const t4c_shape& s, const double* vertices, double c[3], double h[3])
+{
+  c[0] = c[1] = c[2] = 0;
+  switch (s.type)
+  {
+    case T4C_SPHERE:
+      h[0] = h[1] = h[2] = s.params[0];
+      return;
+    case T4C_BOX:
+      h[0] = s.params[0], h[1] = s.params[1], h[2] = s.params[2];
+      return;
+    case T4C_CYLINDER:
+      h[0] = h[1] = s.params[0], h[2] = s.params[1];
+      return;
+    case T4C_CONE:
+      h[0] = h[1] = s.params[0], h[2] = s.params[1] * 0.5;
+      return;
+    case T4C_CAPSULE:
+      h[0] = h[1] = s.params[0], h[2] = s.params[0] + s.params[1];
+      return;
+    default:
+    {
+      const int nv = s.type == T4C_TRIANGLE ? 3 : s.vertex_count;
+      double mn[3] = { 1e300, 1e300, 1e300 }, mx[3] = { -1e300, -1e300, -1e300 };
+      for (int i = 0; i < nv; ++i)
+        for (int k = 0; k < 3; ++k)
+        {
+          const double v = vertices[3 * (size_t)(s.vertex_offset + i) + k];
+          mn[k] = std::min(mn[k], v);
+          mx[k] = std::max(mx[k], v);
+        }
+      if (nv == 0)
+        mn[0] = mn[1] = mn[2] = mx[0] = mx[1] = mx[2] = 0;
+      for (int k = 0; k < 3; ++k)
+      {
+        c[k] = 0.5 * (mn[k] + mx[k]);
+        h[k] = 0.5 * (mx[k] - mn[k]);
+      }
+      return;
+    }
+  }
+}
+
+inline bool isIdentity12(const double* p)
+{
+  static const double I[12] = { 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0 };
+  return std::memcmp(p, I, sizeof(I)) == 0;
+}
+
+// max number of flattened (active shape, active shape) pairs handled by the brute-force active-active kernel
+#define T4_MAX_AA_PAIRS (64ll << 20)
+
+inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
+{
+  const int nl = (int)H.links.size(), ns = (int)H.shapes.size();
+  C = CompiledScene();
+  C.default_margin = (float)H.default_margin;
+  C.max_margin = (float)H.maxMargin();
+  C.link_alink.assign((size_t)nl, -1);
+  for (int i = 0; i < nl; ++i)
+    if (H.links[i].active)
+    {
+      C.link_alink[i] = (int)C.alinks.size();
+      C.alinks.push_back(i);
+    }
+  const int na = (int)C.alinks.size();
+  C.verts.resize(H.vertices.size() / 3);
+  for (size_t i = 0; i < C.verts.size(); ++i)
+  {
+    C.verts[i].x = (float)H.vertices[3 * i], C.verts[i].y = (float)H.vertices[3 * i + 1];
+    C.verts[i].z = (float)H.vertices[3 * i + 2], C.verts[i].w = 0.f;
+  }
+  C.shapes.resize((size_t)ns);
+  C.statics.resize((size_t)ns);
+  std::vector<LbvhBuilder::Box> sbox;
+  std::vector<int32_t> sshape;
+  std::vector<std::vector<int32_t>> link_active_shapes((size_t)nl);
+  for (int i = 0; i < ns; ++i)
+  {
+    const t4c_shape& s = H.shapes[i];
+    if (s.link < 0 || s.link >= nl)
+    {
+      err = "shape refers to an unknown link";
+      return false;
+    }
+    if ((s.type == T4C_HULL || s.type == T4C_TRIANGLE) &&
+        (s.vertex_offset < 0 ||
+         (size_t)s.vertex_offset + (size_t)(s.type == T4C_TRIANGLE ? 3 : s.vertex_count) > C.verts.size()))
+    {
+      err = "shape vertex range out of bounds";
+      return false;
+    }
+    DShape& d = C.shapes[i];
+    std::memset(&d, 0, sizeof(d));
+    for (int k = 0; k < 12; ++k)
+      d.lpose[k] = (float)s.pose[k];
+    d.params[0] = (float)s.params[0], d.params[1] = (float)s.params[1], d.params[2] = (float)s.params[2];
+    double c[3], h[3];
+    shapeLocalBox(s, H.vertices.data(), c, h);
+    const double rad = s.type == T4C_SPHERE ? s.params[0] : std::sqrt(h[0] * h[0] + h[1] * h[1] + h[2] * h[2]);
+    for (int k = 0; k < 3; ++k)
+    {
+      d.bc[k] = (float)c[k];
+      d.bh[k] = roundUp(h[k] + std::fabs(c[k] - (double)(float)c[k]));
+    }
+    d.bc[3] = roundUp(rad * (1.0 + 1e-6));
+    d.type = s.type, d.link = s.link, d.vert_off = s.vertex_offset, d.vert_cnt = s.vertex_count;
+    d.shape_id = s.shape_id, d.subshape_id = s.subshape_id;
+    d.alink = C.link_alink[s.link];
+    d.identity_lpose = isIdentity12(s.pose) ? 1 : 0;
+    const HostLink& L = H.links[s.link];
+    if (!L.enabled)
+      continue;  // disabled objects take no part in any test (bullet_utils.h:381-386)
+    if (L.active)
+    {
+      link_active_shapes[s.link].push_back(i);
+      C.active_shapes.push_back(i);
+      continue;
+    }
+    // static shape: world pose + bounding data in FP64, rounded once
+    const Xf<double> xw = Xf<double>::from12(L.pose) * Xf<double>::from12(s.pose);
+    DStaticW& w = C.statics[i];
+    Xf<float> xf = xw.cast<float>();
+    xf.to12(w.pose);
+    V3<double> mn, mx;
+    boxAabb(xw, V3<double>(c[0], c[1], c[2]), V3<double>(h[0], h[1], h[2]), mn, mx);
+    const V3<double> cw = xw(V3<double>(c[0], c[1], c[2]));
+    w.bs[0] = (float)cw.x, w.bs[1] = (float)cw.y, w.bs[2] = (float)cw.z;
+    w.bs[3] = roundUp(rad * (1.0 + 1e-6) + 1e-6);
+    LbvhBuilder::Box b;
+    const double pad = 1e-6;
+    b.mn[0] = roundDown(mn.x - pad), b.mn[1] = roundDown(mn.y - pad), b.mn[2] = roundDown(mn.z - pad);
+    b.mx[0] = roundUp(mx.x + pad), b.mx[1] = roundUp(mx.y + pad), b.mx[2] = roundUp(mx.z + pad);
+    sbox.push_back(b);
+    sshape.push_back(i);
+  }
+  // ---- LBVH over the static shapes
+  const int nst = (int)sbox.size();
+  if (nst > 0)
+  {
+    float smn[3] = { 1e30f, 1e30f, 1e30f }, smx[3] = { -1e30f, -1e30f, -1e30f };
+    for (auto& b : sbox)
+      for (int k = 0; k < 3; ++k)
+      {
+        smn[k] = std::min(smn[k], 0.5f * (b.mn[k] + b.mx[k]));
+        smx[k] = std::max(smx[k], 0.5f * (b.mn[k] + b.mx[k]));
+      }
+    std::vector<uint32_t> code((size_t)nst);
+    std::vector<int32_t> order((size_t)nst);
+    for (int i = 0; i < nst; ++i)
+    {
+      uint32_t m = 0;
+      for (int k = 0; k < 3; ++k)
+      {
+        const float ext = std::max(smx[k] - smn[k], 1e-9f);
+        float t = (0.5f * (sbox[i].mn[k] + sbox[i].mx[k]) - smn[k]) / ext;
+        t = std::min(std::max(t * 1024.f, 0.f), 1023.f);
+        m |= expandBits10((uint32_t)t) << (2 - k);
+      }
+      code[i] = m;
+      order[i] = i;
+    }
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return code[a] < code[b]; });
+    std::vector<LbvhBuilder::Box> boxes((size_t)nst);
+    std::vector<uint32_t> codes((size_t)nst);
+    std::vector<int32_t> leaf((size_t)nst);
+    for (int i = 0; i < nst; ++i)
+    {
+      boxes[i] = sbox[order[i]];
+      codes[i] = code[order[i]];
+      leaf[i] = sshape[order[i]];
+    }
+    C.bvh.reserve((size_t)nst);
+    LbvhBuilder B{ boxes, codes, leaf, C.bvh };
+    if (nst == 1)
+    {
+      DBvhNode n;
+      std::memset(&n, 0, sizeof(n));
+      for (int k = 0; k < 3; ++k)
+      {
+        n.lmn[k] = boxes[0].mn[k], n.lmx[k] = boxes[0].mx[k];
+        n.rmn[k] = 1e30f, n.rmx[k] = -1e30f;  // empty box: never overlaps
+      }
+      n.left = ~leaf[0];
+      n.right = ~leaf[0];
+      C.bvh.push_back(n);
+    }
+    else
+    {
+      LbvhBuilder::Box root;
+      B.build(0, nst, root);
+    }
+  }
+  // ---- ACM bit-matrix [n_alinks][n_links]: bit set = pair never tested
+  C.acm_words = (nl + 31) / 32;
+  C.acm_bits.assign((size_t)std::max(na, 1) * (size_t)std::max(C.acm_words, 1), 0u);
+  for (uint64_t key : H.acm)
+  {
+    const int a = (int)(key >> 32), b = (int)(key & 0xffffffffu);
+    if (a >= nl || b >= nl)
+      continue;
+    if (C.link_alink[a] >= 0)
+      C.acm_bits[(size_t)C.link_alink[a] * C.acm_words + (b >> 5)] |= 1u << (b & 31);
+    if (C.link_alink[b] >= 0)
+      C.acm_bits[(size_t)C.link_alink[b] * C.acm_words + (a >> 5)] |= 1u << (a & 31);
+  }
+  // ---- per-pair margins (dense table only when overrides exist)
+  if (!H.pair_margins.empty())
+  {
+    if ((size_t)na * (size_t)nl > (size_t)256 << 20)
+    {
+      err = "pair-margin table too large";
+      return false;
+    }
+    C.pair_margin.assign((size_t)std::max(na, 1) * (size_t)nl, (float)H.default_margin);
+    for (auto& kv : H.pair_margins)
+    {
+      const int a = (int)(kv.first >> 32), b = (int)(kv.first & 0xffffffffu);
+      if (a >= nl || b >= nl)
+        continue;
+      if (C.link_alink[a] >= 0)
+        C.pair_margin[(size_t)C.link_alink[a] * nl + b] = (float)kv.second;
+      if (C.link_alink[b] >= 0)
+        C.pair_margin[(size_t)C.link_alink[b] * nl + a] = (float)kv.second;
+    }
+  }
+  // ---- active x active shape pairs (enabled, different links, not allowed by the ACM)
+  long long n_pairs = 0;
+  for (int i = 0; i < na; ++i)
+    for (int j = i + 1; j < na; ++j)
+    {
+      const int la = C.alinks[i], lb = C.alinks[j];
+      if (link_active_shapes[la].empty() || link_active_shapes[lb].empty())
+        continue;
+      if (H.acm.count(hostPairKey(la, lb)))
+        continue;
+      n_pairs += (long long)link_active_shapes[la].size() * (long long)link_active_shapes[lb].size();
+      if (n_pairs > T4_MAX_AA_PAIRS)
+      {
+        err = "too many active-active shape pairs for the brute-force kinematic-kinematic broadphase";
+        return false;
+      }
+      for (int sa : link_active_shapes[la])
+        for (int sb : link_active_shapes[lb])
+        {
+          C.aa_pairs.push_back(sa);
+          C.aa_pairs.push_back(sb);
+        }
+    }
+  return true;
+}
+
+}  // namespace t4
+#endif

@@ -168,7 +168,7 @@ inline void minU64(unsigned long long* p, unsigned long long v)
 #endif
 
 template <class T>
-T4_HD Xf<T> loadPose(const float* p)
+T4_KD Xf<T> loadPose(const float* p)
 {
   Xf<T> x;
   const f4* q = reinterpret_cast<const f4*>(p);
@@ -181,7 +181,7 @@ T4_HD Xf<T> loadPose(const float* p)
 
 // world pose(s) of shape `sh` in state s
 template <class T>
-T4_HD void shapePose(const KParams& P, const DShape& S, int sh, int64_t s, Xf<T>& x0, Xf<T>& x1)
+T4_KD void shapePose(const KParams& P, const DShape& S, int sh, int64_t s, Xf<T>& x0, Xf<T>& x1)
 {
   if (S.alink < 0)
   {
@@ -204,12 +204,12 @@ T4_HD void shapePose(const KParams& P, const DShape& S, int sh, int64_t s, Xf<T>
     x1 = x0;
 }
 
-T4_HD bool acmAllowed(const KParams& P, int alink, int linkB)
+T4_KD bool acmAllowed(const KParams& P, int alink, int linkB)
 {
   return (P.acm_bits[(size_t)alink * P.acm_words + (linkB >> 5)] >> (linkB & 31)) & 1u;
 }
 
-T4_HD float pairMargin(const KParams& P, int alink, int linkB)
+T4_KD float pairMargin(const KParams& P, int alink, int linkB)
 {
   return P.pair_margin ? P.pair_margin[(size_t)alink * P.n_links + linkB] : P.default_margin;
 }
@@ -217,7 +217,7 @@ T4_HD float pairMargin(const KParams& P, int alink, int linkB)
 // ---------------------------------------------------------------------------------------------------------------
 // FK
 // ---------------------------------------------------------------------------------------------------------------
-T4_HD double loadQ(const KParams& P, const void* q, int64_t s, int j)
+T4_KD double loadQ(const KParams& P, const void* q, int64_t s, int j)
 {
   if (P.q_layout == T4C_Q_F32_SOA)
     return (double)((const float*)q)[(size_t)j * (size_t)P.q_stride_n + (size_t)s];
@@ -226,7 +226,7 @@ T4_HD double loadQ(const KParams& P, const void* q, int64_t s, int j)
   return (double)((const float*)q)[(size_t)s * P.n_q + j];
 }
 
-T4_HD void fkOne(const KParams& P, const void* q, int64_t s, Xf<double>* Tj)
+T4_KD void fkOne(const KParams& P, const void* q, int64_t s, Xf<double>* Tj)
 {
   for (int j = 0; j < P.n_joints; ++j)
   {
@@ -258,7 +258,7 @@ T4_HD void fkOne(const KParams& P, const void* q, int64_t s, Xf<double>* Tj)
   }
 }
 
-T4_HD void storePoseF(float* dst, const Xf<double>& x)
+T4_KD void storePoseF(float* dst, const Xf<double>& x)
 {
   f4* d = reinterpret_cast<f4*>(dst);
   f4 a, b, c;
@@ -269,7 +269,7 @@ T4_HD void storePoseF(float* dst, const Xf<double>& x)
 }
 
 // item = state.  Writes poses0 (and poses1 for cast) of the kinematic links, or fk_out (all links, FP64).
-T4_HD void fkBody(int64_t s, const KParams& P)
+T4_KD void fkBody(int64_t s, const KParams& P)
 {
   Xf<double> Tj[T4_MAX_JOINTS];
   for (int pass = 0; pass < (P.cast ? 2 : 1); ++pass)
@@ -296,7 +296,7 @@ T4_HD void fkBody(int64_t s, const KParams& P)
 }
 
 // item = (state, active link): FK bypass, FP64 host poses -> FP32 device poses
-T4_HD void convertPosesBody(int64_t i, const KParams& P)
+T4_KD void convertPosesBody(int64_t i, const KParams& P)
 {
   const double* src0 = P.poses_in0 + (size_t)i * 12;
   storePoseF(P.poses0 + (size_t)i * 12, Xf<double>::from12(src0));
@@ -307,12 +307,12 @@ T4_HD void convertPosesBody(int64_t i, const KParams& P)
 // ---------------------------------------------------------------------------------------------------------------
 // broadphase
 // ---------------------------------------------------------------------------------------------------------------
-T4_HD bool boxesOverlap(const V3<float>& mn, const V3<float>& mx, const float* bmn, const float* bmx)
+T4_KD bool boxesOverlap(const V3<float>& mn, const V3<float>& mx, const float* bmn, const float* bmx)
 {
   return !(mn.x > bmx[0] || mx.x < bmn[0] || mn.y > bmx[1] || mx.y < bmn[1] || mn.z > bmx[2] || mx.z < bmn[2]);
 }
 
-T4_HD void shapeWorldBox(const KParams& P, const DShape& S, const Xf<float>& x0, const Xf<float>& x1, V3<float>& mn,
+T4_KD void shapeWorldBox(const KParams& P, const DShape& S, const Xf<float>& x0, const Xf<float>& x1, V3<float>& mn,
                          V3<float>& mx)
 {
   const V3<float> c(S.bc[0], S.bc[1], S.bc[2]), h(S.bh[0], S.bh[1], S.bh[2]);
@@ -326,7 +326,7 @@ T4_HD void shapeWorldBox(const KParams& P, const DShape& S, const Xf<float>& x0,
   }
 }
 
-T4_HD void pushCandidate(const KParams& P, int64_t s, int a, int b)
+T4_KD void pushCandidate(const KParams& P, int64_t s, int a, int b)
 {
   const uint32_t k = qAppend(&P.qcount[Q_CAND]);
   if (k < P.cand_cap)
@@ -341,7 +341,7 @@ T4_HD void pushCandidate(const KParams& P, int64_t s, int a, int b)
 #define T4_CULL_SLACK 2e-5f
 
 // item = a_ord * n + s  (shape-major, so that a warp works on 32 states of the SAME robot shape)
-T4_HD void broadStaticBody(int64_t item, const KParams& P)
+T4_KD void broadStaticBody(int64_t item, const KParams& P)
 {
   const int a_ord = (int)(item / P.n);
   const int64_t s = item - (int64_t)a_ord * P.n;
@@ -415,7 +415,7 @@ T4_HD void broadStaticBody(int64_t item, const KParams& P)
 }
 
 // item = pair * n + s ; pairs are (active shape, active shape) of two different links, ACM-filtered on the host
-T4_HD void broadActiveBody(int64_t item, const KParams& P)
+T4_KD void broadActiveBody(int64_t item, const KParams& P)
 {
   const int pr = (int)(item / P.n);
   const int64_t s = item - (int64_t)pr * P.n;

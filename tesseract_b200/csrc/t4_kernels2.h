@@ -10,7 +10,7 @@
 namespace t4
 {
 template <class T>
-T4_HD void loadPairShapes(const KParams& P, int64_t s, int a, int b, ShapeW<T>& A, ShapeW<T>& B)
+T4_KD void loadPairShapes(const KParams& P, int64_t s, int a, int b, ShapeW<T>& A, ShapeW<T>& B)
 {
   const DShape& Sa = P.shapes[a];
   const DShape& Sb = P.shapes[b];
@@ -21,7 +21,7 @@ T4_HD void loadPairShapes(const KParams& P, int64_t s, int a, int b, ShapeW<T>& 
   B = makeShapeW<T>(Sb, P.verts, b0, b1, P.cast && Sb.alink >= 0);
 }
 
-T4_HD bool analyticPair(int ta, int tb)
+T4_KD bool analyticPair(int ta, int tb)
 {
   if (ta == SH_SPHERE && (tb == SH_SPHERE || tb == SH_TRIANGLE || tb == SH_CAPSULE))
     return true;
@@ -32,7 +32,7 @@ T4_HD bool analyticPair(int ta, int tb)
   return false;
 }
 
-T4_HD void pushSurvivor(const KParams& P, uint32_t c, const V3<float>& axis)
+T4_KD void pushSurvivor(const KParams& P, uint32_t c, const V3<float>& axis)
 {
   const uint32_t k = qAppend(&P.qcount[Q_SURV]);
   if (k < P.surv_cap)
@@ -47,7 +47,7 @@ T4_HD void pushSurvivor(const KParams& P, uint32_t c, const V3<float>& axis)
 // item = candidate index.  FP32 GJK used ONLY to discard pairs that are provably farther apart than the contact
 // cut-off (and, for boolean FIRST queries without contact output, to accept pairs that are provably inside it).
 // Everything that is reported goes through exactBody.
-T4_HD void cullBody(int64_t c, const KParams& P)
+T4_KD void cullBody(int64_t c, const KParams& P)
 {
   const int64_t s = P.cand_state[c];
   // FIRST (or flags-only output): the state already has its contact (ContactTestData::done, core/common.h:129-133)
@@ -101,7 +101,7 @@ T4_HD void cullBody(int64_t c, const KParams& P)
   pushSurvivor(P, (uint32_t)c, g.v);
 }
 
-T4_HD uint32_t orderedBits(float f)
+T4_KD uint32_t orderedBits(float f)
 {
   uint32_t u;
 #ifdef T4_DEVICE_BUILD
@@ -120,7 +120,7 @@ T4_HD uint32_t orderedBits(float f)
 
 // item = survivor index: the exact (FP64) query and the reference's result bridging.
 template <class EPA_T>
-T4_HD void exactBody(int64_t k, const KParams& P, EPA_T& epa)
+T4_KD void exactBody(int64_t k, const KParams& P, EPA_T& epa)
 {
   const uint32_t c = P.surv[k];
   const int64_t s = P.cand_state[c];
@@ -218,7 +218,7 @@ T4_HD void exactBody(int64_t k, const KParams& P, EPA_T& epa)
   }
 }
 
-T4_HD unsigned long long mix64(unsigned long long x)
+T4_KD unsigned long long mix64(unsigned long long x)
 {
   x ^= x >> 33;
   x *= 0xff51afd7ed558ccdULL;
@@ -228,7 +228,7 @@ T4_HD unsigned long long mix64(unsigned long long x)
   return x;
 }
 
-T4_HD bool sameKey(const t4c_contact& x, const t4c_contact& y)
+T4_KD bool sameKey(const t4c_contact& x, const t4c_contact& y)
 {
   if (x.state != y.state)
     return false;
@@ -238,7 +238,7 @@ T4_HD bool sameKey(const t4c_contact& x, const t4c_contact& y)
 // ContactTestType::CLOSEST (core/common.h:151-157): keep the minimum-distance contact per (state, link pair).
 // item = raw contact index.  Pass 1 finds / claims the hash slot of the key and atomically minimises
 // (ordered distance bits, raw index); pass 2 lets every winner copy itself to the output.
-T4_HD uint32_t closestSlot(const KParams& P, uint32_t i, bool insert)
+T4_KD uint32_t closestSlot(const KParams& P, uint32_t i, bool insert)
 {
   const t4c_contact& c = P.raw[i];
   const unsigned lo = (unsigned)(c.link[0] < c.link[1] ? c.link[0] : c.link[1]);
@@ -263,7 +263,7 @@ T4_HD uint32_t closestSlot(const KParams& P, uint32_t i, bool insert)
   return 0xffffffffu;
 }
 
-T4_HD void closestInsertBody(int64_t i, const KParams& P)
+T4_KD void closestInsertBody(int64_t i, const KParams& P)
 {
   const uint32_t h = closestSlot(P, (uint32_t)i, true);
   if (h == 0xffffffffu)
@@ -272,7 +272,7 @@ T4_HD void closestInsertBody(int64_t i, const KParams& P)
   minU64(&P.ht_best[h], key);
 }
 
-T4_HD void closestEmitBody(int64_t i, const KParams& P)
+T4_KD void closestEmitBody(int64_t i, const KParams& P)
 {
   const uint32_t h = closestSlot(P, (uint32_t)i, false);
   if (h == 0xffffffffu)

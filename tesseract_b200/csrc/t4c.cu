@@ -1,0 +1,1204 @@
+/*
+ * t4c.cu -- the C ABI of include/t4c.h: scene objects, kernel launches, batched discrete / cast checks.
+ *
+ * Built by nvcc for sm_100a into libt4c.so (the product; no CPU execution path: every compute entry returns
+ * T4C_ERR_CUDA when no device is usable).  The same source also compiles with g++ -DT4C_HOSTSIM into
+ * tests/hostsim/libt4c_hostsim.so, a TEST-ONLY simulator that runs the identical kernel bodies serially on the host
+ * so numerics can be debugged without a GPU; it is never loaded by the tesseract_b200 package.
+ */
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "t4_host_scene.h"
+#include "t4_kernels2.h"
+
+#ifndef T4C_HOSTSIM
+#include <cuda_runtime.h>
+#endif
+
+using namespace t4;
+
+// ===================================================================================================================
+// platform layer
+// ===================================================================================================================
+static thread_local std::string g_err;
+static std::atomic<unsigned long long> g_launches{ 0 };
+
+static t4c_status fail(t4c_status st, const char* fmt, ...)
+{
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return st;
+}
+
+#ifdef T4C_HOSTSIM
+typedef void* t4stream;
+namespace plat
+{
+static bool ok() { return true; }
+static int deviceCount() { return 1; }
+static bool setDevice(int) { return true; }
+static void* alloc(size_t n) { return std::malloc(n ? n : 1); }
+static void release(void* p) { std::free(p); }
+static bool h2d(void* d, const void* s, size_t n, t4stream) { std::memcpy(d, s, n); return true; }
+static bool d2h(void* d, const void* s, size_t n, t4stream) { std::memcpy(d, s, n); return true; }
+static bool zero(void* d, size_t n, t4stream) { std::memset(d, 0, n); return true; }
+static bool fill(void* d, int v, size_t n, t4stream) { std::memset(d, v, n); return true; }
+static bool sync(t4stream) { return true; }
+static t4stream newStream() { return nullptr; }
+static void freeStream(t4stream) {}
+static const char* lastError() { return "hostsim"; }
+}  // namespace plat
+#else
+typedef cudaStream_t t4stream;
+namespace plat
+{
+static cudaError_t g_last = cudaSuccess;
+static bool chk(cudaError_t e)
+{
+  if (e != cudaSuccess)
+  {
+    g_last = e;
+    return false;
+  }
+  return true;
+}
+static int deviceCount()
+{
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess)
+    return 0;
+  return n;
+}
+static bool setDevice(int d) { return chk(cudaSetDevice(d)); }
+static void* alloc(size_t n)
+{
+  void* p = nullptr;
+  if (!chk(cudaMalloc(&p, n ? n : 1)))
+    return nullptr;
+  return p;
+}
+static void release(void* p) { cudaFree(p); }
+static bool h2d(void* d, const void* s, size_t n, t4stream st)
+{
+  return n == 0 || chk(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, st));
+}
+static bool d2h(void* d, const void* s, size_t n, t4stream st)
+{
+  return n == 0 || chk(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, st));
+}
+static bool zero(void* d, size_t n, t4stream st) { return n == 0 || chk(cudaMemsetAsync(d, 0, n, st)); }
+static bool fill(void* d, int v, size_t n, t4stream st) { return n == 0 || chk(cudaMemsetAsync(d, v, n, st)); }
+static bool sync(t4stream st) { return chk(cudaStreamSynchronize(st)); }
+static t4stream newStream()
+{
+  cudaStream_t s = nullptr;
+  if (!chk(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)))
+    return nullptr;
+  return s;
+}
+static void freeStream(t4stream s)
+{
+  if (s)
+    cudaStreamDestroy(s);
+}
+static const char* lastError() { return cudaGetErrorString(g_last); }
+}  // namespace plat
+#endif
+
+// growable device buffer
+struct DevBuf
+{
+  void* p = nullptr;
+  size_t cap = 0;
+  ~DevBuf() { reset(); }
+  void reset()
+  {
+    if (p)
+      plat::release(p);
+    p = nullptr;
+    cap = 0;
+  }
+  bool ensure(size_t bytes)
+  {
+    if (bytes <= cap)
+      return true;
+    reset();
+    size_t want = bytes + bytes / 8 + 256;
+    p = plat::alloc(want);
+    if (!p)
+      return false;
+    cap = want;
+    return true;
+  }
+  template <class T>
+  T* as() const
+  {
+    return reinterpret_cast<T*>(p);
+  }
+};
+
+template <class T>
+static bool upload(DevBuf& b, const std::vector<T>& v, t4stream st)
+{
+  if (!b.ensure(std::max<size_t>(v.size(), 1) * sizeof(T)))
+    return false;
+  return plat::h2d(b.p, v.data(), v.size() * sizeof(T), st);
+}
+
+// ===================================================================================================================
+// kernels (sm_100a) / serial loops (host simulator)
+// ===================================================================================================================
+#ifndef T4C_HOSTSIM
+#define T4_SM_COUNT_FALLBACK 148
+static int g_sm_count = 0;
+static int smCount()
+{
+  if (!g_sm_count)
+  {
+    int dev = 0, n = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = T4_SM_COUNT_FALLBACK;
+    g_sm_count = n;
+  }
+  return g_sm_count;
+}
+// grids are a whole number of waves: SM count x resident CTAs per SM, grid-stride over the items
+static int gridFor(int64_t n, int block, int ctas_per_sm)
+{
+  const int64_t need = (n + block - 1) / block;
+  const int64_t full = (int64_t)smCount() * ctas_per_sm;
+  return (int)std::max<int64_t>(1, std::min<int64_t>(need, full));
+}
+
+__global__ void __launch_bounds__(128) fkKernel(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    fkBody(i, P);
+}
+__global__ void __launch_bounds__(256) convertPosesKernel(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    convertPosesBody(i, P);
+}
+__global__ void __launch_bounds__(256) broadStaticKernel(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    broadStaticBody(i, P);
+}
+__global__ void __launch_bounds__(256) broadActiveKernel(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    broadActiveBody(i, P);
+}
+__global__ void __launch_bounds__(256) cullKernel(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    cullBody(i, P);
+}
+__global__ void __launch_bounds__(128) exactKernel(KParams P, int64_t n)
+{
+  Epa<double> epa;  // polytope pools live in thread-local memory
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    exactBody(i, P, epa);
+}
+__global__ void __launch_bounds__(256) closestInsertKernel(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    closestInsertBody(i, P);
+}
+__global__ void __launch_bounds__(256) closestEmitKernel(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    closestEmitBody(i, P);
+}
+__global__ void __launch_bounds__(256) countHitKernel(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    statAdd(P.stats, ST_COLLIDING, P.hit[i] ? 1u : 0u);
+}
+__global__ void fmaPeakKernel(float* out, int iters)
+{
+  float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f,
+        a6 = a0 + 6.f, a7 = a0 + 7.f;
+  const float b = 1.0000001f, c = 1e-7f;
+  for (int i = 0; i < iters; ++i)
+  {
+    a0 = fmaf(a0, b, c), a1 = fmaf(a1, b, c), a2 = fmaf(a2, b, c), a3 = fmaf(a3, b, c);
+    a4 = fmaf(a4, b, c), a5 = fmaf(a5, b, c), a6 = fmaf(a6, b, c), a7 = fmaf(a7, b, c);
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+#define T4_LAUNCH(KERNEL, BLOCK, CTAS, P, n, st)                                                                       \
+  do                                                                                                                   \
+  {                                                                                                                    \
+    if ((n) > 0)                                                                                                       \
+    {                                                                                                                  \
+      KERNEL<<<gridFor((n), (BLOCK), (CTAS)), (BLOCK), 0, (st)>>>((P), (n));                                           \
+      ++g_launches;                                                                                                    \
+    }                                                                                                                  \
+  } while (0)
+static bool launchOk() { return plat::chk(cudaGetLastError()); }
+static void launchFk(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(fkKernel, 128, 8, P, n, st); }
+static void launchConvert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(convertPosesKernel, 256, 8, P, n, st); }
+static void launchBroadStatic(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadStaticKernel, 256, 8, P, n, st); }
+static void launchBroadActive(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadActiveKernel, 256, 8, P, n, st); }
+static void launchCull(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(cullKernel, 256, 4, P, n, st); }
+static void launchExact(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(exactKernel, 128, 4, P, n, st); }
+static void launchClosestInsert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestInsertKernel, 256, 8, P, n, st); }
+static void launchClosestEmit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestEmitKernel, 256, 8, P, n, st); }
+static void launchCountHit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(countHitKernel, 256, 8, P, n, st); }
+#else
+#define T4_SERIAL(BODY, P, n)                                                                                          \
+  do                                                                                                                   \
+  {                                                                                                                    \
+    for (int64_t _i = 0; _i < (n); ++_i)                                                                               \
+      BODY(_i, (P));                                                                                                   \
+    if ((n) > 0)                                                                                                       \
+      ++g_launches;                                                                                                    \
+  } while (0)
+static bool launchOk() { return true; }
+static void launchFk(const KParams& P, int64_t n, t4stream) { T4_SERIAL(fkBody, P, n); }
+static void launchConvert(const KParams& P, int64_t n, t4stream) { T4_SERIAL(convertPosesBody, P, n); }
+static void launchBroadStatic(const KParams& P, int64_t n, t4stream) { T4_SERIAL(broadStaticBody, P, n); }
+static void launchBroadActive(const KParams& P, int64_t n, t4stream) { T4_SERIAL(broadActiveBody, P, n); }
+static void launchCull(const KParams& P, int64_t n, t4stream) { T4_SERIAL(cullBody, P, n); }
+static void launchExact(const KParams& P, int64_t n, t4stream)
+{
+  std::unique_ptr<Epa<double>> epa(new Epa<double>());
+  for (int64_t i = 0; i < n; ++i)
+    exactBody(i, P, *epa);
+  if (n > 0)
+    ++g_launches;
+}
+static void launchClosestInsert(const KParams& P, int64_t n, t4stream) { T4_SERIAL(closestInsertBody, P, n); }
+static void launchClosestEmit(const KParams& P, int64_t n, t4stream) { T4_SERIAL(closestEmitBody, P, n); }
+static void launchCountHit(const KParams& P, int64_t n, t4stream)
+{
+  for (int64_t i = 0; i < n; ++i)
+    statAdd(P.stats, ST_COLLIDING, P.hit[i] ? 1u : 0u);
+}
+#endif
+
+// ===================================================================================================================
+// scene / FK model objects
+// ===================================================================================================================
+struct t4c_fk_model
+{
+  int n_links = 0, n_q = 0, root_link = 0;
+  std::vector<t4c_joint> joints;  // parent-before-child
+};
+
+struct FkCache
+{
+  unsigned long long scene_rev = ~0ull;
+  DevBuf joints, alink_joint, alink_static, link_joint, link_static;
+  int n_joints = 0;
+};
+
+struct t4c_scene
+{
+  int device = 0;
+  HostScene host;
+  unsigned long long rev = 1;       // bumped by every mutation
+  unsigned long long uploaded = 0;  // rev of the device copy
+  CompiledScene comp;
+  t4stream stream = nullptr;
+  // device scene
+  DevBuf d_shapes, d_statics, d_verts, d_bvh, d_active, d_aa, d_acm, d_margin;
+  // per-call workspace
+  DevBuf d_q0, d_q1, d_pin0, d_pin1, d_poses0, d_poses1;
+  DevBuf d_cand_state, d_cand_a, d_cand_b, d_surv, d_surv_axis;
+  DevBuf d_qcount, d_stats, d_hit, d_claim, d_raw, d_raw_local, d_ht_rep, d_ht_best;
+  DevBuf d_out, d_out_local, d_fk_out, d_hit_full;
+  uint32_t cand_cap = 0;
+  std::unordered_map<const t4c_fk_model*, std::unique_ptr<FkCache>> fk;
+
+  ~t4c_scene()
+  {
+    fk.clear();
+    plat::freeStream(stream);
+  }
+};
+
+static bool bindDevice(const t4c_scene* s)
+{
+  return plat::setDevice(s->device);
+}
+
+static t4c_status syncScene(t4c_scene* s)
+{
+  if (!bindDevice(s))
+    return fail(T4C_ERR_CUDA, "cudaSetDevice(%d): %s", s->device, plat::lastError());
+  if (s->uploaded == s->rev)
+    return T4C_OK;
+  std::string err;
+  if (!compileScene(s->host, s->comp, err))
+    return fail(T4C_ERR_UNSUPPORTED, "%s", err.c_str());
+  CompiledScene& C = s->comp;
+  t4stream st = s->stream;
+  bool ok = upload(s->d_shapes, C.shapes, st) && upload(s->d_statics, C.statics, st) && upload(s->d_verts, C.verts, st) &&
+            upload(s->d_bvh, C.bvh, st) && upload(s->d_active, C.active_shapes, st) && upload(s->d_aa, C.aa_pairs, st) &&
+            upload(s->d_acm, C.acm_bits, st) && upload(s->d_margin, C.pair_margin, st) && plat::sync(st);
+  if (!ok)
+    return fail(T4C_ERR_CUDA, "scene upload failed: %s", plat::lastError());
+  s->uploaded = s->rev;
+  return T4C_OK;
+}
+
+static void fillSceneParams(const t4c_scene* s, KParams& P)
+{
+  const CompiledScene& C = s->comp;
+  std::memset(&P, 0, sizeof(P));
+  P.shapes = s->d_shapes.as<DShape>();
+  P.statics = s->d_statics.as<DStaticW>();
+  P.verts = s->d_verts.as<f4>();
+  P.bvh = s->d_bvh.as<DBvhNode>();
+  P.n_bvh_nodes = (int)C.bvh.size();
+  P.active_shapes = s->d_active.as<int32_t>();
+  P.n_active_shapes = (int)C.active_shapes.size();
+  P.aa_pairs = s->d_aa.as<int32_t>();
+  P.n_aa_pairs = (int)(C.aa_pairs.size() / 2);
+  P.acm_bits = s->d_acm.as<uint32_t>();
+  P.acm_words = C.acm_words;
+  P.pair_margin = C.pair_margin.empty() ? nullptr : s->d_margin.as<float>();
+  P.n_links = (int)s->host.links.size();
+  P.n_alinks = (int)C.alinks.size();
+  P.default_margin = C.default_margin;
+  P.max_margin = C.max_margin;
+}
+
+// FK tables of `model` against the current scene revision (device arrays cached in the scene)
+static t4c_status syncFk(t4c_scene* s, const t4c_fk_model* m, FkCache** out)
+{
+  auto& slot = s->fk[m];
+  if (!slot)
+    slot.reset(new FkCache());
+  FkCache* fc = slot.get();
+  *out = fc;
+  if (fc->scene_rev == s->rev)
+    return T4C_OK;
+  const int nl = (int)s->host.links.size();
+  const int nj = (int)m->joints.size();
+  if (nj > T4_MAX_JOINTS)
+    return fail(T4C_ERR_UNSUPPORTED, "FK model has %d joints (max %d)", nj, T4_MAX_JOINTS);
+  std::vector<DJoint> dj((size_t)nj);
+  std::vector<int32_t> child_joint((size_t)std::max(nl, m->n_links), -1);
+  for (int j = 0; j < nj; ++j)
+  {
+    const t4c_joint& J = m->joints[j];
+    if (J.parent_link < 0 || J.child_link < 0 || J.parent_link >= (int)child_joint.size() ||
+        J.child_link >= (int)child_joint.size())
+      return fail(T4C_ERR_INVALID, "joint %d refers to an unknown link", j);
+    if (J.type != T4C_JOINT_FIXED && (J.q_index < 0 || J.q_index >= m->n_q))
+      return fail(T4C_ERR_INVALID, "joint %d has q_index %d outside [0,%d)", j, J.q_index, m->n_q);
+    DJoint& D = dj[j];
+    std::memset(&D, 0, sizeof(D));
+    std::memcpy(D.origin, J.origin, sizeof(D.origin));
+    const double al = std::sqrt(J.axis[0] * J.axis[0] + J.axis[1] * J.axis[1] + J.axis[2] * J.axis[2]);
+    for (int k = 0; k < 3; ++k)
+      D.axis[k] = al > 0 ? J.axis[k] / al : (k == 2 ? 1.0 : 0.0);
+    D.type = J.type;
+    D.q_index = J.q_index;
+    D.parent_joint = child_joint[J.parent_link];
+    static const double I12[12] = { 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0 };
+    std::memcpy(D.pre, J.parent_link < nl ? s->host.links[J.parent_link].pose : I12, sizeof(D.pre));
+    child_joint[J.child_link] = j;
+  }
+  const CompiledScene& C = s->comp;
+  std::vector<int32_t> aj(std::max<size_t>(C.alinks.size(), 1), -1);
+  std::vector<double> as(std::max<size_t>(C.alinks.size(), 1) * 12, 0.0);
+  for (size_t a = 0; a < C.alinks.size(); ++a)
+  {
+    aj[a] = child_joint[C.alinks[a]];
+    std::memcpy(&as[a * 12], s->host.links[C.alinks[a]].pose, 12 * sizeof(double));
+  }
+  std::vector<int32_t> lj((size_t)std::max(nl, 1), -1);
+  std::vector<double> ls((size_t)std::max(nl, 1) * 12, 0.0);
+  for (int l = 0; l < nl; ++l)
+  {
+    lj[l] = child_joint[l];
+    std::memcpy(&ls[(size_t)l * 12], s->host.links[l].pose, 12 * sizeof(double));
+  }
+  t4stream st = s->stream;
+  bool ok = upload(fc->joints, dj, st) && upload(fc->alink_joint, aj, st) && upload(fc->alink_static, as, st) &&
+            upload(fc->link_joint, lj, st) && upload(fc->link_static, ls, st) && plat::sync(st);
+  if (!ok)
+    return fail(T4C_ERR_CUDA, "FK model upload failed: %s", plat::lastError());
+  fc->n_joints = nj;
+  fc->scene_rev = s->rev;
+  return T4C_OK;
+}
+
+static void fillFkParams(const t4c_fk_model* m, const FkCache* fc, KParams& P)
+{
+  P.joints = fc->joints.as<DJoint>();
+  P.n_joints = fc->n_joints;
+  P.n_q = m->n_q;
+  P.alink_joint = fc->alink_joint.as<int32_t>();
+  P.alink_static = fc->alink_static.as<double>();
+  P.link_joint = fc->link_joint.as<int32_t>();
+  P.link_static = fc->link_static.as<double>();
+}
+
+// ===================================================================================================================
+// batched pipeline
+// ===================================================================================================================
+struct BatchIO
+{
+  int64_t n = 0;
+  bool cast = false;
+  // joint-space input (device pointers), or link poses (device, FP64, n x n_alinks x 12) when model == nullptr
+  const t4c_fk_model* model = nullptr;
+  const void* q0 = nullptr;
+  const void* q1 = nullptr;
+  int q_layout = T4C_Q_F64_ROWMAJOR;
+  const double* poses0 = nullptr;
+  const double* poses1 = nullptr;
+  t4c_request req{ T4C_TEST_FIRST, 1, 1 };
+  // outputs (device pointers, may be null)
+  uint8_t* hit = nullptr;
+  t4c_contact* contacts = nullptr;
+  float* cc_local = nullptr;
+  int64_t capacity = 0;
+  // results
+  int64_t n_contacts = 0;
+  t4c_stats stats{};
+};
+
+static int64_t chunkStates()
+{
+  static int64_t v = 0;
+  if (!v)
+  {
+    const char* e = std::getenv("T4C_CHUNK_STATES");
+    v = e ? std::max<long long>(1, std::atoll(e)) : (1ll << 20);
+  }
+  return v;
+}
+
+static uint32_t nextPow2(uint64_t x)
+{
+  uint64_t p = 16;
+  while (p < x)
+    p <<= 1;
+  return (uint32_t)std::min<uint64_t>(p, 1ull << 31);
+}
+
+#define T4_TRY(expr, what)                                                                                             \
+  do                                                                                                                   \
+  {                                                                                                                    \
+    if (!(expr))                                                                                                       \
+      return fail(T4C_ERR_CUDA, "%s: %s", what, plat::lastError());                                                    \
+  } while (0)
+
+static t4c_status runBatch(t4c_scene* s, BatchIO& io)
+{
+  t4c_status rc = syncScene(s);
+  if (rc != T4C_OK)
+    return rc;
+  if (io.req.type < T4C_TEST_FIRST || io.req.type > T4C_TEST_ALL)
+    return fail(T4C_ERR_INVALID, "unknown ContactTestType %d (LIMITED is not implemented by the reference either)",
+                io.req.type);
+  t4stream st = s->stream;
+  KParams P;
+  fillSceneParams(s, P);
+  FkCache* fc = nullptr;
+  if (io.model)
+  {
+    rc = syncFk(s, io.model, &fc);
+    if (rc != T4C_OK)
+      return rc;
+    fillFkParams(io.model, fc, P);
+  }
+  P.cast = io.cast ? 1 : 0;
+  P.test_type = io.req.type;
+  P.calc_pen = io.req.calculate_penetration;
+  P.calc_dist = io.req.calculate_distance;
+  P.hit_only = io.contacts == nullptr ? 1 : 0;
+  P.q_layout = io.q_layout;
+  P.q_stride_n = io.n;
+  T4_TRY(s->d_qcount.ensure(Q_COUNT * sizeof(uint32_t)) && s->d_stats.ensure(ST_COUNT * sizeof(unsigned long long)),
+         "workspace");
+  P.qcount = s->d_qcount.as<uint32_t>();
+  P.stats = s->d_stats.as<unsigned long long>();
+  T4_TRY(plat::zero(P.stats, ST_COUNT * sizeof(unsigned long long), st), "memset");
+  unsigned long long stats_host[ST_COUNT];
+  std::memset(stats_host, 0, sizeof(stats_host));
+  const int na = P.n_alinks;
+  const int64_t CH = chunkStates();
+  int64_t total = 0;
+  const size_t qelem = io.q_layout == T4C_Q_F64_ROWMAJOR ? sizeof(double) : sizeof(float);
+  for (int64_t base = 0; base < io.n; base += CH)
+  {
+    const int64_t nc = std::min<int64_t>(CH, io.n - base);
+    P.n = nc;
+    P.state_base = base;
+    // ---- poses of the kinematic links
+    const size_t pose_elems = (size_t)nc * (size_t)std::max(na, 1) * 12;
+    T4_TRY(s->d_poses0.ensure(pose_elems * sizeof(float)), "workspace");
+    P.poses0 = s->d_poses0.as<float>();
+    if (io.cast)
+    {
+      T4_TRY(s->d_poses1.ensure(pose_elems * sizeof(float)), "workspace");
+      P.poses1 = s->d_poses1.as<float>();
+    }
+    P.fk_out = nullptr;
+    if (io.model)
+    {
+      const size_t qoff = io.q_layout == T4C_Q_F32_SOA ? (size_t)base : (size_t)base * (size_t)io.model->n_q;
+      P.q0 = (const char*)io.q0 + qoff * qelem;
+      P.q1 = io.q1 ? (const char*)io.q1 + qoff * qelem : nullptr;
+      launchFk(P, nc, st);
+    }
+    else if (na > 0)
+    {
+      P.poses_in0 = io.poses0 + (size_t)base * na * 12;
+      P.poses_in1 = io.poses1 ? io.poses1 + (size_t)base * na * 12 : nullptr;
+      launchConvert(P, nc * na, st);
+    }
+    // ---- per-state flags
+    if (io.hit)
+      P.hit = io.hit + base;
+    else
+    {
+      T4_TRY(s->d_hit.ensure((size_t)nc), "workspace");
+      P.hit = s->d_hit.as<uint8_t>();
+    }
+    T4_TRY(plat::zero(P.hit, (size_t)nc, st), "memset");
+    if (io.req.type == T4C_TEST_FIRST && io.contacts)
+    {
+      T4_TRY(s->d_claim.ensure((size_t)nc * sizeof(uint32_t)), "workspace");
+      P.first_claim = s->d_claim.as<uint32_t>();
+      T4_TRY(plat::zero(P.first_claim, (size_t)nc * sizeof(uint32_t), st), "memset");
+    }
+    // ---- broadphase (retried with a larger queue when it overflows)
+    uint32_t qc[Q_COUNT];
+    if (s->cand_cap == 0)
+      s->cand_cap = (uint32_t)std::min<int64_t>(std::max<int64_t>(1 << 16, 24 * nc), 1ll << 30);
+    for (int attempt = 0;; ++attempt)
+    {
+      const size_t cb = (size_t)s->cand_cap * sizeof(uint32_t);
+      T4_TRY(s->d_cand_state.ensure(cb) && s->d_cand_a.ensure(cb) && s->d_cand_b.ensure(cb), "candidate queue");
+      P.cand_state = s->d_cand_state.as<uint32_t>();
+      P.cand_a = s->d_cand_a.as<uint32_t>();
+      P.cand_b = s->d_cand_b.as<uint32_t>();
+      P.cand_cap = s->cand_cap;
+      T4_TRY(plat::zero(P.qcount, Q_COUNT * sizeof(uint32_t), st), "memset");
+      if (P.n_bvh_nodes > 0)
+        launchBroadStatic(P, nc * (int64_t)P.n_active_shapes, st);
+      launchBroadActive(P, nc * (int64_t)P.n_aa_pairs, st);
+      T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "broadphase");
+      if (qc[Q_CAND] <= s->cand_cap)
+        break;
+      if (attempt >= 2)
+        return fail(T4C_ERR_NOMEM, "candidate queue overflow (%u pairs)", qc[Q_CAND]);
+      s->cand_cap = (uint32_t)std::min<uint64_t>((uint64_t)qc[Q_CAND] + qc[Q_CAND] / 8 + 1024, 0xfffffff0ull);
+      T4_TRY(plat::h2d(P.stats, stats_host, sizeof(stats_host), st), "stats restore");
+    }
+    const uint32_t ncand = qc[Q_CAND];
+    // ---- FP32 cull
+    T4_TRY(s->d_surv.ensure(std::max<size_t>(ncand, 1) * sizeof(uint32_t)) &&
+               s->d_surv_axis.ensure(std::max<size_t>(ncand, 1) * 3 * sizeof(float)),
+           "survivor queue");
+    P.surv = s->d_surv.as<uint32_t>();
+    P.surv_axis = s->d_surv_axis.as<float>();
+    P.surv_cap = ncand;
+    launchCull(P, ncand, st);
+    T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "cull");
+    const uint32_t nsurv = qc[Q_SURV];
+    // ---- FP64 exact pass
+    const bool closest = io.req.type == T4C_TEST_CLOSEST && io.contacts;
+    const int64_t room = std::max<int64_t>(0, io.capacity - total);
+    P.raw = nullptr;
+    P.raw_local = nullptr;
+    P.raw_cap = 0;
+    if (io.contacts)
+    {
+      if (closest)
+      {
+        T4_TRY(s->d_raw.ensure(std::max<size_t>(nsurv, 1) * sizeof(t4c_contact)), "contact staging");
+        P.raw = s->d_raw.as<t4c_contact>();
+        P.raw_cap = nsurv;
+        if (io.cast && io.cc_local)
+        {
+          T4_TRY(s->d_raw_local.ensure(std::max<size_t>(nsurv, 1) * 6 * sizeof(float)), "contact staging");
+          P.raw_local = s->d_raw_local.as<float>();
+        }
+      }
+      else
+      {
+        P.raw = io.contacts + std::min<int64_t>(total, io.capacity);
+        P.raw_cap = (uint32_t)std::min<int64_t>(room, 0xfffffff0ll);
+        P.raw_local = (io.cast && io.cc_local) ? io.cc_local + (size_t)std::min<int64_t>(total, io.capacity) * 6 : nullptr;
+      }
+    }
+    launchExact(P, nsurv, st);
+    T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase");
+    const uint32_t nraw = qc[Q_RAW];
+    if (closest)
+    {
+      // ---- ContactTestType::CLOSEST: minimum per (state, link pair)
+      P.ht_size = nextPow2(2ull * nraw);
+      T4_TRY(s->d_ht_rep.ensure((size_t)P.ht_size * sizeof(int32_t)) &&
+                 s->d_ht_best.ensure((size_t)P.ht_size * sizeof(unsigned long long)),
+             "hash table");
+      P.ht_rep = s->d_ht_rep.as<int32_t>();
+      P.ht_best = s->d_ht_best.as<unsigned long long>();
+      T4_TRY(plat::fill(P.ht_rep, 0xff, (size_t)P.ht_size * sizeof(int32_t), st) &&
+                 plat::fill(P.ht_best, 0xff, (size_t)P.ht_size * sizeof(unsigned long long), st),
+             "memset");
+      P.out = io.contacts + std::min<int64_t>(total, io.capacity);
+      P.out_cap = (uint32_t)std::min<int64_t>(room, 0xfffffff0ll);
+      P.out_local = (io.cast && io.cc_local) ? io.cc_local + (size_t)std::min<int64_t>(total, io.capacity) * 6 : nullptr;
+      launchClosestInsert(P, nraw, st);
+      launchClosestEmit(P, nraw, st);
+      T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "closest reduction");
+      total += qc[Q_OUT];
+    }
+    else
+      total += nraw;
+    launchCountHit(P, nc, st);
+    T4_TRY(launchOk() && plat::d2h(stats_host, P.stats, sizeof(stats_host), st) && plat::sync(st), "stats");
+  }
+  io.n_contacts = total;
+  stats_host[ST_STATES] = (unsigned long long)io.n;
+  stats_host[ST_CONTACTS] = (unsigned long long)total;
+  io.stats.states = stats_host[ST_STATES];
+  io.stats.bvh_nodes = stats_host[ST_BVH_NODES];
+  io.stats.candidates = stats_host[ST_CANDIDATES];
+  io.stats.culled = stats_host[ST_CULLED];
+  io.stats.gjk_pairs = stats_host[ST_GJK_PAIRS];
+  io.stats.gjk_iterations = stats_host[ST_GJK_ITERS];
+  io.stats.epa_pairs = stats_host[ST_EPA_PAIRS];
+  io.stats.epa_iterations = stats_host[ST_EPA_ITERS];
+  io.stats.contacts = stats_host[ST_CONTACTS];
+  io.stats.colliding_states = stats_host[ST_COLLIDING];
+  if (io.contacts && total > io.capacity)
+    return fail(T4C_ERR_CAPACITY, "contact buffer too small: %lld needed, capacity %lld", (long long)total,
+                (long long)io.capacity);
+  return T4C_OK;
+}
+
+// ===================================================================================================================
+// C ABI
+// ===================================================================================================================
+static t4c_status hostRun(t4c_scene* s, BatchIO& io, const double* hq0, const double* hq1, const double* hp0,
+                          const double* hp1, t4c_result* r)
+{
+  if (!s || !r || io.n < 0)
+    return fail(T4C_ERR_INVALID, "null scene / result or negative n");
+  if (!bindDevice(s))
+    return fail(T4C_ERR_CUDA, "cudaSetDevice(%d): %s", s->device, plat::lastError());
+  t4c_status rc = syncScene(s);
+  if (rc != T4C_OK)
+    return rc;
+  t4stream st = s->stream;
+  const int na = (int)s->comp.alinks.size();
+  if (io.model)
+  {
+    const size_t qb = (size_t)io.n * (size_t)io.model->n_q * sizeof(double);
+    T4_TRY(s->d_q0.ensure(qb) && plat::h2d(s->d_q0.p, hq0, qb, st), "upload q");
+    io.q0 = s->d_q0.p;
+    if (io.cast)
+    {
+      T4_TRY(s->d_q1.ensure(qb) && plat::h2d(s->d_q1.p, hq1, qb, st), "upload q1");
+      io.q1 = s->d_q1.p;
+    }
+    io.q_layout = T4C_Q_F64_ROWMAJOR;
+  }
+  else
+  {
+    const size_t pb = (size_t)io.n * (size_t)na * 12 * sizeof(double);
+    T4_TRY(s->d_pin0.ensure(pb) && plat::h2d(s->d_pin0.p, hp0, pb, st), "upload poses");
+    io.poses0 = s->d_pin0.as<double>();
+    if (io.cast)
+    {
+      T4_TRY(s->d_pin1.ensure(pb) && plat::h2d(s->d_pin1.p, hp1, pb, st), "upload poses1");
+      io.poses1 = s->d_pin1.as<double>();
+    }
+  }
+  if (r->hit)
+  {
+    T4_TRY(s->d_hit_full.ensure((size_t)std::max<int64_t>(io.n, 1)), "workspace");
+    io.hit = s->d_hit_full.as<uint8_t>();
+  }
+  if (r->contacts)
+  {
+    T4_TRY(s->d_out.ensure((size_t)std::max<int64_t>(r->capacity, 1) * sizeof(t4c_contact)), "workspace");
+    io.contacts = s->d_out.as<t4c_contact>();
+    io.capacity = r->capacity;
+    if (r->cc_local && io.cast)
+    {
+      T4_TRY(s->d_out_local.ensure((size_t)std::max<int64_t>(r->capacity, 1) * 6 * sizeof(float)), "workspace");
+      io.cc_local = s->d_out_local.as<float>();
+    }
+  }
+  rc = runBatch(s, io);
+  r->n_contacts = io.n_contacts;
+  r->stats = io.stats;
+  if (rc != T4C_OK && rc != T4C_ERR_CAPACITY)
+    return rc;
+  const int64_t ncopy = std::min<int64_t>(io.n_contacts, r->capacity);
+  bool ok = true;
+  if (r->hit)
+    ok = ok && plat::d2h(r->hit, io.hit, (size_t)io.n, st);
+  if (r->contacts)
+    ok = ok && plat::d2h(r->contacts, io.contacts, (size_t)ncopy * sizeof(t4c_contact), st);
+  if (r->contacts && r->cc_local && io.cast)
+    ok = ok && plat::d2h(r->cc_local, io.cc_local, (size_t)ncopy * 6 * sizeof(float), st);
+  T4_TRY(ok && plat::sync(st), "download results");
+  return rc;
+}
+
+// Eigen::VectorXd::LinSpaced (core/utils.h:194-200)
+static double linspaced(int64_t cnt, double low, double high, int64_t i)
+{
+  const int64_t size1 = cnt == 1 ? 1 : cnt - 1;
+  const double step = cnt == 1 ? 0.0 : (high - low) / double(cnt - 1);
+  const bool flip = std::fabs(high) < std::fabs(low);
+  if (flip)
+    return (i == 0) ? low : (high - double(size1 - i) * step);
+  return (i == size1) ? high : (low + double(i) * step);
+}
+
+// LVS expansion (tesseract_environment/core/utils.h:189-205 continuous, :328-347 discrete)
+static void lvsExpand(const double* traj, int64_t n_traj, int n_wp, int n_q, double lvs, bool cast,
+                      std::vector<double>& q0, std::vector<double>& q1)
+{
+  std::vector<double> sa((size_t)n_q), sb((size_t)n_q);
+  for (int64_t t = 0; t < n_traj; ++t)
+  {
+    const double* tr = traj + (size_t)t * n_wp * n_q;
+    const int last = cast ? n_wp - 1 : n_wp;
+    for (int s = 0; s < last; ++s)
+    {
+      const double* a = tr + (size_t)s * n_q;
+      const double* b = tr + (size_t)(s + 1) * n_q;
+      double dist = -1;
+      if (s < n_wp - 1)
+      {
+        double acc = 0;
+        for (int k = 0; k < n_q; ++k)
+          acc += (b[k] - a[k]) * (b[k] - a[k]);
+        dist = std::sqrt(acc);
+      }
+      if (dist > 0 && dist > lvs)
+      {
+        const int64_t cnt = (int64_t)std::ceil(dist / lvs) + 1;
+        for (int64_t i = 0; i < cnt - 1; ++i)
+        {
+          for (int k = 0; k < n_q; ++k)
+          {
+            sa[k] = linspaced(cnt, a[k], b[k], i);
+            sb[k] = linspaced(cnt, a[k], b[k], i + 1);
+          }
+          q0.insert(q0.end(), sa.begin(), sa.end());
+          if (cast)
+            q1.insert(q1.end(), sb.begin(), sb.end());
+        }
+      }
+      else
+      {
+        q0.insert(q0.end(), a, a + n_q);
+        if (cast)
+          q1.insert(q1.end(), b, b + n_q);
+      }
+    }
+  }
+}
+
+extern "C" {
+const char* t4c_last_error(void) { return g_err.c_str(); }
+int32_t t4c_abi_version(void) { return T4C_ABI_VERSION; }
+int32_t t4c_device_count(void) { return plat::deviceCount(); }
+uint64_t t4c_kernel_launch_count(void) { return g_launches.load(); }
+
+t4c_status t4c_scene_create(const t4c_scene_desc* d, int32_t device, t4c_scene** out)
+{
+  if (!d || !out)
+    return fail(T4C_ERR_INVALID, "null argument");
+  if (d->n_links < 0 || d->n_shapes < 0 || d->n_vertices < 0 || d->n_acm_pairs < 0 || d->n_margin_pairs < 0)
+    return fail(T4C_ERR_INVALID, "negative count in scene description");
+  if (device < 0 || device >= plat::deviceCount())
+    return fail(T4C_ERR_CUDA, "no usable CUDA device %d (%d visible); this library has no CPU path", device,
+                plat::deviceCount());
+  std::unique_ptr<t4c_scene> s(new t4c_scene());
+  s->device = device;
+  if (!plat::setDevice(device))
+    return fail(T4C_ERR_CUDA, "cudaSetDevice(%d): %s", device, plat::lastError());
+  HostScene& H = s->host;
+  H.links.resize((size_t)d->n_links);
+  for (int i = 0; i < d->n_links; ++i)
+  {
+    H.links[i].name = d->links[i].name ? d->links[i].name : "";
+    H.links[i].type_id = d->links[i].type_id;
+    H.links[i].enabled = d->links[i].enabled != 0;
+    H.links[i].active = d->links[i].active != 0;
+    std::memcpy(H.links[i].pose, d->links[i].pose, sizeof(H.links[i].pose));
+  }
+  H.shapes.assign(d->shapes, d->shapes + d->n_shapes);
+  for (auto& sh : H.shapes)
+    if (sh.type < T4C_SPHERE || sh.type > T4C_TRIANGLE || sh.link < 0 || sh.link >= d->n_links)
+      return fail(T4C_ERR_INVALID, "bad shape record (type %d, link %d)", sh.type, sh.link);
+  H.vertices.assign(d->vertices, d->vertices + 3 * (size_t)d->n_vertices);
+  for (int i = 0; i < d->n_acm_pairs; ++i)
+    H.acm.insert(hostPairKey(d->acm_pairs[2 * i], d->acm_pairs[2 * i + 1]));
+  H.default_margin = d->default_margin;
+  for (int i = 0; i < d->n_margin_pairs; ++i)
+    H.pair_margins[hostPairKey(d->margin_pairs[2 * i], d->margin_pairs[2 * i + 1])] = d->margin_values[i];
+  s->stream = plat::newStream();
+  t4c_status rc = syncScene(s.get());
+  if (rc != T4C_OK)
+    return rc;
+  *out = s.release();
+  return T4C_OK;
+}
+
+t4c_status t4c_scene_clone(const t4c_scene* src, t4c_scene** out)
+{
+  if (!src || !out)
+    return fail(T4C_ERR_INVALID, "null argument");
+  std::unique_ptr<t4c_scene> s(new t4c_scene());
+  s->device = src->device;
+  s->host = src->host;
+  if (!plat::setDevice(s->device))
+    return fail(T4C_ERR_CUDA, "cudaSetDevice(%d): %s", s->device, plat::lastError());
+  s->stream = plat::newStream();
+  t4c_status rc = syncScene(s.get());
+  if (rc != T4C_OK)
+    return rc;
+  *out = s.release();
+  return T4C_OK;
+}
+
+void t4c_scene_destroy(t4c_scene* s)
+{
+  if (!s)
+    return;
+  plat::setDevice(s->device);
+  delete s;
+}
+
+t4c_status t4c_scene_set_active(t4c_scene* s, const int32_t* flags)
+{
+  if (!s || !flags)
+    return fail(T4C_ERR_INVALID, "null argument");
+  for (size_t i = 0; i < s->host.links.size(); ++i)
+    s->host.links[i].active = flags[i] != 0;
+  ++s->rev;
+  return T4C_OK;
+}
+t4c_status t4c_scene_set_enabled(t4c_scene* s, int32_t link, int32_t enabled)
+{
+  if (!s || link < 0 || link >= (int)s->host.links.size())
+    return fail(T4C_ERR_INVALID, "unknown link %d", link);
+  s->host.links[link].enabled = enabled != 0;
+  ++s->rev;
+  return T4C_OK;
+}
+t4c_status t4c_scene_set_acm(t4c_scene* s, int32_t n, const int32_t* pairs)
+{
+  if (!s || n < 0 || (n > 0 && !pairs))
+    return fail(T4C_ERR_INVALID, "bad argument");
+  s->host.acm.clear();
+  for (int i = 0; i < n; ++i)
+    s->host.acm.insert(hostPairKey(pairs[2 * i], pairs[2 * i + 1]));
+  ++s->rev;
+  return T4C_OK;
+}
+t4c_status t4c_scene_set_margins(t4c_scene* s, double def, int32_t n, const int32_t* pairs, const double* values)
+{
+  if (!s || n < 0 || (n > 0 && (!pairs || !values)))
+    return fail(T4C_ERR_INVALID, "bad argument");
+  s->host.default_margin = def;
+  s->host.pair_margins.clear();
+  for (int i = 0; i < n; ++i)
+    s->host.pair_margins[hostPairKey(pairs[2 * i], pairs[2 * i + 1])] = values[i];
+  ++s->rev;
+  return T4C_OK;
+}
+t4c_status t4c_scene_set_link_pose(t4c_scene* s, int32_t link, const double* pose12)
+{
+  if (!s || !pose12 || link < 0 || link >= (int)s->host.links.size())
+    return fail(T4C_ERR_INVALID, "unknown link %d", link);
+  std::memcpy(s->host.links[link].pose, pose12, 12 * sizeof(double));
+  ++s->rev;
+  return T4C_OK;
+}
+int32_t t4c_scene_num_active(const t4c_scene* s)
+{
+  if (!s)
+    return 0;
+  int n = 0;
+  for (auto& l : s->host.links)
+    n += l.active ? 1 : 0;
+  return n;
+}
+
+t4c_status t4c_fk_model_create(const t4c_fk_model_desc* d, const t4c_scene*, t4c_fk_model** out)
+{
+  if (!d || !out || d->n_joints < 0 || d->n_q < 0)
+    return fail(T4C_ERR_INVALID, "bad FK model description");
+  if (d->n_joints > T4_MAX_JOINTS)
+    return fail(T4C_ERR_UNSUPPORTED, "FK model has %d joints (max %d)", d->n_joints, T4_MAX_JOINTS);
+  std::unique_ptr<t4c_fk_model> m(new t4c_fk_model());
+  m->n_links = d->n_links;
+  m->n_q = d->n_q;
+  m->root_link = d->root_link;
+  m->joints.assign(d->joints, d->joints + d->n_joints);
+  std::vector<char> placed((size_t)std::max(d->n_links, 1), 0);
+  for (auto& j : m->joints)
+  {
+    if (j.parent_link < 0 || j.parent_link >= d->n_links || j.child_link < 0 || j.child_link >= d->n_links)
+      return fail(T4C_ERR_INVALID, "joint refers to a link outside [0,%d)", d->n_links);
+    if (placed[j.child_link])
+      return fail(T4C_ERR_INVALID, "link %d has two parent joints", j.child_link);
+    placed[j.child_link] = 1;
+  }
+  std::fill(placed.begin(), placed.end(), 0);
+  for (auto& j : m->joints)
+  {
+    // parent-before-child: the parent must be a root or already produced
+    bool parent_is_child_later = false;
+    for (auto& k : m->joints)
+      if (&k > &j && k.child_link == j.parent_link)
+        parent_is_child_later = true;
+    if (parent_is_child_later)
+      return fail(T4C_ERR_INVALID, "joints are not ordered parent-before-child");
+  }
+  *out = m.release();
+  return T4C_OK;
+}
+void t4c_fk_model_destroy(t4c_fk_model* m) { delete m; }
+}  // extern "C"
+
+extern "C" {
+t4c_status t4c_fk(const t4c_fk_model* m, const t4c_scene* scene_c, const double* q, int64_t n, double* link_poses)
+{
+  t4c_scene* s = const_cast<t4c_scene*>(scene_c);
+  if (!m || !s || !q || !link_poses || n < 0)
+    return fail(T4C_ERR_INVALID, "null argument");
+  t4c_status rc = syncScene(s);
+  if (rc != T4C_OK)
+    return rc;
+  FkCache* fc = nullptr;
+  rc = syncFk(s, m, &fc);
+  if (rc != T4C_OK)
+    return rc;
+  t4stream st = s->stream;
+  const int nl = (int)s->host.links.size();
+  KParams P;
+  fillSceneParams(s, P);
+  fillFkParams(m, fc, P);
+  const int64_t CH = chunkStates();
+  for (int64_t base = 0; base < n; base += CH)
+  {
+    const int64_t nc = std::min<int64_t>(CH, n - base);
+    const size_t qb = (size_t)nc * (size_t)m->n_q * sizeof(double);
+    const size_t ob = (size_t)nc * (size_t)nl * 12 * sizeof(double);
+    T4_TRY(s->d_q0.ensure(qb) && s->d_fk_out.ensure(ob) && plat::h2d(s->d_q0.p, q + (size_t)base * m->n_q, qb, st),
+           "FK workspace");
+    P.n = nc;
+    P.q0 = s->d_q0.p;
+    P.q_layout = T4C_Q_F64_ROWMAJOR;
+    P.q_stride_n = nc;
+    P.cast = 0;
+    P.fk_out = s->d_fk_out.as<double>();
+    launchFk(P, nc, st);
+    T4_TRY(launchOk() && plat::d2h(link_poses + (size_t)base * nl * 12, P.fk_out, ob, st) && plat::sync(st), "FK");
+  }
+  return T4C_OK;
+}
+
+t4c_status t4c_check_discrete(t4c_scene* s, const t4c_fk_model* m, const double* q, int64_t n, const t4c_request* req,
+                              t4c_result* r)
+{
+  if (!s || !m || !req || !r || (n > 0 && !q))
+    return fail(T4C_ERR_INVALID, "null argument");
+  BatchIO io;
+  io.n = n;
+  io.model = m;
+  io.req = *req;
+  return hostRun(s, io, q, nullptr, nullptr, nullptr, r);
+}
+
+t4c_status t4c_check_link_poses_discrete(t4c_scene* s, const double* poses, int64_t n, const t4c_request* req,
+                                         t4c_result* r)
+{
+  if (!s || !req || !r)
+    return fail(T4C_ERR_INVALID, "null argument");
+  BatchIO io;
+  io.n = n;
+  io.req = *req;
+  return hostRun(s, io, nullptr, nullptr, poses, nullptr, r);
+}
+
+t4c_status t4c_check_cast(t4c_scene* s, const t4c_fk_model* m, const double* q0, const double* q1, int64_t n,
+                          const t4c_request* req, t4c_result* r)
+{
+  if (!s || !m || !req || !r || (n > 0 && (!q0 || !q1)))
+    return fail(T4C_ERR_INVALID, "null argument");
+  BatchIO io;
+  io.n = n;
+  io.cast = true;
+  io.model = m;
+  io.req = *req;
+  return hostRun(s, io, q0, q1, nullptr, nullptr, r);
+}
+
+t4c_status t4c_check_link_poses_cast(t4c_scene* s, const double* p0, const double* p1, int64_t n,
+                                     const t4c_request* req, t4c_result* r)
+{
+  if (!s || !req || !r)
+    return fail(T4C_ERR_INVALID, "null argument");
+  BatchIO io;
+  io.n = n;
+  io.cast = true;
+  io.req = *req;
+  return hostRun(s, io, nullptr, nullptr, p0, p1, r);
+}
+
+static t4c_status checkTrajectories(t4c_scene* s, const t4c_fk_model* m, const double* traj, int64_t n_traj,
+                                    int32_t n_wp, double lvs, const t4c_request* req, t4c_result* r, int64_t* n_items,
+                                    bool cast)
+{
+  if (!s || !m || !req || !r || !traj || n_traj < 0 || n_wp < (cast ? 2 : 1) || !(lvs > 0))
+    return fail(T4C_ERR_INVALID, "bad trajectory arguments");
+  std::vector<double> q0, q1;
+  lvsExpand(traj, n_traj, n_wp, m->n_q, lvs, cast, q0, q1);
+  const int64_t n = (int64_t)(q0.size() / (size_t)std::max(m->n_q, 1));
+  if (n_items)
+    *n_items = n;
+  if (r->hit && r->capacity >= 0 && false)
+    return T4C_OK;
+  BatchIO io;
+  io.n = n;
+  io.cast = cast;
+  io.model = m;
+  io.req = *req;
+  return hostRun(s, io, q0.data(), cast ? q1.data() : nullptr, nullptr, nullptr, r);
+}
+
+t4c_status t4c_lvs_count(const double* traj, int64_t n_traj, int32_t n_wp, int32_t n_q, double lvs, int32_t cast,
+                         int64_t* n_items)
+{
+  if (!traj || !n_items || n_q <= 0 || !(lvs > 0))
+    return fail(T4C_ERR_INVALID, "bad arguments");
+  std::vector<double> q0, q1;
+  lvsExpand(traj, n_traj, n_wp, n_q, lvs, cast != 0, q0, q1);
+  *n_items = (int64_t)(q0.size() / (size_t)n_q);
+  return T4C_OK;
+}
+
+t4c_status t4c_check_trajectories_discrete(t4c_scene* s, const t4c_fk_model* m, const double* traj, int64_t n_traj,
+                                           int32_t n_wp, double lvs, const t4c_request* req, t4c_result* r,
+                                           int64_t* n_items)
+{
+  return checkTrajectories(s, m, traj, n_traj, n_wp, lvs, req, r, n_items, false);
+}
+t4c_status t4c_check_trajectories_cast(t4c_scene* s, const t4c_fk_model* m, const double* traj, int64_t n_traj,
+                                       int32_t n_wp, double lvs, const t4c_request* req, t4c_result* r,
+                                       int64_t* n_items)
+{
+  return checkTrajectories(s, m, traj, n_traj, n_wp, lvs, req, r, n_items, true);
+}
+
+t4c_status t4c_check_discrete_device(t4c_scene* s, const t4c_fk_model* m, int64_t n, const t4c_request* req,
+                                     t4c_device_io* d)
+{
+  if (!s || !m || !req || !d || (n > 0 && !d->q))
+    return fail(T4C_ERR_INVALID, "null argument");
+  BatchIO io;
+  io.n = n;
+  io.model = m;
+  io.req = *req;
+  io.q0 = d->q;
+  io.q_layout = d->q_layout;
+  io.hit = d->hit;
+  io.contacts = d->contacts;
+  io.capacity = d->capacity;
+  const t4c_status rc = runBatch(s, io);
+  d->n_contacts = io.n_contacts;
+  d->stats = io.stats;
+  return rc;
+}
+
+t4c_status t4c_check_cast_device(t4c_scene* s, const t4c_fk_model* m, int64_t n, const void* q1,
+                                 const t4c_request* req, t4c_device_io* d)
+{
+  if (!s || !m || !req || !d || (n > 0 && (!d->q || !q1)))
+    return fail(T4C_ERR_INVALID, "null argument");
+  BatchIO io;
+  io.n = n;
+  io.cast = true;
+  io.model = m;
+  io.req = *req;
+  io.q0 = d->q;
+  io.q1 = q1;
+  io.q_layout = d->q_layout;
+  io.hit = d->hit;
+  io.contacts = d->contacts;
+  io.cc_local = d->cc_local;
+  io.capacity = d->capacity;
+  const t4c_status rc = runBatch(s, io);
+  d->n_contacts = io.n_contacts;
+  d->stats = io.stats;
+  return rc;
+}
+
+t4c_status t4c_measure_fp32_peak(int32_t device, double* tflops)
+{
+  if (!tflops)
+    return fail(T4C_ERR_INVALID, "null argument");
+#ifdef T4C_HOSTSIM
+  (void)device;
+  return fail(T4C_ERR_CUDA, "host simulator has no device");
+#else
+  if (device < 0 || device >= plat::deviceCount())
+    return fail(T4C_ERR_CUDA, "no usable CUDA device %d", device);
+  plat::setDevice(device);
+  g_sm_count = 0;
+  const int blocks = smCount() * 8, threads = 256, iters = 1 << 15;
+  float* out = (float*)plat::alloc((size_t)blocks * threads * sizeof(float));
+  if (!out)
+    return fail(T4C_ERR_NOMEM, "alloc");
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  double best = 0;
+  for (int rep = 0; rep < 5; ++rep)
+  {
+    cudaEventRecord(e0);
+    fmaPeakKernel<<<blocks, threads>>>(out, iters);
+    ++g_launches;
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess)
+      break;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double fl = 2.0 * 8.0 * (double)iters * (double)blocks * threads;
+    if (ms > 0)
+      best = std::max(best, fl / (ms * 1e-3) / 1e12);
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  plat::release(out);
+  *tflops = best;
+  return best > 0 ? T4C_OK : fail(T4C_ERR_CUDA, "FMA peak kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
+#endif
+}
+}  // extern "C"
