@@ -247,6 +247,12 @@ t4c_status t4c_check_cast_device(t4c_scene* scene, const t4c_fk_model* model, in
                                  const void* q1, const t4c_request* request, t4c_device_io* io);
 /* number of this library's kernel launches since load (bench.py "gpu_launches") */
 uint64_t t4c_kernel_launch_count(void);
+/* Per-kernel device timing (CUDA events recorded on the launching stream around every launch of this library).
+ * Kernel order: fk, convert_poses, broad_static, broad_active, cull_fp32, exact_fp64, closest_insert, closest_emit,
+ * count_hit.  Process-wide, not thread safe: meant for bench.py / profiling runs only. */
+void t4c_profile_enable(int32_t on);
+void t4c_profile_reset(void);
+int32_t t4c_profile_get(double* ms, uint64_t* launches, int32_t capacity); /* returns the number of kernels */
 /* measured-peak helper: runs an FP32 FMA loop on every SM, returns TFLOP/s (roofline denominator) */
 t4c_status t4c_measure_fp32_peak(int32_t device, double* tflops);
 

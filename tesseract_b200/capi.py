@@ -122,6 +122,11 @@ def load_library(path=None):
     lib.t4c_check_discrete_device.argtypes = [VP, VP, I64, C.POINTER(Request), C.POINTER(DeviceIO)]
     lib.t4c_check_cast_device.argtypes = [VP, VP, I64, VP, C.POINTER(Request), C.POINTER(DeviceIO)]
     lib.t4c_kernel_launch_count.restype = C.c_uint64
+    lib.t4c_profile_enable.argtypes = [I32]
+    lib.t4c_profile_enable.restype = None
+    lib.t4c_profile_reset.restype = None
+    lib.t4c_profile_get.argtypes = [DP, C.POINTER(C.c_uint64), I32]
+    lib.t4c_profile_get.restype = I32
     lib.t4c_measure_fp32_peak.argtypes = [I32, DP]
     for name in ("t4c_scene_create", "t4c_scene_clone", "t4c_scene_set_active", "t4c_scene_set_enabled",
                  "t4c_scene_set_acm", "t4c_scene_set_margins", "t4c_scene_set_link_pose", "t4c_scene_num_active",
@@ -133,6 +138,17 @@ def load_library(path=None):
     if path is None:
         _lib = lib
     return lib
+
+
+KERNEL_NAMES = ("fk", "convert_poses", "broad_static", "broad_active", "cull_fp32", "exact_fp64", "closest_insert",
+                "closest_emit", "count_hit")
+
+
+def profile_get(lib):
+    ms = (C.c_double * 16)()
+    n = (C.c_uint64 * 16)()
+    k = lib.t4c_profile_get(ms, n, 16)
+    return {KERNEL_NAMES[i]: (float(ms[i]), int(n[i])) for i in range(min(k, len(KERNEL_NAMES)))}
 
 
 class T4CError(RuntimeError):

@@ -242,25 +242,82 @@ __global__ void fmaPeakKernel(float* out, int iters)
   out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
 }
 
-#define T4_LAUNCH(KERNEL, BLOCK, CTAS, P, n, st)                                                                       \
+// optional per-kernel timing with CUDA events recorded on the launching stream (bench.py roofline figures)
+enum
+{
+  PK_FK = 0,
+  PK_CONVERT,
+  PK_BROAD_STATIC,
+  PK_BROAD_ACTIVE,
+  PK_CULL,
+  PK_EXACT,
+  PK_CLOSEST_INSERT,
+  PK_CLOSEST_EMIT,
+  PK_COUNT_HIT,
+  PK_COUNT
+};
+struct ProfRec
+{
+  int k;
+  cudaEvent_t e0, e1;
+};
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof_pending;
+static double g_prof_ms[PK_COUNT];
+static unsigned long long g_prof_n[PK_COUNT];
+static void profBegin(int k, cudaStream_t st)
+{
+  if (!g_prof_on)
+    return;
+  ProfRec r;
+  r.k = k;
+  cudaEventCreate(&r.e0);
+  cudaEventCreate(&r.e1);
+  cudaEventRecord(r.e0, st);
+  g_prof_pending.push_back(r);
+}
+static void profEnd(cudaStream_t st)
+{
+  if (g_prof_on && !g_prof_pending.empty())
+    cudaEventRecord(g_prof_pending.back().e1, st);
+}
+static void profResolve()
+{
+  for (auto& r : g_prof_pending)
+  {
+    float ms = 0;
+    if (cudaEventSynchronize(r.e1) == cudaSuccess && cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess)
+    {
+      g_prof_ms[r.k] += ms;
+      g_prof_n[r.k] += 1;
+    }
+    cudaEventDestroy(r.e0);
+    cudaEventDestroy(r.e1);
+  }
+  g_prof_pending.clear();
+}
+
+#define T4_LAUNCH(KERNEL, PK, BLOCK, CTAS, P, n, st)                                                                   \
   do                                                                                                                   \
   {                                                                                                                    \
     if ((n) > 0)                                                                                                       \
     {                                                                                                                  \
+      profBegin((PK), (st));                                                                                           \
       KERNEL<<<gridFor((n), (BLOCK), (CTAS)), (BLOCK), 0, (st)>>>((P), (n));                                           \
+      profEnd((st));                                                                                                   \
       ++g_launches;                                                                                                    \
     }                                                                                                                  \
   } while (0)
 static bool launchOk() { return plat::chk(cudaGetLastError()); }
-static void launchFk(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(fkKernel, 128, 8, P, n, st); }
-static void launchConvert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(convertPosesKernel, 256, 8, P, n, st); }
-static void launchBroadStatic(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadStaticKernel, 256, 8, P, n, st); }
-static void launchBroadActive(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadActiveKernel, 256, 8, P, n, st); }
-static void launchCull(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(cullKernel, 256, 4, P, n, st); }
-static void launchExact(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(exactKernel, 128, 4, P, n, st); }
-static void launchClosestInsert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestInsertKernel, 256, 8, P, n, st); }
-static void launchClosestEmit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestEmitKernel, 256, 8, P, n, st); }
-static void launchCountHit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(countHitKernel, 256, 8, P, n, st); }
+static void launchFk(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(fkKernel, PK_FK, 128, 8, P, n, st); }
+static void launchConvert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(convertPosesKernel, PK_CONVERT, 256, 8, P, n, st); }
+static void launchBroadStatic(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadStaticKernel, PK_BROAD_STATIC, 256, 8, P, n, st); }
+static void launchBroadActive(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadActiveKernel, PK_BROAD_ACTIVE, 256, 8, P, n, st); }
+static void launchCull(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(cullKernel, PK_CULL, 256, 4, P, n, st); }
+static void launchExact(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(exactKernel, PK_EXACT, 128, 4, P, n, st); }
+static void launchClosestInsert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestInsertKernel, PK_CLOSEST_INSERT, 256, 8, P, n, st); }
+static void launchClosestEmit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestEmitKernel, PK_CLOSEST_EMIT, 256, 8, P, n, st); }
+static void launchCountHit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(countHitKernel, PK_COUNT_HIT, 256, 8, P, n, st); }
 #else
 #define T4_SERIAL(BODY, P, n)                                                                                          \
   do                                                                                                                   \
@@ -826,6 +883,37 @@ const char* t4c_last_error(void) { return g_err.c_str(); }
 int32_t t4c_abi_version(void) { return T4C_ABI_VERSION; }
 int32_t t4c_device_count(void) { return plat::deviceCount(); }
 uint64_t t4c_kernel_launch_count(void) { return g_launches.load(); }
+void t4c_profile_enable(int32_t on)
+{
+#ifndef T4C_HOSTSIM
+  g_prof_on = on != 0;
+#else
+  (void)on;
+#endif
+}
+void t4c_profile_reset(void)
+{
+#ifndef T4C_HOSTSIM
+  profResolve();
+  std::memset(g_prof_ms, 0, sizeof(g_prof_ms));
+  std::memset(g_prof_n, 0, sizeof(g_prof_n));
+#endif
+}
+int32_t t4c_profile_get(double* ms, uint64_t* launches, int32_t capacity)
+{
+#ifndef T4C_HOSTSIM
+  profResolve();
+  for (int i = 0; i < PK_COUNT && i < capacity; ++i)
+  {
+    ms[i] = g_prof_ms[i];
+    launches[i] = g_prof_n[i];
+  }
+  return PK_COUNT;
+#else
+  (void)ms, (void)launches, (void)capacity;
+  return 0;
+#endif
+}
 
 t4c_status t4c_scene_create(const t4c_scene_desc* d, int32_t device, t4c_scene** out)
 {
