@@ -1298,6 +1298,10 @@ struct RobustEPA
   int rv[3];
   double rp[3];
   bool ok = false;
+  double saved_depth = -1e300;
+  Face saved_face;
+  Vert saved_verts[3];
+  bool have_saved = false, deteriorated = false;
 
   bool makeFace(int a, int b, int c, Face& f) const
   {
@@ -1357,6 +1361,22 @@ struct RobustEPA
           best = i;
       if (best < 0)
         return false;
+      // The closest-face distance of an expanding polytope is a LOWER bound of the penetration depth and can only
+      // grow.  On curved supports (cylinder rims) sliver faces eventually corrupt the hull and the bound drops:
+      // stop there and report the tightest bound seen.
+      if (faces[best].d + 1e-12 < saved_depth)
+      {
+        deteriorated = true;
+        break;
+      }
+      if (faces[best].d >= saved_depth)
+      {
+        saved_depth = faces[best].d;
+        saved_face = faces[best];
+        for (int k = 0; k < 3; ++k)
+          saved_verts[k] = verts[faces[best].v[k]];
+        have_saved = true;
+      }
       Vert nv;
       nv.d = faces[best].n;
       nv.w = shape.Support(nv.d);
@@ -1453,6 +1473,17 @@ struct RobustEPA
     }
     if (best < 0)
       return false;
+    if (have_saved && (deteriorated || faces[best].d < saved_depth))
+    {
+      // report the tightest lower bound (see above); its three vertices were copied when it was recorded
+      for (int k = 0; k < 3; ++k)
+      {
+        verts.push_back(saved_verts[k]);
+        saved_face.v[k] = (int)verts.size() - 1;
+      }
+      faces.push_back(saved_face);
+      best = (int)faces.size() - 1;
+    }
     const Face& o = faces[best];
     normal = o.n;
     depth = o.d;
@@ -1508,7 +1539,9 @@ bool gjkEpaPenetration(const Convex& a, const Xf& wtrs0, const Convex& b, const 
       if (unconverged && gjk.m_simplex->rank == 4)
       {
         RobustEPA repa;
-        if (repa.run(shape, *gjk.m_simplex))
+        // both the faithful polytope's closest face and the robust one are lower bounds of the depth: keep the
+        // tighter (the faithful result is reported by the generic branch below)
+        if (repa.run(shape, *gjk.m_simplex) && (epa_status == EPA::Failed || repa.depth >= epa.m_depth))
         {
           results.epa_iterations += repa.iterations;
           V3 w0(0, 0, 0);

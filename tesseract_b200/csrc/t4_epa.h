@@ -29,7 +29,7 @@ struct EpaResult
   bool converged;
 };
 
-template <class T, int MAXV = 80, int MAXF = 160>
+template <class T, int MAXV = 96, int MAXF = 192>
 struct Epa
 {
   struct Face
@@ -211,6 +211,9 @@ struct Epa
     int mark = 0;
     int best = -1;
     int it = 0;
+    T saved_d = -Eps<T>::large();
+    V3<T> saved_n, saved_w[3], saved_p[3];
+    bool have_saved = false, deteriorated = false;
     for (; it < max_iter; ++it)
     {
       best = -1;
@@ -219,6 +222,25 @@ struct Epa
           best = i;
       if (best < 0)
         return false;
+      // The closest-face distance is a LOWER bound of the depth and can only grow.  On curved supports (cylinder /
+      // cone rims) the faces shrink to rounding-noise size near convergence and the hull eventually corrupts: the
+      // bound then drops.  Stop there and report the tightest bound recorded.
+      if (F[best].d + T(1e-12) < saved_d)
+      {
+        deteriorated = true;
+        break;
+      }
+      if (F[best].d >= saved_d)
+      {
+        saved_d = F[best].d;
+        saved_n = F[best].n;
+        for (int k = 0; k < 3; ++k)
+        {
+          saved_w[k] = W[F[best].v[k]];
+          saved_p[k] = P[F[best].v[k]];
+        }
+        have_saved = true;
+      }
       if (nv >= MAXV)
         break;
       V3<T> w, p;
@@ -354,6 +376,22 @@ struct Epa
         best = i;
     if (best < 0)
       return false;
+    if (have_saved && (deteriorated || F[best].d < saved_d))
+    {
+      // report the recorded tightest bound; foot-point weights on its own triangle (clamped)
+      const V3<T> pr = saved_n * saved_d;
+      T c0 = saved_n.dot((saved_w[1] - pr).cross(saved_w[2] - pr));
+      T c1 = saved_n.dot((saved_w[2] - pr).cross(saved_w[0] - pr));
+      T c2 = saved_n.dot((saved_w[0] - pr).cross(saved_w[1] - pr));
+      c0 = t4max(c0, T(0)), c1 = t4max(c1, T(0)), c2 = t4max(c2, T(0));
+      const T sum = c0 + c1 + c2;
+      if (!(sum > T(0)))
+        return false;
+      res.normal = saved_n;
+      res.depth = saved_d;
+      res.pA = saved_p[0] * (c0 / sum) + saved_p[1] * (c1 / sum) + saved_p[2] * (c2 / sum);
+      return true;
+    }
     // A flat face of A-B is usually split into several coplanar triangles with the same plane distance: take the one
     // that actually contains the foot point of the origin (signed barycentric coordinates), otherwise the witness
     // blend below would extrapolate.

@@ -44,16 +44,19 @@ struct CompiledScene
 {
   std::vector<DShape> shapes;
   std::vector<DStaticW> statics;
+  std::vector<double> shape_d;    // [shape][16]
+  std::vector<double> statics_d;  // [shape][12]
   std::vector<f4> verts;
   std::vector<DBvhNode> bvh;
   std::vector<int32_t> active_shapes;
   std::vector<int32_t> aa_pairs;
   std::vector<uint32_t> acm_bits;
   int acm_words = 0;
-  std::vector<float> pair_margin;  // empty: default only
+  std::vector<double> pair_margin;  // empty: default only
   std::vector<int32_t> alinks;     // link index of every active link, ascending
   std::vector<int32_t> link_alink; // per link: active ordinal or -1
   float default_margin = 0, max_margin = 0;
+  double default_margin_d = 0, max_margin_d = 0;
   bool cast_unsupported = false;
 };
 
@@ -197,8 +200,10 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
 {
   const int nl = (int)H.links.size(), ns = (int)H.shapes.size();
   C = CompiledScene();
-  C.default_margin = (float)H.default_margin;
-  C.max_margin = (float)H.maxMargin();
+  C.default_margin_d = H.default_margin;
+  C.max_margin_d = H.maxMargin();
+  C.default_margin = roundUp(H.default_margin);
+  C.max_margin = roundUp(H.maxMargin());
   C.link_alink.assign((size_t)nl, -1);
   for (int i = 0; i < nl; ++i)
     if (H.links[i].active)
@@ -215,6 +220,8 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
   }
   C.shapes.resize((size_t)ns);
   C.statics.resize((size_t)ns);
+  C.shape_d.assign((size_t)std::max(ns, 1) * 16, 0.0);
+  C.statics_d.assign((size_t)std::max(ns, 1) * 12, 0.0);
   std::vector<LbvhBuilder::Box> sbox;
   std::vector<int32_t> sshape;
   std::vector<std::vector<int32_t>> link_active_shapes((size_t)nl);
@@ -238,6 +245,10 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
     for (int k = 0; k < 12; ++k)
       d.lpose[k] = (float)s.pose[k];
     d.params[0] = (float)s.params[0], d.params[1] = (float)s.params[1], d.params[2] = (float)s.params[2];
+    for (int k = 0; k < 3; ++k)
+      C.shape_d[(size_t)i * 16 + k] = s.params[k];
+    for (int k = 0; k < 12; ++k)
+      C.shape_d[(size_t)i * 16 + 4 + k] = s.pose[k];
     double c[3], h[3];
     shapeLocalBox(s, H.vertices.data(), c, h);
     const double rad = s.type == T4C_SPHERE ? s.params[0] : std::sqrt(h[0] * h[0] + h[1] * h[1] + h[2] * h[2]);
@@ -263,6 +274,7 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
     // static shape: world pose + bounding data in FP64, rounded once
     const Xf<double> xw = Xf<double>::from12(L.pose) * Xf<double>::from12(s.pose);
     DStaticW& w = C.statics[i];
+    xw.to12(&C.statics_d[(size_t)i * 12]);
     Xf<float> xf = xw.cast<float>();
     xf.to12(w.pose);
     V3<double> mn, mx;
@@ -355,16 +367,16 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
       err = "pair-margin table too large";
       return false;
     }
-    C.pair_margin.assign((size_t)std::max(na, 1) * (size_t)nl, (float)H.default_margin);
+    C.pair_margin.assign((size_t)std::max(na, 1) * (size_t)nl, H.default_margin);
     for (auto& kv : H.pair_margins)
     {
       const int a = (int)(kv.first >> 32), b = (int)(kv.first & 0xffffffffu);
       if (a >= nl || b >= nl)
         continue;
       if (C.link_alink[a] >= 0)
-        C.pair_margin[(size_t)C.link_alink[a] * nl + b] = (float)kv.second;
+        C.pair_margin[(size_t)C.link_alink[a] * nl + b] = kv.second;
       if (C.link_alink[b] >= 0)
-        C.pair_margin[(size_t)C.link_alink[b] * nl + a] = (float)kv.second;
+        C.pair_margin[(size_t)C.link_alink[b] * nl + a] = kv.second;
     }
   }
   // ---- active x active shape pairs (enabled, different links, not allowed by the ACM)

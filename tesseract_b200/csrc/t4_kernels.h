@@ -61,6 +61,8 @@ struct KParams
   // ---- scene (read only)
   const DShape* shapes;
   const DStaticW* statics;  // indexed by shape index (valid for static shapes)
+  const double* shape_d;    // [shape][16]: params[3], pad, lpose[12]  -- FP64 copies for the exact pass
+  const double* statics_d;  // [shape][12]: world pose of static shapes, FP64
   const f4* verts;
   const DBvhNode* bvh;
   int32_t n_bvh_nodes;
@@ -70,9 +72,10 @@ struct KParams
   int32_t n_aa_pairs;
   const uint32_t* acm_bits;  // [n_alinks][acm_words]
   int32_t acm_words;
-  const float* pair_margin;  // [n_alinks][n_links] or null
+  const double* pair_margin;  // [n_alinks][n_links] or null
   int32_t n_links, n_alinks;
-  float default_margin, max_margin;
+  float default_margin, max_margin;  // rounded UP (conservative culling)
+  double default_margin_d, max_margin_d;  // exact values for the accept / reject decisions
   // ---- FK model
   const DJoint* joints;
   int32_t n_joints, n_q;
@@ -89,6 +92,8 @@ struct KParams
   int64_t q_stride_n;  // total n of the SoA array (SoA layout only)
   float* poses0;       // [n][n_alinks][12]
   float* poses1;
+  double* poses0d;     // same poses in FP64 (exact pass: identical inputs to the reference's FP64 path)
+  double* poses1d;
   const double* poses_in0;  // FK bypass input (device, double)
   const double* poses_in1;
   double* fk_out;  // t4c_fk
@@ -204,14 +209,38 @@ T4_KD void shapePose(const KParams& P, const DShape& S, int sh, int64_t s, Xf<T>
     x1 = x0;
 }
 
+// FP64 variant for the exact pass
+T4_KD void shapePoseD(const KParams& P, const DShape& S, int sh, int64_t s, Xf<double>& x0, Xf<double>& x1)
+{
+  if (S.alink < 0)
+  {
+    x0 = Xf<double>::from12(P.statics_d + (size_t)sh * 12);
+    x1 = x0;
+    return;
+  }
+  const size_t off = ((size_t)s * (size_t)P.n_alinks + (size_t)S.alink) * 12;
+  x0 = Xf<double>::from12(P.poses0d + off);
+  if (P.cast)
+    x1 = Xf<double>::from12(P.poses1d + off);
+  if (!S.identity_lpose)
+  {
+    const Xf<double> l = Xf<double>::from12(P.shape_d + (size_t)sh * 16 + 4);
+    x0 = x0 * l;
+    if (P.cast)
+      x1 = x1 * l;
+  }
+  if (!P.cast)
+    x1 = x0;
+}
+
 T4_KD bool acmAllowed(const KParams& P, int alink, int linkB)
 {
   return (P.acm_bits[(size_t)alink * P.acm_words + (linkB >> 5)] >> (linkB & 31)) & 1u;
 }
 
-T4_KD float pairMargin(const KParams& P, int alink, int linkB)
+T4_KD double pairMargin(const KParams& P, int alink, int linkB)
 {
-  return P.pair_margin ? P.pair_margin[(size_t)alink * P.n_links + linkB] : P.default_margin;
+  return P.pair_margin ? P.pair_margin[(size_t)alink * P.n_links + linkB] : P.default_margin_d;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -286,11 +315,13 @@ T4_KD void fkBody(int64_t s, const KParams& P)
       return;
     }
     float* dst = pass ? P.poses1 : P.poses0;
+    double* dstd = pass ? P.poses1d : P.poses0d;
     for (int a = 0; a < P.n_alinks; ++a)
     {
       const int j = P.alink_joint[a];
       const Xf<double> x = j >= 0 ? Tj[j] : Xf<double>::from12(P.alink_static + (size_t)a * 12);
       storePoseF(dst + ((size_t)s * P.n_alinks + a) * 12, x);
+      x.to12(dstd + ((size_t)s * P.n_alinks + a) * 12);
     }
   }
 }
@@ -300,8 +331,15 @@ T4_KD void convertPosesBody(int64_t i, const KParams& P)
 {
   const double* src0 = P.poses_in0 + (size_t)i * 12;
   storePoseF(P.poses0 + (size_t)i * 12, Xf<double>::from12(src0));
+  for (int k = 0; k < 12; ++k)
+    P.poses0d[(size_t)i * 12 + k] = src0[k];
   if (P.cast)
-    storePoseF(P.poses1 + (size_t)i * 12, Xf<double>::from12(P.poses_in1 + (size_t)i * 12));
+  {
+    const double* src1 = P.poses_in1 + (size_t)i * 12;
+    storePoseF(P.poses1 + (size_t)i * 12, Xf<double>::from12(src1));
+    for (int k = 0; k < 12; ++k)
+      P.poses1d[(size_t)i * 12 + k] = src1[k];
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------------

@@ -21,6 +21,28 @@ T4_KD void loadPairShapes(const KParams& P, int64_t s, int a, int b, ShapeW<T>& 
   B = makeShapeW<T>(Sb, P.verts, b0, b1, P.cast && Sb.alink >= 0);
 }
 
+T4_KD void loadPairShapesD(const KParams& P, int64_t s, int a, int b, ShapeW<double>& A, ShapeW<double>& B)
+{
+  const DShape& Sa = P.shapes[a];
+  const DShape& Sb = P.shapes[b];
+  Xf<double> a0, a1, b0, b1;
+  shapePoseD(P, Sa, a, s, a0, a1);
+  shapePoseD(P, Sb, b, s, b0, b1);
+  A = makeShapeW<double>(Sa, P.verts, a0, a1, P.cast && Sa.alink >= 0);
+  B = makeShapeW<double>(Sb, P.verts, b0, b1, P.cast && Sb.alink >= 0);
+  // FP64 shape parameters (the FP32 record is only good for culling)
+  const double* pa = P.shape_d + (size_t)a * 16;
+  const double* pb = P.shape_d + (size_t)b * 16;
+  if (A.type == SH_BOX)
+    A.he = V3<double>(pa[0], pa[1], pa[2]);
+  else if (A.type != SH_HULL && A.type != SH_TRIANGLE)
+    A.r = pa[0], A.h = pa[1];
+  if (B.type == SH_BOX)
+    B.he = V3<double>(pb[0], pb[1], pb[2]);
+  else if (B.type != SH_HULL && B.type != SH_TRIANGLE)
+    B.r = pb[0], B.h = pb[1];
+}
+
 T4_KD bool analyticPair(int ta, int tb)
 {
   if (ta == SH_SPHERE && (tb == SH_SPHERE || tb == SH_TRIANGLE || tb == SH_CAPSULE))
@@ -43,6 +65,10 @@ T4_KD void pushSurvivor(const KParams& P, uint32_t c, const V3<float>& axis)
     P.surv_axis[3 * (size_t)k + 2] = axis.z;
   }
 }
+
+// The reference's GJK may stop early with an upper bound up to ~1e-4 m above the true distance (t4_bullet.h), so a pair
+// is accepted on the FP32 bound alone only when it is this far inside the margin; the rest goes to the exact pass.
+#define T4_ACCEPT_SLACK 5e-4f
 
 // item = candidate index.  FP32 GJK used ONLY to discard pairs that are provably farther apart than the contact
 // cut-off (and, for boolean FIRST queries without contact output, to accept pairs that are provably inside it).
@@ -67,14 +93,14 @@ T4_KD void cullBody(int64_t c, const KParams& P)
   A.x1.p -= offset;
   B.x0.p -= offset;
   B.x1.p -= offset;
-  const float msum = A.innerMargin() + B.innerMargin();
+  const float msum = A.margin() + B.margin();
   const float cutoff = msum + P.max_margin + T4_CULL_SLACK;
   float accept = cutoff;  // anything within the cut-off is decided by the exact pass
   bool bool_mode = false;
   if (P.hit_only && P.calc_dist)
   {
-    const float pm = t4min(pairMargin(P, P.shapes[a].alink, P.shapes[b].link), P.max_margin);
-    accept = msum + pm - T4_CULL_SLACK;
+    const float pm = t4min((float)pairMargin(P, P.shapes[a].alink, P.shapes[b].link), P.max_margin);
+    accept = msum + pm - T4_ACCEPT_SLACK;
     bool_mode = accept > 0.f;
     if (!bool_mode)
       accept = cutoff;
@@ -129,23 +155,23 @@ T4_KD void exactBody(int64_t k, const KParams& P, EPA_T& epa)
     return;
   const int a = (int)P.cand_a[c], b = (int)P.cand_b[c];
   ShapeW<double> A, B;
-  loadPairShapes<double>(P, s, a, b, A, B);
+  loadPairShapesD(P, s, a, b, A, B);
   const V3<double> axis0((double)P.surv_axis[3 * (size_t)k], (double)P.surv_axis[3 * (size_t)k + 1],
                          (double)P.surv_axis[3 * (size_t)k + 2]);
   PairResult<double> pr;
-  exactPair<double>(A, B, (double)P.max_margin, P.calc_pen != 0, P.calc_dist != 0, axis0, pr, epa);
+  exactPair<double>(A, B, P.max_margin_d, P.calc_pen != 0, P.calc_dist != 0, axis0, pr, epa);
   statAdd(P.stats, ST_GJK_ITERS, (uint32_t)pr.gjk_iters);
   statAdd(P.stats, ST_EPA_PAIRS, pr.used_epa ? 1u : 0u);
   statAdd(P.stats, ST_EPA_ITERS, (uint32_t)pr.epa_iters);
   if (!pr.has)
     return;
   // TesseractBroadphaseBridgedManifoldResult::addContactPoint / addSingleResult: reject beyond the max margin
-  if (pr.distance > (double)P.max_margin)
+  if (pr.distance > P.max_margin_d)
     return;
   const DShape& Sa = P.shapes[a];
   const DShape& Sb = P.shapes[b];
   // processResult (core/common.h:114-167): per-pair margin unless both calculate_* flags are off
-  if ((P.calc_dist || P.calc_pen) && pr.distance > (double)pairMargin(P, Sa.alink, Sb.link))
+  if ((P.calc_dist || P.calc_pen) && pr.distance > pairMargin(P, Sa.alink, Sb.link))
     return;
   if (P.hit)
     P.hit[s] = 1;
@@ -171,7 +197,7 @@ T4_KD void exactBody(int64_t k, const KParams& P, EPA_T& epa)
     // addCastSingleResult (bullet_utils.h:527-611): continuous data per cast side; a single cast side is reported as
     // index 1 (:595-607)
     const size_t offA = ((size_t)s * (size_t)P.n_alinks + (size_t)Sa.alink) * 12;
-    const Xf<double> linkA0 = loadPose<double>(P.poses0 + offA);
+    const Xf<double> linkA0 = Xf<double>::from12(P.poses0d + offA);
     ShapeW<double> Au = A;
     Au.cast = false;
     double t;
@@ -183,7 +209,7 @@ T4_KD void exactBody(int64_t k, const KParams& P, EPA_T& epa)
       ct.cc_time[0] = (float)t, ct.cc_type[0] = (uint8_t)ty;
       local[0][0] = pl.x, local[0][1] = pl.y, local[0][2] = pl.z;
       const size_t offB = ((size_t)s * (size_t)P.n_alinks + (size_t)Sb.alink) * 12;
-      const Xf<double> linkB0 = loadPose<double>(P.poses0 + offB);
+      const Xf<double> linkB0 = Xf<double>::from12(P.poses0d + offB);
       ShapeW<double> Bu = B;
       Bu.cast = false;
       V3<double> plb = linkB0.invApply(pr.pointOnB);

@@ -12,7 +12,7 @@
 #ifndef T4_PAIR_H_
 #define T4_PAIR_H_
 
-#include "t4_epa.h"
+#include "t4_bullet_detector.h"
 
 namespace t4
 {
@@ -63,6 +63,11 @@ T4_HD ShapeW<T> makeShapeW(const DShape& s, const f4* verts, const Xf<T>& x0, co
   w.cast = cast;
   w.x0 = x0;
   w.x1 = x1;
+  if (cast)
+  {
+    w.t01 = x0.invTimes(x1);
+    w.x1 = x0 * w.t01;  // tfWorld1 as the reference forms it (bullet_utils.h:466)
+  }
   return w;
 }
 
@@ -307,64 +312,18 @@ T4_HDN void exactPair(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold, boo
     return;
   }
 
-  // ---- GJK / EPA, in a frame centred between the two shape origins (tesseract_gjk_pair_detector.cpp:694-698)
-  ShapeW<T> A = A0, B = B0;
-  const V3<T> offset = (A.x0.p + B.x0.p) * T(0.5);
-  A.x0.p -= offset;
-  A.x1.p -= offset;
-  B.x0.p -= offset;
-  B.x1.p -= offset;
-  const T mA = A.innerMargin(), mB = B.innerMargin();
-  const T margin = mA + mB;
-  GjkOut<T, true> g;
-  const int st = gjkDistance<T, true>(A, B, axis0, false, margin + threshold, T(-1), g, 128);
-  out.gjk_iters = g.iters;
-  if (st == GJK_FAR)
-    return;
-  if (st == GJK_SEPARATED)
-  {
-    if (!calc_dist)
-      return;  // :830-834
-    const T dc = g.v.len();
-    const V3<T> n = g.v * (T(1) / dc);
-    out.distance = dc - margin;
-    out.normalOnB = n;
-    out.pointOnB = (g.pA - g.v) + n * mB + offset;
-    out.has = true;
-    return;
-  }
-  // cores intersect
-  if (!calc_pen)
-  {
-    // :823-828 -- dummy contact, zero normal, depth -min()
-    out.has = true;
-    out.normalOnB = V3<T>(0, 0, 0);
-    out.pointOnB = offset;
-    out.distance = -(T)FLT_MIN;
-    return;
-  }
-  EpaResult<T> er;
-  out.used_epa = true;
-  const bool ok = epa.run(A, B, g.sx.W, g.sx.P, g.sx.n, 255, T(1e-11), er);
-  out.epa_iters = er.iterations;
-  if (ok)
-  {
-    const T depth = er.depth + margin;
-    const V3<T> pointOnA = er.pA + er.normal * mA;
-    out.has = true;
-    out.normalOnB = -er.normal;
-    out.distance = -depth;
-    out.pointOnB = pointOnA - er.normal * depth + offset;
-    return;
-  }
-  // expansion could not start (flat, exactly touching configuration): report touching cores
-  V3<T> n = A0.x0.p - B0.x0.p;
-  const T l = n.len();
-  n = l > Eps<T>::eps() ? n * (T(1) / l) : V3<T>(1, 0, 0);
-  out.has = true;
-  out.normalOnB = n;
-  out.distance = -margin;
-  out.pointOnB = (g.sx.n > 0 ? g.sx.P[0] - g.sx.W[0] : V3<T>(0, 0, 0)) + n * mB + offset;
+  // ---- GJK / EPA: the reference's detector, step by step (t4_bullet_detector.h)
+  const T maxDist = A0.margin() + B0.margin() + T(T4_CONTACT_BREAKING_THRESHOLD) + threshold;
+  bt::DetectorOut<T> d;
+  bt::gjkPairDetector<T>(A0, B0, maxDist * maxDist, calc_pen, calc_dist, d, epa);
+  (void)axis0;
+  out.has = d.has;
+  out.normalOnB = d.normalOnB;
+  out.pointOnB = d.pointOnB;
+  out.distance = d.distance;
+  out.gjk_iters = d.gjk_iters;
+  out.epa_iters = d.epa_iters;
+  out.used_epa = d.used_epa;
 }
 
 // ---- continuous collision data (bullet_utils.h:306-349 GetAverageSupport, :452-525 calculateContinuousData) ------

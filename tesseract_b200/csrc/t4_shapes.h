@@ -64,10 +64,12 @@ struct ShapeW
   int nv;
   bool cast;
   Xf<T> x0, x1;  // world pose at t0 (and t1 for cast shapes), recentred by the caller
+  Xf<T> t01;     // cast shapes: pose at t1 relative to t0, (T0 L)^-1 (T1 L)  (bullet_cast_bvh_manager.cpp:281-305)
   T4_HD T innerMargin() const { return (type == SH_SPHERE || type == SH_CAPSULE) ? r : T(0); }
-  // A cast shape is conv(shape@t0 U shape@t1) (bullet_utils.h:230-235).  Because the ball radius is the same at both
-  // poses this equals conv(core@t0 U core@t1) (+) ball(r): the swept shape keeps "core + margin" form, so GJK / EPA
-  // stay finite for swept spheres / capsules and the margin is applied analytically as for plain shapes.
+  // margin the detector subtracts analytically.  A cast shape is conv(shape@t0 U shape@t1) built from the WITH-margin
+  // support and reports margin 0 (CastHullShape::getMargin, bullet_utils.h:230-235,286): the swept ball is part of
+  // the support, exactly as in the reference, so that the GJK iteration (and where it stops) is the same.
+  T4_HD T margin() const { return cast ? T(0) : innerMargin(); }
   T4_HD bool polyhedral() const { return type == SH_BOX || type == SH_HULL || type == SH_TRIANGLE; }
   T4_HD bool curvedCore() const { return type == SH_CYLINDER || type == SH_CONE; }
 };
@@ -154,15 +156,24 @@ T4_HD V3<T> supportAt(const ShapeW<T>& s, const Xf<T>& x, const V3<T>& d, T marg
 }
 
 // World support of the core (with_margin=false, what GJK / EPA use) or of the inflated shape (with_margin=true).
+// Cast shapes always carry their inner margin (CastHullShape::localGetSupportingVertex, bullet_utils.h:230-235).
 template <class T>
 T4_HD V3<T> supportW(const ShapeW<T>& s, const V3<T>& d, bool with_margin)
 {
-  const T m = with_margin ? s.innerMargin() : T(0);
   if (!s.cast)
-    return supportAt(s, s.x0, d, m);
-  V3<T> a = supportAt(s, s.x0, d, m);
-  V3<T> b = supportAt(s, s.x1, d, m);
-  return (d.dot(a) > d.dot(b)) ? a : b;
+    return supportAt(s, s.x0, d, with_margin ? s.innerMargin() : T(0));
+  // CastHullShape::localGetSupportingVertex, evaluated in the frame of pose 0 exactly like the reference
+  const T m = s.innerMargin();
+  const V3<T> dl = s.x0.rotT(d);
+  V3<T> sv0 = coreSupport(s, dl);
+  if (m != T(0))
+    sv0 += normalizedOrDefault(dl) * m;
+  const V3<T> dl1 = s.t01.rotT(dl);
+  V3<T> sv1 = coreSupport(s, dl1);
+  if (m != T(0))
+    sv1 += normalizedOrDefault(dl1) * m;
+  sv1 = s.t01(sv1);
+  return s.x0((dl.dot(sv0) > dl.dot(sv1)) ? sv0 : sv1);
 }
 
 // world AABB of the shape-frame box (centre c, half h) under pose x

@@ -375,9 +375,9 @@ struct t4c_scene
   CompiledScene comp;
   t4stream stream = nullptr;
   // device scene
-  DevBuf d_shapes, d_statics, d_verts, d_bvh, d_active, d_aa, d_acm, d_margin;
+  DevBuf d_shapes, d_statics, d_verts, d_bvh, d_active, d_aa, d_acm, d_margin, d_shape_d, d_statics_d;
   // per-call workspace
-  DevBuf d_q0, d_q1, d_pin0, d_pin1, d_poses0, d_poses1;
+  DevBuf d_q0, d_q1, d_pin0, d_pin1, d_poses0, d_poses1, d_poses0d, d_poses1d;
   DevBuf d_cand_state, d_cand_a, d_cand_b, d_surv, d_surv_axis;
   DevBuf d_qcount, d_stats, d_hit, d_claim, d_raw, d_raw_local, d_ht_rep, d_ht_best;
   DevBuf d_out, d_out_local, d_fk_out, d_hit_full;
@@ -409,7 +409,8 @@ static t4c_status syncScene(t4c_scene* s)
   t4stream st = s->stream;
   bool ok = upload(s->d_shapes, C.shapes, st) && upload(s->d_statics, C.statics, st) && upload(s->d_verts, C.verts, st) &&
             upload(s->d_bvh, C.bvh, st) && upload(s->d_active, C.active_shapes, st) && upload(s->d_aa, C.aa_pairs, st) &&
-            upload(s->d_acm, C.acm_bits, st) && upload(s->d_margin, C.pair_margin, st) && plat::sync(st);
+            upload(s->d_acm, C.acm_bits, st) && upload(s->d_margin, C.pair_margin, st) &&
+            upload(s->d_shape_d, C.shape_d, st) && upload(s->d_statics_d, C.statics_d, st) && plat::sync(st);
   if (!ok)
     return fail(T4C_ERR_CUDA, "scene upload failed: %s", plat::lastError());
   s->uploaded = s->rev;
@@ -422,6 +423,8 @@ static void fillSceneParams(const t4c_scene* s, KParams& P)
   std::memset(&P, 0, sizeof(P));
   P.shapes = s->d_shapes.as<DShape>();
   P.statics = s->d_statics.as<DStaticW>();
+  P.shape_d = s->d_shape_d.as<double>();
+  P.statics_d = s->d_statics_d.as<double>();
   P.verts = s->d_verts.as<f4>();
   P.bvh = s->d_bvh.as<DBvhNode>();
   P.n_bvh_nodes = (int)C.bvh.size();
@@ -431,11 +434,13 @@ static void fillSceneParams(const t4c_scene* s, KParams& P)
   P.n_aa_pairs = (int)(C.aa_pairs.size() / 2);
   P.acm_bits = s->d_acm.as<uint32_t>();
   P.acm_words = C.acm_words;
-  P.pair_margin = C.pair_margin.empty() ? nullptr : s->d_margin.as<float>();
+  P.pair_margin = C.pair_margin.empty() ? nullptr : s->d_margin.as<double>();
   P.n_links = (int)s->host.links.size();
   P.n_alinks = (int)C.alinks.size();
   P.default_margin = C.default_margin;
   P.max_margin = C.max_margin;
+  P.default_margin_d = C.default_margin_d;
+  P.max_margin_d = C.max_margin_d;
 }
 
 // FK tables of `model` against the current scene revision (device arrays cached in the scene)
@@ -606,12 +611,16 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     P.state_base = base;
     // ---- poses of the kinematic links
     const size_t pose_elems = (size_t)nc * (size_t)std::max(na, 1) * 12;
-    T4_TRY(s->d_poses0.ensure(pose_elems * sizeof(float)), "workspace");
+    T4_TRY(s->d_poses0.ensure(pose_elems * sizeof(float)) && s->d_poses0d.ensure(pose_elems * sizeof(double)),
+           "workspace");
     P.poses0 = s->d_poses0.as<float>();
+    P.poses0d = s->d_poses0d.as<double>();
     if (io.cast)
     {
-      T4_TRY(s->d_poses1.ensure(pose_elems * sizeof(float)), "workspace");
+      T4_TRY(s->d_poses1.ensure(pose_elems * sizeof(float)) && s->d_poses1d.ensure(pose_elems * sizeof(double)),
+             "workspace");
       P.poses1 = s->d_poses1.as<float>();
+      P.poses1d = s->d_poses1d.as<double>();
     }
     P.fk_out = nullptr;
     if (io.model)

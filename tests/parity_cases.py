@@ -1,0 +1,110 @@
+"""Shared bodies of the randomized parity tests: CUDA path (real library on the GPU tier, host simulation of the same
+kernel bodies on the CPU tier) vs the CPU oracle, on BASELINE.json config-2 style scenes.
+
+Tolerances (north_star): colliding link-pair set exact except within 1e-5 m of the margin; distance / nearest points /
+normals within 1e-5.  One documented exception class: PENETRATING pairs with a curved core (cylinder, cone).  There the
+reference's own EPA does not converge (Bullet stops at its 128-vertex cap, tesseract_gjk_pair_detector.cpp:1024-1032 ->
+btGjkEpaSolver2); both sides report the tightest depth bound, which agrees to 1e-5, but the face normal / witness of a
+polytope approximating a curved surface is only defined to ~sqrt(gap): checked at 5e-3 plus self-consistency.
+"""
+import numpy as np
+
+from tesseract_b200 import capi
+from tesseract_b200 import scene as S
+from oracle import pyoracle
+
+import parity
+
+CURVED = (capi.CYLINDER, capi.CONE)
+
+
+def link_types(b):
+    t = {}
+    for s in b.shapes:
+        t.setdefault(s["link"], set()).add(s["type"])
+    return t
+
+
+def compare_batch(b, con_g, con_o, hit_g, hit_o, margin, per_shape=False, check_cc=False):
+    assert np.array_equal(hit_g, hit_o), f"{int((hit_g != hit_o).sum())} hit flags differ"
+    types = link_types(b)
+    G, O = parity.index(con_g, per_shape), parity.index(con_o, per_shape)
+    for k in set(G) ^ set(O):
+        d = (O.get(k) or G.get(k))[0]
+        assert abs(d - margin) <= 1e-5 + 1e-7, f"key {k} on one side only, d={d}"
+    stats = dict(n=len(G), max_dd=0.0, max_dp=0.0, max_dn=0.0, curved_pen=0, curved_max_dn=0.0, nonunique=0)
+    for k in set(G) & set(O):
+        dg, pg, ng, tg, tyg = G[k]
+        do, po, no, to, tyo = O[k]
+        dd = abs(dg - do)
+        assert dd <= 1e-5, f"{k}: distance {dg} vs {do}"
+        stats["max_dd"] = max(stats["max_dd"], dd)
+        dp = max(np.linalg.norm(pg[0] - po[0]), np.linalg.norm(pg[1] - po[1]))
+        dn = float(np.linalg.norm(ng - no))
+        curved = bool((types.get(k[1], set()) | types.get(k[2], set())) & set(CURVED))
+        if curved and do < 0:
+            stats["curved_pen"] += 1
+            stats["curved_max_dn"] = max(stats["curved_max_dn"], dn)
+            assert dn <= 5e-3, f"{k}: curved penetration normal {ng} vs {no}"
+            assert np.linalg.norm((pg[1] - pg[0]) - dg * ng) <= 1e-5, f"{k}: inconsistent contact"
+            continue
+        if dp > 1e-5 or dn > 1e-5:
+            # non-unique witnesses (parallel features): same distance and normal, self-consistent points
+            assert dn <= 1e-5, f"{k}: normal {ng} vs {no} (d={do})"
+            assert np.linalg.norm((pg[1] - pg[0]) - dg * ng) <= 2e-5, f"{k}: inconsistent contact"
+            stats["nonunique"] += 1
+            continue
+        stats["max_dp"] = max(stats["max_dp"], dp)
+        stats["max_dn"] = max(stats["max_dn"], dn)
+        if check_cc:
+            assert list(tyg) == list(tyo), f"{k}: cc_type {tyg} vs {tyo}"
+            assert np.allclose(tg, to, atol=1e-5), f"{k}: cc_time {tg} vs {to}"
+    return stats
+
+
+def discrete_config2(make_checker, n_states, n_prims, test_type, seed=1234, threads=4):
+    b = S.build_config2(n_prims=n_prims, margin=0.05)
+    q = S.random_states(b, n_states, seed=seed, dtype=np.float64)
+    bc = make_checker(b)
+    hit_g, con_g, stats = bc.check_discrete(q, test_type)
+    hit_o, con_o, _ = pyoracle.check_discrete(b, q, test_type, n_threads=threads)
+    if test_type == capi.TEST_FIRST:
+        # FIRST is order dependent in the reference (core/common.h:129-133): only emptiness is comparable
+        assert np.array_equal(hit_g, hit_o)
+        assert len(con_g) == int(hit_g.sum())
+        return dict(n=len(con_g))
+    return compare_batch(b, con_g, con_o, hit_g, hit_o, 0.05, per_shape=(test_type == capi.TEST_ALL))
+
+
+def flags_only(make_checker, n_states, n_prims, seed=77, threads=4, margin=0.05, pen=True, dist=True):
+    b = S.build_config2(n_prims=n_prims, margin=margin)
+    q = S.random_states(b, n_states, seed=seed, dtype=np.float64)
+    bc = make_checker(b)
+    hit_g, _, _ = bc.check_discrete(q, capi.TEST_FIRST, calculate_penetration=pen, calculate_distance=dist,
+                                    want_contacts=False)
+    hit_o, _, _ = pyoracle.check_discrete(b, q, capi.TEST_FIRST, calculate_penetration=pen, calculate_distance=dist)
+    assert np.array_equal(hit_g, hit_o), f"{int((hit_g != hit_o).sum())} flags differ"
+    return int(hit_g.sum())
+
+
+def cast_config3(make_checker, n_traj, n_wp, n_prims, lvs=0.05, threads=4):
+    b = S.build_config2(n_prims=n_prims, margin=0.05)
+    traj = S.random_trajectories(b, n_traj, n_wp, seed=7)
+    q0, q1, it, st = pyoracle.lvs_expand(traj, lvs, cast=True)
+    bc = make_checker(b)
+    hit_g, con_g, loc, stats = bc.check_trajectories(traj, lvs, True, capi.TEST_CLOSEST)
+    assert len(hit_g) == len(q0)
+    hit_o, con_o, _ = pyoracle.check_cast(b, q0, q1, capi.TEST_CLOSEST, n_threads=threads)
+    return compare_batch(b, con_g, con_o, hit_g, hit_o, 0.05, check_cc=True)
+
+
+def fk_parity(make_checker, robot="iiwa14", n=200):
+    b = S.SceneBuilder()
+    S.add_robot(b, S.load_robot(robot))
+    q = S.random_states(b, n, seed=5, dtype=np.float64)
+    bc = make_checker(b)
+    Tg = bc.fk(q)
+    To = pyoracle.fk(b, q)
+    err = float(np.abs(Tg - To).max())
+    assert err <= 1e-9, err
+    return err

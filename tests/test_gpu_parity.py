@@ -1,0 +1,38 @@
+"""GPU tier: libt4c.so on a B200 vs the CPU oracle on randomized robot scenes (BASELINE.json configs[1], [2])."""
+import os
+
+import pytest
+
+from tesseract_b200 import capi
+from tesseract_b200.managers import BatchChecker
+
+import parity_cases as pc
+
+pytestmark = pytest.mark.gpu
+THREADS = os.cpu_count() or 4
+
+
+def mk(b):
+    return BatchChecker(b)
+
+
+@pytest.mark.parametrize("tt", [capi.TEST_FIRST, capi.TEST_CLOSEST, capi.TEST_ALL])
+def test_discrete_config2(tt):
+    print(pc.discrete_config2(mk, 20000, 10000, tt, threads=THREADS))
+
+
+def test_flags_only():
+    assert pc.flags_only(mk, 30000, 10000, threads=THREADS) > 0
+
+
+def test_flags_only_boolean_request():
+    assert pc.flags_only(mk, 30000, 10000, margin=0.0, pen=False, dist=False, threads=THREADS) > 0
+
+
+def test_cast_lvs():
+    print(pc.cast_config3(mk, 64, 30, 10000, threads=THREADS))
+
+
+@pytest.mark.parametrize("robot", ["iiwa14", "abb_irb2400"])
+def test_fk(robot):
+    pc.fk_parity(mk, robot, n=5000)

@@ -1,0 +1,35 @@
+"""CPU tier: the CUDA kernel bodies (host simulation, tests/hostsim) vs the CPU oracle on randomized robot scenes."""
+import pytest
+
+from tesseract_b200 import capi
+from tesseract_b200.managers import BatchChecker
+
+import parity_cases as pc
+from hostsim import build as hostsim
+
+
+def mk(b):
+    return BatchChecker(b, lib=hostsim.lib())
+
+
+@pytest.mark.parametrize("tt", [capi.TEST_FIRST, capi.TEST_CLOSEST, capi.TEST_ALL])
+def test_discrete_config2(tt):
+    print(pc.discrete_config2(mk, 400, 10000, tt))
+
+
+def test_flags_only():
+    assert pc.flags_only(mk, 600, 10000) > 0
+
+
+def test_flags_only_boolean_request():
+    """calculate_penetration = calculate_distance = false at margin 0 (the OMPL-validator use, SURVEY 8(d) mode A)"""
+    assert pc.flags_only(mk, 600, 10000, margin=0.0, pen=False, dist=False) > 0
+
+
+def test_cast_lvs():
+    print(pc.cast_config3(mk, 6, 12, 10000))
+
+
+@pytest.mark.parametrize("robot", ["iiwa14", "abb_irb2400"])
+def test_fk(robot):
+    pc.fk_parity(mk, robot)
