@@ -183,11 +183,7 @@ static int gridFor(int64_t n, int block, int ctas_per_sm)
   return (int)std::max<int64_t>(1, std::min<int64_t>(need, full));
 }
 
-__global__ void __launch_bounds__(128) fkKernel(KParams P, int64_t n)
-{
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    fkBody(i, P);
-}
+void t4LaunchFk(const KParams& P, int64_t n, int grid, cudaStream_t st);  // t4c_exact.cu (-fmad=false)
 __global__ void __launch_bounds__(256) convertPosesKernel(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -208,12 +204,7 @@ __global__ void __launch_bounds__(256) cullKernel(KParams P, int64_t n)
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     cullBody(i, P);
 }
-__global__ void __launch_bounds__(128) exactKernel(KParams P, int64_t n)
-{
-  Epa<double> epa;  // polytope pools live in thread-local memory
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    exactBody(i, P, epa);
-}
+void t4LaunchExact(const KParams& P, int64_t n, int grid, cudaStream_t st);  // t4c_exact.cu (-fmad=false)
 __global__ void __launch_bounds__(256) closestInsertKernel(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -309,12 +300,28 @@ static void profResolve()
     }                                                                                                                  \
   } while (0)
 static bool launchOk() { return plat::chk(cudaGetLastError()); }
-static void launchFk(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(fkKernel, PK_FK, 128, 8, P, n, st); }
+static void launchFk(const KParams& P, int64_t n, t4stream st)
+{
+  if (n <= 0)
+    return;
+  profBegin(PK_FK, st);
+  t4LaunchFk(P, n, gridFor(n, 128, 8), st);
+  profEnd(st);
+  ++g_launches;
+}
 static void launchConvert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(convertPosesKernel, PK_CONVERT, 256, 8, P, n, st); }
 static void launchBroadStatic(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadStaticKernel, PK_BROAD_STATIC, 256, 8, P, n, st); }
 static void launchBroadActive(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadActiveKernel, PK_BROAD_ACTIVE, 256, 8, P, n, st); }
 static void launchCull(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(cullKernel, PK_CULL, 256, 4, P, n, st); }
-static void launchExact(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(exactKernel, PK_EXACT, 128, 4, P, n, st); }
+static void launchExact(const KParams& P, int64_t n, t4stream st)
+{
+  if (n <= 0)
+    return;
+  profBegin(PK_EXACT, st);
+  t4LaunchExact(P, n, gridFor(n, 128, 4), st);
+  profEnd(st);
+  ++g_launches;
+}
 static void launchClosestInsert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestInsertKernel, PK_CLOSEST_INSERT, 256, 8, P, n, st); }
 static void launchClosestEmit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestEmitKernel, PK_CLOSEST_EMIT, 256, 8, P, n, st); }
 static void launchCountHit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(countHitKernel, PK_COUNT_HIT, 256, 8, P, n, st); }

@@ -220,6 +220,18 @@ class BatchChecker:
                                        False)
         return hit, out, stats
 
+    def check_link_poses(self, T0, T1=None, test_type=capi.TEST_CLOSEST, want_contacts=True, capacity=None):
+        """FK bypass: T0 (and T1 for cast) are (n, n_links, 3, 4) world poses of ALL links; the kinematic links'
+        rows are handed to t4c_check_link_poses_{discrete,cast}."""
+        act = self.b.active_link_indices()
+        p0 = np.ascontiguousarray(np.asarray(T0, dtype=np.float64)[:, act].reshape(len(T0), len(act), 12))
+        if T1 is None:
+            return self._run(self.lib.t4c_check_link_poses_discrete, (self.scene.h, _dp(p0), len(p0)), len(p0),
+                             test_type, True, True, want_contacts, capacity, False)
+        p1 = np.ascontiguousarray(np.asarray(T1, dtype=np.float64)[:, act].reshape(len(T1), len(act), 12))
+        return self._run(self.lib.t4c_check_link_poses_cast, (self.scene.h, _dp(p0), _dp(p1), len(p0)), len(p0),
+                         test_type, True, True, want_contacts, capacity, True)
+
     def check_cast(self, q0, q1, test_type=capi.TEST_CLOSEST, want_contacts=True, capacity=None):
         q0 = np.ascontiguousarray(q0, dtype=np.float64).reshape(-1, self.fk_desc.n_q)
         q1 = np.ascontiguousarray(q1, dtype=np.float64).reshape(-1, self.fk_desc.n_q)

@@ -17,6 +17,16 @@ def test_discrete_config2(tt):
     print(pc.discrete_config2(mk, 400, 10000, tt))
 
 
+@pytest.mark.parametrize("tt", [capi.TEST_FIRST, capi.TEST_CLOSEST])
+def test_discrete_config2_device_fk(tt):
+    """full path: FK on the device (see parity_cases.flip_statistics)"""
+    print(pc.discrete_config2(mk, 300, 10000, tt, device_fk=True))
+
+
+def test_cast_trajectories_device_fk():
+    print(pc.cast_config3(mk, 4, 10, 10000, device_fk=True))
+
+
 def test_flags_only():
     assert pc.flags_only(mk, 600, 10000) > 0
 
