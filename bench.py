@@ -245,8 +245,8 @@ def main():
         per_state = {"fk": 9 * 80 + 63 * 2.0,
                      "broad_static": (stats["bvh_nodes"] * 12 + stats["candidates"] * 30) / max(1, stats["states"]),
                      "cull_fp32": (stats["gjk_iterations"] * (6 * V + 33 + 36 + 100)) / max(1, stats["states"]),
-                     "exact_fp64": (stats["gjk_iterations"] * (6 * V + 33 + 36 + 100) + stats["epa_iterations"] * 400) /
-                     max(1, stats["states"])}
+                     "gjk_fp64": (stats["gjk_iterations"] * (6 * V + 33 + 36 + 100)) / max(1, stats["states"]),
+                     "epa_fp64": (stats["epa_iterations"] * (400 + 2 * (6 * V + 33))) / max(1, stats["states"])}
         flops = per_state.get(top, 0.0) * n
         ach = flops / (ms_top * 1e-3) / 1e12 if ms_top > 0 else 0.0
         peaks = {}

@@ -248,7 +248,7 @@ t4c_status t4c_check_cast_device(t4c_scene* scene, const t4c_fk_model* model, in
 /* number of this library's kernel launches since load (bench.py "gpu_launches") */
 uint64_t t4c_kernel_launch_count(void);
 /* Per-kernel device timing (CUDA events recorded on the launching stream around every launch of this library).
- * Kernel order: fk, convert_poses, broad_static, broad_active, cull_fp32, exact_fp64, closest_insert, closest_emit,
+ * Kernel order: fk, convert_poses, broad_static, broad_active, cull_fp32, gjk_fp64, epa_fp64, closest_insert, closest_emit,
  * count_hit.  Process-wide, not thread safe: meant for bench.py / profiling runs only. */
 void t4c_profile_enable(int32_t on);
 void t4c_profile_reset(void);

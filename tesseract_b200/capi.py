@@ -140,8 +140,8 @@ def load_library(path=None):
     return lib
 
 
-KERNEL_NAMES = ("fk", "convert_poses", "broad_static", "broad_active", "cull_fp32", "exact_fp64", "closest_insert",
-                "closest_emit", "count_hit")
+KERNEL_NAMES = ("fk", "convert_poses", "broad_static", "broad_active", "cull_fp32", "gjk_fp64", "epa_fp64",
+                "closest_insert", "closest_emit", "count_hit")
 
 
 def profile_get(lib):

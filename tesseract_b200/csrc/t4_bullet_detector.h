@@ -33,186 +33,223 @@ struct DetectorOut
   bool used_epa;
 };
 
-// A, B: shapes with WORLD poses.  maxDist2 = (marginA + marginB + contactBreakingThreshold + max margin)^2  (:435-440 of
-// tesseract_convex_convex_algorithm.cpp)
-template <class T, class EPA_T>
-T4_HD void gjkPairDetector(const ShapeW<T>& A0, const ShapeW<T>& B0, T maxDist2, bool calc_pen, bool calc_dist,
-                           DetectorOut<T>& out, EPA_T& epa)
+// running state of one query between the phases (also what the GJK kernel hands to the EPA kernel)
+template <class T>
+struct DetectorState
 {
-  out.has = false;
-  out.gjk_iters = 0;
-  out.epa_iters = 0;
-  out.used_epa = false;
-  T distance = 0;
-  V3<T> normalInB(0, 0, 0);
-  V3<T> pointOnA(0, 0, 0), pointOnB(0, 0, 0);
-  ShapeW<T> A = A0, B = B0;
+  T distance;
+  V3<T> normalInB, pointOnA, pointOnB, orgNormalInB;
+  int isValid, status;
+};
+
+enum
+{
+  DET_DONE = 0,    // finished: `out` is final (possibly out.has == false)
+  DET_PHASE4 = 1,  // phases 1-2 produced the answer: run phase 4
+  DET_PHASE3 = 2   // penetration / degenerate: run phase 3, then phase 4
+};
+
+// recentre both shapes about the midpoint of their origins (:694-698); returns the offset
+template <class T>
+T4_HD V3<T> recentre(ShapeW<T>& A, ShapeW<T>& B)
+{
   const V3<T> positionOffset = (A.x0.p + B.x0.p) * T(0.5);
   A.x0.p -= positionOffset;
   A.x1.p -= positionOffset;
   B.x0.p -= positionOffset;
   B.x1.p -= positionOffset;
+  return positionOffset;
+}
+
+// phases 1 and 2 on RECENTRED shapes
+template <class T>
+T4_HD int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& positionOffset, T maxDist2, bool calc_pen,
+                        bool calc_dist, DetectorState<T>& S, DetectorOut<T>& out)
+{
+  out.has = false;
+  out.gjk_iters = 0;
+  out.epa_iters = 0;
+  out.used_epa = false;
+  S.distance = 0;
+  S.normalInB = V3<T>(0, 0, 0);
+  S.pointOnA = V3<T>(0, 0, 0);
+  S.pointOnB = V3<T>(0, 0, 0);
+  S.orgNormalInB = V3<T>(0, 0, 0);
+  S.isValid = 0;
   const T marginA = A.margin(), marginB = B.margin();
   const T margin = marginA + marginB;
   V3<T> cachedSeparatingAxis(0, 1, 0);
-  bool isValid = false, checkSimplex = false;
+  bool checkSimplex = false;
   int degenerateSimplex = 0;
-  V3<T> orgNormalInB(0, 0, 0);
   int it1 = 0;
   const int status = booleanGjk(A, B, it1);
+  S.status = status;
   out.gjk_iters += it1;
 
   if (status == 0 && !calc_pen)
   {
     out.has = true;
-    out.normalOnB = normalInB;
+    out.normalOnB = S.normalInB;
     out.pointOnB = positionOffset;
     out.distance = -(T)FLT_MIN;  // reference: -numeric_limits<btScalar>::min(); only the sign is meaningful
-    return;
+    return DET_DONE;
   }
   if (status == -1 && !calc_dist)
-    return;
+    return DET_DONE;
+  if (status == 0)
+    return DET_PHASE3;  // phase 2 is skipped when the cores intersect: the penetration result always supersedes it
 
-  if (status != 0)
+  T squaredDistance = Eps<T>::large();
+  T delta = 0;
+  VoronoiSimplexSolver<T> solver;
+  solver.reset();
+  int curIter = 0;
+  for (;;)
   {
-    // ---- phase 2 (skipped when the cores intersect: the penetration result always supersedes it)
-    T squaredDistance = Eps<T>::large();
-    T delta = 0;
-    VoronoiSimplexSolver<T> solver;
-    solver.reset();
-    int curIter = 0;
-    for (;;)
+    const V3<T> pWorld = supportW(A, -cachedSeparatingAxis, false);
+    const V3<T> qWorld = supportW(B, cachedSeparatingAxis, false);
+    ++out.gjk_iters;
+    const V3<T> w = pWorld - qWorld;
+    delta = cachedSeparatingAxis.dot(w);
+    if ((delta > T(0)) && (delta * delta > squaredDistance * maxDist2))
     {
-      const V3<T> pWorld = supportW(A, -cachedSeparatingAxis, false);
-      const V3<T> qWorld = supportW(B, cachedSeparatingAxis, false);
-      ++out.gjk_iters;
-      const V3<T> w = pWorld - qWorld;
-      delta = cachedSeparatingAxis.dot(w);
-      if ((delta > T(0)) && (delta * delta > squaredDistance * maxDist2))
-      {
-        degenerateSimplex = 10;
-        checkSimplex = true;
-        break;
-      }
-      if (solver.inSimplex(w))
-      {
-        degenerateSimplex = 1;
-        checkSimplex = true;
-        break;
-      }
-      const T f0 = squaredDistance - delta;
-      const T f1 = squaredDistance * K<T>::relError2();
-      if (f0 <= f1)
-      {
-        degenerateSimplex = (f0 <= T(0)) ? 2 : 11;
-        checkSimplex = true;
-        break;
-      }
-      solver.addVertex(w, pWorld, qWorld);
-      V3<T> newAxis;
-      if (!solver.closest(newAxis))
-      {
-        degenerateSimplex = 3;
-        checkSimplex = true;
-        break;
-      }
-      if (newAxis.len2() < K<T>::relError2())
-      {
-        cachedSeparatingAxis = newAxis;
-        degenerateSimplex = 6;
-        checkSimplex = true;
-        break;
-      }
-      const T previousSquaredDistance = squaredDistance;
-      squaredDistance = newAxis.len2();
-      if (previousSquaredDistance - squaredDistance <= K<T>::simdEps() * previousSquaredDistance)
-      {
-        checkSimplex = true;
-        degenerateSimplex = 12;
-        break;
-      }
+      degenerateSimplex = 10;
+      checkSimplex = true;
+      break;
+    }
+    if (solver.inSimplex(w))
+    {
+      degenerateSimplex = 1;
+      checkSimplex = true;
+      break;
+    }
+    const T f0 = squaredDistance - delta;
+    const T f1 = squaredDistance * K<T>::relError2();
+    if (f0 <= f1)
+    {
+      degenerateSimplex = (f0 <= T(0)) ? 2 : 11;
+      checkSimplex = true;
+      break;
+    }
+    solver.addVertex(w, pWorld, qWorld);
+    V3<T> newAxis;
+    if (!solver.closest(newAxis))
+    {
+      degenerateSimplex = 3;
+      checkSimplex = true;
+      break;
+    }
+    if (newAxis.len2() < K<T>::relError2())
+    {
       cachedSeparatingAxis = newAxis;
-      if (curIter++ > 1000)
-        break;
-      if (solver.fullSimplex())
-      {
-        degenerateSimplex = 13;
-        break;
-      }
+      degenerateSimplex = 6;
+      checkSimplex = true;
+      break;
     }
-    if (checkSimplex)
+    const T previousSquaredDistance = squaredDistance;
+    squaredDistance = newAxis.len2();
+    if (previousSquaredDistance - squaredDistance <= K<T>::simdEps() * previousSquaredDistance)
     {
-      solver.compute_points(pointOnA, pointOnB);
-      normalInB = cachedSeparatingAxis;
-      const T lenSqr = cachedSeparatingAxis.len2();
-      if (lenSqr < K<T>::relError2())
-        degenerateSimplex = 5;
-      if (lenSqr > K<T>::simdEps() * K<T>::simdEps())
-      {
-        const T rlen = T(1) / t4sqrt(lenSqr);
-        normalInB = normalInB * rlen;
-        const T s = t4sqrt(squaredDistance);
-        pointOnA -= cachedSeparatingAxis * (marginA / s);
-        pointOnB += cachedSeparatingAxis * (marginB / s);
-        distance = (T(1) / rlen) - margin;
-        isValid = true;
-        orgNormalInB = normalInB;
-      }
+      checkSimplex = true;
+      degenerateSimplex = 12;
+      break;
+    }
+    cachedSeparatingAxis = newAxis;
+    if (curIter++ > 1000)
+      break;
+    if (solver.fullSimplex())
+    {
+      degenerateSimplex = 13;
+      break;
     }
   }
-
-  const bool catchDegeneratePenetrationCase = (degenerateSimplex != 0) && ((distance + margin) < K<T>::penTol());
-  if (!isValid || catchDegeneratePenetrationCase || status == 0)
+  if (checkSimplex)
   {
-    // ---- phase 3
-    out.used_epa = true;
-    GjkOut<T, true> g;
-    const V3<T> axis0 = A.x0.p - B.x0.p;
-    const int st = gjkDistance<T, true>(A, B, axis0, false, Eps<T>::large(), T(-1), g, 128);
-    out.gjk_iters += g.iters;
-    bool have2 = false;
-    T distance2 = 0;
-    V3<T> n2, pA2, pB2;
-    if (st == GJK_INTERSECT)
+    solver.compute_points(S.pointOnA, S.pointOnB);
+    S.normalInB = cachedSeparatingAxis;
+    const T lenSqr = cachedSeparatingAxis.len2();
+    if (lenSqr < K<T>::relError2())
+      degenerateSimplex = 5;
+    if (lenSqr > K<T>::simdEps() * K<T>::simdEps())
     {
-      EpaResult<T> er;
-      if (epa.run(A, B, g.sx.W, g.sx.P, g.sx.n, 255, T(1e-12), er))
-      {
-        out.epa_iters = er.iterations;
-        const T depth = er.depth + margin;
-        pA2 = er.pA + er.normal * marginA;
-        pB2 = pA2 - er.normal * depth;
-        n2 = -er.normal;
-        distance2 = -depth;
-        have2 = true;
-      }
-    }
-    else if (st == GJK_SEPARATED)
-    {
-      const T dc = g.v.len();
-      if (dc > T(0))
-      {
-        const V3<T> n = g.v * (T(1) / dc);
-        pA2 = g.pA - n * marginA;
-        pB2 = (g.pA - g.v) + n * marginB;
-        n2 = n;
-        distance2 = dc - margin;
-        have2 = true;
-      }
-    }
-    if (have2 && (!isValid || distance2 < distance))
-    {
-      distance = distance2;
-      pointOnA = pA2;
-      pointOnB = pB2;
-      normalInB = n2;
-      isValid = true;
+      const T rlen = T(1) / t4sqrt(lenSqr);
+      S.normalInB = S.normalInB * rlen;
+      const T s = t4sqrt(squaredDistance);
+      S.pointOnA -= cachedSeparatingAxis * (marginA / s);
+      S.pointOnB += cachedSeparatingAxis * (marginB / s);
+      S.distance = (T(1) / rlen) - margin;
+      S.isValid = 1;
+      S.orgNormalInB = S.normalInB;
     }
   }
+  const bool catchDegeneratePenetrationCase = (degenerateSimplex != 0) && ((S.distance + margin) < K<T>::penTol());
+  if (!S.isValid || catchDegeneratePenetrationCase)
+    return DET_PHASE3;
+  return DET_PHASE4;
+}
 
-  if (isValid && ((distance < T(0)) || (distance * distance < maxDist2)))
+// phase 3 on RECENTRED shapes
+template <class T, class EPA_T>
+T4_HD void detectPhase3(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T>& S, DetectorOut<T>& out, EPA_T& epa)
+{
+  const T marginA = A.margin(), marginB = B.margin();
+  const T margin = marginA + marginB;
+  out.used_epa = true;
+  GjkOut<T, true> g;
+  const V3<T> axis0 = A.x0.p - B.x0.p;
+  const int st = gjkDistance<T, true>(A, B, axis0, false, Eps<T>::large(), T(-1), g, 128);
+  out.gjk_iters += g.iters;
+  bool have2 = false;
+  T distance2 = 0;
+  V3<T> n2, pA2, pB2;
+  if (st == GJK_INTERSECT)
   {
-    // ---- phase 4
+    EpaResult<T> er;
+    if (epa.run(A, B, g.sx.W, g.sx.P, g.sx.n, 255, T(1e-12), er))
+    {
+      out.epa_iters = er.iterations;
+      const T depth = er.depth + margin;
+      pA2 = er.pA + er.normal * marginA;
+      pB2 = pA2 - er.normal * depth;
+      n2 = -er.normal;
+      distance2 = -depth;
+      have2 = true;
+    }
+  }
+  else if (st == GJK_SEPARATED)
+  {
+    const T dc = g.v.len();
+    if (dc > T(0))
+    {
+      const V3<T> n = g.v * (T(1) / dc);
+      pA2 = g.pA - n * marginA;
+      pB2 = (g.pA - g.v) + n * marginB;
+      n2 = n;
+      distance2 = dc - margin;
+      have2 = true;
+    }
+  }
+  if (have2 && (!S.isValid || distance2 < S.distance))
+  {
+    S.distance = distance2;
+    S.pointOnA = pA2;
+    S.pointOnB = pB2;
+    S.normalInB = n2;
+    S.isValid = 1;
+  }
+}
+
+// phase 4 on RECENTRED shapes: acceptance + normal-direction sanity
+template <class T>
+T4_HD void detectPhase4(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& positionOffset, T maxDist2,
+                        DetectorState<T>& S, DetectorOut<T>& out)
+{
+  const T margin = A.margin() + B.margin();
+  T distance = S.distance;
+  V3<T> normalInB = S.normalInB;
+  const V3<T> orgNormalInB = S.orgNormalInB;
+  if (S.isValid && ((distance < T(0)) || (distance * distance < maxDist2)))
+  {
     T d2 = 0;
     {
       const V3<T> pW = supportW(A, -orgNormalInB, false);
@@ -244,9 +281,26 @@ T4_HD void gjkPairDetector(const ShapeW<T>& A0, const ShapeW<T>& B0, T maxDist2,
     }
     out.has = true;
     out.normalOnB = normalInB;
-    out.pointOnB = pointOnB + positionOffset;
+    out.pointOnB = S.pointOnB + positionOffset;
     out.distance = distance;
   }
+}
+
+// A, B: shapes with WORLD poses.  maxDist2 = (marginA + marginB + contactBreakingThreshold + max margin)^2  (:435-440 of
+// tesseract_convex_convex_algorithm.cpp).  Single-call form (all phases in one thread).
+template <class T, class EPA_T>
+T4_HD void gjkPairDetector(const ShapeW<T>& A0, const ShapeW<T>& B0, T maxDist2, bool calc_pen, bool calc_dist,
+                           DetectorOut<T>& out, EPA_T& epa)
+{
+  ShapeW<T> A = A0, B = B0;
+  const V3<T> positionOffset = recentre(A, B);
+  DetectorState<T> S;
+  const int r = detectPhase12(A, B, positionOffset, maxDist2, calc_pen, calc_dist, S, out);
+  if (r == DET_DONE)
+    return;
+  if (r == DET_PHASE3)
+    detectPhase3(A, B, S, out, epa);
+  detectPhase4(A, B, positionOffset, maxDist2, S, out);
 }
 
 }  // namespace bt

@@ -40,7 +40,9 @@ enum
 enum
 {
   Q_CAND = 0,   // candidate pairs appended by the broadphase
-  Q_SURV,       // survivors of the FP32 cull
+  Q_SURV,       // survivors of the FP32 cull (FIRST with records: one certain contact per state)
+  Q_SURV2,      // FIRST with records: every other survivor, processed only for states still without a contact
+  Q_TASK,       // pairs handed from the GJK kernel to the EPA kernel
   Q_RAW,        // raw contacts (CLOSEST staging) or final contacts (ALL / FIRST)
   Q_OUT,        // final contacts emitted by the CLOSEST reduction
   Q_COUNT
@@ -54,6 +56,15 @@ struct alignas(16) DJoint
   double axis[3];  // normalised
   int32_t type, parent_joint, q_index, pad;
   double pre[12];  // world pose of the parent link when parent_joint < 0
+};
+
+// one pair handed from the GJK kernel (phases 1-2) to the EPA kernel (phases 3-4)
+struct alignas(8) EpaTask
+{
+  uint32_t cand;
+  int32_t is_valid;
+  double distance;
+  double normalInB[3], pointOnA[3], pointOnB[3], orgNormalInB[3];
 };
 
 struct KParams
@@ -105,9 +116,13 @@ struct KParams
   uint32_t* cand_a;
   uint32_t* cand_b;
   uint32_t cand_cap;
-  uint32_t* surv;
-  float* surv_axis;
+  uint32_t* surv;      // queue read by the GJK kernel in this launch
   uint32_t surv_cap;
+  uint32_t* surv_w;    // queues written by the cull kernel
+  uint32_t* surv2_w;
+  uint32_t* cull_claim;  // [n] FIRST with records: the state already has its certain pair
+  EpaTask* tasks;
+  uint32_t task_cap;
   uint32_t* qcount;       // [Q_COUNT]
   unsigned long long* stats;  // [ST_COUNT]
   uint8_t* hit;           // [n] (chunk-relative) or null

@@ -54,16 +54,18 @@ T4_KD bool analyticPair(int ta, int tb)
   return false;
 }
 
-T4_KD void pushSurvivor(const KParams& P, uint32_t c, const V3<float>& axis)
+T4_KD void pushSurvivor(const KParams& P, uint32_t c, bool reserve)
 {
+  if (reserve)
+  {
+    const uint32_t k = qAppend(&P.qcount[Q_SURV2]);
+    if (k < P.surv_cap)
+      P.surv2_w[k] = c;
+    return;
+  }
   const uint32_t k = qAppend(&P.qcount[Q_SURV]);
   if (k < P.surv_cap)
-  {
-    P.surv[k] = c;
-    P.surv_axis[3 * (size_t)k + 0] = axis.x;
-    P.surv_axis[3 * (size_t)k + 1] = axis.y;
-    P.surv_axis[3 * (size_t)k + 2] = axis.z;
-  }
+    P.surv_w[k] = c;
 }
 
 // The reference's GJK may stop early with an upper bound up to ~1e-4 m above the true distance (t4_bullet.h), so a pair
@@ -71,23 +73,27 @@ T4_KD void pushSurvivor(const KParams& P, uint32_t c, const V3<float>& axis)
 #define T4_ACCEPT_SLACK 5e-4f
 
 // item = candidate index.  FP32 GJK used ONLY to discard pairs that are provably farther apart than the contact
-// cut-off (and, for boolean FIRST queries without contact output, to accept pairs that are provably inside it).
-// Everything that is reported goes through exactBody.
+// cut-off, and to recognise pairs that are certainly inside it:
+//   - flags-only output: a certain contact sets the state's flag, nothing else is queued for it;
+//   - FIRST with records: ONE certain, non-penetrating pair per state goes to the primary queue (its record is the
+//     state's contact); every other survivor goes to the reserve queue, which is only looked at for states that are
+//     still without a contact afterwards (ContactTestData::done semantics, core/common.h:129-133).
+// Everything that is reported goes through the exact FP64 pass.
 T4_KD void cullBody(int64_t c, const KParams& P)
 {
   const int64_t s = P.cand_state[c];
-  // FIRST (or flags-only output): the state already has its contact (ContactTestData::done, core/common.h:129-133)
-  if ((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit && P.hit[s])
+  const bool first_rec = P.test_type == T4C_TEST_FIRST && !P.hit_only;
+  if (P.hit_only && P.hit[s])
     return;
   const int a = (int)P.cand_a[c], b = (int)P.cand_b[c];
   ShapeW<float> A, B;
   loadPairShapes<float>(P, s, a, b, A, B);
-  const V3<float> axis0 = A.x0.p - B.x0.p;
   if (!A.cast && !B.cast && analyticPair(A.type, B.type))
   {
-    pushSurvivor(P, (uint32_t)c, axis0);
+    pushSurvivor(P, (uint32_t)c, first_rec);
     return;
   }
+  const V3<float> axis0 = A.x0.p - B.x0.p;
   const V3<float> offset = (A.x0.p + B.x0.p) * 0.5f;
   A.x0.p -= offset;
   A.x1.p -= offset;
@@ -97,7 +103,7 @@ T4_KD void cullBody(int64_t c, const KParams& P)
   const float cutoff = msum + P.max_margin + T4_CULL_SLACK;
   float accept = cutoff;  // anything within the cut-off is decided by the exact pass
   bool bool_mode = false;
-  if (P.hit_only && P.calc_dist)
+  if ((P.hit_only || first_rec) && P.calc_dist)
   {
     const float pm = t4min((float)pairMargin(P, P.shapes[a].alink, P.shapes[b].link), P.max_margin);
     accept = msum + pm - T4_ACCEPT_SLACK;
@@ -124,7 +130,13 @@ T4_KD void cullBody(int64_t c, const KParams& P)
       return;
     }
   }
-  pushSurvivor(P, (uint32_t)c, g.v);
+  if (first_rec)
+  {
+    const bool certain = st == GJK_NEAR && bool_mode && g.v.len2() > 1e-8f;
+    pushSurvivor(P, (uint32_t)c, !(certain && casU32(&P.cull_claim[s], 0u, 1u) == 0u));
+    return;
+  }
+  pushSurvivor(P, (uint32_t)c, false);
 }
 
 T4_KD uint32_t orderedBits(float f)
@@ -144,40 +156,25 @@ T4_KD uint32_t orderedBits(float f)
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
-// item = survivor index: the exact (FP64) query and the reference's result bridging.
-template <class EPA_T>
-T4_KD void exactBody(int64_t k, const KParams& P, EPA_T& epa)
+// TesseractBroadphaseBridgedManifoldResult::addContactPoint -> add{Discrete,Cast}SingleResult -> processResult
+// (bullet_utils.h:388-441,527-611,757-802 ; core/common.h:114-167)
+T4_KD void emitContact(const KParams& P, int64_t s, int a, int b, const ShapeW<double>& A, const ShapeW<double>& B,
+                       const PairResult<double>& pr)
 {
-  const uint32_t c = P.surv[k];
-  const int64_t s = P.cand_state[c];
-  const bool first = P.test_type == T4C_TEST_FIRST;
-  if ((first || P.hit_only) && P.hit && P.hit[s])
-    return;
-  const int a = (int)P.cand_a[c], b = (int)P.cand_b[c];
-  ShapeW<double> A, B;
-  loadPairShapesD(P, s, a, b, A, B);
-  const V3<double> axis0((double)P.surv_axis[3 * (size_t)k], (double)P.surv_axis[3 * (size_t)k + 1],
-                         (double)P.surv_axis[3 * (size_t)k + 2]);
-  PairResult<double> pr;
-  exactPair<double>(A, B, P.max_margin_d, P.calc_pen != 0, P.calc_dist != 0, axis0, pr, epa);
-  statAdd(P.stats, ST_GJK_ITERS, (uint32_t)pr.gjk_iters);
-  statAdd(P.stats, ST_EPA_PAIRS, pr.used_epa ? 1u : 0u);
-  statAdd(P.stats, ST_EPA_ITERS, (uint32_t)pr.epa_iters);
   if (!pr.has)
     return;
-  // TesseractBroadphaseBridgedManifoldResult::addContactPoint / addSingleResult: reject beyond the max margin
-  if (pr.distance > P.max_margin_d)
+  if (pr.distance > P.max_margin_d)  // reject beyond the max margin (:717, :759)
     return;
   const DShape& Sa = P.shapes[a];
   const DShape& Sb = P.shapes[b];
-  // processResult (core/common.h:114-167): per-pair margin unless both calculate_* flags are off
+  // per-pair margin unless both calculate_* flags are off (core/common.h:122-124)
   if ((P.calc_dist || P.calc_pen) && pr.distance > pairMargin(P, Sa.alink, Sb.link))
     return;
   if (P.hit)
     P.hit[s] = 1;
   if (P.hit_only || !P.raw)
     return;
-  if (first && casU32(&P.first_claim[s], 0u, 1u) != 0u)
+  if (P.test_type == T4C_TEST_FIRST && casU32(&P.first_claim[s], 0u, 1u) != 0u)
     return;
   const uint32_t slot = qAppend(&P.qcount[Q_RAW]);
   if (slot >= P.raw_cap)
@@ -242,6 +239,90 @@ T4_KD void exactBody(int64_t k, const KParams& P, EPA_T& epa)
       for (int q = 0; q < 3; ++q)
         L[3 * j + q] = (float)local[j][q];
   }
+}
+
+// item = survivor index: phases 1-2 of the exact (FP64) query.  Pairs that need the penetration solver are handed to
+// the EPA kernel through the task queue, so that a warp never mixes the short GJK path with the long EPA path.
+T4_KD void gjkBody(int64_t k, const KParams& P)
+{
+  const uint32_t c = P.surv[k];
+  const int64_t s = P.cand_state[c];
+  if ((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit[s])
+    return;
+  const int a = (int)P.cand_a[c], b = (int)P.cand_b[c];
+  ShapeW<double> A, B;
+  loadPairShapesD(P, s, a, b, A, B);
+  PairResult<double> pr;
+  if (analyticPairQuery(A, B, P.max_margin_d, pr))
+  {
+    emitContact(P, s, a, b, A, B, pr);
+    return;
+  }
+  ShapeW<double> Ar = A, Br = B;
+  const V3<double> offset = bt::recentre(Ar, Br);
+  const double maxDist2 = detectorMaxDist2(A, B, P.max_margin_d);
+  bt::DetectorState<double> S;
+  bt::DetectorOut<double> d;
+  const int r = bt::detectPhase12(Ar, Br, offset, maxDist2, P.calc_pen != 0, P.calc_dist != 0, S, d);
+  statAdd(P.stats, ST_GJK_ITERS, (uint32_t)d.gjk_iters);
+  if (r == bt::DET_PHASE3)
+  {
+    const uint32_t t = qAppend(&P.qcount[Q_TASK]);
+    if (t < P.task_cap)
+    {
+      EpaTask& T = P.tasks[t];
+      T.cand = c;
+      T.is_valid = S.isValid;
+      T.distance = S.distance;
+      T.normalInB[0] = S.normalInB.x, T.normalInB[1] = S.normalInB.y, T.normalInB[2] = S.normalInB.z;
+      T.pointOnA[0] = S.pointOnA.x, T.pointOnA[1] = S.pointOnA.y, T.pointOnA[2] = S.pointOnA.z;
+      T.pointOnB[0] = S.pointOnB.x, T.pointOnB[1] = S.pointOnB.y, T.pointOnB[2] = S.pointOnB.z;
+      T.orgNormalInB[0] = S.orgNormalInB.x, T.orgNormalInB[1] = S.orgNormalInB.y, T.orgNormalInB[2] = S.orgNormalInB.z;
+    }
+    return;
+  }
+  if (r == bt::DET_PHASE4)
+    bt::detectPhase4(Ar, Br, offset, maxDist2, S, d);
+  copyOut(d, pr);
+  emitContact(P, s, a, b, A, B, pr);
+}
+
+// item = EPA task: phase 3 (penetration) and phase 4 of the exact query
+template <class EPA_T>
+T4_KD void epaBody(int64_t t, const KParams& P, EPA_T& epa)
+{
+  const EpaTask& T = P.tasks[t];
+  const uint32_t c = T.cand;
+  const int64_t s = P.cand_state[c];
+  if ((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit[s])
+    return;
+  const int a = (int)P.cand_a[c], b = (int)P.cand_b[c];
+  ShapeW<double> A, B;
+  loadPairShapesD(P, s, a, b, A, B);
+  ShapeW<double> Ar = A, Br = B;
+  const V3<double> offset = bt::recentre(Ar, Br);
+  const double maxDist2 = detectorMaxDist2(A, B, P.max_margin_d);
+  bt::DetectorState<double> S;
+  S.isValid = T.is_valid;
+  S.status = 0;
+  S.distance = T.distance;
+  S.normalInB = V3<double>(T.normalInB[0], T.normalInB[1], T.normalInB[2]);
+  S.pointOnA = V3<double>(T.pointOnA[0], T.pointOnA[1], T.pointOnA[2]);
+  S.pointOnB = V3<double>(T.pointOnB[0], T.pointOnB[1], T.pointOnB[2]);
+  S.orgNormalInB = V3<double>(T.orgNormalInB[0], T.orgNormalInB[1], T.orgNormalInB[2]);
+  bt::DetectorOut<double> d;
+  d.has = false;
+  d.gjk_iters = 0;
+  d.epa_iters = 0;
+  d.used_epa = false;
+  bt::detectPhase3(Ar, Br, S, d, epa);
+  bt::detectPhase4(Ar, Br, offset, maxDist2, S, d);
+  statAdd(P.stats, ST_GJK_ITERS, (uint32_t)d.gjk_iters);
+  statAdd(P.stats, ST_EPA_PAIRS, 1u);
+  statAdd(P.stats, ST_EPA_ITERS, (uint32_t)d.epa_iters);
+  PairResult<double> pr;
+  copyOut(d, pr);
+  emitContact(P, s, a, b, A, B, pr);
 }
 
 T4_KD unsigned long long mix64(unsigned long long x)

@@ -234,25 +234,25 @@ T4_HD bool sphereTriangleCollide(const V3<T>& c, T radius, const V3<T>* tv, V3<T
 }
 
 /*
- * One exact convex-convex query (the thing TesseractConvexConvexAlgorithm::processCollision does for one pair,
- * tesseract_convex_convex_algorithm.cpp:289-444,764).  A and B carry WORLD poses; threshold = max contact margin.
- * `axis0` warm-starts GJK (any vector; zero -> default).
+ * Analytic members of the dispatch matrix (sphere-sphere, sphere-triangle, capsule pairs).  Returns false when the
+ * pair belongs to the GJK / EPA detector instead.  A and B carry WORLD poses; threshold = max contact margin.
  */
-template <class T, class EPA_T>
-T4_HDN void exactPair(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold, bool calc_pen, bool calc_dist,
-                      V3<T> axis0, PairResult<T>& out, EPA_T& epa)
+template <class T>
+T4_HD bool analyticPairQuery(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold, PairResult<T>& out)
 {
   out.has = false;
   out.gjk_iters = 0;
   out.epa_iters = 0;
   out.used_epa = false;
   const bool plain = !A0.cast && !B0.cast;
-  if (plain && A0.type == SH_SPHERE && B0.type == SH_SPHERE)
+  if (!plain)
+    return false;
+  if (A0.type == SH_SPHERE && B0.type == SH_SPHERE)
   {
     const V3<T> diff = A0.x0.p - B0.x0.p;
     const T len = diff.len();
     if (len > A0.r + B0.r + threshold)
-      return;
+      return true;
     V3<T> n(1, 0, 0);
     if (len > Eps<T>::eps())
       n = diff * (T(1) / len);
@@ -260,9 +260,9 @@ T4_HDN void exactPair(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold, boo
     out.normalOnB = n;
     out.pointOnB = B0.x0.p + n * B0.r;
     out.distance = len - (A0.r + B0.r);
-    return;
+    return true;
   }
-  if (plain && A0.type == SH_SPHERE && B0.type == SH_TRIANGLE)
+  if (A0.type == SH_SPHERE && B0.type == SH_TRIANGLE)
   {
     V3<T> tv[3] = { vtx<T>(B0.verts, 0), vtx<T>(B0.verts, 1), vtx<T>(B0.verts, 2) };
     V3<T> point, normal;
@@ -275,9 +275,9 @@ T4_HDN void exactPair(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold, boo
       out.pointOnB = B0.x0(point);
       out.distance = depth;
     }
-    return;
+    return true;
   }
-  if (plain && A0.type == SH_TRIANGLE && B0.type == SH_SPHERE)
+  if (A0.type == SH_TRIANGLE && B0.type == SH_SPHERE)
   {
     V3<T> tv[3] = { vtx<T>(A0.verts, 0), vtx<T>(A0.verts, 1), vtx<T>(A0.verts, 2) };
     V3<T> point, normal;
@@ -291,10 +291,10 @@ T4_HDN void exactPair(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold, boo
       out.pointOnB = A0.x0(point) + nt * depth;
       out.distance = depth;
     }
-    return;
+    return true;
   }
-  if (plain && ((A0.type == SH_CAPSULE && (B0.type == SH_CAPSULE || B0.type == SH_SPHERE)) ||
-                (A0.type == SH_SPHERE && B0.type == SH_CAPSULE)))
+  if ((A0.type == SH_CAPSULE && (B0.type == SH_CAPSULE || B0.type == SH_SPHERE)) ||
+      (A0.type == SH_SPHERE && B0.type == SH_CAPSULE))
   {
     const T thr = T(T4_CONTACT_BREAKING_THRESHOLD) + threshold;
     V3<T> n, p;
@@ -309,14 +309,21 @@ T4_HDN void exactPair(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold, boo
       out.pointOnB = p;
       out.distance = dist;
     }
-    return;
+    return true;
   }
+  return false;
+}
 
-  // ---- GJK / EPA: the reference's detector, step by step (t4_bullet_detector.h)
+template <class T>
+T4_HD T detectorMaxDist2(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold)
+{
   const T maxDist = A0.margin() + B0.margin() + T(T4_CONTACT_BREAKING_THRESHOLD) + threshold;
-  bt::DetectorOut<T> d;
-  bt::gjkPairDetector<T>(A0, B0, maxDist * maxDist, calc_pen, calc_dist, d, epa);
-  (void)axis0;
+  return maxDist * maxDist;
+}
+
+template <class T>
+T4_HD void copyOut(const bt::DetectorOut<T>& d, PairResult<T>& out)
+{
   out.has = d.has;
   out.normalOnB = d.normalOnB;
   out.pointOnB = d.pointOnB;
@@ -324,6 +331,22 @@ T4_HDN void exactPair(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold, boo
   out.gjk_iters = d.gjk_iters;
   out.epa_iters = d.epa_iters;
   out.used_epa = d.used_epa;
+}
+
+/*
+ * One exact convex-convex query in a single call (the thing TesseractConvexConvexAlgorithm::processCollision does for
+ * one pair, tesseract_convex_convex_algorithm.cpp:289-444,764).  The kernels run the same phases split over two
+ * launches (t4_kernels2.h: gjkBody / epaBody).
+ */
+template <class T, class EPA_T>
+T4_HDN void exactPair(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold, bool calc_pen, bool calc_dist,
+                      PairResult<T>& out, EPA_T& epa)
+{
+  if (analyticPairQuery(A0, B0, threshold, out))
+    return;
+  bt::DetectorOut<T> d;
+  bt::gjkPairDetector<T>(A0, B0, detectorMaxDist2(A0, B0, threshold), calc_pen, calc_dist, d, epa);
+  copyOut(d, out);
 }
 
 // ---- continuous collision data (bullet_utils.h:306-349 GetAverageSupport, :452-525 calculateContinuousData) ------

@@ -204,7 +204,8 @@ __global__ void __launch_bounds__(256) cullKernel(KParams P, int64_t n)
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     cullBody(i, P);
 }
-void t4LaunchExact(const KParams& P, int64_t n, int grid, cudaStream_t st);  // t4c_exact.cu (-fmad=false)
+void t4LaunchGjk(const KParams& P, int64_t n, int grid, cudaStream_t st);  // t4c_exact.cu (-fmad=false)
+void t4LaunchEpa(const KParams& P, int64_t n, int grid, cudaStream_t st);
 __global__ void __launch_bounds__(256) closestInsertKernel(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -241,7 +242,8 @@ enum
   PK_BROAD_STATIC,
   PK_BROAD_ACTIVE,
   PK_CULL,
-  PK_EXACT,
+  PK_GJK,
+  PK_EPA,
   PK_CLOSEST_INSERT,
   PK_CLOSEST_EMIT,
   PK_COUNT_HIT,
@@ -313,12 +315,21 @@ static void launchConvert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(
 static void launchBroadStatic(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadStaticKernel, PK_BROAD_STATIC, 256, 8, P, n, st); }
 static void launchBroadActive(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadActiveKernel, PK_BROAD_ACTIVE, 256, 8, P, n, st); }
 static void launchCull(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(cullKernel, PK_CULL, 256, 4, P, n, st); }
-static void launchExact(const KParams& P, int64_t n, t4stream st)
+static void launchGjk(const KParams& P, int64_t n, t4stream st)
 {
   if (n <= 0)
     return;
-  profBegin(PK_EXACT, st);
-  t4LaunchExact(P, n, gridFor(n, 128, 4), st);
+  profBegin(PK_GJK, st);
+  t4LaunchGjk(P, n, gridFor(n, 128, 4), st);
+  profEnd(st);
+  ++g_launches;
+}
+static void launchEpa(const KParams& P, int64_t n, t4stream st)
+{
+  if (n <= 0)
+    return;
+  profBegin(PK_EPA, st);
+  t4LaunchEpa(P, n, gridFor(n, 128, 4), st);
   profEnd(st);
   ++g_launches;
 }
@@ -340,11 +351,12 @@ static void launchConvert(const KParams& P, int64_t n, t4stream) { T4_SERIAL(con
 static void launchBroadStatic(const KParams& P, int64_t n, t4stream) { T4_SERIAL(broadStaticBody, P, n); }
 static void launchBroadActive(const KParams& P, int64_t n, t4stream) { T4_SERIAL(broadActiveBody, P, n); }
 static void launchCull(const KParams& P, int64_t n, t4stream) { T4_SERIAL(cullBody, P, n); }
-static void launchExact(const KParams& P, int64_t n, t4stream)
+static void launchGjk(const KParams& P, int64_t n, t4stream) { T4_SERIAL(gjkBody, P, n); }
+static void launchEpa(const KParams& P, int64_t n, t4stream)
 {
   std::unique_ptr<Epa<double>> epa(new Epa<double>());
   for (int64_t i = 0; i < n; ++i)
-    exactBody(i, P, *epa);
+    epaBody(i, P, *epa);
   if (n > 0)
     ++g_launches;
 }
@@ -385,7 +397,7 @@ struct t4c_scene
   DevBuf d_shapes, d_statics, d_verts, d_bvh, d_active, d_aa, d_acm, d_margin, d_shape_d, d_statics_d;
   // per-call workspace
   DevBuf d_q0, d_q1, d_pin0, d_pin1, d_poses0, d_poses1, d_poses0d, d_poses1d;
-  DevBuf d_cand_state, d_cand_a, d_cand_b, d_surv, d_surv_axis;
+  DevBuf d_cand_state, d_cand_a, d_cand_b, d_surv, d_surv2, d_cull_claim, d_tasks;
   DevBuf d_qcount, d_stats, d_hit, d_claim, d_raw, d_raw_local, d_ht_rep, d_ht_best;
   DevBuf d_out, d_out_local, d_fk_out, d_hit_full;
   uint32_t cand_cap = 0;
@@ -684,16 +696,25 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     }
     const uint32_t ncand = qc[Q_CAND];
     // ---- FP32 cull
-    T4_TRY(s->d_surv.ensure(std::max<size_t>(ncand, 1) * sizeof(uint32_t)) &&
-               s->d_surv_axis.ensure(std::max<size_t>(ncand, 1) * 3 * sizeof(float)),
-           "survivor queue");
-    P.surv = s->d_surv.as<uint32_t>();
-    P.surv_axis = s->d_surv_axis.as<float>();
+    const bool first_rec = io.req.type == T4C_TEST_FIRST && io.contacts;
+    T4_TRY(s->d_surv.ensure(std::max<size_t>(ncand, 1) * sizeof(uint32_t)), "survivor queue");
+    P.surv_w = s->d_surv.as<uint32_t>();
+    P.surv2_w = nullptr;
+    P.cull_claim = nullptr;
+    if (first_rec)
+    {
+      T4_TRY(s->d_surv2.ensure(std::max<size_t>(ncand, 1) * sizeof(uint32_t)) &&
+                 s->d_cull_claim.ensure((size_t)nc * sizeof(uint32_t)) &&
+                 plat::zero(s->d_cull_claim.p, (size_t)nc * sizeof(uint32_t), st),
+             "survivor queue");
+      P.surv2_w = s->d_surv2.as<uint32_t>();
+      P.cull_claim = s->d_cull_claim.as<uint32_t>();
+    }
     P.surv_cap = ncand;
     launchCull(P, ncand, st);
     T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "cull");
-    const uint32_t nsurv = qc[Q_SURV];
-    // ---- FP64 exact pass
+    const uint32_t nsurv = qc[Q_SURV], nsurv2 = qc[Q_SURV2];
+    // ---- FP64 exact pass: GJK kernel (phases 1-2) -> task queue -> EPA kernel (phases 3-4)
     const bool closest = io.req.type == T4C_TEST_CLOSEST && io.contacts;
     const int64_t room = std::max<int64_t>(0, io.capacity - total);
     P.raw = nullptr;
@@ -719,8 +740,21 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
         P.raw_local = (io.cast && io.cc_local) ? io.cc_local + (size_t)std::min<int64_t>(total, io.capacity) * 6 : nullptr;
       }
     }
-    launchExact(P, nsurv, st);
-    T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase");
+    T4_TRY(s->d_tasks.ensure(std::max<size_t>(std::max(nsurv, nsurv2), 1) * sizeof(EpaTask)), "EPA task queue");
+    P.tasks = s->d_tasks.as<EpaTask>();
+    P.task_cap = std::max(nsurv, nsurv2);
+    for (int pass = 0; pass < 2; ++pass)
+    {
+      const uint32_t nq = pass == 0 ? nsurv : nsurv2;
+      if (nq == 0)
+        continue;
+      P.surv = pass == 0 ? s->d_surv.as<uint32_t>() : s->d_surv2.as<uint32_t>();
+      T4_TRY(plat::zero(P.qcount + Q_TASK, sizeof(uint32_t), st), "memset");
+      launchGjk(P, nq, st);
+      T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (GJK)");
+      launchEpa(P, std::min(qc[Q_TASK], P.task_cap), st);
+    }
+    T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (EPA)");
     const uint32_t nraw = qc[Q_RAW];
     if (closest)
     {

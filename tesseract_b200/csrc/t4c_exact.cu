@@ -11,11 +11,17 @@
 
 using namespace t4;
 
-__global__ void __launch_bounds__(128) exactKernel(KParams P, int64_t n)
+__global__ void __launch_bounds__(128) gjkKernel(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    gjkBody(i, P);
+}
+
+__global__ void __launch_bounds__(128) epaKernel(KParams P, int64_t n)
 {
   Epa<double> epa;  // polytope pools live in thread-local memory
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    exactBody(i, P, epa);
+    epaBody(i, P, epa);
 }
 
 // FK feeds the exact pass: same two-rounding arithmetic so that link poses equal the reference's FP64 FK
@@ -30,7 +36,12 @@ void t4LaunchFk(const KParams& P, int64_t n, int grid, cudaStream_t st)
   fkKernel<<<grid, 128, 0, st>>>(P, n);
 }
 
-void t4LaunchExact(const KParams& P, int64_t n, int grid, cudaStream_t st)
+void t4LaunchGjk(const KParams& P, int64_t n, int grid, cudaStream_t st)
 {
-  exactKernel<<<grid, 128, 0, st>>>(P, n);
+  gjkKernel<<<grid, 128, 0, st>>>(P, n);
+}
+
+void t4LaunchEpa(const KParams& P, int64_t n, int grid, cudaStream_t st)
+{
+  epaKernel<<<grid, 128, 0, st>>>(P, n);
 }
