@@ -253,6 +253,11 @@ uint64_t t4c_kernel_launch_count(void);
 void t4c_profile_enable(int32_t on);
 void t4c_profile_reset(void);
 int32_t t4c_profile_get(double* ms, uint64_t* launches, int32_t capacity); /* returns the number of kernels */
+/* Test hook, host only: hull support of `shape` for n directions (xyz triples) through the support table and by the
+ * plain scan; out[4*i..4*i+3] = vertex index {table FP64, scan FP64, table FP32, scan FP32}; mean_candidates =
+ * average table cell length (-1: the hull has no table). */
+t4c_status t4c_debug_hull_support(t4c_scene* scene, int32_t shape, const double* dirs, int64_t n, int32_t* out,
+                                  double* mean_candidates);
 /* measured-peak helper: runs an FP32 FMA loop on every SM, returns TFLOP/s (roofline denominator) */
 t4c_status t4c_measure_fp32_peak(int32_t device, double* tflops);
 

@@ -128,12 +128,13 @@ def load_library(path=None):
     lib.t4c_profile_get.argtypes = [DP, C.POINTER(C.c_uint64), I32]
     lib.t4c_profile_get.restype = I32
     lib.t4c_measure_fp32_peak.argtypes = [I32, DP]
+    lib.t4c_debug_hull_support.argtypes = [VP, I32, DP, I64, C.POINTER(I32), DP]
     for name in ("t4c_scene_create", "t4c_scene_clone", "t4c_scene_set_active", "t4c_scene_set_enabled",
                  "t4c_scene_set_acm", "t4c_scene_set_margins", "t4c_scene_set_link_pose", "t4c_scene_num_active",
                  "t4c_fk_model_create", "t4c_fk", "t4c_check_discrete", "t4c_check_link_poses_discrete",
                  "t4c_check_cast", "t4c_check_link_poses_cast", "t4c_check_trajectories_discrete",
                  "t4c_check_trajectories_cast", "t4c_check_discrete_device", "t4c_check_cast_device",
-                 "t4c_measure_fp32_peak", "t4c_lvs_count"):
+                 "t4c_measure_fp32_peak", "t4c_lvs_count", "t4c_debug_hull_support"):
         getattr(lib, name).restype = I32
     if path is None:
         _lib = lib

@@ -47,6 +47,8 @@ struct CompiledScene
   std::vector<double> shape_d;    // [shape][16]
   std::vector<double> statics_d;  // [shape][12]
   std::vector<f4> verts;
+  std::vector<uint32_t> sup_cells;  // hull support tables: per hull 6*R*R+1 CSR offsets into sup_cand
+  std::vector<uint16_t> sup_cand;
   std::vector<DBvhNode> bvh;
   std::vector<int32_t> active_shapes;
   std::vector<int32_t> aa_pairs;
@@ -193,6 +195,55 @@ inline bool isIdentity12(const double* p)
   return std::memcmp(p, I, sizeof(I)) == 0;
 }
 
+/*
+ * Support table of one hull (t4_shapes.h coreSupport, SH_HULL).  Directions are bucketed on a cube map: face = major
+ * axis and its sign, (u, v) = the other two components divided by |major|, T4_SUP_R x T4_SUP_R cells per face.  A cell
+ * lists, in ascending index order, every vertex w that can win the arg-max for SOME direction d of the cell.
+ * Necessary condition used (conservative): with u* the winner at the cell centre d_c, a winner w at d = d_c + delta
+ * satisfies d.(w - u*) >= 0, and d.(w - u*) <= d_c.(w - u*) + hu |(w-u*)_a| + hv |(w-u*)_b|.  Half widths are padded
+ * for the FP32 / FP64 rounding of the device's cell computation, the comparison by eps for the rounding of its dots.
+ * Vertices are the FP32-rounded pool values the device reads.
+ */
+inline void buildSupportTable(const f4* v, int nv, std::vector<uint32_t>& cells, std::vector<uint16_t>& cand)
+{
+  const int R = T4_SUP_R;
+  double vmax = 0;
+  for (int i = 0; i < nv; ++i)
+    vmax = std::max(vmax, std::max(std::fabs((double)v[i].x), std::max(std::fabs((double)v[i].y), std::fabs((double)v[i].z))));
+  const double eps = 1e-9 * vmax + 1e-300;
+  const double half = 1.0 / R + 1e-5;
+  std::vector<double> p((size_t)nv);
+  for (int face = 0; face < 6; ++face)
+  {
+    const int m = face >> 1, a = m == 0 ? 1 : 0, b = m == 2 ? 1 : 2;  // (u, v) axes as in coreSupport
+    const double sgn = (face & 1) ? -1.0 : 1.0;
+    for (int iu = 0; iu < R; ++iu)
+      for (int iv = 0; iv < R; ++iv)
+      {
+        double dc[3];
+        dc[m] = sgn;
+        dc[a] = (iu + 0.5) * (2.0 / R) - 1.0;
+        dc[b] = (iv + 0.5) * (2.0 / R) - 1.0;
+        int best = 0;
+        for (int i = 0; i < nv; ++i)
+        {
+          p[i] = dc[0] * (double)v[i].x + dc[1] * (double)v[i].y + dc[2] * (double)v[i].z;
+          if (p[i] > p[best])
+            best = i;
+        }
+        const double vb[3] = { (double)v[best].x, (double)v[best].y, (double)v[best].z };
+        cells.push_back((uint32_t)cand.size());
+        for (int i = 0; i < nv; ++i)
+        {
+          const double vi[3] = { (double)v[i].x, (double)v[i].y, (double)v[i].z };
+          if (p[i] - p[best] + half * (std::fabs(vi[a] - vb[a]) + std::fabs(vi[b] - vb[b])) >= -eps)
+            cand.push_back((uint16_t)i);
+        }
+      }
+  }
+  cells.push_back((uint32_t)cand.size());
+}
+
 // max number of flattened (active shape, active shape) pairs handled by the brute-force active-active kernel
 #define T4_MAX_AA_PAIRS (64ll << 20)
 
@@ -288,6 +339,27 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
     b.mx[0] = roundUp(mx.x + pad), b.mx[1] = roundUp(mx.y + pad), b.mx[2] = roundUp(mx.z + pad);
     sbox.push_back(b);
     sshape.push_back(i);
+  }
+  // ---- hull support tables (one per distinct vertex range, shared by every shape that uses it)
+  {
+    std::unordered_map<uint64_t, int32_t> table_of;
+    for (int i = 0; i < ns; ++i)
+    {
+      DShape& d = C.shapes[i];
+      d.sup_off = -1;
+      if (d.type != SH_HULL || d.vert_cnt < T4_SUP_MIN_VERTS || d.vert_cnt > 65535 || !H.links[d.link].enabled)
+        continue;
+      const uint64_t key = ((uint64_t)(uint32_t)d.vert_off << 32) | (uint32_t)d.vert_cnt;
+      auto it = table_of.find(key);
+      if (it == table_of.end())
+      {
+        if (C.sup_cand.size() > ((size_t)256 << 20))
+          continue;  // table budget exhausted: remaining hulls keep the plain scan
+        it = table_of.emplace(key, (int32_t)C.sup_cells.size()).first;
+        buildSupportTable(C.verts.data() + d.vert_off, d.vert_cnt, C.sup_cells, C.sup_cand);
+      }
+      d.sup_off = it->second;
+    }
   }
   // ---- LBVH over the static shapes
   const int nst = (int)sbox.size();

@@ -75,6 +75,8 @@ struct KParams
   const double* shape_d;    // [shape][16]: params[3], pad, lpose[12]  -- FP64 copies for the exact pass
   const double* statics_d;  // [shape][12]: world pose of static shapes, FP64
   const f4* verts;
+  const uint32_t* sup_cells;  // hull support tables (t4_shapes.h), CSR offsets into sup_cand
+  const uint16_t* sup_cand;
   const DBvhNode* bvh;
   int32_t n_bvh_nodes;
   const int32_t* active_shapes;

@@ -17,8 +17,8 @@ T4_KD void loadPairShapes(const KParams& P, int64_t s, int a, int b, ShapeW<T>& 
   Xf<T> a0, a1, b0, b1;
   shapePose<T>(P, Sa, a, s, a0, a1);
   shapePose<T>(P, Sb, b, s, b0, b1);
-  A = makeShapeW<T>(Sa, P.verts, a0, a1, P.cast && Sa.alink >= 0);
-  B = makeShapeW<T>(Sb, P.verts, b0, b1, P.cast && Sb.alink >= 0);
+  A = makeShapeW<T>(Sa, P.verts, P.sup_cells, P.sup_cand, a0, a1, P.cast && Sa.alink >= 0);
+  B = makeShapeW<T>(Sb, P.verts, P.sup_cells, P.sup_cand, b0, b1, P.cast && Sb.alink >= 0);
 }
 
 T4_KD void loadPairShapesD(const KParams& P, int64_t s, int a, int b, ShapeW<double>& A, ShapeW<double>& B)
@@ -28,8 +28,8 @@ T4_KD void loadPairShapesD(const KParams& P, int64_t s, int a, int b, ShapeW<dou
   Xf<double> a0, a1, b0, b1;
   shapePoseD(P, Sa, a, s, a0, a1);
   shapePoseD(P, Sb, b, s, b0, b1);
-  A = makeShapeW<double>(Sa, P.verts, a0, a1, P.cast && Sa.alink >= 0);
-  B = makeShapeW<double>(Sb, P.verts, b0, b1, P.cast && Sb.alink >= 0);
+  A = makeShapeW<double>(Sa, P.verts, P.sup_cells, P.sup_cand, a0, a1, P.cast && Sa.alink >= 0);
+  B = makeShapeW<double>(Sb, P.verts, P.sup_cells, P.sup_cand, b0, b1, P.cast && Sb.alink >= 0);
   // FP64 shape parameters (the FP32 record is only good for culling)
   const double* pa = P.shape_d + (size_t)a * 16;
   const double* pb = P.shape_d + (size_t)b * 16;

@@ -34,13 +34,16 @@ struct PairResult
 };
 
 template <class T>
-T4_HD ShapeW<T> makeShapeW(const DShape& s, const f4* verts, const Xf<T>& x0, const Xf<T>& x1, bool cast)
+T4_HD ShapeW<T> makeShapeW(const DShape& s, const f4* verts, const uint32_t* sup_cells, const uint16_t* sup_cand,
+                            const Xf<T>& x0, const Xf<T>& x1, bool cast)
 {
   ShapeW<T> w;
   w.type = s.type;
   w.r = 0, w.h = 0;
   w.nv = 0;
   w.verts = nullptr;
+  w.sup_cells = nullptr;
+  w.sup_cand = nullptr;
   switch (s.type)
   {
     case SH_SPHERE:
@@ -58,6 +61,11 @@ T4_HD ShapeW<T> makeShapeW(const DShape& s, const f4* verts, const Xf<T>& x0, co
     default:
       w.verts = verts + s.vert_off;
       w.nv = s.type == SH_TRIANGLE ? 3 : s.vert_cnt;
+      if (s.type == SH_HULL && s.sup_off >= 0 && sup_cells)
+      {
+        w.sup_cells = sup_cells + s.sup_off;
+        w.sup_cand = sup_cand;
+      }
       break;
   }
   w.cast = cast;

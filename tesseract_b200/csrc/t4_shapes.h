@@ -12,6 +12,11 @@
 
 #include "t4_math.h"
 
+// resolution of the hull support tables: 6 cube-map faces x T4_SUP_R x T4_SUP_R cells (even)
+#define T4_SUP_R 16
+// hulls with fewer vertices than this keep the plain scan
+#define T4_SUP_MIN_VERTS 24
+
 namespace t4
 {
 enum
@@ -31,7 +36,8 @@ struct alignas(16) DShape
   float lpose[12];  // pose in the link frame, 3x4 row-major
   float params[4];  // sphere: r | box: hx hy hz | cylinder: r, half length | cone: r, height | capsule: r, half length
   float bc[4];      // shape-frame bounding box centre xyz, [3] = bounding-sphere radius about that centre
-  float bh[4];      // shape-frame bounding box half extents (margins included), [3] unused
+  float bh[3];      // shape-frame bounding box half extents (margins included)
+  int32_t sup_off;  // hulls: first cell of the support table in KParams::sup_cells, or -1 (brute-force scan)
   int32_t type, link, vert_off, vert_cnt;
   int32_t shape_id, subshape_id, alink, identity_lpose;  // alink: active-link ordinal or -1 (static)
 };
@@ -62,6 +68,8 @@ struct ShapeW
   V3<T> he;
   const f4* verts;
   int nv;
+  const uint32_t* sup_cells;  // hull support table (T4_SUP_R^2 * 6 + 1 CSR offsets into sup_cand) or null
+  const uint16_t* sup_cand;
   bool cast;
   Xf<T> x0, x1;  // world pose at t0 (and t1 for cast shapes), recentred by the caller
   Xf<T> t01;     // cast shapes: pose at t1 relative to t0, (T0 L)^-1 (T1 L)  (bullet_cast_bvh_manager.cpp:281-305)
@@ -122,6 +130,43 @@ T4_HD V3<T> coreSupport(const ShapeW<T>& s, const V3<T>& d)
     {
       int best = 0;
       T mx = -Eps<T>::large();
+      if (s.sup_cells)
+      {
+        // cube-map cell of d -> the (index-ordered) vertices that can be the maximiser anywhere in that cell; the scan
+        // below evaluates the same dot products with the same strict '>' as the full scan: identical result.
+        const T ax = t4abs(d.x), ay = t4abs(d.y), az = t4abs(d.z);
+        const T m = t4max(ax, t4max(ay, az));
+        if (m > T(1e-30) && m < T(1e30))  // 1/m and the dots stay finite; anything else takes the plain scan
+        {
+          const T inv = T(1) / m;
+          int face;
+          T u, v;
+          if (ax >= ay && ax >= az)
+            face = d.x < T(0) ? 1 : 0, u = d.y * inv, v = d.z * inv;
+          else if (ay >= az)
+            face = d.y < T(0) ? 3 : 2, u = d.x * inv, v = d.z * inv;
+          else
+            face = d.z < T(0) ? 5 : 4, u = d.x * inv, v = d.y * inv;
+          int iu = (int)((u + T(1)) * T(T4_SUP_R / 2));
+          int iv = (int)((v + T(1)) * T(T4_SUP_R / 2));
+          iu = iu < 0 ? 0 : (iu > T4_SUP_R - 1 ? T4_SUP_R - 1 : iu);
+          iv = iv < 0 ? 0 : (iv > T4_SUP_R - 1 ? T4_SUP_R - 1 : iv);
+          const int cell = (face * T4_SUP_R + iu) * T4_SUP_R + iv;
+          const uint32_t beg = s.sup_cells[cell], end = s.sup_cells[cell + 1];
+          for (uint32_t k = beg; k < end; ++k)
+          {
+            const int i = (int)s.sup_cand[k];
+            f4 w = s.verts[i];
+            T dt = d.x * (T)w.x + d.y * (T)w.y + d.z * (T)w.z;
+            if (dt > mx)
+            {
+              mx = dt;
+              best = i;
+            }
+          }
+          return vtx<T>(s.verts, best);
+        }
+      }
       for (int i = 0; i < s.nv; ++i)
       {
         f4 v = s.verts[i];

@@ -394,7 +394,7 @@ struct t4c_scene
   CompiledScene comp;
   t4stream stream = nullptr;
   // device scene
-  DevBuf d_shapes, d_statics, d_verts, d_bvh, d_active, d_aa, d_acm, d_margin, d_shape_d, d_statics_d;
+  DevBuf d_shapes, d_statics, d_verts, d_sup_cells, d_sup_cand, d_bvh, d_active, d_aa, d_acm, d_margin, d_shape_d, d_statics_d;
   // per-call workspace
   DevBuf d_q0, d_q1, d_pin0, d_pin1, d_poses0, d_poses1, d_poses0d, d_poses1d;
   DevBuf d_cand_state, d_cand_a, d_cand_b, d_surv, d_surv2, d_cull_claim, d_tasks;
@@ -427,6 +427,7 @@ static t4c_status syncScene(t4c_scene* s)
   CompiledScene& C = s->comp;
   t4stream st = s->stream;
   bool ok = upload(s->d_shapes, C.shapes, st) && upload(s->d_statics, C.statics, st) && upload(s->d_verts, C.verts, st) &&
+            upload(s->d_sup_cells, C.sup_cells, st) && upload(s->d_sup_cand, C.sup_cand, st) &&
             upload(s->d_bvh, C.bvh, st) && upload(s->d_active, C.active_shapes, st) && upload(s->d_aa, C.aa_pairs, st) &&
             upload(s->d_acm, C.acm_bits, st) && upload(s->d_margin, C.pair_margin, st) &&
             upload(s->d_shape_d, C.shape_d, st) && upload(s->d_statics_d, C.statics_d, st) && plat::sync(st);
@@ -445,6 +446,8 @@ static void fillSceneParams(const t4c_scene* s, KParams& P)
   P.shape_d = s->d_shape_d.as<double>();
   P.statics_d = s->d_statics_d.as<double>();
   P.verts = s->d_verts.as<f4>();
+  P.sup_cells = C.sup_cells.empty() ? nullptr : s->d_sup_cells.as<uint32_t>();
+  P.sup_cand = s->d_sup_cand.as<uint16_t>();
   P.bvh = s->d_bvh.as<DBvhNode>();
   P.n_bvh_nodes = (int)C.bvh.size();
   P.active_shapes = s->d_active.as<int32_t>();
@@ -1296,6 +1299,54 @@ t4c_status t4c_check_cast_device(t4c_scene* s, const t4c_fk_model* m, int64_t n,
   d->n_contacts = io.n_contacts;
   d->stats = io.stats;
   return rc;
+}
+
+// Test hook (host only, no device work): evaluates the hull support mapping of shape `shape` for n directions twice,
+// through the support table and by the plain scan, in FP64 and FP32.  out[4*i..] = table64, scan64, table32, scan32.
+t4c_status t4c_debug_hull_support(t4c_scene* s, int32_t shape, const double* dirs, int64_t n, int32_t* out,
+                                  double* mean_candidates)
+{
+  if (!s || !dirs || !out || shape < 0 || shape >= (int)s->comp.shapes.size())
+    return fail(T4C_ERR_INVALID, "bad argument");
+  const CompiledScene& C = s->comp;
+  const DShape& D = C.shapes[shape];
+  if (D.type != SH_HULL)
+    return fail(T4C_ERR_INVALID, "shape %d is not a hull", shape);
+  Xf<double> I;
+  Xf<float> If;
+  ShapeW<double> t64 = makeShapeW<double>(D, C.verts.data(), C.sup_cells.data(), C.sup_cand.data(), I, I, false);
+  ShapeW<float> t32 = makeShapeW<float>(D, C.verts.data(), C.sup_cells.data(), C.sup_cand.data(), If, If, false);
+  ShapeW<double> b64 = t64;
+  ShapeW<float> b32 = t32;
+  b64.sup_cells = nullptr, b32.sup_cells = nullptr;
+  auto indexOf = [&](double x, double y, double z) {
+    for (int i = 0; i < D.vert_cnt; ++i)
+    {
+      const f4& v = C.verts[(size_t)D.vert_off + i];
+      if ((double)v.x == x && (double)v.y == y && (double)v.z == z)
+        return i;
+    }
+    return -1;
+  };
+  for (int64_t i = 0; i < n; ++i)
+  {
+    const V3<double> d(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]);
+    const V3<float> df((float)d.x, (float)d.y, (float)d.z);
+    const V3<double> a = coreSupport(t64, d), b = coreSupport(b64, d);
+    const V3<float> c = coreSupport(t32, df), e = coreSupport(b32, df);
+    out[4 * i + 0] = indexOf(a.x, a.y, a.z), out[4 * i + 1] = indexOf(b.x, b.y, b.z);
+    out[4 * i + 2] = indexOf(c.x, c.y, c.z), out[4 * i + 3] = indexOf(e.x, e.y, e.z);
+  }
+  if (mean_candidates)
+  {
+    *mean_candidates = -1;
+    if (D.sup_off >= 0)
+    {
+      const int cells = 6 * T4_SUP_R * T4_SUP_R;
+      *mean_candidates = double(C.sup_cells[D.sup_off + cells] - C.sup_cells[D.sup_off]) / cells;
+    }
+  }
+  return T4C_OK;
 }
 
 t4c_status t4c_measure_fp32_peak(int32_t device, double* tflops)
