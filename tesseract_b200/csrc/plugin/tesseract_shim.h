@@ -195,3 +195,342 @@ private:
   }
 };
 }  // namespace tesseract_common
+
+namespace tesseract_geometry
+{
+enum GeometryType
+{
+  SPHERE,
+  CYLINDER,
+  CAPSULE,
+  CONE,
+  BOX,
+  PLANE,
+  MESH,
+  CONVEX_MESH,
+  SDF_MESH,
+  OCTREE
+};
+
+class Geometry
+{
+public:
+  using Ptr = std::shared_ptr<Geometry>;
+  using ConstPtr = std::shared_ptr<const Geometry>;
+  explicit Geometry(GeometryType type) : type_(type) {}
+  virtual ~Geometry() = default;
+  Geometry(const Geometry&) = delete;
+  Geometry& operator=(const Geometry&) = delete;
+  GeometryType getType() const { return type_; }
+
+private:
+  GeometryType type_;
+};
+
+class Box : public Geometry
+{
+public:
+  Box(double x, double y, double z) : Geometry(BOX), x_(x), y_(y), z_(z) {}
+  double getX() const { return x_; }
+  double getY() const { return y_; }
+  double getZ() const { return z_; }
+
+private:
+  double x_, y_, z_;
+};
+class Sphere : public Geometry
+{
+public:
+  explicit Sphere(double r) : Geometry(SPHERE), r_(r) {}
+  double getRadius() const { return r_; }
+
+private:
+  double r_;
+};
+#define T4_SHIM_RL(NAME, TYPE)                                                                                         \
+  class NAME : public Geometry                                                                                         \
+  {                                                                                                                    \
+  public:                                                                                                              \
+    NAME(double r, double l) : Geometry(TYPE), r_(r), l_(l) {}                                                         \
+    double getRadius() const { return r_; }                                                                            \
+    double getLength() const { return l_; }                                                                            \
+                                                                                                                       \
+  private:                                                                                                             \
+    double r_, l_;                                                                                                     \
+  }
+T4_SHIM_RL(Cylinder, CYLINDER);
+T4_SHIM_RL(Cone, CONE);
+T4_SHIM_RL(Capsule, CAPSULE);
+#undef T4_SHIM_RL
+
+// mesh.h:148-166 / convex_mesh.h:146-164: triangles / faces are "n, i0, .., in-1" runs in one index vector
+class Mesh : public Geometry
+{
+public:
+  Mesh(std::shared_ptr<const tesseract_common::VectorVector3d> vertices, std::shared_ptr<const Eigen::VectorXi> triangles,
+       GeometryType type = MESH)
+    : Geometry(type), vertices_(std::move(vertices)), triangles_(std::move(triangles))
+  {
+    vertice_count_ = (int)vertices_->size();
+    triangle_count_ = 0;
+    for (size_t i = 0; i < triangles_->size(); i += (size_t)(*triangles_)[i] + 1)
+      ++triangle_count_;
+  }
+  const std::shared_ptr<const tesseract_common::VectorVector3d>& getVertices() const { return vertices_; }
+  const std::shared_ptr<const Eigen::VectorXi>& getTriangles() const { return triangles_; }
+  int getVerticeCount() const { return vertice_count_; }
+  int getTriangleCount() const { return triangle_count_; }
+
+private:
+  std::shared_ptr<const tesseract_common::VectorVector3d> vertices_;
+  std::shared_ptr<const Eigen::VectorXi> triangles_;
+  int vertice_count_, triangle_count_;
+};
+class ConvexMesh : public Geometry
+{
+public:
+  ConvexMesh(std::shared_ptr<const tesseract_common::VectorVector3d> vertices,
+             std::shared_ptr<const Eigen::VectorXi> faces = nullptr)
+    : Geometry(CONVEX_MESH), vertices_(std::move(vertices)), faces_(std::move(faces))
+  {
+  }
+  const std::shared_ptr<const tesseract_common::VectorVector3d>& getVertices() const { return vertices_; }
+  const std::shared_ptr<const Eigen::VectorXi>& getFaces() const { return faces_; }
+  int getVerticeCount() const { return (int)vertices_->size(); }
+
+private:
+  std::shared_ptr<const tesseract_common::VectorVector3d> vertices_;
+  std::shared_ptr<const Eigen::VectorXi> faces_;
+};
+
+// octree.h:47-120 wraps an octomap::OcTree; the stand-in carries the occupied max-depth leaves the reference
+// iterates (bullet_utils.cpp:164-172): centre xyz + edge length, in leaf-iterator order.
+class Octree : public Geometry
+{
+public:
+  enum SubType
+  {
+    BOX,
+    SPHERE_INSIDE,
+    SPHERE_OUTSIDE
+  };
+  struct Leaf
+  {
+    double x, y, z, size;
+  };
+  Octree(std::vector<Leaf> leaves, SubType sub_type) : Geometry(OCTREE), leaves_(std::move(leaves)), sub_type_(sub_type)
+  {
+  }
+  SubType getSubType() const { return sub_type_; }
+  const std::vector<Leaf>& getLeaves() const { return leaves_; }
+
+private:
+  std::vector<Leaf> leaves_;
+  SubType sub_type_;
+};
+}  // namespace tesseract_geometry
+
+namespace tesseract_collision
+{
+using CollisionShapesConst = std::vector<tesseract_geometry::Geometry::ConstPtr>;
+using CollisionShapeConstPtr = tesseract_geometry::Geometry::ConstPtr;
+using CollisionMarginData = tesseract_common::CollisionMarginData;
+using CollisionMarginOverrideType = tesseract_common::CollisionMarginOverrideType;
+using PairsCollisionMarginData = tesseract_common::PairsCollisionMarginData;
+using IsContactAllowedFn = std::function<bool(const std::string&, const std::string&)>;
+
+enum class ContinuousCollisionType
+{
+  CCType_None,
+  CCType_Time0,
+  CCType_Time1,
+  CCType_Between
+};
+enum class ContactTestType
+{
+  FIRST = 0,
+  CLOSEST = 1,
+  ALL = 2,
+  LIMITED = 3
+};
+
+// types.h:89-161
+struct ContactResult
+{
+  double distance;
+  std::array<int, 2> type_id;
+  std::array<std::string, 2> link_names;
+  std::array<int, 2> shape_id;
+  std::array<int, 2> subshape_id;
+  std::array<Eigen::Vector3d, 2> nearest_points;
+  std::array<Eigen::Vector3d, 2> nearest_points_local;
+  std::array<Eigen::Isometry3d, 2> transform;
+  Eigen::Vector3d normal;
+  std::array<double, 2> cc_time;
+  std::array<ContinuousCollisionType, 2> cc_type;
+  std::array<Eigen::Isometry3d, 2> cc_transform;
+  bool single_contact_point = false;
+  ContactResult() { clear(); }
+  void clear()
+  {
+    distance = std::numeric_limits<double>::max();
+    for (int i = 0; i < 2; ++i)
+    {
+      nearest_points[i].setZero();
+      nearest_points_local[i].setZero();
+      transform[i] = Eigen::Isometry3d::Identity();
+      cc_transform[i] = Eigen::Isometry3d::Identity();
+      link_names[i] = "";
+      shape_id[i] = -1;
+      subshape_id[i] = -1;
+      type_id[i] = 0;
+      cc_time[i] = -1;
+      cc_type[i] = ContinuousCollisionType::CCType_None;
+    }
+    normal.setZero();
+    single_contact_point = false;
+  }
+};
+using ContactResultVector = tesseract_common::AlignedVector<ContactResult>;
+using ContactResultMap = tesseract_common::AlignedMap<std::pair<std::string, std::string>, ContactResultVector>;
+using IsContactResultValidFn = std::function<bool(const ContactResult&)>;
+
+struct ContactRequest
+{
+  ContactTestType type = ContactTestType::ALL;
+  bool calculate_penetration = true;
+  bool calculate_distance = true;
+  long contact_limit = 0;
+  IsContactResultValidFn is_valid = nullptr;
+  ContactRequest(ContactTestType type = ContactTestType::ALL) : type(type) {}
+};
+
+// discrete_contact_manager.h:65-207
+class DiscreteContactManager
+{
+public:
+  using Ptr = std::shared_ptr<DiscreteContactManager>;
+  using ConstPtr = std::shared_ptr<const DiscreteContactManager>;
+  DiscreteContactManager() = default;
+  virtual ~DiscreteContactManager() = default;
+  DiscreteContactManager(const DiscreteContactManager&) = delete;
+  DiscreteContactManager& operator=(const DiscreteContactManager&) = delete;
+  virtual std::shared_ptr<DiscreteContactManager> clone() const = 0;
+  virtual bool addCollisionObject(const std::string& name, const int& mask_id, const CollisionShapesConst& shapes,
+                                  const tesseract_common::VectorIsometry3d& shape_poses, bool enabled = true) = 0;
+  virtual const CollisionShapesConst& getCollisionObjectGeometries(const std::string& name) const = 0;
+  virtual const tesseract_common::VectorIsometry3d&
+  getCollisionObjectGeometriesTransforms(const std::string& name) const = 0;
+  virtual bool hasCollisionObject(const std::string& name) const = 0;
+  virtual bool removeCollisionObject(const std::string& name) = 0;
+  virtual bool enableCollisionObject(const std::string& name) = 0;
+  virtual bool disableCollisionObject(const std::string& name) = 0;
+  virtual void setCollisionObjectsTransform(const std::string& name, const Eigen::Isometry3d& pose) = 0;
+  virtual void setCollisionObjectsTransform(const std::vector<std::string>& names,
+                                            const tesseract_common::VectorIsometry3d& poses) = 0;
+  virtual void setCollisionObjectsTransform(const tesseract_common::TransformMap& transforms) = 0;
+  virtual const std::vector<std::string>& getCollisionObjects() const = 0;
+  virtual void setActiveCollisionObjects(const std::vector<std::string>& names) = 0;
+  virtual const std::vector<std::string>& getActiveCollisionObjects() const = 0;
+  virtual void
+  setCollisionMarginData(CollisionMarginData collision_margin_data,
+                         CollisionMarginOverrideType override_type = CollisionMarginOverrideType::REPLACE) = 0;
+  virtual void setDefaultCollisionMarginData(double default_collision_margin) = 0;
+  virtual void setPairCollisionMarginData(const std::string& name1, const std::string& name2,
+                                          double collision_margin) = 0;
+  virtual const CollisionMarginData& getCollisionMarginData() const = 0;
+  virtual void setIsContactAllowedFn(IsContactAllowedFn fn) = 0;
+  virtual IsContactAllowedFn getIsContactAllowedFn() const = 0;
+  virtual void contactTest(ContactResultMap& collisions, const ContactRequest& request) = 0;
+};
+}  // namespace tesseract_collision
+
+namespace tesseract_collision
+{
+// continuous_contact_manager.h:65-256
+class ContinuousContactManager
+{
+public:
+  using Ptr = std::shared_ptr<ContinuousContactManager>;
+  using ConstPtr = std::shared_ptr<const ContinuousContactManager>;
+  ContinuousContactManager() = default;
+  virtual ~ContinuousContactManager() = default;
+  ContinuousContactManager(const ContinuousContactManager&) = delete;
+  ContinuousContactManager& operator=(const ContinuousContactManager&) = delete;
+  virtual std::shared_ptr<ContinuousContactManager> clone() const = 0;
+  virtual bool addCollisionObject(const std::string& name, const int& mask_id, const CollisionShapesConst& shapes,
+                                  const tesseract_common::VectorIsometry3d& shape_poses, bool enabled = true) = 0;
+  virtual const CollisionShapesConst& getCollisionObjectGeometries(const std::string& name) const = 0;
+  virtual const tesseract_common::VectorIsometry3d&
+  getCollisionObjectGeometriesTransforms(const std::string& name) const = 0;
+  virtual bool hasCollisionObject(const std::string& name) const = 0;
+  virtual bool removeCollisionObject(const std::string& name) = 0;
+  virtual bool enableCollisionObject(const std::string& name) = 0;
+  virtual bool disableCollisionObject(const std::string& name) = 0;
+  virtual void setCollisionObjectsTransform(const std::string& name, const Eigen::Isometry3d& pose) = 0;
+  virtual void setCollisionObjectsTransform(const std::vector<std::string>& names,
+                                            const tesseract_common::VectorIsometry3d& poses) = 0;
+  virtual void setCollisionObjectsTransform(const tesseract_common::TransformMap& transforms) = 0;
+  virtual void setCollisionObjectsTransform(const std::string& name, const Eigen::Isometry3d& pose1,
+                                            const Eigen::Isometry3d& pose2) = 0;
+  virtual void setCollisionObjectsTransform(const std::vector<std::string>& names,
+                                            const tesseract_common::VectorIsometry3d& pose1,
+                                            const tesseract_common::VectorIsometry3d& pose2) = 0;
+  virtual void setCollisionObjectsTransform(const tesseract_common::TransformMap& pose1,
+                                            const tesseract_common::TransformMap& pose2) = 0;
+  virtual const std::vector<std::string>& getCollisionObjects() const = 0;
+  virtual void setActiveCollisionObjects(const std::vector<std::string>& names) = 0;
+  virtual const std::vector<std::string>& getActiveCollisionObjects() const = 0;
+  virtual void
+  setCollisionMarginData(CollisionMarginData collision_margin_data,
+                         CollisionMarginOverrideType override_type = CollisionMarginOverrideType::REPLACE) = 0;
+  virtual void setDefaultCollisionMarginData(double default_collision_margin) = 0;
+  virtual void setPairCollisionMarginData(const std::string& name1, const std::string& name2,
+                                          double collision_margin) = 0;
+  virtual const CollisionMarginData& getCollisionMarginData() const = 0;
+  virtual void setIsContactAllowedFn(IsContactAllowedFn fn) = 0;
+  virtual IsContactAllowedFn getIsContactAllowedFn() const = 0;
+  virtual void contactTest(ContactResultMap& collisions, const ContactRequest& request) = 0;
+};
+}  // namespace tesseract_collision
+#endif  // !T4_USE_TESSERACT_HEADERS
+
+// ---------------------------------------------------------------------------------------------------------------
+// adapters: the only code that depends on which of the two header sets is in use
+// ---------------------------------------------------------------------------------------------------------------
+namespace tesseract_b200
+{
+inline void toPose12(const Eigen::Isometry3d& T, double* p)
+{
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 4; ++c)
+      p[4 * r + c] = T(r, c);
+}
+inline Eigen::Isometry3d fromPose12(const double* p)
+{
+  Eigen::Isometry3d T = Eigen::Isometry3d::Identity();
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 4; ++c)
+      T(r, c) = p[4 * r + c];
+  return T;
+}
+
+struct OctreeLeaf
+{
+  double x, y, z, size;
+};
+// occupied leaves at maximum depth, leaf-iterator order (bullet_utils.cpp:164-172)
+inline void octreeLeaves(const tesseract_geometry::Octree& g, std::vector<OctreeLeaf>& out)
+{
+#ifdef T4_USE_TESSERACT_HEADERS
+  const octomap::OcTree& octree = *(g.getOctree());
+  for (auto it = octree.begin(static_cast<unsigned char>(octree.getTreeDepth())), end = octree.end(); it != end; ++it)
+    if (octree.isNodeOccupied(*it))
+      out.push_back({ it.getX(), it.getY(), it.getZ(), it.getSize() });
+#else
+  for (const auto& l : g.getLeaves())
+    out.push_back({ l.x, l.y, l.z, l.size });
+#endif
+}
+}  // namespace tesseract_b200
+#endif  // T4_TESSERACT_SHIM_H_

@@ -272,7 +272,7 @@ struct VoronoiSimplexSolver
     return true;
   }
 
-  T4_HD bool updateClosestVectorAndPoints()
+  T4_HDN bool updateClosestVectorAndPoints()
   {
     if (needsUpdate)
     {

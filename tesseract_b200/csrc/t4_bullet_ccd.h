@@ -275,7 +275,7 @@ T4_HD int doSimplex4(CcdSimplex<T>& s, V3<T>& dir)
 }
 
 template <class T>
-T4_HD int doSimplex(CcdSimplex<T>& s, V3<T>& dir)
+T4_HDN int doSimplex(CcdSimplex<T>& s, V3<T>& dir)
 {
   if (s.size() == 2)
     return doSimplex2(s, dir);
@@ -286,7 +286,7 @@ T4_HD int doSimplex(CcdSimplex<T>& s, V3<T>& dir)
 
 // phase 1 driver: 0 = cores intersect, -1 = separated (tesseract_gjk_pair_detector.cpp:732-821)
 template <class T>
-T4_HD int booleanGjk(const ShapeW<T>& A, const ShapeW<T>& B, int& iters)
+T4_HDN int booleanGjk(const ShapeW<T>& A, const ShapeW<T>& B, int& iters)
 {
   int status = -2;
   CcdSimplex<T> simplex;

@@ -63,7 +63,7 @@ T4_HD V3<T> recentre(ShapeW<T>& A, ShapeW<T>& B)
 
 // phases 1 and 2 on RECENTRED shapes
 template <class T>
-T4_HD int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& positionOffset, T maxDist2, bool calc_pen,
+T4_HDN int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& positionOffset, T maxDist2, bool calc_pen,
                         bool calc_dist, DetectorState<T>& S, DetectorOut<T>& out)
 {
   out.has = false;
@@ -190,7 +190,7 @@ T4_HD int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& pos
 
 // phase 3 on RECENTRED shapes
 template <class T, class EPA_T>
-T4_HD void detectPhase3(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T>& S, DetectorOut<T>& out, EPA_T& epa)
+T4_HDN void detectPhase3(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T>& S, DetectorOut<T>& out, EPA_T& epa)
 {
   const T marginA = A.margin(), marginB = B.margin();
   const T margin = marginA + marginB;
@@ -241,7 +241,7 @@ T4_HD void detectPhase3(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T>
 
 // phase 4 on RECENTRED shapes: acceptance + normal-direction sanity
 template <class T>
-T4_HD void detectPhase4(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& positionOffset, T maxDist2,
+T4_HDN void detectPhase4(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& positionOffset, T maxDist2,
                         DetectorState<T>& S, DetectorOut<T>& out)
 {
   const T margin = A.margin() + B.margin();

@@ -52,14 +52,14 @@ struct Epa
   const ShapeW<T>* A;
   const ShapeW<T>* B;
 
-  T4_HD void support(const V3<T>& d, V3<T>& w, V3<T>& p) const
+  T4_HDN void support(const V3<T>& d, V3<T>& w, V3<T>& p) const
   {
     p = supportW(*A, d, false);
     w = p - supportW(*B, -d, false);
   }
   T4_HD static T det3(const V3<T>& a, const V3<T>& b, const V3<T>& c) { return a.dot(b.cross(c)); }
 
-  T4_HD bool pushSupport(const V3<T>& d)
+  T4_HDN bool pushSupport(const V3<T>& d)
   {
     if (nv >= MAXV)
       return false;
@@ -69,7 +69,7 @@ struct Epa
   }
   // btGjkEpaSolver2 GJK::EncloseOrigin: grow the simplex (W[0..nv)) to a non-degenerate tetrahedron
   T4_HD bool enclose4() const { return t4abs(det3(W[0] - W[3], W[1] - W[3], W[2] - W[3])) > T(0); }
-  T4_HD bool enclose3()
+  T4_HDN bool enclose3()
   {
     const V3<T> n = (W[1] - W[0]).cross(W[2] - W[0]);
     if (n.len2() > T(0))
@@ -85,7 +85,7 @@ struct Epa
     }
     return false;
   }
-  T4_HD bool enclose2()
+  T4_HDN bool enclose2()
   {
     const V3<T> d = W[1] - W[0];
     for (int i = 0; i < 3; ++i)
@@ -107,7 +107,7 @@ struct Epa
     }
     return false;
   }
-  T4_HD bool enclose1()
+  T4_HDN bool enclose1()
   {
     for (int i = 0; i < 3; ++i)
     {
@@ -156,7 +156,7 @@ struct Epa
   }
 
   // simplex: up to 4 points of A-B (and their A witnesses) around the origin, from the GJK that found the overlap
-  T4_HD bool run(const ShapeW<T>& a, const ShapeW<T>& b, const V3<T>* sw, const V3<T>* sp, int rank, int max_iter,
+  T4_HDN bool run(const ShapeW<T>& a, const ShapeW<T>& b, const V3<T>* sw, const V3<T>* sp, int rank, int max_iter,
                  T tol, EpaResult<T>& res)
   {
     A = &a;

@@ -226,7 +226,7 @@ struct Simplex
   }
   // closest point of the simplex to the origin; drops the vertices that do not support it.
   // returns 0: ok (v = closest), 1: origin enclosed (v = 0, simplex kept with 4 vertices), 2: degenerate
-  T4_HD int closest(V3<T>& v)
+  T4_HDN int closest(V3<T>& v)
   {
     SubSimplex<T> bc;
     bc.degenerate = false;

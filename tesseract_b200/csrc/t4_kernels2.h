@@ -158,7 +158,7 @@ T4_KD uint32_t orderedBits(float f)
 
 // TesseractBroadphaseBridgedManifoldResult::addContactPoint -> add{Discrete,Cast}SingleResult -> processResult
 // (bullet_utils.h:388-441,527-611,757-802 ; core/common.h:114-167)
-T4_KD void emitContact(const KParams& P, int64_t s, int a, int b, const ShapeW<double>& A, const ShapeW<double>& B,
+T4_KDN void emitContact(const KParams& P, int64_t s, int a, int b, const ShapeW<double>& A, const ShapeW<double>& B,
                        const PairResult<double>& pr)
 {
   if (!pr.has)

@@ -18,11 +18,13 @@
 #define T4_HD __host__ __device__ __forceinline__
 #define T4_HDN __host__ __device__ __noinline__
 #define T4_KD __device__ __forceinline__ /* kernel bodies: may use device-only primitives */
+#define T4_KDN static __device__ __noinline__
 #define T4_DEVICE_BUILD 1
 #else
 #define T4_HD inline
 #define T4_HDN
 #define T4_KD inline
+#define T4_KDN inline
 #endif
 
 namespace t4

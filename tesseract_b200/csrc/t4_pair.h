@@ -246,7 +246,7 @@ T4_HD bool sphereTriangleCollide(const V3<T>& c, T radius, const V3<T>* tv, V3<T
  * pair belongs to the GJK / EPA detector instead.  A and B carry WORLD poses; threshold = max contact margin.
  */
 template <class T>
-T4_HD bool analyticPairQuery(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold, PairResult<T>& out)
+T4_HDN bool analyticPairQuery(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold, PairResult<T>& out)
 {
   out.has = false;
   out.gjk_iters = 0;
@@ -359,7 +359,7 @@ T4_HDN void exactPair(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold, boo
 
 // ---- continuous collision data (bullet_utils.h:306-349 GetAverageSupport, :452-525 calculateContinuousData) ------
 template <class T>
-T4_HD void averageSupport(const ShapeW<T>& s, const V3<T>& n, T& outsupport, V3<T>& outpt)
+T4_HDN void averageSupport(const ShapeW<T>& s, const V3<T>& n, T& outsupport, V3<T>& outpt)
 {
   if (s.polyhedral())
   {
@@ -406,7 +406,7 @@ T4_HD void averageSupport(const ShapeW<T>& s, const V3<T>& n, T& outsupport, V3<
 
 // s: the UN-swept shape with x0 / x1 = its world pose at t0 / t1; link0_inv: inverse of the link pose at t0
 template <class T>
-T4_HD void continuousData(const ShapeW<T>& s, const Xf<T>& link0, const V3<T>& pt_world, const V3<T>& normal_world,
+T4_HDN void continuousData(const ShapeW<T>& s, const Xf<T>& link0, const V3<T>& pt_world, const V3<T>& normal_world,
                           T& cc_time, int& cc_type, V3<T>& point_local)
 {
   const V3<T> nl0 = s.x0.rotT(normal_world), nl1 = s.x1.rotT(normal_world);

@@ -7,21 +7,47 @@
  */
 #include <cuda_runtime.h>
 
+#include <cstdlib>
+
 #include "t4_kernels2.h"
 
 using namespace t4;
 
-__global__ void __launch_bounds__(128) gjkKernel(KParams P, int64_t n)
+__global__ void __launch_bounds__(128, 2) gjkKernel(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    gjkBody(i, P);
+}
+// same body under a 128-register budget (twice the resident warps): the default (measured faster on B200, r1d);
+// T4C_EXACT_REGS=255 selects the unconstrained build
+__global__ void __launch_bounds__(128, 4) gjkKernelR128(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     gjkBody(i, P);
 }
 
-__global__ void __launch_bounds__(128) epaKernel(KParams P, int64_t n)
+__global__ void __launch_bounds__(128, 2) epaKernel(KParams P, int64_t n)
 {
   Epa<double> epa;  // polytope pools live in thread-local memory
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     epaBody(i, P, epa);
+}
+__global__ void __launch_bounds__(128, 4) epaKernelR128(KParams P, int64_t n)
+{
+  Epa<double> epa;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    epaBody(i, P, epa);
+}
+
+static int exactRegs()
+{
+  static int v = 0;
+  if (!v)
+  {
+    const char* e = std::getenv("T4C_EXACT_REGS");
+    v = (e && std::atoi(e) == 255) ? 255 : 128;
+  }
+  return v;
 }
 
 // FK feeds the exact pass: same two-rounding arithmetic so that link poses equal the reference's FP64 FK
@@ -38,10 +64,16 @@ void t4LaunchFk(const KParams& P, int64_t n, int grid, cudaStream_t st)
 
 void t4LaunchGjk(const KParams& P, int64_t n, int grid, cudaStream_t st)
 {
-  gjkKernel<<<grid, 128, 0, st>>>(P, n);
+  if (exactRegs() == 128)
+    gjkKernelR128<<<grid, 128, 0, st>>>(P, n);
+  else
+    gjkKernel<<<grid, 128, 0, st>>>(P, n);
 }
 
 void t4LaunchEpa(const KParams& P, int64_t n, int grid, cudaStream_t st)
 {
-  epaKernel<<<grid, 128, 0, st>>>(P, n);
+  if (exactRegs() == 128)
+    epaKernelR128<<<grid, 128, 0, st>>>(P, n);
+  else
+    epaKernel<<<grid, 128, 0, st>>>(P, n);
 }
