@@ -41,7 +41,8 @@ enum
 {
   Q_CAND = 0,   // candidate pairs appended by the broadphase
   Q_SURV,       // survivors of the FP32 cull (FIRST with records: one certain contact per state)
-  Q_SURV2,      // FIRST with records: every other survivor, processed only for states still without a contact
+  Q_SURV2,      // FIRST with records: one certainly PENETRATING pair per state (looked at only if still no contact)
+  Q_SURV3,      // FIRST with records: every other survivor (looked at only if still no contact after the first two)
   Q_TASK,       // pairs handed from the GJK kernel to the EPA kernel
   Q_RAW,        // raw contacts (CLOSEST staging) or final contacts (ALL / FIRST)
   Q_OUT,        // final contacts emitted by the CLOSEST reduction
@@ -122,7 +123,8 @@ struct KParams
   uint32_t surv_cap;
   uint32_t* surv_w;    // queues written by the cull kernel
   uint32_t* surv2_w;
-  uint32_t* cull_claim;  // [n] FIRST with records: the state already has its certain pair
+  uint32_t* surv3_w;
+  uint32_t* cull_claim;  // [n] FIRST with records: bit 0 = has its certain separated pair, bit 1 = its certain penetrating pair
   EpaTask* tasks;
   uint32_t task_cap;
   uint32_t* qcount;       // [Q_COUNT]
@@ -144,9 +146,12 @@ struct KParams
 // device / host-simulator primitives
 // ---------------------------------------------------------------------------------------------------------------
 #ifdef T4_DEVICE_BUILD
+// warp-aggregated append: lanes that target the SAME counter are grouped (the tiered survivor queues make lanes of
+// one converged warp append to different queues), one atomicAdd per group
 __device__ __forceinline__ uint32_t qAppend(uint32_t* ctr)
 {
-  const unsigned m = __activemask();
+  const unsigned active = __activemask();
+  const unsigned m = __match_any_sync(active, (unsigned long long)ctr);
   const int lane = threadIdx.x & 31;
   const int leader = __ffs(m) - 1;
   uint32_t base = 0;
@@ -163,11 +168,18 @@ __device__ __forceinline__ void statAdd(unsigned long long* stats, int k, uint32
     atomicAdd(&stats[k], (unsigned long long)s);
 }
 __device__ __forceinline__ uint32_t casU32(uint32_t* p, uint32_t cmp, uint32_t val) { return atomicCAS(p, cmp, val); }
+__device__ __forceinline__ uint32_t orU32(uint32_t* p, uint32_t val) { return atomicOr(p, val); }
 __device__ __forceinline__ int32_t casI32(int32_t* p, int32_t cmp, int32_t val) { return atomicCAS(p, cmp, val); }
 __device__ __forceinline__ void minU64(unsigned long long* p, unsigned long long v) { atomicMin(p, v); }
 #else
 inline uint32_t qAppend(uint32_t* ctr) { return (*ctr)++; }
 inline void statAdd(unsigned long long* stats, int k, uint32_t v) { stats[k] += v; }
+inline uint32_t orU32(uint32_t* p, uint32_t val)
+{
+  uint32_t o = *p;
+  *p = o | val;
+  return o;
+}
 inline uint32_t casU32(uint32_t* p, uint32_t cmp, uint32_t val)
 {
   uint32_t o = *p;

@@ -54,18 +54,12 @@ T4_KD bool analyticPair(int ta, int tb)
   return false;
 }
 
-T4_KD void pushSurvivor(const KParams& P, uint32_t c, bool reserve)
+T4_KD void pushSurvivor(const KParams& P, uint32_t c, int tier)
 {
-  if (reserve)
-  {
-    const uint32_t k = qAppend(&P.qcount[Q_SURV2]);
-    if (k < P.surv_cap)
-      P.surv2_w[k] = c;
-    return;
-  }
-  const uint32_t k = qAppend(&P.qcount[Q_SURV]);
+  uint32_t* q = tier == 0 ? P.surv_w : (tier == 1 ? P.surv2_w : P.surv3_w);
+  const uint32_t k = qAppend(&P.qcount[tier == 0 ? Q_SURV : (tier == 1 ? Q_SURV2 : Q_SURV3)]);
   if (k < P.surv_cap)
-    P.surv_w[k] = c;
+    q[k] = c;
 }
 
 // The reference's GJK may stop early with an upper bound up to ~1e-4 m above the true distance (t4_bullet.h), so a pair
@@ -76,8 +70,9 @@ T4_KD void pushSurvivor(const KParams& P, uint32_t c, bool reserve)
 // cut-off, and to recognise pairs that are certainly inside it:
 //   - flags-only output: a certain contact sets the state's flag, nothing else is queued for it;
 //   - FIRST with records: ONE certain, non-penetrating pair per state goes to the primary queue (its record is the
-//     state's contact); every other survivor goes to the reserve queue, which is only looked at for states that are
-//     still without a contact afterwards (ContactTestData::done semantics, core/common.h:129-133).
+//     state's contact), ONE certainly penetrating pair per state to the second queue, every other survivor to the
+//     third; the later queues are only looked at for states that are still without a contact afterwards
+//     (ContactTestData::done semantics, core/common.h:129-133).
 // Everything that is reported goes through the exact FP64 pass.
 T4_KD void cullBody(int64_t c, const KParams& P)
 {
@@ -90,7 +85,7 @@ T4_KD void cullBody(int64_t c, const KParams& P)
   loadPairShapes<float>(P, s, a, b, A, B);
   if (!A.cast && !B.cast && analyticPair(A.type, B.type))
   {
-    pushSurvivor(P, (uint32_t)c, first_rec);
+    pushSurvivor(P, (uint32_t)c, first_rec ? 2 : 0);
     return;
   }
   const V3<float> axis0 = A.x0.p - B.x0.p;
@@ -132,11 +127,19 @@ T4_KD void cullBody(int64_t c, const KParams& P)
   }
   if (first_rec)
   {
+    // tier 0: one certainly-in-contact, separated pair per state (GJK only); tier 1: one certainly penetrating pair
+    // per state (needs EPA; only looked at when tier 0 left the state without a contact); tier 2: the rest.
     const bool certain = st == GJK_NEAR && bool_mode && g.v.len2() > 1e-8f;
-    pushSurvivor(P, (uint32_t)c, !(certain && casU32(&P.cull_claim[s], 0u, 1u) == 0u));
+    const bool deep = st == GJK_INTERSECT && g.v.len2() == 0.f && P.calc_pen;
+    int tier = 2;
+    if (certain && (orU32(&P.cull_claim[s], 1u) & 1u) == 0u)
+      tier = 0;
+    else if (deep && (orU32(&P.cull_claim[s], 2u) & 2u) == 0u)
+      tier = 1;
+    pushSurvivor(P, (uint32_t)c, tier);
     return;
   }
-  pushSurvivor(P, (uint32_t)c, false);
+  pushSurvivor(P, (uint32_t)c, 0);
 }
 
 T4_KD uint32_t orderedBits(float f)

@@ -397,7 +397,7 @@ struct t4c_scene
   DevBuf d_shapes, d_statics, d_verts, d_sup_cells, d_sup_cand, d_bvh, d_active, d_aa, d_acm, d_margin, d_shape_d, d_statics_d;
   // per-call workspace
   DevBuf d_q0, d_q1, d_pin0, d_pin1, d_poses0, d_poses1, d_poses0d, d_poses1d;
-  DevBuf d_cand_state, d_cand_a, d_cand_b, d_surv, d_surv2, d_cull_claim, d_tasks;
+  DevBuf d_cand_state, d_cand_a, d_cand_b, d_surv, d_surv2, d_surv3, d_cull_claim, d_tasks;
   DevBuf d_qcount, d_stats, d_hit, d_claim, d_raw, d_raw_local, d_ht_rep, d_ht_best;
   DevBuf d_out, d_out_local, d_fk_out, d_hit_full;
   uint32_t cand_cap = 0;
@@ -703,20 +703,23 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     T4_TRY(s->d_surv.ensure(std::max<size_t>(ncand, 1) * sizeof(uint32_t)), "survivor queue");
     P.surv_w = s->d_surv.as<uint32_t>();
     P.surv2_w = nullptr;
+    P.surv3_w = nullptr;
     P.cull_claim = nullptr;
     if (first_rec)
     {
       T4_TRY(s->d_surv2.ensure(std::max<size_t>(ncand, 1) * sizeof(uint32_t)) &&
+                 s->d_surv3.ensure(std::max<size_t>(ncand, 1) * sizeof(uint32_t)) &&
                  s->d_cull_claim.ensure((size_t)nc * sizeof(uint32_t)) &&
                  plat::zero(s->d_cull_claim.p, (size_t)nc * sizeof(uint32_t), st),
              "survivor queue");
       P.surv2_w = s->d_surv2.as<uint32_t>();
+      P.surv3_w = s->d_surv3.as<uint32_t>();
       P.cull_claim = s->d_cull_claim.as<uint32_t>();
     }
     P.surv_cap = ncand;
     launchCull(P, ncand, st);
     T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "cull");
-    const uint32_t nsurv = qc[Q_SURV], nsurv2 = qc[Q_SURV2];
+    const uint32_t nsurv = qc[Q_SURV], nsurv2 = qc[Q_SURV2], nsurv3 = qc[Q_SURV3];
     // ---- FP64 exact pass: GJK kernel (phases 1-2) -> task queue -> EPA kernel (phases 3-4)
     const bool closest = io.req.type == T4C_TEST_CLOSEST && io.contacts;
     const int64_t room = std::max<int64_t>(0, io.capacity - total);
@@ -743,15 +746,16 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
         P.raw_local = (io.cast && io.cc_local) ? io.cc_local + (size_t)std::min<int64_t>(total, io.capacity) * 6 : nullptr;
       }
     }
-    T4_TRY(s->d_tasks.ensure(std::max<size_t>(std::max(nsurv, nsurv2), 1) * sizeof(EpaTask)), "EPA task queue");
+    const uint32_t nsurv_max = std::max(nsurv, std::max(nsurv2, nsurv3));
+    T4_TRY(s->d_tasks.ensure(std::max<size_t>(nsurv_max, 1) * sizeof(EpaTask)), "EPA task queue");
     P.tasks = s->d_tasks.as<EpaTask>();
-    P.task_cap = std::max(nsurv, nsurv2);
-    for (int pass = 0; pass < 2; ++pass)
+    P.task_cap = nsurv_max;
+    for (int pass = 0; pass < 3; ++pass)
     {
-      const uint32_t nq = pass == 0 ? nsurv : nsurv2;
+      const uint32_t nq = pass == 0 ? nsurv : (pass == 1 ? nsurv2 : nsurv3);
       if (nq == 0)
         continue;
-      P.surv = pass == 0 ? s->d_surv.as<uint32_t>() : s->d_surv2.as<uint32_t>();
+      P.surv = pass == 0 ? s->d_surv.as<uint32_t>() : (pass == 1 ? s->d_surv2.as<uint32_t>() : s->d_surv3.as<uint32_t>());
       T4_TRY(plat::zero(P.qcount + Q_TASK, sizeof(uint32_t), st), "memset");
       launchGjk(P, nq, st);
       T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (GJK)");
