@@ -121,7 +121,7 @@ struct VoronoiSimplexSolver
     return found;
   }
 
-  T4_HD static bool closestPtPointTriangle(const V3<T>& p, const V3<T>& a, const V3<T>& b, const V3<T>& c,
+  T4_HDN static bool closestPtPointTriangle(const V3<T>& p, const V3<T>& a, const V3<T>& b, const V3<T>& c,
                                            SubSimplexResult<T>& r)
   {
     r.used[0] = r.used[1] = r.used[2] = r.used[3] = false;
@@ -197,7 +197,7 @@ struct VoronoiSimplexSolver
     return signp * signd < T(0) ? 1 : 0;
   }
 
-  T4_HD static bool closestPtPointTetrahedron(const V3<T>& p, const V3<T>& a, const V3<T>& b, const V3<T>& c,
+  T4_HDN static bool closestPtPointTetrahedron(const V3<T>& p, const V3<T>& a, const V3<T>& b, const V3<T>& c,
                                               const V3<T>& d, SubSimplexResult<T>& fr)
   {
     SubSimplexResult<T> tmp;

@@ -53,7 +53,7 @@ T4_HD V3<T> tripleCross(const V3<T>& a, const V3<T>& b, const V3<T>& c)
 }
 
 template <class T>
-T4_HD T pointSegmentDist2(const V3<T>& P, const V3<T>& x0, const V3<T>& b, bool want_witness, V3<T>& witness)
+T4_HDN T pointSegmentDist2(const V3<T>& P, const V3<T>& x0, const V3<T>& b, bool want_witness, V3<T>& witness)
 {
   T dist, t;
   V3<T> d = b - x0;
@@ -88,7 +88,7 @@ T4_HD T pointSegmentDist2(const V3<T>& P, const V3<T>& x0, const V3<T>& b, bool 
 
 // __ccdVec3PointTriDist2 without a witness (tesseract_gjk_pair_detector.cpp:320-405)
 template <class T>
-T4_HD T pointTriDist2(const V3<T>& P, const V3<T>& x0, const V3<T>& B, const V3<T>& C)
+T4_HDN T pointTriDist2(const V3<T>& P, const V3<T>& x0, const V3<T>& B, const V3<T>& C)
 {
   const V3<T> d1 = B - x0, d2 = C - x0, a = x0 - P;
   const T u = a.dot(a), v = d1.dot(d1), w = d2.dot(d2), p = a.dot(d1), q = a.dot(d2), r = d1.dot(d2);
@@ -120,7 +120,7 @@ T4_HD T pointTriDist2(const V3<T>& P, const V3<T>& x0, const V3<T>& B, const V3<
 }
 
 template <class T>
-T4_HD int doSimplex2(CcdSimplex<T>& s, V3<T>& dir)
+T4_HDN int doSimplex2(CcdSimplex<T>& s, V3<T>& dir)
 {
   const V3<T> A = s.ps[s.last];
   const V3<T> B = s.ps[0];
@@ -142,7 +142,7 @@ T4_HD int doSimplex2(CcdSimplex<T>& s, V3<T>& dir)
 }
 
 template <class T>
-T4_HD int doSimplex3(CcdSimplex<T>& s, V3<T>& dir)
+T4_HDN int doSimplex3(CcdSimplex<T>& s, V3<T>& dir)
 {
   const V3<T> A = s.ps[s.last];
   const V3<T> B = s.ps[1];
@@ -223,7 +223,7 @@ T4_HD int doSimplex3(CcdSimplex<T>& s, V3<T>& dir)
 }
 
 template <class T>
-T4_HD int doSimplex4(CcdSimplex<T>& s, V3<T>& dir)
+T4_HDN int doSimplex4(CcdSimplex<T>& s, V3<T>& dir)
 {
   const V3<T> A = s.ps[s.last];
   const V3<T> B = s.ps[2];
@@ -284,48 +284,77 @@ T4_HDN int doSimplex(CcdSimplex<T>& s, V3<T>& dir)
   return doSimplex4(s, dir);
 }
 
+// phase 1 (tesseract_gjk_pair_detector.cpp:732-821) as a resumable iteration: the state between two support
+// evaluations.  status: 0 = cores intersect, -1 = separated, -2 = undecided after 1000 iterations.
+template <class T>
+struct Phase1State
+{
+  CcdSimplex<T> simplex;
+  V3<T> dir;
+  int status, it, started;
+  T4_HD void reset()
+  {
+    simplex.last = -1;
+    dir = V3<T>(1, 0, 0);
+    status = -2;
+    it = 0;
+    started = 0;
+  }
+};
+
+// consumes w = support_A(dir) - support_B(-dir); returns true when phase 1 is over (st.status holds the outcome)
+template <class T>
+T4_HDN bool phase1Step(Phase1State<T>& st, const V3<T>& w)
+{
+  if (!st.started)
+  {
+    st.started = 1;
+    st.simplex.add(w);
+    st.dir = -w;
+    return false;
+  }
+  if (w.dot(st.dir) < 0)
+  {
+    st.status = -1;
+    return true;
+  }
+  st.simplex.add(w);
+  const int res = doSimplex(st.simplex, st.dir);
+  if (res == 1)
+  {
+    st.status = 0;
+    return true;
+  }
+  else if (res == -1)
+  {
+    st.status = -1;
+    return true;
+  }
+  if (fuzzyZero(st.dir.dot(st.dir)))
+    st.status = -1;
+  if (st.dir.len2() < K<T>::simdEps())
+  {
+    st.status = -1;
+    return true;
+  }
+  return ++st.it >= 1000;
+}
+
 // phase 1 driver: 0 = cores intersect, -1 = separated (tesseract_gjk_pair_detector.cpp:732-821)
 template <class T>
 T4_HDN int booleanGjk(const ShapeW<T>& A, const ShapeW<T>& B, int& iters)
 {
-  int status = -2;
-  CcdSimplex<T> simplex;
-  simplex.last = -1;
-  V3<T> dir(1, 0, 0);
-  V3<T> w = supportW(A, dir, false) - supportW(B, -dir, false);
-  iters = 1;
-  simplex.add(w);
-  dir = -w;
-  for (int it = 0; it < 1000; ++it)
+  Phase1State<T> st;
+  st.reset();
+  iters = 0;
+  for (;;)
   {
-    w = supportW(A, dir, false) - supportW(B, -dir, false);
+    const V3<T> w = supportW(A, st.dir, false) - supportW(B, -st.dir, false);
     ++iters;
-    if (w.dot(dir) < 0)
-    {
-      status = -1;
+    if (phase1Step(st, w))
       break;
-    }
-    simplex.add(w);
-    const int res = doSimplex(simplex, dir);
-    if (res == 1)
-    {
-      status = 0;
-      break;
-    }
-    else if (res == -1)
-    {
-      status = -1;
-      break;
-    }
-    if (fuzzyZero(dir.dot(dir)))
-      status = -1;
-    if (dir.len2() < K<T>::simdEps())
-    {
-      status = -1;
-      break;
-    }
   }
-  return status;
+  return st.status;
 }
 
 }  // namespace bt

@@ -61,6 +61,129 @@ T4_HD V3<T> recentre(ShapeW<T>& A, ShapeW<T>& B)
   return positionOffset;
 }
 
+// phase 2 (Bullet GJK with the Voronoi simplex solver, :836-971) as a resumable iteration
+template <class T>
+struct Phase2State
+{
+  VoronoiSimplexSolver<T> solver;
+  V3<T> axis;  // cachedSeparatingAxis
+  T squaredDistance;
+  int curIter, degenerateSimplex;
+  bool checkSimplex;
+  T4_HD void reset()
+  {
+    solver.reset();
+    axis = V3<T>(0, 1, 0);
+    squaredDistance = Eps<T>::large();
+    curIter = 0;
+    degenerateSimplex = 0;
+    checkSimplex = false;
+  }
+};
+
+// consumes pWorld = support_A(-axis), qWorld = support_B(axis); returns true when the loop is over
+template <class T>
+T4_HDN bool phase2Step(Phase2State<T>& st, const V3<T>& pWorld, const V3<T>& qWorld, T maxDist2)
+{
+  const V3<T> w = pWorld - qWorld;
+  const T delta = st.axis.dot(w);
+  if ((delta > T(0)) && (delta * delta > st.squaredDistance * maxDist2))
+  {
+    st.degenerateSimplex = 10;
+    st.checkSimplex = true;
+    return true;
+  }
+  if (st.solver.inSimplex(w))
+  {
+    st.degenerateSimplex = 1;
+    st.checkSimplex = true;
+    return true;
+  }
+  const T f0 = st.squaredDistance - delta;
+  const T f1 = st.squaredDistance * K<T>::relError2();
+  if (f0 <= f1)
+  {
+    st.degenerateSimplex = (f0 <= T(0)) ? 2 : 11;
+    st.checkSimplex = true;
+    return true;
+  }
+  st.solver.addVertex(w, pWorld, qWorld);
+  V3<T> newAxis;
+  if (!st.solver.closest(newAxis))
+  {
+    st.degenerateSimplex = 3;
+    st.checkSimplex = true;
+    return true;
+  }
+  if (newAxis.len2() < K<T>::relError2())
+  {
+    st.axis = newAxis;
+    st.degenerateSimplex = 6;
+    st.checkSimplex = true;
+    return true;
+  }
+  const T previousSquaredDistance = st.squaredDistance;
+  st.squaredDistance = newAxis.len2();
+  if (previousSquaredDistance - st.squaredDistance <= K<T>::simdEps() * previousSquaredDistance)
+  {
+    st.checkSimplex = true;
+    st.degenerateSimplex = 12;
+    return true;
+  }
+  st.axis = newAxis;
+  if (st.curIter++ > 1000)
+    return true;
+  if (st.solver.fullSimplex())
+  {
+    st.degenerateSimplex = 13;
+    return true;
+  }
+  return false;
+}
+
+template <class T>
+T4_HD void resetDetectorState(DetectorState<T>& S)
+{
+  S.distance = 0;
+  S.normalInB = V3<T>(0, 0, 0);
+  S.pointOnA = V3<T>(0, 0, 0);
+  S.pointOnB = V3<T>(0, 0, 0);
+  S.orgNormalInB = V3<T>(0, 0, 0);
+  S.isValid = 0;
+  S.status = 0;
+}
+
+// witness points, margins, validity after the phase-2 loop (:973-1006); returns DET_PHASE3 or DET_PHASE4
+template <class T>
+T4_HDN int phase2Finish(Phase2State<T>& st, T marginA, T marginB, DetectorState<T>& S)
+{
+  const T margin = marginA + marginB;
+  if (st.checkSimplex)
+  {
+    st.solver.compute_points(S.pointOnA, S.pointOnB);
+    S.normalInB = st.axis;
+    const T lenSqr = st.axis.len2();
+    if (lenSqr < K<T>::relError2())
+      st.degenerateSimplex = 5;
+    if (lenSqr > K<T>::simdEps() * K<T>::simdEps())
+    {
+      const T rlen = T(1) / t4sqrt(lenSqr);
+      S.normalInB = S.normalInB * rlen;
+      const T s = t4sqrt(st.squaredDistance);
+      S.pointOnA -= st.axis * (marginA / s);
+      S.pointOnB += st.axis * (marginB / s);
+      S.distance = (T(1) / rlen) - margin;
+      S.isValid = 1;
+      S.orgNormalInB = S.normalInB;
+    }
+  }
+  const bool catchDegeneratePenetrationCase =
+      (st.degenerateSimplex != 0) && ((S.distance + margin) < K<T>::penTol());
+  if (!S.isValid || catchDegeneratePenetrationCase)
+    return DET_PHASE3;
+  return DET_PHASE4;
+}
+
 // phases 1 and 2 on RECENTRED shapes
 template <class T>
 T4_HDN int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& positionOffset, T maxDist2, bool calc_pen,
@@ -70,17 +193,7 @@ T4_HDN int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& po
   out.gjk_iters = 0;
   out.epa_iters = 0;
   out.used_epa = false;
-  S.distance = 0;
-  S.normalInB = V3<T>(0, 0, 0);
-  S.pointOnA = V3<T>(0, 0, 0);
-  S.pointOnB = V3<T>(0, 0, 0);
-  S.orgNormalInB = V3<T>(0, 0, 0);
-  S.isValid = 0;
-  const T marginA = A.margin(), marginB = B.margin();
-  const T margin = marginA + marginB;
-  V3<T> cachedSeparatingAxis(0, 1, 0);
-  bool checkSimplex = false;
-  int degenerateSimplex = 0;
+  resetDetectorState(S);
   int it1 = 0;
   const int status = booleanGjk(A, B, it1);
   S.status = status;
@@ -99,93 +212,17 @@ T4_HDN int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& po
   if (status == 0)
     return DET_PHASE3;  // phase 2 is skipped when the cores intersect: the penetration result always supersedes it
 
-  T squaredDistance = Eps<T>::large();
-  T delta = 0;
-  VoronoiSimplexSolver<T> solver;
-  solver.reset();
-  int curIter = 0;
+  Phase2State<T> st;
+  st.reset();
   for (;;)
   {
-    const V3<T> pWorld = supportW(A, -cachedSeparatingAxis, false);
-    const V3<T> qWorld = supportW(B, cachedSeparatingAxis, false);
+    const V3<T> pWorld = supportW(A, -st.axis, false);
+    const V3<T> qWorld = supportW(B, st.axis, false);
     ++out.gjk_iters;
-    const V3<T> w = pWorld - qWorld;
-    delta = cachedSeparatingAxis.dot(w);
-    if ((delta > T(0)) && (delta * delta > squaredDistance * maxDist2))
-    {
-      degenerateSimplex = 10;
-      checkSimplex = true;
+    if (phase2Step(st, pWorld, qWorld, maxDist2))
       break;
-    }
-    if (solver.inSimplex(w))
-    {
-      degenerateSimplex = 1;
-      checkSimplex = true;
-      break;
-    }
-    const T f0 = squaredDistance - delta;
-    const T f1 = squaredDistance * K<T>::relError2();
-    if (f0 <= f1)
-    {
-      degenerateSimplex = (f0 <= T(0)) ? 2 : 11;
-      checkSimplex = true;
-      break;
-    }
-    solver.addVertex(w, pWorld, qWorld);
-    V3<T> newAxis;
-    if (!solver.closest(newAxis))
-    {
-      degenerateSimplex = 3;
-      checkSimplex = true;
-      break;
-    }
-    if (newAxis.len2() < K<T>::relError2())
-    {
-      cachedSeparatingAxis = newAxis;
-      degenerateSimplex = 6;
-      checkSimplex = true;
-      break;
-    }
-    const T previousSquaredDistance = squaredDistance;
-    squaredDistance = newAxis.len2();
-    if (previousSquaredDistance - squaredDistance <= K<T>::simdEps() * previousSquaredDistance)
-    {
-      checkSimplex = true;
-      degenerateSimplex = 12;
-      break;
-    }
-    cachedSeparatingAxis = newAxis;
-    if (curIter++ > 1000)
-      break;
-    if (solver.fullSimplex())
-    {
-      degenerateSimplex = 13;
-      break;
-    }
   }
-  if (checkSimplex)
-  {
-    solver.compute_points(S.pointOnA, S.pointOnB);
-    S.normalInB = cachedSeparatingAxis;
-    const T lenSqr = cachedSeparatingAxis.len2();
-    if (lenSqr < K<T>::relError2())
-      degenerateSimplex = 5;
-    if (lenSqr > K<T>::simdEps() * K<T>::simdEps())
-    {
-      const T rlen = T(1) / t4sqrt(lenSqr);
-      S.normalInB = S.normalInB * rlen;
-      const T s = t4sqrt(squaredDistance);
-      S.pointOnA -= cachedSeparatingAxis * (marginA / s);
-      S.pointOnB += cachedSeparatingAxis * (marginB / s);
-      S.distance = (T(1) / rlen) - margin;
-      S.isValid = 1;
-      S.orgNormalInB = S.normalInB;
-    }
-  }
-  const bool catchDegeneratePenetrationCase = (degenerateSimplex != 0) && ((S.distance + margin) < K<T>::penTol());
-  if (!S.isValid || catchDegeneratePenetrationCase)
-    return DET_PHASE3;
-  return DET_PHASE4;
+  return phase2Finish(st, A.margin(), B.margin(), S);
 }
 
 // phase 3 on RECENTRED shapes
@@ -239,51 +276,49 @@ T4_HDN void detectPhase3(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T
   }
 }
 
+// phase 4 (:1111-1179): acceptance test ...
+template <class T>
+T4_HD bool phase4Accepts(const DetectorState<T>& S, T maxDist2)
+{
+  return S.isValid && ((S.distance < T(0)) || (S.distance * S.distance < maxDist2));
+}
+// ... and the normal-direction sanity decision from the three extra support values
+// d2: along +-orgNormalInB, d1: along -+normalInB (flipped), d0: along +-normalInB (all minus the margins)
+template <class T>
+T4_HD void phase4Decide(const DetectorState<T>& S, T d0, T d1, T d2, const V3<T>& positionOffset, DetectorOut<T>& out)
+{
+  T distance = S.distance;
+  V3<T> normalInB = S.normalInB;
+  if (d1 > d0)
+    normalInB = -normalInB;
+  if (S.orgNormalInB.len2() > T(0))
+  {
+    if (d2 > d0 && d2 > d1 && d2 > distance)
+    {
+      normalInB = S.orgNormalInB;
+      distance = d2;
+    }
+  }
+  out.has = true;
+  out.normalOnB = normalInB;
+  out.pointOnB = S.pointOnB + positionOffset;
+  out.distance = distance;
+}
+
 // phase 4 on RECENTRED shapes: acceptance + normal-direction sanity
 template <class T>
 T4_HDN void detectPhase4(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& positionOffset, T maxDist2,
                         DetectorState<T>& S, DetectorOut<T>& out)
 {
   const T margin = A.margin() + B.margin();
-  T distance = S.distance;
-  V3<T> normalInB = S.normalInB;
-  const V3<T> orgNormalInB = S.orgNormalInB;
-  if (S.isValid && ((distance < T(0)) || (distance * distance < maxDist2)))
-  {
-    T d2 = 0;
-    {
-      const V3<T> pW = supportW(A, -orgNormalInB, false);
-      const V3<T> qW = supportW(B, orgNormalInB, false);
-      d2 = orgNormalInB.dot(pW - qW) - margin;
-    }
-    T d1 = 0;
-    {
-      const V3<T> pW = supportW(A, normalInB, false);
-      const V3<T> qW = supportW(B, -normalInB, false);
-      d1 = (-normalInB).dot(pW - qW) - margin;
-    }
-    T d0 = 0;
-    {
-      const V3<T> pW = supportW(A, -normalInB, false);
-      const V3<T> qW = supportW(B, normalInB, false);
-      d0 = normalInB.dot(pW - qW) - margin;
-    }
-    out.gjk_iters += 3;
-    if (d1 > d0)
-      normalInB = -normalInB;
-    if (orgNormalInB.len2() > T(0))
-    {
-      if (d2 > d0 && d2 > d1 && d2 > distance)
-      {
-        normalInB = orgNormalInB;
-        distance = d2;
-      }
-    }
-    out.has = true;
-    out.normalOnB = normalInB;
-    out.pointOnB = S.pointOnB + positionOffset;
-    out.distance = distance;
-  }
+  if (!phase4Accepts(S, maxDist2))
+    return;
+  const V3<T> normalInB = S.normalInB, orgNormalInB = S.orgNormalInB;
+  const T d2 = orgNormalInB.dot(supportW(A, -orgNormalInB, false) - supportW(B, orgNormalInB, false)) - margin;
+  const T d1 = (-normalInB).dot(supportW(A, normalInB, false) - supportW(B, -normalInB, false)) - margin;
+  const T d0 = normalInB.dot(supportW(A, -normalInB, false) - supportW(B, normalInB, false)) - margin;
+  out.gjk_iters += 3;
+  phase4Decide(S, d0, d1, d2, positionOffset, out);
 }
 
 // A, B: shapes with WORLD poses.  maxDist2 = (marginA + marginB + contactBreakingThreshold + max margin)^2  (:435-440 of

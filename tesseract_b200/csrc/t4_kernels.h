@@ -44,6 +44,7 @@ enum
   Q_SURV2,      // FIRST with records: one certainly PENETRATING pair per state (looked at only if still no contact)
   Q_SURV3,      // FIRST with records: every other survivor (looked at only if still no contact after the first two)
   Q_TASK,       // pairs handed from the GJK kernel to the EPA kernel
+  Q_FETCH,      // next survivor to hand to a lane of the GJK kernel (lane-refill loop)
   Q_RAW,        // raw contacts (CLOSEST staging) or final contacts (ALL / FIRST)
   Q_OUT,        // final contacts emitted by the CLOSEST reduction
   Q_COUNT
@@ -104,7 +105,8 @@ struct KParams
   const void* q1;
   int32_t q_layout;
   int64_t q_stride_n;  // total n of the SoA array (SoA layout only)
-  float* poses0;       // [n][n_alinks][12]
+  float* poses0;       // [n_alinks][n][12]: link-major, so that a warp working on 32 states of ONE link
+                       // (broadphase item order, FK stores) touches consecutive 48 B records
   float* poses1;
   double* poses0d;     // same poses in FP64 (exact pass: identical inputs to the reference's FP64 path)
   double* poses1d;
@@ -201,6 +203,9 @@ inline void minU64(unsigned long long* p, unsigned long long v)
 }
 #endif
 
+// element offset of the pose of active link `alink` in state s of the current chunk
+T4_KD size_t poseOffset(const KParams& P, int64_t s, int alink) { return ((size_t)alink * (size_t)P.n + (size_t)s) * 12; }
+
 template <class T>
 T4_KD Xf<T> loadPose(const float* p)
 {
@@ -223,7 +228,7 @@ T4_KD void shapePose(const KParams& P, const DShape& S, int sh, int64_t s, Xf<T>
     x1 = x0;
     return;
   }
-  const size_t off = ((size_t)s * (size_t)P.n_alinks + (size_t)S.alink) * 12;
+  const size_t off = poseOffset(P, s, S.alink);
   x0 = loadPose<T>(P.poses0 + off);
   if (P.cast)
     x1 = loadPose<T>(P.poses1 + off);
@@ -247,7 +252,7 @@ T4_KD void shapePoseD(const KParams& P, const DShape& S, int sh, int64_t s, Xf<d
     x1 = x0;
     return;
   }
-  const size_t off = ((size_t)s * (size_t)P.n_alinks + (size_t)S.alink) * 12;
+  const size_t off = poseOffset(P, s, S.alink);
   x0 = Xf<double>::from12(P.poses0d + off);
   if (P.cast)
     x1 = Xf<double>::from12(P.poses1d + off);
@@ -327,9 +332,10 @@ T4_KD void storePoseF(float* dst, const Xf<double>& x)
 }
 
 // item = state.  Writes poses0 (and poses1 for cast) of the kinematic links, or fk_out (all links, FP64).
-T4_KD void fkBody(int64_t s, const KParams& P)
+template <int MAXJ>
+T4_KD void fkBodyT(int64_t s, const KParams& P)
 {
-  Xf<double> Tj[T4_MAX_JOINTS];
+  Xf<double> Tj[MAXJ];  // joint frames of this state (thread-local; 96 B each)
   for (int pass = 0; pass < (P.cast ? 2 : 1); ++pass)
   {
     fkOne(P, pass ? P.q1 : P.q0, s, Tj);
@@ -349,25 +355,30 @@ T4_KD void fkBody(int64_t s, const KParams& P)
     {
       const int j = P.alink_joint[a];
       const Xf<double> x = j >= 0 ? Tj[j] : Xf<double>::from12(P.alink_static + (size_t)a * 12);
-      storePoseF(dst + ((size_t)s * P.n_alinks + a) * 12, x);
-      x.to12(dstd + ((size_t)s * P.n_alinks + a) * 12);
+      storePoseF(dst + poseOffset(P, s, a), x);
+      x.to12(dstd + poseOffset(P, s, a));
     }
   }
 }
 
+T4_KD void fkBody(int64_t s, const KParams& P) { fkBodyT<T4_MAX_JOINTS>(s, P); }
+
 // item = (state, active link): FK bypass, FP64 host poses -> FP32 device poses
 T4_KD void convertPosesBody(int64_t i, const KParams& P)
 {
+  const int64_t s = i / P.n_alinks;
+  const int a = (int)(i - s * P.n_alinks);
+  const size_t o = poseOffset(P, s, a);
   const double* src0 = P.poses_in0 + (size_t)i * 12;
-  storePoseF(P.poses0 + (size_t)i * 12, Xf<double>::from12(src0));
+  storePoseF(P.poses0 + o, Xf<double>::from12(src0));
   for (int k = 0; k < 12; ++k)
-    P.poses0d[(size_t)i * 12 + k] = src0[k];
+    P.poses0d[o + k] = src0[k];
   if (P.cast)
   {
     const double* src1 = P.poses_in1 + (size_t)i * 12;
-    storePoseF(P.poses1 + (size_t)i * 12, Xf<double>::from12(src1));
+    storePoseF(P.poses1 + o, Xf<double>::from12(src1));
     for (int k = 0; k < 12; ++k)
-      P.poses1d[(size_t)i * 12 + k] = src1[k];
+      P.poses1d[o + k] = src1[k];
   }
 }
 

@@ -196,7 +196,7 @@ T4_KDN void emitContact(const KParams& P, int64_t s, int a, int b, const ShapeW<
   {
     // addCastSingleResult (bullet_utils.h:527-611): continuous data per cast side; a single cast side is reported as
     // index 1 (:595-607)
-    const size_t offA = ((size_t)s * (size_t)P.n_alinks + (size_t)Sa.alink) * 12;
+    const size_t offA = poseOffset(P, s, Sa.alink);
     const Xf<double> linkA0 = Xf<double>::from12(P.poses0d + offA);
     ShapeW<double> Au = A;
     Au.cast = false;
@@ -208,7 +208,7 @@ T4_KDN void emitContact(const KParams& P, int64_t s, int a, int b, const ShapeW<
       continuousData(Au, linkA0, pointA, -pr.normalOnB, t, ty, pl);
       ct.cc_time[0] = (float)t, ct.cc_type[0] = (uint8_t)ty;
       local[0][0] = pl.x, local[0][1] = pl.y, local[0][2] = pl.z;
-      const size_t offB = ((size_t)s * (size_t)P.n_alinks + (size_t)Sb.alink) * 12;
+      const size_t offB = poseOffset(P, s, Sb.alink);
       const Xf<double> linkB0 = Xf<double>::from12(P.poses0d + offB);
       ShapeW<double> Bu = B;
       Bu.cast = false;
@@ -288,6 +288,223 @@ T4_KD void gjkBody(int64_t k, const KParams& P)
     bt::detectPhase4(Ar, Br, offset, maxDist2, S, d);
   copyOut(d, pr);
   emitContact(P, s, a, b, A, B, pr);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Lane-refill form of the exact GJK pass.  gjkBody above runs one pair per thread from start to end: lanes of a warp
+// sit in different phases with different iteration counts, and the ncu source view (r1e) showed 2-4 active threads
+// per instruction in the simplex code.  Here every trip of the loop evaluates exactly ONE support pair per lane --
+// the common, hottest block -- then advances that lane's state machine (phase 1 simplex, phase 2 Voronoi step, or
+// one of the three phase-4 evaluations); a lane whose pair is finished fetches the next survivor at once instead of
+// idling until the slowest lane of the warp is done.  The arithmetic per pair is exactly that of gjkBody.
+// ---------------------------------------------------------------------------------------------------------------
+enum
+{
+  LP_PHASE1 = 0,
+  LP_PHASE2,
+  LP_PHASE4_ORG,   // support along -/+ orgNormalInB  -> d2
+  LP_PHASE4_FLIP,  // support along +/- normalInB     -> d1
+  LP_PHASE4_FWD    // support along -/+ normalInB     -> d0
+};
+
+struct GjkLane
+{
+  uint32_t c;
+  int64_t s;
+  int a, b, phase, gjk_iters;
+  ShapeW<double> A, B;  // recentred
+  V3<double> offset;
+  double maxDist2, d1, d2;
+  bt::Phase1State<double> p1;
+  bt::Phase2State<double> p2;
+  bt::DetectorState<double> S;
+};
+
+T4_KDN void lanePushEpaTask(const KParams& P, const GjkLane& L)
+{
+  const uint32_t t = qAppend(&P.qcount[Q_TASK]);
+  if (t >= P.task_cap)
+    return;
+  EpaTask& T = P.tasks[t];
+  T.cand = L.c;
+  T.is_valid = L.S.isValid;
+  T.distance = L.S.distance;
+  T.normalInB[0] = L.S.normalInB.x, T.normalInB[1] = L.S.normalInB.y, T.normalInB[2] = L.S.normalInB.z;
+  T.pointOnA[0] = L.S.pointOnA.x, T.pointOnA[1] = L.S.pointOnA.y, T.pointOnA[2] = L.S.pointOnA.z;
+  T.pointOnB[0] = L.S.pointOnB.x, T.pointOnB[1] = L.S.pointOnB.y, T.pointOnB[2] = L.S.pointOnB.z;
+  T.orgNormalInB[0] = L.S.orgNormalInB.x, T.orgNormalInB[1] = L.S.orgNormalInB.y, T.orgNormalInB[2] = L.S.orgNormalInB.z;
+}
+
+T4_KDN void laneEmit(const KParams& P, const GjkLane& L, const bt::DetectorOut<double>& d)
+{
+  PairResult<double> pr;
+  copyOut(d, pr);
+  if (!pr.has)
+    return;
+  if (P.cast)
+  {
+    // continuous data needs the shapes at their world poses (not recentred): reload, exactly as gjkBody holds them
+    ShapeW<double> A, B;
+    loadPairShapesD(P, L.s, L.a, L.b, A, B);
+    emitContact(P, L.s, L.a, L.b, A, B, pr);
+  }
+  else
+    emitContact(P, L.s, L.a, L.b, L.A, L.B, pr);
+}
+
+// fetch + set up the next survivor for this lane; false when the queue is exhausted.  Pairs that need no iteration
+// (state already decided, analytic pairs) are completed here.
+T4_KDN bool laneFetch(const KParams& P, int64_t n, GjkLane& L)
+{
+  for (;;)
+  {
+    const uint32_t k = qAppend(&P.qcount[Q_FETCH]);
+    if ((int64_t)k >= n)
+      return false;
+    L.c = P.surv[k];
+    L.s = P.cand_state[L.c];
+    if ((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit[L.s])
+      continue;
+    L.a = (int)P.cand_a[L.c], L.b = (int)P.cand_b[L.c];
+    loadPairShapesD(P, L.s, L.a, L.b, L.A, L.B);
+    PairResult<double> pr;
+    if (analyticPairQuery(L.A, L.B, P.max_margin_d, pr))
+    {
+      emitContact(P, L.s, L.a, L.b, L.A, L.B, pr);
+      continue;
+    }
+    L.maxDist2 = detectorMaxDist2(L.A, L.B, P.max_margin_d);
+    L.offset = bt::recentre(L.A, L.B);
+    bt::resetDetectorState(L.S);
+    L.p1.reset();
+    L.phase = LP_PHASE1;
+    L.gjk_iters = 0;
+    return true;
+  }
+}
+
+// advance the lane by one support pair (pW on A along dA, qW on B along -dA); true when the pair is finished
+T4_KDN bool laneStep(const KParams& P, GjkLane& L, const V3<double>& pW, const V3<double>& qW)
+{
+  ++L.gjk_iters;
+  bt::DetectorOut<double> d;
+  d.has = false;
+  d.gjk_iters = 0;
+  d.epa_iters = 0;
+  d.used_epa = false;
+  const double margin = L.A.margin() + L.B.margin();
+  switch (L.phase)
+  {
+    case LP_PHASE1:
+    {
+      if (!bt::phase1Step(L.p1, pW - qW))
+        return false;
+      const int status = L.p1.status;
+      L.S.status = status;
+      if (status == 0 && !P.calc_pen)
+      {
+        d.has = true;
+        d.normalOnB = L.S.normalInB;
+        d.pointOnB = L.offset;
+        d.distance = -(double)FLT_MIN;
+        laneEmit(P, L, d);
+        return true;
+      }
+      if (status == -1 && !P.calc_dist)
+        return true;
+      if (status == 0)
+      {
+        lanePushEpaTask(P, L);
+        return true;
+      }
+      L.p2.reset();
+      L.phase = LP_PHASE2;
+      return false;
+    }
+    case LP_PHASE2:
+    {
+      if (!bt::phase2Step(L.p2, pW, qW, L.maxDist2))
+        return false;
+      if (bt::phase2Finish(L.p2, L.A.margin(), L.B.margin(), L.S) == bt::DET_PHASE3)
+      {
+        lanePushEpaTask(P, L);
+        return true;
+      }
+      if (!bt::phase4Accepts(L.S, L.maxDist2))
+        return true;
+      L.phase = LP_PHASE4_ORG;
+      return false;
+    }
+    case LP_PHASE4_ORG:
+      L.d2 = L.S.orgNormalInB.dot(pW - qW) - margin;
+      L.phase = LP_PHASE4_FLIP;
+      return false;
+    case LP_PHASE4_FLIP:
+      L.d1 = (-L.S.normalInB).dot(pW - qW) - margin;
+      L.phase = LP_PHASE4_FWD;
+      return false;
+    default:
+    {
+      const double d0 = L.S.normalInB.dot(pW - qW) - margin;
+      bt::phase4Decide(L.S, d0, L.d1, L.d2, L.offset, d);
+      laneEmit(P, L, d);
+      return true;
+    }
+  }
+}
+
+// direction of the next support evaluation on A (B gets the negated direction; negation is exact)
+T4_KD V3<double> laneDirection(const GjkLane& L)
+{
+  switch (L.phase)
+  {
+    case LP_PHASE1:
+      return L.p1.dir;
+    case LP_PHASE2:
+      return -L.p2.axis;
+    case LP_PHASE4_ORG:
+      return -L.S.orgNormalInB;
+    case LP_PHASE4_FLIP:
+      return L.S.normalInB;
+    default:
+      return -L.S.normalInB;
+  }
+}
+
+#ifdef T4_DEVICE_BUILD
+#define T4_WARP_ANY(x) __any_sync(0xffffffffu, (x))
+#else
+#define T4_WARP_ANY(x) (x)
+#endif
+
+// whole-kernel body: n = number of survivors in P.surv; P.qcount[Q_FETCH] must be zero at launch
+T4_KD void gjkLaneLoop(const KParams& P, int64_t n)
+{
+  GjkLane L;
+  bool have = false, more = true;
+  uint32_t iters = 0;
+  for (;;)
+  {
+    if (!have && more)
+    {
+      have = laneFetch(P, n, L);
+      more = have;
+    }
+    if (!T4_WARP_ANY(have))
+      break;
+    if (have)
+    {
+      const V3<double> dA = laneDirection(L);
+      const V3<double> pW = supportW(L.A, dA, false);
+      const V3<double> qW = supportW(L.B, -dA, false);
+      if (laneStep(P, L, pW, qW))
+      {
+        iters += (uint32_t)L.gjk_iters;
+        have = false;
+      }
+    }
+  }
+  statAdd(P.stats, ST_GJK_ITERS, iters);
 }
 
 // item = EPA task: phase 3 (penetration) and phase 4 of the exact query

@@ -91,7 +91,7 @@ T4_HD V3<T> vtx(const f4* verts, int i)
 
 // btConvexShape::localGetSupportVertexWithoutMarginNonVirtual and the virtual cone / capsule variants
 template <class T>
-T4_HD V3<T> coreSupport(const ShapeW<T>& s, const V3<T>& d)
+T4_HD V3<T> coreSupportInline(const ShapeW<T>& s, const V3<T>& d)
 {
   switch (s.type)
   {
@@ -189,12 +189,26 @@ T4_HD V3<T> coreSupport(const ShapeW<T>& s, const V3<T>& d)
   }
 }
 
+template <class T>
+T4_HDN V3<T> coreSupportCall(const ShapeW<T>& s, const V3<T>& d)
+{
+  return coreSupportInline(s, d);
+}
+template <class T>
+T4_HD V3<T> coreSupport(const ShapeW<T>& s, const V3<T>& d)
+{
+  if constexpr (sizeof(T) == 8)
+    return coreSupportCall(s, d);
+  else
+    return coreSupportInline(s, d);
+}
+
 // support of the shape placed by `x`, world direction d; with_margin adds margin * d/|d|
 template <class T>
 T4_HD V3<T> supportAt(const ShapeW<T>& s, const Xf<T>& x, const V3<T>& d, T margin)
 {
   V3<T> dl = x.rotT(d);
-  V3<T> sv = coreSupport(s, dl);
+  V3<T> sv = coreSupportInline(s, dl);  // the hot, non-swept path: one inlined copy inside supportWCall
   if (margin != T(0))
     sv += normalizedOrDefault(dl) * margin;
   return x(sv);

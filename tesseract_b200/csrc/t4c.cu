@@ -324,12 +324,24 @@ static void launchGjk(const KParams& P, int64_t n, t4stream st)
   profEnd(st);
   ++g_launches;
 }
+// resident CTAs per SM of the EPA kernel: its polytope pools live in local memory (20 KB per thread), fewer resident
+// threads keep that working set closer to the L2 share of an SM
+static int epaCtas()
+{
+  static int v = 0;
+  if (!v)
+  {
+    const char* e = std::getenv("T4C_EPA_CTAS");
+    v = e ? std::max(1, std::min(4, std::atoi(e))) : 4;
+  }
+  return v;
+}
 static void launchEpa(const KParams& P, int64_t n, t4stream st)
 {
   if (n <= 0)
     return;
   profBegin(PK_EPA, st);
-  t4LaunchEpa(P, n, gridFor(n, 128, 4), st);
+  t4LaunchEpa(P, n, gridFor(n, 128, epaCtas()), st);
   profEnd(st);
   ++g_launches;
 }
@@ -351,7 +363,19 @@ static void launchConvert(const KParams& P, int64_t n, t4stream) { T4_SERIAL(con
 static void launchBroadStatic(const KParams& P, int64_t n, t4stream) { T4_SERIAL(broadStaticBody, P, n); }
 static void launchBroadActive(const KParams& P, int64_t n, t4stream) { T4_SERIAL(broadActiveBody, P, n); }
 static void launchCull(const KParams& P, int64_t n, t4stream) { T4_SERIAL(cullBody, P, n); }
-static void launchGjk(const KParams& P, int64_t n, t4stream) { T4_SERIAL(gjkBody, P, n); }
+static void launchGjk(const KParams& P, int64_t n, t4stream)
+{
+  // same selection as the device build (t4c_exact.cu): pair-per-thread body by default, the lane-refill loop (with a
+  // single lane: same state machine as the device kernel) under T4C_GJK_LANES=1
+  const char* e = std::getenv("T4C_GJK_LANES");
+  if (n > 0 && e && std::atoi(e) == 1)
+  {
+    gjkLaneLoop(P, n);
+    ++g_launches;
+    return;
+  }
+  T4_SERIAL(gjkBody, P, n);
+}
 static void launchEpa(const KParams& P, int64_t n, t4stream)
 {
   std::unique_ptr<Epa<double>> epa(new Epa<double>());
@@ -756,7 +780,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       if (nq == 0)
         continue;
       P.surv = pass == 0 ? s->d_surv.as<uint32_t>() : (pass == 1 ? s->d_surv2.as<uint32_t>() : s->d_surv3.as<uint32_t>());
-      T4_TRY(plat::zero(P.qcount + Q_TASK, sizeof(uint32_t), st), "memset");
+      T4_TRY(plat::zero(P.qcount + Q_TASK, 2 * sizeof(uint32_t), st), "memset");  // Q_TASK, Q_FETCH
       launchGjk(P, nq, st);
       T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (GJK)");
       launchEpa(P, std::min(qc[Q_TASK], P.task_cap), st);

@@ -39,6 +39,24 @@ __global__ void __launch_bounds__(128, 4) epaKernelR128(KParams P, int64_t n)
     epaBody(i, P, epa);
 }
 
+// lane-refill GJK (t4_kernels2.h gjkLaneLoop).  Measured 2x SLOWER than the pair-per-thread kernel on B200 (r1g/r1h:
+// the per-lane state machine lives in local memory and every trip reloads it), so it is opt-in: T4C_GJK_LANES=1.
+__global__ void __launch_bounds__(128, 4) gjkLaneKernel(KParams P, int64_t n)
+{
+  gjkLaneLoop(P, n);
+}
+
+static int gjkLanes()
+{
+  static int v = -1;
+  if (v < 0)
+  {
+    const char* e = std::getenv("T4C_GJK_LANES");
+    v = (e && std::atoi(e) == 1) ? 1 : 0;
+  }
+  return v;
+}
+
 static int exactRegs()
 {
   static int v = 0;
@@ -57,14 +75,26 @@ __global__ void __launch_bounds__(128) fkKernel(KParams P, int64_t n)
     fkBody(i, P);
 }
 
+// robots with at most 16 joints (iiwa: 9, IRB2400: 8) keep the joint frames in a 1.5 KB frame instead of 6 KB
+__global__ void __launch_bounds__(128) fkKernel16(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    fkBodyT<16>(i, P);
+}
+
 void t4LaunchFk(const KParams& P, int64_t n, int grid, cudaStream_t st)
 {
-  fkKernel<<<grid, 128, 0, st>>>(P, n);
+  if (P.n_joints <= 16)
+    fkKernel16<<<grid, 128, 0, st>>>(P, n);
+  else
+    fkKernel<<<grid, 128, 0, st>>>(P, n);
 }
 
 void t4LaunchGjk(const KParams& P, int64_t n, int grid, cudaStream_t st)
 {
-  if (exactRegs() == 128)
+  if (gjkLanes())
+    gjkLaneKernel<<<grid, 128, 0, st>>>(P, n);
+  else if (exactRegs() == 128)
     gjkKernelR128<<<grid, 128, 0, st>>>(P, n);
   else
     gjkKernel<<<grid, 128, 0, st>>>(P, n);
