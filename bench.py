@@ -257,8 +257,17 @@ def main():
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
         bytes_state = 4 * nq + 1 + (80 * stats["contacts"] / max(1, stats["states"]) if want else 0)
+        # DRAM bytes per launch of that kernel from the committed ncu --set full capture (same workload only)
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                tj = json.load(f)
+            if tj["_config"] == {"mode": args.mode, "states": n, "prims": args.prims}:
+                traffic = tj.get(top)
+        except Exception:
+            pass
         roof = {"bound": "fp32", "kernel": top, "achieved": ach, "peak": tf.value, "unit": "TFLOP/s",
-                "frac": ach / tf.value if tf.value else None, "traffic": None,
+                "frac": ach / tf.value if tf.value else None, "traffic": traffic,
                 "peak_source": "measured in this run by t4c_measure_fp32_peak (FFMA loop on every SM)",
                 "kernel_ms_per_step": {k: v[0] / max(1, args.steps) for k, v in kern.items()},
                 "hbm": {"achieved": bytes_state * n / (ms_dev * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",

@@ -383,6 +383,86 @@ T4_KD void convertPosesBody(int64_t i, const KParams& P)
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// LVS subdivision of trajectories (tesseract_environment/core/utils.h:189-205 continuous, :328-347 discrete)
+// ---------------------------------------------------------------------------------------------------------------
+struct LvsParams
+{
+  const double* traj;  // [n_traj][n_wp][n_q]
+  int64_t n_traj;
+  int32_t n_wp, n_q, cast;
+  double lvs;
+  uint64_t* counts;         // [n_traj * steps] work items of every waypoint step
+  const uint64_t* offsets;  // exclusive prefix sum of counts
+  double* q0;               // [n_items][n_q]
+  double* q1;               // cast only
+  T4_HD int steps() const { return cast ? n_wp - 1 : n_wp; }
+};
+
+// Eigen::VectorXd::LinSpaced(cnt, low, high)(i) (core/utils.h:194-200)
+T4_HD double lvsLinspaced(int64_t cnt, double low, double high, int64_t i)
+{
+  const int64_t size1 = cnt == 1 ? 1 : cnt - 1;
+  const double step = cnt == 1 ? 0.0 : (high - low) / double(cnt - 1);
+  const bool flip = t4abs(high) < t4abs(low);
+  if (flip)
+    return (i == 0) ? low : (high - double(size1 - i) * step);
+  return (i == size1) ? high : (low + double(i) * step);
+}
+
+// number of LinSpaced points of waypoint step (a -> b), or 0 when the step is not subdivided
+T4_HD int64_t lvsPoints(const LvsParams& L, const double* a, const double* b, bool has_next)
+{
+  if (!has_next)
+    return 0;
+  double acc = 0;
+  for (int k = 0; k < L.n_q; ++k)
+    acc += (b[k] - a[k]) * (b[k] - a[k]);
+  const double dist = t4sqrt(acc);
+  if (dist > 0 && dist > L.lvs)
+    return (int64_t)ceil(dist / L.lvs) + 1;
+  return 0;
+}
+
+// item = t * steps + s
+T4_KD void lvsCountBody(int64_t i, const LvsParams& L)
+{
+  const int steps = L.steps();
+  const int64_t t = i / steps;
+  const int s = (int)(i - t * steps);
+  const double* a = L.traj + ((size_t)t * L.n_wp + s) * L.n_q;
+  const int64_t cnt = lvsPoints(L, a, a + L.n_q, s < L.n_wp - 1);
+  L.counts[i] = cnt > 0 ? (uint64_t)(cnt - 1) : 1ull;
+}
+
+T4_KD void lvsExpandBody(int64_t i, const LvsParams& L)
+{
+  const int steps = L.steps();
+  const int64_t t = i / steps;
+  const int s = (int)(i - t * steps);
+  const double* a = L.traj + ((size_t)t * L.n_wp + s) * L.n_q;
+  const double* b = a + L.n_q;
+  const int64_t cnt = lvsPoints(L, a, b, s < L.n_wp - 1);
+  const size_t base = (size_t)L.offsets[i];
+  if (cnt == 0)
+  {
+    for (int k = 0; k < L.n_q; ++k)
+    {
+      L.q0[base * L.n_q + k] = a[k];
+      if (L.cast)
+        L.q1[base * L.n_q + k] = b[k];
+    }
+    return;
+  }
+  for (int64_t j = 0; j < cnt - 1; ++j)
+    for (int k = 0; k < L.n_q; ++k)
+    {
+      L.q0[(base + j) * L.n_q + k] = lvsLinspaced(cnt, a[k], b[k], j);
+      if (L.cast)
+        L.q1[(base + j) * L.n_q + k] = lvsLinspaced(cnt, a[k], b[k], j + 1);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // broadphase
 // ---------------------------------------------------------------------------------------------------------------
 T4_KD bool boxesOverlap(const V3<float>& mn, const V3<float>& mx, const float* bmn, const float* bmx)

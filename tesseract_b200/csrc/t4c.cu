@@ -21,6 +21,7 @@
 
 #ifndef T4C_HOSTSIM
 #include <cuda_runtime.h>
+#include <cub/device/device_scan.cuh>
 #endif
 
 using namespace t4;
@@ -205,6 +206,8 @@ __global__ void __launch_bounds__(256) cullKernel(KParams P, int64_t n)
     cullBody(i, P);
 }
 void t4LaunchGjk(const KParams& P, int64_t n, int grid, cudaStream_t st);  // t4c_exact.cu (-fmad=false)
+void t4LaunchLvsCount(const LvsParams& L, int64_t n, int grid, cudaStream_t st);
+void t4LaunchLvsExpand(const LvsParams& L, int64_t n, int grid, cudaStream_t st);
 void t4LaunchEpa(const KParams& P, int64_t n, int grid, cudaStream_t st);
 __global__ void __launch_bounds__(256) closestInsertKernel(KParams P, int64_t n)
 {
@@ -424,6 +427,7 @@ struct t4c_scene
   DevBuf d_cand_state, d_cand_a, d_cand_b, d_surv, d_surv2, d_surv3, d_cull_claim, d_tasks;
   DevBuf d_qcount, d_stats, d_hit, d_claim, d_raw, d_raw_local, d_ht_rep, d_ht_best;
   DevBuf d_out, d_out_local, d_fk_out, d_hit_full;
+  DevBuf d_traj, d_lvs_counts, d_lvs_offsets, d_lvs_tmp;
   uint32_t cand_cap = 0;
   std::unordered_map<const t4c_fk_model*, std::unique_ptr<FkCache>> fk;
 
@@ -846,7 +850,11 @@ static t4c_status hostRun(t4c_scene* s, BatchIO& io, const double* hq0, const do
     return rc;
   t4stream st = s->stream;
   const int na = (int)s->comp.alinks.size();
-  if (io.model)
+  if (io.model && !hq0 && io.q0)
+  {
+    // joint vectors already on the device (LVS expansion kernels)
+  }
+  else if (io.model)
   {
     const size_t qb = (size_t)io.n * (size_t)io.model->n_q * sizeof(double);
     T4_TRY(s->d_q0.ensure(qb) && plat::h2d(s->d_q0.p, hq0, qb, st), "upload q");
@@ -1247,19 +1255,73 @@ static t4c_status checkTrajectories(t4c_scene* s, const t4c_fk_model* m, const d
 {
   if (!s || !m || !req || !r || !traj || n_traj < 0 || n_wp < (cast ? 2 : 1) || !(lvs > 0))
     return fail(T4C_ERR_INVALID, "bad trajectory arguments");
+#ifdef T4C_HOSTSIM
   std::vector<double> q0, q1;
   lvsExpand(traj, n_traj, n_wp, m->n_q, lvs, cast, q0, q1);
   const int64_t n = (int64_t)(q0.size() / (size_t)std::max(m->n_q, 1));
   if (n_items)
     *n_items = n;
-  if (r->hit && r->capacity >= 0 && false)
-    return T4C_OK;
   BatchIO io;
   io.n = n;
   io.cast = cast;
   io.model = m;
   io.req = *req;
   return hostRun(s, io, q0.data(), cast ? q1.data() : nullptr, nullptr, nullptr, r);
+#else
+  // LVS subdivision on the device: count per waypoint step -> exclusive scan -> expansion into q0 / q1
+  if (!bindDevice(s))
+    return fail(T4C_ERR_CUDA, "cudaSetDevice(%d): %s", s->device, plat::lastError());
+  t4stream st = s->stream;
+  LvsParams L;
+  L.n_traj = n_traj, L.n_wp = n_wp, L.n_q = m->n_q, L.cast = cast ? 1 : 0, L.lvs = lvs;
+  const int64_t n_steps = n_traj * (int64_t)L.steps();
+  int64_t n = 0;
+  if (n_steps > 0)
+  {
+    const size_t tb = (size_t)n_traj * n_wp * m->n_q * sizeof(double);
+    T4_TRY(s->d_traj.ensure(tb) && plat::h2d(s->d_traj.p, traj, tb, st) &&
+               s->d_lvs_counts.ensure((size_t)n_steps * sizeof(uint64_t)) &&
+               s->d_lvs_offsets.ensure((size_t)n_steps * sizeof(uint64_t)),
+           "LVS workspace");
+    L.traj = s->d_traj.as<double>();
+    L.counts = s->d_lvs_counts.as<uint64_t>();
+    L.offsets = s->d_lvs_offsets.as<uint64_t>();
+    L.q0 = L.q1 = nullptr;
+    t4LaunchLvsCount(L, n_steps, gridFor(n_steps, 256, 8), st);
+    ++g_launches;
+    size_t tmp_bytes = 0;
+    T4_TRY(plat::chk(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, L.counts, s->d_lvs_offsets.as<uint64_t>(), n_steps, st)) &&
+               s->d_lvs_tmp.ensure(tmp_bytes) &&
+               plat::chk(cub::DeviceScan::ExclusiveSum(s->d_lvs_tmp.p, tmp_bytes, L.counts,
+                                                       s->d_lvs_offsets.as<uint64_t>(), n_steps, st)),
+           "LVS scan");
+    uint64_t last[2] = { 0, 0 };
+    T4_TRY(plat::d2h(&last[0], L.offsets + (n_steps - 1), sizeof(uint64_t), st) &&
+               plat::d2h(&last[1], L.counts + (n_steps - 1), sizeof(uint64_t), st) && plat::sync(st),
+           "LVS count");
+    n = (int64_t)(last[0] + last[1]);
+    const size_t qb = (size_t)n * m->n_q * sizeof(double);
+    T4_TRY(s->d_q0.ensure(qb) && (!cast || s->d_q1.ensure(qb)), "LVS workspace");
+    L.q0 = s->d_q0.as<double>();
+    L.q1 = cast ? s->d_q1.as<double>() : nullptr;
+    t4LaunchLvsExpand(L, n_steps, gridFor(n_steps, 256, 8), st);
+    ++g_launches;
+    T4_TRY(launchOk(), "LVS expansion");
+  }
+  if (n_items)
+    *n_items = n;
+  BatchIO io;
+  io.n = n;
+  io.cast = cast;
+  io.model = m;
+  io.req = *req;
+  if (n == 0)
+    return hostRun(s, io, traj, traj, nullptr, nullptr, r);
+  io.q0 = s->d_q0.p;
+  io.q1 = cast ? s->d_q1.p : nullptr;
+  io.q_layout = T4C_Q_F64_ROWMAJOR;
+  return hostRun(s, io, nullptr, nullptr, nullptr, nullptr, r);
+#endif
 }
 
 t4c_status t4c_lvs_count(const double* traj, int64_t n_traj, int32_t n_wp, int32_t n_q, double lvs, int32_t cast,

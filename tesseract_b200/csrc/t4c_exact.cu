@@ -90,6 +90,20 @@ void t4LaunchFk(const KParams& P, int64_t n, int grid, cudaStream_t st)
     fkKernel<<<grid, 128, 0, st>>>(P, n);
 }
 
+// LVS subdivision: FP64, two roundings per a*b+c like the host formula it restates (Eigen LinSpaced)
+__global__ void __launch_bounds__(256) lvsCountKernel(LvsParams L, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    lvsCountBody(i, L);
+}
+__global__ void __launch_bounds__(256) lvsExpandKernel(LvsParams L, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    lvsExpandBody(i, L);
+}
+void t4LaunchLvsCount(const LvsParams& L, int64_t n, int grid, cudaStream_t st) { lvsCountKernel<<<grid, 256, 0, st>>>(L, n); }
+void t4LaunchLvsExpand(const LvsParams& L, int64_t n, int grid, cudaStream_t st) { lvsExpandKernel<<<grid, 256, 0, st>>>(L, n); }
+
 void t4LaunchGjk(const KParams& P, int64_t n, int grid, cudaStream_t st)
 {
   if (gjkLanes())

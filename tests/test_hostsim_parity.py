@@ -43,3 +43,10 @@ def test_cast_lvs():
 @pytest.mark.parametrize("robot", ["iiwa14", "abb_irb2400"])
 def test_fk(robot):
     pc.fk_parity(mk, robot)
+
+
+def test_lane_refill_state_machine(monkeypatch):
+    """the opt-in lane-refill form of the exact GJK pass (t4_kernels2.h gjkLaneLoop) gives the same contacts"""
+    monkeypatch.setenv("T4C_GJK_LANES", "1")
+    print(pc.discrete_config2(mk, 300, 10000, capi.TEST_CLOSEST))
+    print(pc.cast_config3(mk, 4, 10, 10000))
