@@ -127,6 +127,18 @@ def cast_config3(make_checker, n_traj, n_wp, n_prims, lvs=0.05, threads=4, devic
     return compare_batch(b, con_g, con_o, hit_g, hit_o, 0.05, check_cc=True)
 
 
+def discrete_lvs(make_checker, n_traj, n_wp, n_prims, lvs=0.05, threads=4):
+    """checkTrajectory(LVS_DISCRETE) (core/utils.h:309-428): LVS sub-states through the trajectory entry point"""
+    b = S.build_config2(n_prims=n_prims, margin=0.05)
+    traj = S.random_trajectories(b, n_traj, n_wp, seed=11, sigma=0.03)
+    q0, _, it, st = pyoracle.lvs_expand(traj, lvs, cast=False)
+    bc = make_checker(b)
+    hit_o, con_o, _ = pyoracle.check_discrete(b, q0, capi.TEST_CLOSEST, n_threads=threads)
+    hit_g, con_g, loc, stats = bc.check_trajectories(traj, lvs, False, capi.TEST_CLOSEST)
+    assert len(hit_g) == len(q0)
+    return flip_statistics(b, con_g, con_o, hit_g, hit_o, 0.05)
+
+
 def fk_parity(make_checker, robot="iiwa14", n=200):
     b = S.SceneBuilder()
     S.add_robot(b, S.load_robot(robot))

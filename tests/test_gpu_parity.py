@@ -39,6 +39,10 @@ def test_flags_only_boolean_request():
     assert pc.flags_only(mk, 30000, 10000, margin=0.0, pen=False, dist=False, threads=THREADS) > 0
 
 
+def test_discrete_lvs():
+    print(pc.discrete_lvs(mk, 64, 30, 10000, threads=THREADS))
+
+
 def test_cast_lvs():
     print(pc.cast_config3(mk, 64, 30, 10000, threads=THREADS))
 

@@ -36,6 +36,10 @@ def test_flags_only_boolean_request():
     assert pc.flags_only(mk, 600, 10000, margin=0.0, pen=False, dist=False) > 0
 
 
+def test_discrete_lvs():
+    print(pc.discrete_lvs(mk, 4, 10, 10000))
+
+
 def test_cast_lvs():
     print(pc.cast_config3(mk, 6, 12, 10000))
 

@@ -3,7 +3,7 @@
 subdivision (tesseract_environment/core/utils.h:172-297), through the C ABI.  Unit of work = LVS sub-segment.
 
   value : t4c_check_cast_device on pre-expanded sub-segments already in HBM (FP64 row-major q0 / q1)
-  e2e   : t4c_check_trajectories_cast on host trajectories (LVS expansion on the host + H2D + check + D2H)
+  e2e   : t4c_check_trajectories_cast on host trajectories (H2D + LVS subdivision kernels + check + D2H)
 Not part of the driver's bench contract (bench.py is); prints one JSON line."""
 import argparse
 import ctypes as C
@@ -103,7 +103,7 @@ def main():
                                              f"waypoints, LVS {args.lvs} rad -> {n} sub-segments, 10k-primitive "
                                              "environment, margin 0.05 m", "request": args.mode},
                       "e2e": {"value": items / (ms_host * 1e-3), "unit": "sub-segments/s", "ms_per_step": ms_host,
-                              "items": items, "note": "host LVS expansion + H2D + check + D2H"},
+                              "items": items, "note": "H2D of the trajectories + LVS subdivision kernels + check + D2H"},
                       "kernel_ms_per_step": prof, "stats": io.stats.as_dict(), "contacts": int(io.n_contacts)}))
 
 
