@@ -513,7 +513,7 @@ T4_KD void broadStaticBody(int64_t item, const KParams& P)
   mn = mn - V3<float>(grow, grow, grow);
   mx = mx + V3<float>(grow, grow, grow);
   const V3<float> bc(S.bc[0], S.bc[1], S.bc[2]), bh(S.bh[0], S.bh[1], S.bh[2]);
-  const V3<float> cw = x0(bc), cw1 = x1(bc);
+  const V3<float> cw = x0(bc);
   const float ra = S.bc[3];
   uint32_t nodes = 0, culled = 0, cands = 0;
   int stack[64];
@@ -558,24 +558,6 @@ T4_KD void broadStaticBody(int64_t item, const KParams& P)
         const V3<float> e(t4max(t4abs(pl.x) - bh.x, 0.f), t4max(t4abs(pl.y) - bh.y, 0.f),
                           t4max(t4abs(pl.z) - bh.z, 0.f));
         if (e.len2() > reach * reach)
-        {
-          ++culled;
-          continue;
-        }
-      }
-      else
-      {
-        // swept shape = conv(shape at pose 0, shape at pose 1), inside the capsule around the segment of the two
-        // bounding-sphere centres: cull on the distance of the primitive's bounding sphere to that segment
-        const DStaticW& W = P.statics[b];
-        const V3<float> cb(W.bs[0], W.bs[1], W.bs[2]);
-        const V3<float> seg = cw1 - cw, rel = cb - cw;
-        const float l2 = seg.len2();
-        float t = l2 > 0.f ? rel.dot(seg) / l2 : 0.f;
-        t = t4min(t4max(t, 0.f), 1.f);
-        const V3<float> d = rel - seg * t;
-        const float rr = ra + W.bs[3] + grow + 1e-5f;
-        if (d.len2() > rr * rr)
         {
           ++culled;
           continue;
