@@ -87,7 +87,7 @@ def load_library(path=None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = path or LIB_PATH
+    p = path or os.environ.get("T4C_LIB") or LIB_PATH  # T4C_LIB: alternative build of the same library (experiments)
     if not os.path.exists(p):
         raise RuntimeError(f"tesseract_b200 CUDA library not built: {p} (run __graft_entry__.build()); "
                            "there is no CPU fallback")

@@ -225,24 +225,30 @@ T4_HDN int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& po
   return phase2Finish(st, A.margin(), B.margin(), S);
 }
 
-// phase 3 on RECENTRED shapes
-template <class T, class EPA_T>
-T4_HDN void detectPhase3(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T>& S, DetectorOut<T>& out, EPA_T& epa)
+// phase 3 on RECENTRED shapes, in three pieces so that the polytope expansion in the middle can be run one iteration
+// at a time (lane-refill EPA kernel): seed = FP64 GJK on the cores (simplex for EPA, or the separated answer) ...
+template <class T>
+T4_HDN int phase3Seed(const ShapeW<T>& A, const ShapeW<T>& B, GjkOut<T, true>& g)
+{
+  const V3<T> axis0 = A.x0.p - B.x0.p;
+  return gjkDistance<T, true>(A, B, axis0, false, Eps<T>::large(), T(-1), g, 128);
+}
+
+// ... and the merge of its outcome into the detector state (the deeper result wins, :1024-1108).
+// st = outcome of the seed; gv / gpA = its closest vector and witness on A (separated case); epa_ok / er = result of
+// the expansion (intersecting case)
+template <class T>
+T4_HDN void phase3Apply(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T>& S, DetectorOut<T>& out, int st,
+                       const V3<T>& gv, const V3<T>& gpA, bool epa_ok, const EpaResult<T>& er)
 {
   const T marginA = A.margin(), marginB = B.margin();
   const T margin = marginA + marginB;
-  out.used_epa = true;
-  GjkOut<T, true> g;
-  const V3<T> axis0 = A.x0.p - B.x0.p;
-  const int st = gjkDistance<T, true>(A, B, axis0, false, Eps<T>::large(), T(-1), g, 128);
-  out.gjk_iters += g.iters;
   bool have2 = false;
   T distance2 = 0;
   V3<T> n2, pA2, pB2;
   if (st == GJK_INTERSECT)
   {
-    EpaResult<T> er;
-    if (epa.run(A, B, g.sx.W, g.sx.P, g.sx.n, 255, T(1e-12), er))
+    if (epa_ok)
     {
       out.epa_iters = er.iterations;
       const T depth = er.depth + margin;
@@ -255,12 +261,12 @@ T4_HDN void detectPhase3(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T
   }
   else if (st == GJK_SEPARATED)
   {
-    const T dc = g.v.len();
+    const T dc = gv.len();
     if (dc > T(0))
     {
-      const V3<T> n = g.v * (T(1) / dc);
-      pA2 = g.pA - n * marginA;
-      pB2 = (g.pA - g.v) + n * marginB;
+      const V3<T> n = gv * (T(1) / dc);
+      pA2 = gpA - n * marginA;
+      pB2 = (gpA - gv) + n * marginB;
       n2 = n;
       distance2 = dc - margin;
       have2 = true;
@@ -274,6 +280,21 @@ T4_HDN void detectPhase3(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T
     S.normalInB = n2;
     S.isValid = 1;
   }
+}
+
+template <class T, class EPA_T>
+T4_HDN void detectPhase3(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T>& S, DetectorOut<T>& out, EPA_T& epa)
+{
+  out.used_epa = true;
+  GjkOut<T, true> g;
+  const int st = phase3Seed(A, B, g);
+  out.gjk_iters += g.iters;
+  EpaResult<T> er;
+  er.iterations = 0;
+  bool ok = false;
+  if (st == GJK_INTERSECT)
+    ok = epa.run(A, B, g.sx.W, g.sx.P, g.sx.n, 255, T(1e-12), er);
+  phase3Apply(A, B, S, out, st, g.v, g.pA, ok, er);
 }
 
 // phase 4 (:1111-1179): acceptance test ...

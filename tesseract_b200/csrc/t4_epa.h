@@ -155,9 +155,17 @@ struct Epa
     return -1;
   }
 
-  // simplex: up to 4 points of A-B (and their A witnesses) around the origin, from the GJK that found the overlap
-  T4_HDN bool run(const ShapeW<T>& a, const ShapeW<T>& b, const V3<T>* sw, const V3<T>* sp, int rank, int max_iter,
-                 T tol, EpaResult<T>& res)
+  // ---- iteration state (members, so that the expansion can be resumed one iteration at a time: the lane-refill
+  //      EPA kernel advances every lane by ONE iteration per trip and refills finished lanes at once)
+  int mark_, it_, max_iter_;
+  T tol_, saved_d;
+  V3<T> saved_n, saved_w[3], saved_p[3];
+  bool have_saved, deteriorated;
+
+  // simplex: up to 4 points of A-B (and their A witnesses) around the origin, from the GJK that found the overlap.
+  // false: no enclosing tetrahedron could be built (no penetration result)
+  T4_HDN bool begin(const ShapeW<T>& a, const ShapeW<T>& b, const V3<T>* sw, const V3<T>* sp, int rank, int max_iter,
+                    T tol)
   {
     A = &a;
     B = &b;
@@ -168,8 +176,6 @@ struct Epa
       P[i] = sp[i];
       ++nv;
     }
-    res.converged = false;
-    res.iterations = 0;
     bool ok = false;
     if (nv == 0)
     {
@@ -208,167 +214,195 @@ struct Epa
         for (int j = 0; j < 4; ++j)
           if (j != i && edgeIndex(F[j], F[i].v[(e + 1) % 3], F[i].v[e]) >= 0)
             F[i].adj[e] = (int16_t)j;
-    int mark = 0;
+    mark_ = 0;
+    it_ = 0;
+    max_iter_ = max_iter;
+    tol_ = tol;
+    saved_d = -Eps<T>::large();
+    have_saved = false;
+    deteriorated = false;
+    return true;
+  }
+
+  // one expansion iteration: 0 = continue, 1 = finished (call finish), 2 = failed (no result)
+  T4_HDN int step()
+  {
+    if (it_ >= max_iter_)
+      return 1;
     int best = -1;
-    int it = 0;
-    T saved_d = -Eps<T>::large();
-    V3<T> saved_n, saved_w[3], saved_p[3];
-    bool have_saved = false, deteriorated = false;
-    for (; it < max_iter; ++it)
+    for (int i = 0; i < nf_hi; ++i)
+      if (F[i].alive && (best < 0 || F[i].d < F[best].d))
+        best = i;
+    if (best < 0)
+      return 2;
+    // The closest-face distance is a LOWER bound of the depth and can only grow.  On curved supports (cylinder /
+    // cone rims) the faces shrink to rounding-noise size near convergence and the hull eventually corrupts: the
+    // bound then drops.  Stop there and report the tightest bound recorded.
+    if (F[best].d + T(1e-12) < saved_d)
     {
-      best = -1;
-      for (int i = 0; i < nf_hi; ++i)
-        if (F[i].alive && (best < 0 || F[i].d < F[best].d))
-          best = i;
-      if (best < 0)
-        return false;
-      // The closest-face distance is a LOWER bound of the depth and can only grow.  On curved supports (cylinder /
-      // cone rims) the faces shrink to rounding-noise size near convergence and the hull eventually corrupts: the
-      // bound then drops.  Stop there and report the tightest bound recorded.
-      if (F[best].d + T(1e-12) < saved_d)
+      deteriorated = true;
+      return 1;
+    }
+    if (F[best].d >= saved_d)
+    {
+      saved_d = F[best].d;
+      saved_n = F[best].n;
+      for (int k = 0; k < 3; ++k)
       {
-        deteriorated = true;
-        break;
+        saved_w[k] = W[F[best].v[k]];
+        saved_p[k] = P[F[best].v[k]];
       }
-      if (F[best].d >= saved_d)
+      have_saved = true;
+    }
+    if (nv >= MAXV)
+      return 1;
+    V3<T> w, p;
+    support(F[best].n, w, p);
+    const T wdist = F[best].n.dot(w) - F[best].d;
+    if (wdist <= tol_)
+      return 1;
+    const int wi = nv;
+    W[nv] = w;
+    P[nv] = p;
+    ++nv;
+    // visible set: flood fill from the closest face
+    ++mark_;
+    int sp_ = 0, nvis = 0;
+    stack[sp_++] = (int16_t)best;
+    F[best].mark = (int16_t)mark_;
+    while (sp_ > 0)
+    {
+      const int f = stack[--sp_];
+      visible[nvis++] = (int16_t)f;
+      for (int e = 0; e < 3; ++e)
       {
-        saved_d = F[best].d;
-        saved_n = F[best].n;
-        for (int k = 0; k < 3; ++k)
+        const int g = F[f].adj[e];
+        if (g < 0 || F[g].mark == mark_)
+          continue;
+        if (F[g].n.dot(w) - F[g].d > T(1e-14))
         {
-          saved_w[k] = W[F[best].v[k]];
-          saved_p[k] = P[F[best].v[k]];
+          F[g].mark = (int16_t)mark_;
+          stack[sp_++] = (int16_t)g;
         }
-        have_saved = true;
       }
-      if (nv >= MAXV)
-        break;
-      V3<T> w, p;
-      support(F[best].n, w, p);
-      const T wdist = F[best].n.dot(w) - F[best].d;
-      if (wdist <= tol)
+    }
+    // horizon; absorb outside neighbours that would give a zero-area new face
+    int nh = 0;
+    for (int guard = 0; guard < 64; ++guard)
+    {
+      nh = 0;
+      bool grew = false;
+      for (int k = 0; k < nvis && !grew; ++k)
       {
-        res.converged = true;
-        break;
-      }
-      const int wi = nv;
-      W[nv] = w;
-      P[nv] = p;
-      ++nv;
-      // visible set: flood fill from the closest face
-      ++mark;
-      int sp_ = 0, nvis = 0;
-      stack[sp_++] = (int16_t)best;
-      F[best].mark = (int16_t)mark;
-      while (sp_ > 0)
-      {
-        const int f = stack[--sp_];
-        visible[nvis++] = (int16_t)f;
-        for (int e = 0; e < 3; ++e)
+        const int f = visible[k];
+        for (int e = 0; e < 3 && !grew; ++e)
         {
           const int g = F[f].adj[e];
-          if (g < 0 || F[g].mark == mark)
+          if (g >= 0 && F[g].mark == mark_)
             continue;
-          if (F[g].n.dot(w) - F[g].d > T(1e-14))
+          const int va = F[f].v[e], vb = F[f].v[(e + 1) % 3];
+          const V3<T> n = (W[vb] - W[va]).cross(w - W[va]);
+          if (g >= 0 && n.len() < T(1e-14) * (T(1) + w.len2()) && nvis < MAXF)
           {
-            F[g].mark = (int16_t)mark;
-            stack[sp_++] = (int16_t)g;
+            F[g].mark = (int16_t)mark_;
+            visible[nvis++] = (int16_t)g;
+            grew = true;
+            break;
+          }
+          if (nh < MAXF)
+          {
+            hz_a[nh] = (int16_t)va;
+            hz_b[nh] = (int16_t)vb;
+            hz_g[nh] = (int16_t)g;
+            ++nh;
           }
         }
       }
-      // horizon; absorb outside neighbours that would give a zero-area new face
-      int nh = 0;
-      for (int guard = 0; guard < 64; ++guard)
-      {
-        nh = 0;
-        bool grew = false;
-        for (int k = 0; k < nvis && !grew; ++k)
-        {
-          const int f = visible[k];
-          for (int e = 0; e < 3 && !grew; ++e)
-          {
-            const int g = F[f].adj[e];
-            if (g >= 0 && F[g].mark == mark)
-              continue;
-            const int va = F[f].v[e], vb = F[f].v[(e + 1) % 3];
-            const V3<T> n = (W[vb] - W[va]).cross(w - W[va]);
-            if (g >= 0 && n.len() < T(1e-14) * (T(1) + w.len2()) && nvis < MAXF)
-            {
-              F[g].mark = (int16_t)mark;
-              visible[nvis++] = (int16_t)g;
-              grew = true;
-              break;
-            }
-            if (nh < MAXF)
-            {
-              hz_a[nh] = (int16_t)va;
-              hz_b[nh] = (int16_t)vb;
-              hz_g[nh] = (int16_t)g;
-              ++nh;
-            }
-          }
-        }
-        if (!grew)
-          break;
-      }
-      if (nh < 3)
-      {
-        --nv;
+      if (!grew)
         break;
-      }
-      // capacity check before touching the hull
-      if (nh > (MAXF - nf_hi) + n_free + nvis)
-      {
-        --nv;
-        break;
-      }
-      for (int k = 0; k < nvis; ++k)
-      {
-        F[visible[k]].alive = 0;
-        free_list[n_free++] = visible[k];
-      }
-      // new faces (a, b, w): edge0 = horizon edge, edge1 = (b,w), edge2 = (w,a)
-      bool bad = false;
-      int first_new = -1;
-      // remember the slots of the new faces in `stack` (free again at this point)
-      int nnew = 0;
-      for (int k = 0; k < nh; ++k)
-      {
-        const int slot = allocFace();
-        Face nf;
-        if (slot < 0 || !makeFace(hz_a[k], hz_b[k], wi, nf))
-        {
-          bad = true;
-          break;
-        }
-        nf.adj[0] = hz_g[k];
-        nf.mark = 0;
-        F[slot] = nf;
-        stack[nnew++] = (int16_t)slot;
-        if (first_new < 0)
-          first_new = slot;
-        const int g = hz_g[k];
-        if (g >= 0)
-        {
-          const int ge = edgeIndex(F[g], hz_b[k], hz_a[k]);
-          if (ge >= 0)
-            F[g].adj[ge] = (int16_t)slot;
-        }
-      }
-      if (bad)
-        break;
-      for (int i = 0; i < nnew; ++i)
-        for (int j = 0; j < nnew; ++j)
-        {
-          Face& fi = F[stack[i]];
-          const Face& fj = F[stack[j]];
-          if (fj.v[0] == fi.v[1])
-            fi.adj[1] = stack[j];
-          if (fj.v[1] == fi.v[0])
-            fi.adj[2] = stack[j];
-        }
     }
-    res.iterations = it;
+    if (nh < 3)
+    {
+      --nv;
+      return 1;
+    }
+    // capacity check before touching the hull
+    if (nh > (MAXF - nf_hi) + n_free + nvis)
+    {
+      --nv;
+      return 1;
+    }
+    for (int k = 0; k < nvis; ++k)
+    {
+      F[visible[k]].alive = 0;
+      free_list[n_free++] = visible[k];
+    }
+    // new faces (a, b, w): edge0 = horizon edge, edge1 = (b,w), edge2 = (w,a)
+    bool bad = false;
+    int first_new = -1;
+    // remember the slots of the new faces in `stack` (free again at this point)
+    int nnew = 0;
+    for (int k = 0; k < nh; ++k)
+    {
+      const int slot = allocFace();
+      Face nf;
+      if (slot < 0 || !makeFace(hz_a[k], hz_b[k], wi, nf))
+      {
+        bad = true;
+        break;
+      }
+      nf.adj[0] = hz_g[k];
+      nf.mark = 0;
+      F[slot] = nf;
+      stack[nnew++] = (int16_t)slot;
+      if (first_new < 0)
+        first_new = slot;
+      const int g = hz_g[k];
+      if (g >= 0)
+      {
+        const int ge = edgeIndex(F[g], hz_b[k], hz_a[k]);
+        if (ge >= 0)
+          F[g].adj[ge] = (int16_t)slot;
+      }
+    }
+    if (bad)
+      return 1;
+    for (int i = 0; i < nnew; ++i)
+      for (int j = 0; j < nnew; ++j)
+      {
+        Face& fi = F[stack[i]];
+        const Face& fj = F[stack[j]];
+        if (fj.v[0] == fi.v[1])
+          fi.adj[1] = stack[j];
+        if (fj.v[1] == fi.v[0])
+          fi.adj[2] = stack[j];
+      }
+    ++it_;
+    return 0;
+  }
+
+  T4_HDN bool run(const ShapeW<T>& a, const ShapeW<T>& b, const V3<T>* sw, const V3<T>* sp, int rank, int max_iter,
+                 T tol, EpaResult<T>& res)
+  {
+    res.converged = false;
+    res.iterations = 0;
+    if (!begin(a, b, sw, sp, rank, max_iter, tol))
+      return false;
+    int r;
+    while ((r = step()) == 0)
+    {
+    }
+    if (r == 2)
+      return false;
+    return finish(res);
+  }
+
+  // result after the expansion stopped
+  T4_HDN bool finish(EpaResult<T>& res)
+  {
+    res.converged = false;
+    int best = -1;
+    res.iterations = it_;
     // closest ALIVE face (after a break the stored `best` may have been freed)
     best = -1;
     for (int i = 0; i < nf_hi; ++i)

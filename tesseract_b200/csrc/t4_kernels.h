@@ -45,6 +45,7 @@ enum
   Q_SURV3,      // FIRST with records: every other survivor (looked at only if still no contact after the first two)
   Q_TASK,       // pairs handed from the GJK kernel to the EPA kernel
   Q_FETCH,      // next survivor to hand to a lane of the GJK kernel (lane-refill loop)
+  Q_FETCH_EPA,  // next EPA task to hand to a lane of the EPA kernel (lane-refill loop)
   Q_RAW,        // raw contacts (CLOSEST staging) or final contacts (ALL / FIRST)
   Q_OUT,        // final contacts emitted by the CLOSEST reduction
   Q_COUNT

@@ -540,9 +540,123 @@ T4_KD void epaBody(int64_t t, const KParams& P, EPA_T& epa)
   statAdd(P.stats, ST_GJK_ITERS, (uint32_t)d.gjk_iters);
   statAdd(P.stats, ST_EPA_PAIRS, 1u);
   statAdd(P.stats, ST_EPA_ITERS, (uint32_t)d.epa_iters);
+#ifdef T4C_DEBUG_EPA_HIST
+  fprintf(stderr, "EPAHIST %d %d %d\n", A.type, B.type, d.epa_iters);
+#endif
   PairResult<double> pr;
   copyOut(d, pr);
   emitContact(P, s, a, b, A, B, pr);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Lane-refill form of the EPA pass.  The expansion needs 7 iterations (median) for box / sphere / hull pairs but
+// 15-75 against cylinders: with one task per thread from start to end a warp lasts as long as its slowest lane.
+// Here every trip of the loop runs ONE expansion iteration per lane (Epa::step; the polytope already lives in
+// thread-local memory, so resuming costs nothing extra) and a finished lane takes the next task at once.
+// ---------------------------------------------------------------------------------------------------------------
+struct EpaLane
+{
+  uint32_t c;
+  int64_t s;
+  int a, b;
+  ShapeW<double> A, B;  // recentred
+  V3<double> offset;
+  double maxDist2;
+  bt::DetectorState<double> S;
+  bt::DetectorOut<double> d;
+};
+
+// phase 4 + statistics + result bridging of a finished task
+template <class EPA_T>
+T4_KDN void epaLaneFinish(const KParams& P, EpaLane& L, int st, const V3<double>& gv, const V3<double>& gpA, bool ok,
+                          EPA_T& epa)
+{
+  EpaResult<double> er;
+  er.iterations = 0;
+  if (ok)
+    ok = epa.finish(er);
+  bt::phase3Apply(L.A, L.B, L.S, L.d, st, gv, gpA, ok, er);
+  bt::detectPhase4(L.A, L.B, L.offset, L.maxDist2, L.S, L.d);
+  statAdd(P.stats, ST_GJK_ITERS, (uint32_t)L.d.gjk_iters);
+  statAdd(P.stats, ST_EPA_PAIRS, 1u);
+  statAdd(P.stats, ST_EPA_ITERS, (uint32_t)L.d.epa_iters);
+  PairResult<double> pr;
+  copyOut(L.d, pr);
+  if (!pr.has)
+    return;
+  if (P.cast)
+  {
+    ShapeW<double> A, B;
+    loadPairShapesD(P, L.s, L.a, L.b, A, B);
+    emitContact(P, L.s, L.a, L.b, A, B, pr);
+  }
+  else
+    emitContact(P, L.s, L.a, L.b, L.A, L.B, pr);
+}
+
+// fetch + seed the next task; true when the lane now has a polytope to expand
+template <class EPA_T>
+T4_KDN bool epaLaneFetch(const KParams& P, int64_t n, EpaLane& L, EPA_T& epa)
+{
+  for (;;)
+  {
+    const uint32_t k = qAppend(&P.qcount[Q_FETCH_EPA]);
+    if ((int64_t)k >= n)
+      return false;
+    const EpaTask& T = P.tasks[k];
+    L.c = T.cand;
+    L.s = P.cand_state[L.c];
+    if ((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit[L.s])
+      continue;
+    L.a = (int)P.cand_a[L.c], L.b = (int)P.cand_b[L.c];
+    loadPairShapesD(P, L.s, L.a, L.b, L.A, L.B);
+    L.maxDist2 = detectorMaxDist2(L.A, L.B, P.max_margin_d);
+    L.offset = bt::recentre(L.A, L.B);
+    L.S.isValid = T.is_valid;
+    L.S.status = 0;
+    L.S.distance = T.distance;
+    L.S.normalInB = V3<double>(T.normalInB[0], T.normalInB[1], T.normalInB[2]);
+    L.S.pointOnA = V3<double>(T.pointOnA[0], T.pointOnA[1], T.pointOnA[2]);
+    L.S.pointOnB = V3<double>(T.pointOnB[0], T.pointOnB[1], T.pointOnB[2]);
+    L.S.orgNormalInB = V3<double>(T.orgNormalInB[0], T.orgNormalInB[1], T.orgNormalInB[2]);
+    L.d.has = false;
+    L.d.gjk_iters = 0;
+    L.d.epa_iters = 0;
+    L.d.used_epa = true;
+    GjkOut<double, true> g;
+    const int st = bt::phase3Seed(L.A, L.B, g);
+    L.d.gjk_iters += g.iters;
+    if (st == GJK_INTERSECT && epa.begin(L.A, L.B, g.sx.W, g.sx.P, g.sx.n, 255, 1e-12))
+      return true;
+    epaLaneFinish(P, L, st, g.v, g.pA, false, epa);  // separated cores, or no enclosing tetrahedron: done already
+  }
+}
+
+// whole-kernel body: n = number of tasks in P.tasks; P.qcount[Q_FETCH_EPA] must be zero at launch
+template <class EPA_T>
+T4_KD void epaLaneLoop(const KParams& P, int64_t n, EPA_T& epa)
+{
+  EpaLane L;
+  bool have = false, more = true;
+  for (;;)
+  {
+    if (!have && more)
+    {
+      have = epaLaneFetch(P, n, L, epa);
+      more = have;
+    }
+    if (!T4_WARP_ANY(have))
+      break;
+    if (have)
+    {
+      const int r = epa.step();
+      if (r != 0)
+      {
+        epaLaneFinish(P, L, GJK_INTERSECT, V3<double>(0, 0, 0), V3<double>(0, 0, 0), r == 1, epa);
+        have = false;
+      }
+    }
+  }
 }
 
 T4_KD unsigned long long mix64(unsigned long long x)

@@ -200,7 +200,10 @@ __global__ void __launch_bounds__(256) broadActiveKernel(KParams P, int64_t n)
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     broadActiveBody(i, P);
 }
-__global__ void __launch_bounds__(256) cullKernel(KParams P, int64_t n)
+#ifndef T4_CULL_MIN_CTAS
+#define T4_CULL_MIN_CTAS 4  // 64 registers: measured 9-10 % faster than the unconstrained 128-register build (r1n)
+#endif
+__global__ void __launch_bounds__(256, T4_CULL_MIN_CTAS) cullKernel(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     cullBody(i, P);
@@ -317,7 +320,7 @@ static void launchFk(const KParams& P, int64_t n, t4stream st)
 static void launchConvert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(convertPosesKernel, PK_CONVERT, 256, 8, P, n, st); }
 static void launchBroadStatic(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadStaticKernel, PK_BROAD_STATIC, 256, 8, P, n, st); }
 static void launchBroadActive(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadActiveKernel, PK_BROAD_ACTIVE, 256, 8, P, n, st); }
-static void launchCull(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(cullKernel, PK_CULL, 256, 4, P, n, st); }
+static void launchCull(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(cullKernel, PK_CULL, 256, (T4_CULL_MIN_CTAS > 4 ? T4_CULL_MIN_CTAS : 4), P, n, st); }
 static void launchGjk(const KParams& P, int64_t n, t4stream st)
 {
   if (n <= 0)
@@ -382,8 +385,13 @@ static void launchGjk(const KParams& P, int64_t n, t4stream)
 static void launchEpa(const KParams& P, int64_t n, t4stream)
 {
   std::unique_ptr<Epa<double>> epa(new Epa<double>());
-  for (int64_t i = 0; i < n; ++i)
-    epaBody(i, P, *epa);
+  // same selection as the device build (t4c_exact.cu): task-per-thread body unless T4C_EPA_LANES=1
+  const char* e = std::getenv("T4C_EPA_LANES");
+  if (e && std::atoi(e) == 1 && n > 0)
+    epaLaneLoop(P, n, *epa);
+  else
+    for (int64_t i = 0; i < n; ++i)
+      epaBody(i, P, *epa);
   if (n > 0)
     ++g_launches;
 }
@@ -784,7 +792,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       if (nq == 0)
         continue;
       P.surv = pass == 0 ? s->d_surv.as<uint32_t>() : (pass == 1 ? s->d_surv2.as<uint32_t>() : s->d_surv3.as<uint32_t>());
-      T4_TRY(plat::zero(P.qcount + Q_TASK, 2 * sizeof(uint32_t), st), "memset");  // Q_TASK, Q_FETCH
+      T4_TRY(plat::zero(P.qcount + Q_TASK, 3 * sizeof(uint32_t), st), "memset");  // Q_TASK, Q_FETCH, Q_FETCH_EPA
       launchGjk(P, nq, st);
       T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (GJK)");
       launchEpa(P, std::min(qc[Q_TASK], P.task_cap), st);

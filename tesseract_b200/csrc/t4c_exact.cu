@@ -46,6 +46,25 @@ __global__ void __launch_bounds__(128, 4) gjkLaneKernel(KParams P, int64_t n)
   gjkLaneLoop(P, n);
 }
 
+// lane-refill EPA (t4_kernels2.h epaLaneLoop).  Measured 35-50 % SLOWER than the task-per-thread kernel on B200 (r1m:
+// the kernel is bound by local-memory latency, not by idle lanes), so it is opt-in: T4C_EPA_LANES=1.
+__global__ void __launch_bounds__(128, 4) epaLaneKernel(KParams P, int64_t n)
+{
+  Epa<double> epa;
+  epaLaneLoop(P, n, epa);
+}
+
+static int epaLanes()
+{
+  static int v = -1;
+  if (v < 0)
+  {
+    const char* e = std::getenv("T4C_EPA_LANES");
+    v = (e && std::atoi(e) == 1) ? 1 : 0;
+  }
+  return v;
+}
+
 static int gjkLanes()
 {
   static int v = -1;
@@ -116,7 +135,9 @@ void t4LaunchGjk(const KParams& P, int64_t n, int grid, cudaStream_t st)
 
 void t4LaunchEpa(const KParams& P, int64_t n, int grid, cudaStream_t st)
 {
-  if (exactRegs() == 128)
+  if (epaLanes())
+    epaLaneKernel<<<grid, 128, 0, st>>>(P, n);
+  else if (exactRegs() == 128)
     epaKernelR128<<<grid, 128, 0, st>>>(P, n);
   else
     epaKernel<<<grid, 128, 0, st>>>(P, n);

@@ -52,5 +52,6 @@ def test_fk(robot):
 def test_lane_refill_state_machine(monkeypatch):
     """the opt-in lane-refill form of the exact GJK pass (t4_kernels2.h gjkLaneLoop) gives the same contacts"""
     monkeypatch.setenv("T4C_GJK_LANES", "1")
+    monkeypatch.setenv("T4C_EPA_LANES", "1")
     print(pc.discrete_config2(mk, 300, 10000, capi.TEST_CLOSEST))
     print(pc.cast_config3(mk, 4, 10, 10000))
