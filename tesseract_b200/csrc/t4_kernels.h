@@ -129,6 +129,7 @@ struct KParams
   uint32_t* surv3_w;
   uint32_t* cull_claim;  // [n] FIRST with records: bit 0 = has its certain separated pair, bit 1 = its certain penetrating pair
   EpaTask* tasks;
+  const uint32_t* task_order;  // EPA tasks sorted by shape-type pair (null: queue order)
   uint32_t task_cap;
   uint32_t* qcount;       // [Q_COUNT]
   unsigned long long* stats;  // [ST_COUNT]

@@ -511,7 +511,7 @@ T4_KD void gjkLaneLoop(const KParams& P, int64_t n)
 template <class EPA_T>
 T4_KD void epaBody(int64_t t, const KParams& P, EPA_T& epa)
 {
-  const EpaTask& T = P.tasks[t];
+  const EpaTask& T = P.tasks[P.task_order ? P.task_order[t] : (uint32_t)t];
   const uint32_t c = T.cand;
   const int64_t s = P.cand_state[c];
   if ((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit[s])
@@ -603,7 +603,7 @@ T4_KDN bool epaLaneFetch(const KParams& P, int64_t n, EpaLane& L, EPA_T& epa)
     const uint32_t k = qAppend(&P.qcount[Q_FETCH_EPA]);
     if ((int64_t)k >= n)
       return false;
-    const EpaTask& T = P.tasks[k];
+    const EpaTask& T = P.tasks[P.task_order ? P.task_order[k] : k];
     L.c = T.cand;
     L.s = P.cand_state[L.c];
     if ((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit[L.s])

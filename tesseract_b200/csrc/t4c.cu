@@ -21,6 +21,7 @@
 
 #ifndef T4C_HOSTSIM
 #include <cuda_runtime.h>
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #endif
 
@@ -226,6 +227,23 @@ __global__ void __launch_bounds__(256) countHitKernel(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     statAdd(P.stats, ST_COLLIDING, P.hit[i] ? 1u : 0u);
+}
+// sort key of a queued pair: (type of shape A, type of shape B).  Sorting the survivor / EPA task queues by it puts
+// pairs that take the same branches of the support mapping (and similar iteration counts: EPA needs ~7 iterations
+// against boxes and spheres, 15-75 against cylinders) into the same warps.
+__global__ void __launch_bounds__(256) typeKeyKernel(KParams P, const uint32_t* queue, int from_tasks, uint8_t* keys,
+                                                    uint32_t* idx, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+  {
+    const uint32_t c = from_tasks ? P.tasks[i].cand : queue[i];
+    // major: type of B (the environment primitive in robot-vs-environment pairs), then type of A, then which shape A is
+    // (same hull vertices / support table inside a warp)
+    const uint32_t a = P.cand_a[c];
+    keys[i] = (uint8_t)(((P.shapes[P.cand_b[c]].type & 7) << 5) | ((P.shapes[a].type & 3) << 3) | (a & 7u));
+    if (from_tasks)
+      idx[i] = (uint32_t)i;
+  }
 }
 __global__ void fmaPeakKernel(float* out, int iters)
 {
@@ -436,6 +454,7 @@ struct t4c_scene
   DevBuf d_qcount, d_stats, d_hit, d_claim, d_raw, d_raw_local, d_ht_rep, d_ht_best;
   DevBuf d_out, d_out_local, d_fk_out, d_hit_full;
   DevBuf d_traj, d_lvs_counts, d_lvs_offsets, d_lvs_tmp;
+  DevBuf d_sort_keys, d_sort_keys2, d_sort_vals, d_sort_idx, d_sort_tmp;
   uint32_t cand_cap = 0;
   std::unordered_map<const t4c_fk_model*, std::unique_ptr<FkCache>> fk;
 
@@ -625,6 +644,44 @@ static uint32_t nextPow2(uint64_t x)
       return fail(T4C_ERR_CUDA, "%s: %s", what, plat::lastError());                                                    \
   } while (0)
 
+#ifndef T4C_HOSTSIM
+static int sortQueues()
+{
+  static int v = -1;
+  if (v < 0)
+  {
+    const char* e = std::getenv("T4C_SORT_QUEUES");
+    v = (e && std::atoi(e) == 0) ? 0 : 1;
+  }
+  return v;
+}
+// stable radix sort of a queue of n pairs by shape-type key; returns the sorted values (candidate indices when
+// from_tasks == 0, task indices otherwise) or null when sorting is off / not worthwhile
+static const uint32_t* sortByType(t4c_scene* s, const KParams& P, const uint32_t* queue, int from_tasks, uint32_t n)
+{
+  if (!sortQueues() || n < 4096)
+    return nullptr;
+  t4stream st = s->stream;
+  if (!(s->d_sort_keys.ensure(n) && s->d_sort_keys2.ensure(n) && s->d_sort_vals.ensure((size_t)n * 4) &&
+        s->d_sort_idx.ensure((size_t)n * 4)))
+    return nullptr;
+  typeKeyKernel<<<gridFor(n, 256, 8), 256, 0, st>>>(P, queue, from_tasks, s->d_sort_keys.as<uint8_t>(),
+                                                    s->d_sort_idx.as<uint32_t>(), (int64_t)n);
+  ++g_launches;
+  const uint32_t* vals_in = from_tasks ? s->d_sort_idx.as<uint32_t>() : queue;
+  size_t tmp = 0;
+  if (cub::DeviceRadixSort::SortPairs(nullptr, tmp, s->d_sort_keys.as<uint8_t>(), s->d_sort_keys2.as<uint8_t>(), vals_in,
+                                      s->d_sort_vals.as<uint32_t>(), (int)n, 0, 8, st) != cudaSuccess ||
+      !s->d_sort_tmp.ensure(tmp) ||
+      cub::DeviceRadixSort::SortPairs(s->d_sort_tmp.p, tmp, s->d_sort_keys.as<uint8_t>(), s->d_sort_keys2.as<uint8_t>(),
+                                      vals_in, s->d_sort_vals.as<uint32_t>(), (int)n, 0, 8, st) != cudaSuccess)
+    return nullptr;
+  return s->d_sort_vals.as<uint32_t>();
+}
+#else
+static const uint32_t* sortByType(t4c_scene*, const KParams&, const uint32_t*, int, uint32_t) { return nullptr; }
+#endif
+
 static t4c_status runBatch(t4c_scene* s, BatchIO& io)
 {
   t4c_status rc = syncScene(s);
@@ -793,9 +850,14 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
         continue;
       P.surv = pass == 0 ? s->d_surv.as<uint32_t>() : (pass == 1 ? s->d_surv2.as<uint32_t>() : s->d_surv3.as<uint32_t>());
       T4_TRY(plat::zero(P.qcount + Q_TASK, 3 * sizeof(uint32_t), st), "memset");  // Q_TASK, Q_FETCH, Q_FETCH_EPA
+      P.task_order = nullptr;
+      if (const uint32_t* sorted = sortByType(s, P, P.surv, 0, nq))
+        P.surv = const_cast<uint32_t*>(sorted);
       launchGjk(P, nq, st);
       T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (GJK)");
-      launchEpa(P, std::min(qc[Q_TASK], P.task_cap), st);
+      const uint32_t ntask = std::min(qc[Q_TASK], P.task_cap);
+      P.task_order = sortByType(s, P, nullptr, 1, ntask);
+      launchEpa(P, ntask, st);
     }
     T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (EPA)");
     const uint32_t nraw = qc[Q_RAW];
