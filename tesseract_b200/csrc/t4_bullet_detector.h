@@ -55,9 +55,11 @@ T4_HD V3<T> recentre(ShapeW<T>& A, ShapeW<T>& B)
 {
   const V3<T> positionOffset = (A.x0.p + B.x0.p) * T(0.5);
   A.x0.p -= positionOffset;
-  A.x1.p -= positionOffset;
   B.x0.p -= positionOffset;
-  B.x1.p -= positionOffset;
+  if (A.cast)
+    A.x1.p -= positionOffset;
+  if (B.cast)
+    B.x1.p -= positionOffset;
   return positionOffset;
 }
 

@@ -17,8 +17,8 @@ T4_KD void loadPairShapes(const KParams& P, int64_t s, int a, int b, ShapeW<T>& 
   Xf<T> a0, a1, b0, b1;
   shapePose<T>(P, Sa, a, s, a0, a1);
   shapePose<T>(P, Sb, b, s, b0, b1);
-  A = makeShapeW<T>(Sa, P.verts, P.sup_cells, P.sup_cand, a0, a1, P.cast && Sa.alink >= 0);
-  B = makeShapeW<T>(Sb, P.verts, P.sup_cells, P.sup_cand, b0, b1, P.cast && Sb.alink >= 0);
+  makeShapeW<T>(A, Sa, P.verts, P.sup_cells, P.sup_cand, a0, a1, P.cast && Sa.alink >= 0);
+  makeShapeW<T>(B, Sb, P.verts, P.sup_cells, P.sup_cand, b0, b1, P.cast && Sb.alink >= 0);
 }
 
 T4_KD void loadPairShapesD(const KParams& P, int64_t s, int a, int b, ShapeW<double>& A, ShapeW<double>& B)
@@ -28,8 +28,8 @@ T4_KD void loadPairShapesD(const KParams& P, int64_t s, int a, int b, ShapeW<dou
   Xf<double> a0, a1, b0, b1;
   shapePoseD(P, Sa, a, s, a0, a1);
   shapePoseD(P, Sb, b, s, b0, b1);
-  A = makeShapeW<double>(Sa, P.verts, P.sup_cells, P.sup_cand, a0, a1, P.cast && Sa.alink >= 0);
-  B = makeShapeW<double>(Sb, P.verts, P.sup_cells, P.sup_cand, b0, b1, P.cast && Sb.alink >= 0);
+  makeShapeW<double>(A, Sa, P.verts, P.sup_cells, P.sup_cand, a0, a1, P.cast && Sa.alink >= 0);
+  makeShapeW<double>(B, Sb, P.verts, P.sup_cells, P.sup_cand, b0, b1, P.cast && Sb.alink >= 0);
   // FP64 shape parameters (the FP32 record is only good for culling)
   const double* pa = P.shape_d + (size_t)a * 16;
   const double* pb = P.shape_d + (size_t)b * 16;
@@ -91,9 +91,11 @@ T4_KD void cullBody(int64_t c, const KParams& P)
   const V3<float> axis0 = A.x0.p - B.x0.p;
   const V3<float> offset = (A.x0.p + B.x0.p) * 0.5f;
   A.x0.p -= offset;
-  A.x1.p -= offset;
   B.x0.p -= offset;
-  B.x1.p -= offset;
+  if (A.cast)
+    A.x1.p -= offset;
+  if (B.cast)
+    B.x1.p -= offset;
   const float msum = A.margin() + B.margin();
   const float cutoff = msum + P.max_margin + T4_CULL_SLACK;
   float accept = cutoff;  // anything within the cut-off is decided by the exact pass
@@ -261,12 +263,12 @@ T4_KD void gjkBody(int64_t k, const KParams& P)
     emitContact(P, s, a, b, A, B, pr);
     return;
   }
-  ShapeW<double> Ar = A, Br = B;
-  const V3<double> offset = bt::recentre(Ar, Br);
+  // recentre in place (the world-pose copies are only needed for the continuous data of cast contacts: reloaded there)
   const double maxDist2 = detectorMaxDist2(A, B, P.max_margin_d);
+  const V3<double> offset = bt::recentre(A, B);
   bt::DetectorState<double> S;
   bt::DetectorOut<double> d;
-  const int r = bt::detectPhase12(Ar, Br, offset, maxDist2, P.calc_pen != 0, P.calc_dist != 0, S, d);
+  const int r = bt::detectPhase12(A, B, offset, maxDist2, P.calc_pen != 0, P.calc_dist != 0, S, d);
   statAdd(P.stats, ST_GJK_ITERS, (uint32_t)d.gjk_iters);
   if (r == bt::DET_PHASE3)
   {
@@ -285,8 +287,12 @@ T4_KD void gjkBody(int64_t k, const KParams& P)
     return;
   }
   if (r == bt::DET_PHASE4)
-    bt::detectPhase4(Ar, Br, offset, maxDist2, S, d);
+    bt::detectPhase4(A, B, offset, maxDist2, S, d);
   copyOut(d, pr);
+  if (!pr.has)
+    return;
+  if (P.cast)
+    loadPairShapesD(P, s, a, b, A, B);
   emitContact(P, s, a, b, A, B, pr);
 }
 
@@ -519,9 +525,8 @@ T4_KD void epaBody(int64_t t, const KParams& P, EPA_T& epa)
   const int a = (int)P.cand_a[c], b = (int)P.cand_b[c];
   ShapeW<double> A, B;
   loadPairShapesD(P, s, a, b, A, B);
-  ShapeW<double> Ar = A, Br = B;
-  const V3<double> offset = bt::recentre(Ar, Br);
   const double maxDist2 = detectorMaxDist2(A, B, P.max_margin_d);
+  const V3<double> offset = bt::recentre(A, B);
   bt::DetectorState<double> S;
   S.isValid = T.is_valid;
   S.status = 0;
@@ -535,8 +540,8 @@ T4_KD void epaBody(int64_t t, const KParams& P, EPA_T& epa)
   d.gjk_iters = 0;
   d.epa_iters = 0;
   d.used_epa = false;
-  bt::detectPhase3(Ar, Br, S, d, epa);
-  bt::detectPhase4(Ar, Br, offset, maxDist2, S, d);
+  bt::detectPhase3(A, B, S, d, epa);
+  bt::detectPhase4(A, B, offset, maxDist2, S, d);
   statAdd(P.stats, ST_GJK_ITERS, (uint32_t)d.gjk_iters);
   statAdd(P.stats, ST_EPA_PAIRS, 1u);
   statAdd(P.stats, ST_EPA_ITERS, (uint32_t)d.epa_iters);
@@ -545,6 +550,10 @@ T4_KD void epaBody(int64_t t, const KParams& P, EPA_T& epa)
 #endif
   PairResult<double> pr;
   copyOut(d, pr);
+  if (!pr.has)
+    return;
+  if (P.cast)
+    loadPairShapesD(P, s, a, b, A, B);
   emitContact(P, s, a, b, A, B, pr);
 }
 

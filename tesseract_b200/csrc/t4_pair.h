@@ -34,10 +34,9 @@ struct PairResult
 };
 
 template <class T>
-T4_HD ShapeW<T> makeShapeW(const DShape& s, const f4* verts, const uint32_t* sup_cells, const uint16_t* sup_cand,
-                            const Xf<T>& x0, const Xf<T>& x1, bool cast)
+T4_HD void makeShapeW(ShapeW<T>& w, const DShape& s, const f4* verts, const uint32_t* sup_cells,
+                      const uint16_t* sup_cand, const Xf<T>& x0, const Xf<T>& x1, bool cast)
 {
-  ShapeW<T> w;
   w.type = s.type;
   w.r = 0, w.h = 0;
   w.nv = 0;
@@ -70,13 +69,11 @@ T4_HD ShapeW<T> makeShapeW(const DShape& s, const f4* verts, const uint32_t* sup
   }
   w.cast = cast;
   w.x0 = x0;
-  w.x1 = x1;
-  if (cast)
+  if (cast)  // x1 / t01 are only read for swept shapes: discrete queries never touch (or store) them
   {
     w.t01 = x0.invTimes(x1);
     w.x1 = x0 * w.t01;  // tfWorld1 as the reference forms it (bullet_utils.h:466)
   }
-  return w;
 }
 
 // ---- capsule x capsule|sphere (tesseract_convex_convex_algorithm.cpp:67-181) -------------------------------------

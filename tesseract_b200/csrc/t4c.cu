@@ -1474,8 +1474,10 @@ t4c_status t4c_debug_hull_support(t4c_scene* s, int32_t shape, const double* dir
     return fail(T4C_ERR_INVALID, "shape %d is not a hull", shape);
   Xf<double> I;
   Xf<float> If;
-  ShapeW<double> t64 = makeShapeW<double>(D, C.verts.data(), C.sup_cells.data(), C.sup_cand.data(), I, I, false);
-  ShapeW<float> t32 = makeShapeW<float>(D, C.verts.data(), C.sup_cells.data(), C.sup_cand.data(), If, If, false);
+  ShapeW<double> t64;
+  ShapeW<float> t32;
+  makeShapeW<double>(t64, D, C.verts.data(), C.sup_cells.data(), C.sup_cand.data(), I, I, false);
+  makeShapeW<float>(t32, D, C.verts.data(), C.sup_cells.data(), C.sup_cand.data(), If, If, false);
   ShapeW<double> b64 = t64;
   ShapeW<float> b32 = t32;
   b64.sup_cells = nullptr, b32.sup_cells = nullptr;
