@@ -117,11 +117,13 @@ struct KParams
   int32_t cast;
   // ---- request
   int32_t test_type, calc_pen, calc_dist, hit_only;
+  int32_t skip_hit;  // FIRST in rounds: states that already have a contact take no further part (ContactTestData::done)
   // ---- queues / outputs
   uint32_t* cand_state;
   uint32_t* cand_a;
   uint32_t* cand_b;
   uint32_t cand_cap;
+  uint32_t cull_base;  // first candidate of the range the cull kernel works on (FIRST in rounds: candidates append)
   uint32_t* surv;      // queue read by the GJK kernel in this launch
   uint32_t surv_cap;
   uint32_t* surv_w;    // queues written by the cull kernel
@@ -505,6 +507,8 @@ T4_KD void broadStaticBody(int64_t item, const KParams& P)
 {
   const int a_ord = (int)(item / P.n);
   const int64_t s = item - (int64_t)a_ord * P.n;
+  if (P.skip_hit && P.hit[s])
+    return;
   const int sh = P.active_shapes[a_ord];
   const DShape& S = P.shapes[sh];
   Xf<float> x0, x1;
@@ -692,6 +696,8 @@ T4_KD void broadActiveBody(int64_t item, const KParams& P)
 {
   const int pr = (int)(item / P.n);
   const int64_t s = item - (int64_t)pr * P.n;
+  if (P.skip_hit && P.hit[s])
+    return;
   const int a = P.aa_pairs[2 * pr], b = P.aa_pairs[2 * pr + 1];
   const DShape& Sa = P.shapes[a];
   const DShape& Sb = P.shapes[b];

@@ -74,8 +74,9 @@ T4_KD void pushSurvivor(const KParams& P, uint32_t c, int tier)
 //     third; the later queues are only looked at for states that are still without a contact afterwards
 //     (ContactTestData::done semantics, core/common.h:129-133).
 // Everything that is reported goes through the exact FP64 pass.
-T4_KD void cullBody(int64_t c, const KParams& P)
+T4_KD void cullBody(int64_t item, const KParams& P)
 {
+  const int64_t c = item + (int64_t)P.cull_base;
   const int64_t s = P.cand_state[c];
   const bool first_rec = P.test_type == T4C_TEST_FIRST && !P.hit_only;
   if (P.hit_only && P.hit[s])

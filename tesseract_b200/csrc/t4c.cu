@@ -144,12 +144,40 @@ struct DevBuf
     cap = want;
     return true;
   }
+  // grow to at least `bytes`, preserving the first `keep` bytes (queues that are appended to across launches)
+  bool ensureKeep(size_t bytes, size_t keep, t4stream st);
   template <class T>
   T* as() const
   {
     return reinterpret_cast<T*>(p);
   }
 };
+
+
+bool DevBuf::ensureKeep(size_t bytes, size_t keep, t4stream st)
+{
+  if (bytes <= cap)
+    return true;
+  const size_t want = bytes + bytes / 8 + 256;
+  void* q = plat::alloc(want);
+  if (!q)
+    return false;
+  bool ok = true;
+  if (p && keep)
+  {
+#ifdef T4C_HOSTSIM
+    std::memcpy(q, p, std::min(keep, cap));
+#else
+    ok = plat::chk(cudaMemcpyAsync(q, p, std::min(keep, cap), cudaMemcpyDeviceToDevice, st)) && plat::sync(st);
+#endif
+  }
+  (void)st;
+  if (p)
+    plat::release(p);
+  p = q;
+  cap = want;
+  return ok;
+}
 
 template <class T>
 static bool upload(DevBuf& b, const std::vector<T>& v, t4stream st)
@@ -625,6 +653,13 @@ struct BatchIO
   t4c_stats stats{};
 };
 
+// FIRST queries of at least this many states (per chunk) run in rounds over the robot's shapes (runBatch)
+static int64_t roundMinStates()
+{
+  const char* e = std::getenv("T4C_ROUND_MIN_STATES");
+  return e ? std::max<long long>(1, std::atoll(e)) : 16384;
+}
+
 static int64_t chunkStates()
 {
   static int64_t v = 0;
@@ -773,73 +808,144 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       P.first_claim = s->d_claim.as<uint32_t>();
       T4_TRY(plat::zero(P.first_claim, (size_t)nc * sizeof(uint32_t), st), "memset");
     }
-    // ---- broadphase (retried with a larger queue when it overflows)
+    // ---- FIRST queries run in ROUNDS over the robot's shapes: broadphase + cull + exact pass for one slice of the
+    //      active shapes at a time, and states that already have a contact take no part in the later rounds.  This
+    //      is the reference's early exit (ContactTestData::done, core/common.h:129-133: Bullet stops dispatching
+    //      pairs once the first contact is stored) applied per state across the batch.
     uint32_t qc[Q_COUNT];
+    const bool first_rec = io.req.type == T4C_TEST_FIRST && io.contacts;
+    const bool closest = io.req.type == T4C_TEST_CLOSEST && io.contacts;
+    const int64_t room = std::max<int64_t>(0, io.capacity - total);
+    const int32_t* all_active = P.active_shapes;
+    const int n_all_active = P.n_active_shapes, n_all_aa = P.n_aa_pairs;
+    int n_rounds = 1;
+    if (io.req.type == T4C_TEST_FIRST && nc >= roundMinStates() && n_all_active > 1 && P.n_bvh_nodes > 0)
+      n_rounds = std::min(n_all_active, 8);
+    P.skip_hit = n_rounds > 1 ? 1 : 0;
+    // Candidates APPEND across the rounds (survivor queues hold candidate indices).  Per round only the first tier of
+    // survivors is resolved: pairs that are certainly in contact without penetrating -- one cheap GJK each.  The
+    // other tiers (one certainly penetrating pair per state, then the rest) accumulate and are resolved after the
+    // last round, for the states that are still without a contact: EPA runs at most once per such state.
     if (s->cand_cap == 0)
       s->cand_cap = (uint32_t)std::min<int64_t>(std::max<int64_t>(1 << 16, 24 * nc), 1ll << 30);
-    for (int attempt = 0;; ++attempt)
-    {
-      const size_t cb = (size_t)s->cand_cap * sizeof(uint32_t);
-      T4_TRY(s->d_cand_state.ensure(cb) && s->d_cand_a.ensure(cb) && s->d_cand_b.ensure(cb), "candidate queue");
-      P.cand_state = s->d_cand_state.as<uint32_t>();
-      P.cand_a = s->d_cand_a.as<uint32_t>();
-      P.cand_b = s->d_cand_b.as<uint32_t>();
-      P.cand_cap = s->cand_cap;
-      T4_TRY(plat::zero(P.qcount, Q_COUNT * sizeof(uint32_t), st), "memset");
-      if (P.n_bvh_nodes > 0)
-      {
-        // T4C_BROAD_GROUP=1: grouped traversal (one BVH walk per state and group of 8 robot shapes).  It visits 3.4x
-        // fewer nodes but measured 19 % SLOWER on B200 (r1r: 121 registers, 7x fewer threads in flight), and its
-        // state-major candidate order doubles the cull time of flags-only queries: opt-in only.
-        static const int grouped = [] {
-          const char* e = std::getenv("T4C_BROAD_GROUP");
-          return (e && std::atoi(e) == 1) ? 1 : 0;
-        }();
-        if (grouped)
-          launchBroadStaticGroup(P, nc * (int64_t)((P.n_active_shapes + T4_BROAD_GROUP - 1) / T4_BROAD_GROUP), st);
-        else
-          launchBroadStatic(P, nc * (int64_t)P.n_active_shapes, st);
-      }
-      launchBroadActive(P, nc * (int64_t)P.n_aa_pairs, st);
-      T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "broadphase");
-      if (qc[Q_CAND] <= s->cand_cap)
-        break;
-      if (attempt >= 2)
-        return fail(T4C_ERR_NOMEM, "candidate queue overflow (%u pairs)", qc[Q_CAND]);
-      s->cand_cap = (uint32_t)std::min<uint64_t>((uint64_t)qc[Q_CAND] + qc[Q_CAND] / 8 + 1024, 0xfffffff0ull);
-      T4_TRY(plat::h2d(P.stats, stats_host, sizeof(stats_host), st), "stats restore");
-    }
-    const uint32_t ncand = qc[Q_CAND];
-    // ---- FP32 cull
-    const bool first_rec = io.req.type == T4C_TEST_FIRST && io.contacts;
-    T4_TRY(s->d_surv.ensure(std::max<size_t>(ncand, 1) * sizeof(uint32_t)), "survivor queue");
-    P.surv_w = s->d_surv.as<uint32_t>();
+    T4_TRY(plat::zero(P.qcount, Q_COUNT * sizeof(uint32_t), st), "memset");
     P.surv2_w = nullptr;
     P.surv3_w = nullptr;
     P.cull_claim = nullptr;
     if (first_rec)
     {
-      T4_TRY(s->d_surv2.ensure(std::max<size_t>(ncand, 1) * sizeof(uint32_t)) &&
-                 s->d_surv3.ensure(std::max<size_t>(ncand, 1) * sizeof(uint32_t)) &&
-                 s->d_cull_claim.ensure((size_t)nc * sizeof(uint32_t)) &&
+      T4_TRY(s->d_cull_claim.ensure((size_t)nc * sizeof(uint32_t)) &&
                  plat::zero(s->d_cull_claim.p, (size_t)nc * sizeof(uint32_t), st),
              "survivor queue");
-      P.surv2_w = s->d_surv2.as<uint32_t>();
-      P.surv3_w = s->d_surv3.as<uint32_t>();
       P.cull_claim = s->d_cull_claim.as<uint32_t>();
     }
-    P.surv_cap = ncand;
-    launchCull(P, ncand, st);
-    T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "cull");
-    const uint32_t nsurv = qc[Q_SURV], nsurv2 = qc[Q_SURV2], nsurv3 = qc[Q_SURV3];
-    // ---- FP64 exact pass: GJK kernel (phases 1-2) -> task queue -> EPA kernel (phases 3-4)
-    const bool closest = io.req.type == T4C_TEST_CLOSEST && io.contacts;
-    const int64_t room = std::max<int64_t>(0, io.capacity - total);
     P.raw = nullptr;
     P.raw_local = nullptr;
     P.raw_cap = 0;
-    if (io.contacts)
+    if (io.contacts && !closest)
     {
+      P.raw = io.contacts + std::min<int64_t>(total, io.capacity);
+      P.raw_cap = (uint32_t)std::min<int64_t>(room, 0xfffffff0ll);
+      P.raw_local = (io.cast && io.cc_local) ? io.cc_local + (size_t)std::min<int64_t>(total, io.capacity) * 6 : nullptr;
+    }
+    uint32_t cand_begin = 0, nsurv2 = 0, nsurv3 = 0;
+    auto bindQueues = [&]() -> bool {
+      const size_t cb = (size_t)s->cand_cap * sizeof(uint32_t), keep = (size_t)cand_begin * sizeof(uint32_t);
+      if (!(s->d_cand_state.ensureKeep(cb, keep, st) && s->d_cand_a.ensureKeep(cb, keep, st) &&
+            s->d_cand_b.ensureKeep(cb, keep, st) && s->d_surv.ensure(cb)))
+        return false;
+      if (first_rec && !(s->d_surv2.ensureKeep(cb, keep, st) && s->d_surv3.ensureKeep(cb, keep, st)))
+        return false;
+      P.cand_state = s->d_cand_state.as<uint32_t>();
+      P.cand_a = s->d_cand_a.as<uint32_t>();
+      P.cand_b = s->d_cand_b.as<uint32_t>();
+      P.cand_cap = s->cand_cap;
+      P.surv_w = s->d_surv.as<uint32_t>();
+      P.surv_cap = s->cand_cap;
+      if (first_rec)
+      {
+        P.surv2_w = s->d_surv2.as<uint32_t>();
+        P.surv3_w = s->d_surv3.as<uint32_t>();
+      }
+      return true;
+    };
+    // one exact pass over a survivor queue: GJK kernel -> EPA task queue [-> EPA kernel].  With run_epa == false the
+    // tasks stay queued (and the next pass appends to them): a launch of a few hundred EPA tasks lasts as long as its
+    // slowest task, so the rounds share ONE EPA launch instead of paying that tail once per round.
+    uint32_t ntask_pending = 0;
+    auto exactPass = [&](uint32_t* queue, uint32_t nq, bool run_epa) -> t4c_status {
+      if (nq > 0)
+      {
+        T4_TRY(s->d_tasks.ensureKeep(((size_t)ntask_pending + nq) * sizeof(EpaTask),
+                                     (size_t)ntask_pending * sizeof(EpaTask), st),
+               "EPA task queue");
+        P.tasks = s->d_tasks.as<EpaTask>();
+        P.task_cap = ntask_pending + nq;
+        P.surv = queue;
+        T4_TRY(plat::zero(P.qcount + Q_FETCH, 2 * sizeof(uint32_t), st), "memset");  // Q_FETCH, Q_FETCH_EPA
+        P.task_order = nullptr;
+        if (const uint32_t* sorted = sortByType(s, P, P.surv, 0, nq))
+          P.surv = const_cast<uint32_t*>(sorted);
+        launchGjk(P, nq, st);
+        T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (GJK)");
+        ntask_pending = std::min(qc[Q_TASK], P.task_cap);
+      }
+      if (run_epa && ntask_pending > 0)
+      {
+        P.task_order = sortByType(s, P, nullptr, 1, ntask_pending);
+        launchEpa(P, ntask_pending, st);
+        ntask_pending = 0;
+        T4_TRY(plat::zero(P.qcount + Q_TASK, sizeof(uint32_t), st), "memset");
+      }
+      return T4C_OK;
+    };
+    for (int round = 0; round < n_rounds; ++round)
+    {
+      // slices from the far end of the kinematic chain first (distal links sweep the largest volume)
+      const int lo = (int)((int64_t)n_all_active * (n_rounds - 1 - round) / n_rounds);
+      const int hi = (int)((int64_t)n_all_active * (n_rounds - round) / n_rounds);
+      P.active_shapes = all_active + lo;
+      P.n_active_shapes = hi - lo;
+      P.n_aa_pairs = round == 0 ? n_all_aa : 0;
+      // ---- broadphase (retried with a larger queue when it overflows)
+      for (int attempt = 0;; ++attempt)
+      {
+        T4_TRY(bindQueues(), "candidate queue");
+        if (P.n_bvh_nodes > 0)
+        {
+          // T4C_BROAD_GROUP=1: grouped traversal (one BVH walk per state and group of 8 robot shapes).  It visits 3.4x
+          // fewer nodes but measured 19 % SLOWER on B200 (r1r: 121 registers, 7x fewer threads in flight), and its
+          // state-major candidate order doubles the cull time of flags-only queries: opt-in only.
+          static const int grouped = [] {
+            const char* e = std::getenv("T4C_BROAD_GROUP");
+            return (e && std::atoi(e) == 1) ? 1 : 0;
+          }();
+          if (grouped)
+            launchBroadStaticGroup(P, nc * (int64_t)((P.n_active_shapes + T4_BROAD_GROUP - 1) / T4_BROAD_GROUP), st);
+          else
+            launchBroadStatic(P, nc * (int64_t)P.n_active_shapes, st);
+        }
+        launchBroadActive(P, nc * (int64_t)P.n_aa_pairs, st);
+        T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "broadphase");
+        if (qc[Q_CAND] <= s->cand_cap)
+          break;
+        if (attempt >= 2)
+          return fail(T4C_ERR_NOMEM, "candidate queue overflow (%u pairs)", qc[Q_CAND]);
+        // grow (keeping the candidates of the earlier rounds), rewind the append counter to this round's start and
+        // run the round's broadphase again; the statistics counters count the repeated traversal twice
+        s->cand_cap = (uint32_t)std::min<uint64_t>((uint64_t)qc[Q_CAND] + qc[Q_CAND] / 8 + 1024, 0xfffffff0ull);
+        T4_TRY(plat::h2d(P.qcount + Q_CAND, &cand_begin, sizeof(uint32_t), st) && plat::sync(st), "queue rewind");
+      }
+      const uint32_t ncand = qc[Q_CAND];
+      // ---- FP32 cull of this round's candidates
+      T4_TRY(plat::zero(P.qcount + Q_SURV, sizeof(uint32_t), st), "memset");
+      P.cull_base = cand_begin;
+      launchCull(P, ncand - cand_begin, st);
+      T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "cull");
+      cand_begin = ncand;
+      const uint32_t nsurv = qc[Q_SURV];
+      nsurv2 = qc[Q_SURV2], nsurv3 = qc[Q_SURV3];
+      // ---- FP64 exact pass over the first tier
       if (closest)
       {
         T4_TRY(s->d_raw.ensure(std::max<size_t>(nsurv, 1) * sizeof(t4c_contact)), "contact staging");
@@ -851,33 +957,20 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
           P.raw_local = s->d_raw_local.as<float>();
         }
       }
-      else
-      {
-        P.raw = io.contacts + std::min<int64_t>(total, io.capacity);
-        P.raw_cap = (uint32_t)std::min<int64_t>(room, 0xfffffff0ll);
-        P.raw_local = (io.cast && io.cc_local) ? io.cc_local + (size_t)std::min<int64_t>(total, io.capacity) * 6 : nullptr;
-      }
+      rc = exactPass(s->d_surv.as<uint32_t>(), nsurv, round == n_rounds - 1);
+      if (rc != T4C_OK)
+        return rc;
     }
-    const uint32_t nsurv_max = std::max(nsurv, std::max(nsurv2, nsurv3));
-    T4_TRY(s->d_tasks.ensure(std::max<size_t>(nsurv_max, 1) * sizeof(EpaTask)), "EPA task queue");
-    P.tasks = s->d_tasks.as<EpaTask>();
-    P.task_cap = nsurv_max;
-    for (int pass = 0; pass < 3; ++pass)
-    {
-      const uint32_t nq = pass == 0 ? nsurv : (pass == 1 ? nsurv2 : nsurv3);
-      if (nq == 0)
-        continue;
-      P.surv = pass == 0 ? s->d_surv.as<uint32_t>() : (pass == 1 ? s->d_surv2.as<uint32_t>() : s->d_surv3.as<uint32_t>());
-      T4_TRY(plat::zero(P.qcount + Q_TASK, 3 * sizeof(uint32_t), st), "memset");  // Q_TASK, Q_FETCH, Q_FETCH_EPA
-      P.task_order = nullptr;
-      if (const uint32_t* sorted = sortByType(s, P, P.surv, 0, nq))
-        P.surv = const_cast<uint32_t*>(sorted);
-      launchGjk(P, nq, st);
-      T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (GJK)");
-      const uint32_t ntask = std::min(qc[Q_TASK], P.task_cap);
-      P.task_order = sortByType(s, P, nullptr, 1, ntask);
-      launchEpa(P, ntask, st);
-    }
+    // ---- deferred tiers, for the states that are still without a contact
+    rc = exactPass(s->d_surv2.as<uint32_t>(), nsurv2, true);
+    if (rc != T4C_OK)
+      return rc;
+    rc = exactPass(s->d_surv3.as<uint32_t>(), nsurv3, true);
+    if (rc != T4C_OK)
+      return rc;
+    P.active_shapes = all_active;
+    P.n_active_shapes = n_all_active;
+    P.n_aa_pairs = n_all_aa;
     T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (EPA)");
     const uint32_t nraw = qc[Q_RAW];
     if (closest)

@@ -67,3 +67,19 @@ def test_grouped_broadphase(monkeypatch):
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+def test_first_in_rounds():
+    """FIRST queries in rounds over the robot's shapes (t4c.cu runBatch; on by default for >= 16384 states): same
+    flags, one record per colliding state, each record a contact the oracle also reports"""
+    import subprocess, sys, os
+    code = ("import sys; sys.path.insert(0, 'tests'); import parity_cases as pc; from hostsim import build as h; "
+            "from tesseract_b200.managers import BatchChecker; from tesseract_b200 import capi; "
+            "mk = lambda b: BatchChecker(b, lib=h.lib()); "
+            "print(pc.discrete_config2(mk, 400, 10000, capi.TEST_FIRST)); "
+            "print(pc.flags_only(mk, 600, 10000)); "
+            "print(pc.flags_only(mk, 600, 10000, margin=0.0, pen=False, dist=False))")
+    env = dict(os.environ, T4C_ROUND_MIN_STATES="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout + r.stderr
