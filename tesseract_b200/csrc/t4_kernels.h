@@ -42,7 +42,8 @@ enum
   Q_CAND = 0,   // candidate pairs appended by the broadphase
   Q_SURV,       // survivors of the FP32 cull (FIRST with records: one certain contact per state)
   Q_SURV2,      // FIRST with records: one certainly PENETRATING pair per state (looked at only if still no contact)
-  Q_SURV3,      // FIRST with records: every other survivor (looked at only if still no contact after the first two)
+  Q_SURV3,      // FIRST with records: one certainly penetrating pair per state against a CURVED primitive (slow EPA)
+  Q_SURV4,      // FIRST with records: every other survivor (looked at only if still no contact after the others)
   Q_TASK,       // pairs handed from the GJK kernel to the EPA kernel
   Q_FETCH,      // next survivor to hand to a lane of the GJK kernel (lane-refill loop)
   Q_FETCH_EPA,  // next EPA task to hand to a lane of the EPA kernel (lane-refill loop)
@@ -129,7 +130,8 @@ struct KParams
   uint32_t* surv_w;    // queues written by the cull kernel
   uint32_t* surv2_w;
   uint32_t* surv3_w;
-  uint32_t* cull_claim;  // [n] FIRST with records: bit 0 = has its certain separated pair, bit 1 = its certain penetrating pair
+  uint32_t* surv4_w;
+  uint32_t* cull_claim;  // [n] FIRST with records: bit 0 = has its certain separated pair, bit 1 / 2 = its certain penetrating pair (flat / curved)
   EpaTask* tasks;
   const uint32_t* task_order;  // EPA tasks sorted by shape-type pair (null: queue order)
   uint32_t task_cap;

@@ -56,8 +56,8 @@ T4_KD bool analyticPair(int ta, int tb)
 
 T4_KD void pushSurvivor(const KParams& P, uint32_t c, int tier)
 {
-  uint32_t* q = tier == 0 ? P.surv_w : (tier == 1 ? P.surv2_w : P.surv3_w);
-  const uint32_t k = qAppend(&P.qcount[tier == 0 ? Q_SURV : (tier == 1 ? Q_SURV2 : Q_SURV3)]);
+  uint32_t* q = tier == 0 ? P.surv_w : (tier == 1 ? P.surv2_w : (tier == 2 ? P.surv3_w : P.surv4_w));
+  const uint32_t k = qAppend(&P.qcount[Q_SURV + tier]);
   if (k < P.surv_cap)
     q[k] = c;
 }
@@ -86,7 +86,7 @@ T4_KD void cullBody(int64_t item, const KParams& P)
   loadPairShapes<float>(P, s, a, b, A, B);
   if (!A.cast && !B.cast && analyticPair(A.type, B.type))
   {
-    pushSurvivor(P, (uint32_t)c, first_rec ? 2 : 0);
+    pushSurvivor(P, (uint32_t)c, first_rec ? 3 : 0);
     return;
   }
   const V3<float> axis0 = A.x0.p - B.x0.p;
@@ -130,15 +130,20 @@ T4_KD void cullBody(int64_t item, const KParams& P)
   }
   if (first_rec)
   {
-    // tier 0: one certainly-in-contact, separated pair per state (GJK only); tier 1: one certainly penetrating pair
-    // per state (needs EPA; only looked at when tier 0 left the state without a contact); tier 2: the rest.
+    // tier 0: one certainly-in-contact, separated pair per state (GJK only); tiers 1 / 2: one certainly penetrating
+    // pair per state (needs EPA; only looked at when the earlier tiers left the state without a contact) -- against a
+    // flat-faced or point-core shape (median 7 EPA iterations) before one against a cylinder / cone (15-75 iterations:
+    // the polytope has to approximate the curved surface); tier 3: the rest.
     const bool certain = st == GJK_NEAR && bool_mode && g.v.len2() > 1e-8f;
     const bool deep = st == GJK_INTERSECT && g.v.len2() == 0.f && P.calc_pen;
-    int tier = 2;
+    const bool curved = A.curvedCore() || B.curvedCore();
+    int tier = 3;
     if (certain && (orU32(&P.cull_claim[s], 1u) & 1u) == 0u)
       tier = 0;
-    else if (deep && (orU32(&P.cull_claim[s], 2u) & 2u) == 0u)
+    else if (deep && !curved && (orU32(&P.cull_claim[s], 2u) & 2u) == 0u)
       tier = 1;
+    else if (deep && curved && (orU32(&P.cull_claim[s], 4u) & 4u) == 0u)
+      tier = 2;
     pushSurvivor(P, (uint32_t)c, tier);
     return;
   }

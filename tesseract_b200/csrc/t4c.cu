@@ -485,7 +485,7 @@ struct t4c_scene
   DevBuf d_shapes, d_statics, d_verts, d_sup_cells, d_sup_cand, d_bvh, d_active, d_aa, d_acm, d_margin, d_shape_d, d_statics_d;
   // per-call workspace
   DevBuf d_q0, d_q1, d_pin0, d_pin1, d_poses0, d_poses1, d_poses0d, d_poses1d;
-  DevBuf d_cand_state, d_cand_a, d_cand_b, d_surv, d_surv2, d_surv3, d_cull_claim, d_tasks;
+  DevBuf d_cand_state, d_cand_a, d_cand_b, d_surv, d_surv2, d_surv3, d_surv4, d_cull_claim, d_tasks;
   DevBuf d_qcount, d_stats, d_hit, d_claim, d_raw, d_raw_local, d_ht_rep, d_ht_best;
   DevBuf d_out, d_out_local, d_fk_out, d_hit_full;
   DevBuf d_traj, d_lvs_counts, d_lvs_offsets, d_lvs_tmp;
@@ -660,6 +660,20 @@ static int64_t roundMinStates()
   return e ? std::max<long long>(1, std::atoll(e)) : 16384;
 }
 
+static int maxRounds()
+{
+  const char* e = std::getenv("T4C_ROUNDS");
+  return e ? std::max(1, std::min(64, std::atoi(e))) : 8;
+}
+// 0: last active shapes first (distal links of a serial arm), 1: first shapes first.  Measured on configs[1] (r1v):
+// flags-only queries are fastest distal-first (157 M vs 138 M states/s), queries with records proximal-first
+// (38.0 M vs 36.1 M: fewer states end up needing EPA iterations); T4C_ROUND_ORDER overrides.
+static int roundOrder(bool with_records)
+{
+  const char* e = std::getenv("T4C_ROUND_ORDER");
+  return e ? std::atoi(e) : (with_records ? 1 : 0);
+}
+
 static int64_t chunkStates()
 {
   static int64_t v = 0;
@@ -820,7 +834,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     const int n_all_active = P.n_active_shapes, n_all_aa = P.n_aa_pairs;
     int n_rounds = 1;
     if (io.req.type == T4C_TEST_FIRST && nc >= roundMinStates() && n_all_active > 1 && P.n_bvh_nodes > 0)
-      n_rounds = std::min(n_all_active, 8);
+      n_rounds = std::min(n_all_active, maxRounds());
     P.skip_hit = n_rounds > 1 ? 1 : 0;
     // Candidates APPEND across the rounds (survivor queues hold candidate indices).  Per round only the first tier of
     // survivors is resolved: pairs that are certainly in contact without penetrating -- one cheap GJK each.  The
@@ -831,6 +845,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     T4_TRY(plat::zero(P.qcount, Q_COUNT * sizeof(uint32_t), st), "memset");
     P.surv2_w = nullptr;
     P.surv3_w = nullptr;
+    P.surv4_w = nullptr;
     P.cull_claim = nullptr;
     if (first_rec)
     {
@@ -848,13 +863,14 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       P.raw_cap = (uint32_t)std::min<int64_t>(room, 0xfffffff0ll);
       P.raw_local = (io.cast && io.cc_local) ? io.cc_local + (size_t)std::min<int64_t>(total, io.capacity) * 6 : nullptr;
     }
-    uint32_t cand_begin = 0, nsurv2 = 0, nsurv3 = 0;
+    uint32_t cand_begin = 0, nsurv2 = 0, nsurv3 = 0, nsurv4 = 0;
     auto bindQueues = [&]() -> bool {
       const size_t cb = (size_t)s->cand_cap * sizeof(uint32_t), keep = (size_t)cand_begin * sizeof(uint32_t);
       if (!(s->d_cand_state.ensureKeep(cb, keep, st) && s->d_cand_a.ensureKeep(cb, keep, st) &&
             s->d_cand_b.ensureKeep(cb, keep, st) && s->d_surv.ensure(cb)))
         return false;
-      if (first_rec && !(s->d_surv2.ensureKeep(cb, keep, st) && s->d_surv3.ensureKeep(cb, keep, st)))
+      if (first_rec && !(s->d_surv2.ensureKeep(cb, keep, st) && s->d_surv3.ensureKeep(cb, keep, st) &&
+                         s->d_surv4.ensureKeep(cb, keep, st)))
         return false;
       P.cand_state = s->d_cand_state.as<uint32_t>();
       P.cand_a = s->d_cand_a.as<uint32_t>();
@@ -866,6 +882,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       {
         P.surv2_w = s->d_surv2.as<uint32_t>();
         P.surv3_w = s->d_surv3.as<uint32_t>();
+        P.surv4_w = s->d_surv4.as<uint32_t>();
       }
       return true;
     };
@@ -902,8 +919,9 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     for (int round = 0; round < n_rounds; ++round)
     {
       // slices from the far end of the kinematic chain first (distal links sweep the largest volume)
-      const int lo = (int)((int64_t)n_all_active * (n_rounds - 1 - round) / n_rounds);
-      const int hi = (int)((int64_t)n_all_active * (n_rounds - round) / n_rounds);
+      const int slice = roundOrder(first_rec) ? round : n_rounds - 1 - round;
+      const int lo = (int)((int64_t)n_all_active * slice / n_rounds);
+      const int hi = (int)((int64_t)n_all_active * (slice + 1) / n_rounds);
       P.active_shapes = all_active + lo;
       P.n_active_shapes = hi - lo;
       P.n_aa_pairs = round == 0 ? n_all_aa : 0;
@@ -944,7 +962,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "cull");
       cand_begin = ncand;
       const uint32_t nsurv = qc[Q_SURV];
-      nsurv2 = qc[Q_SURV2], nsurv3 = qc[Q_SURV3];
+      nsurv2 = qc[Q_SURV2], nsurv3 = qc[Q_SURV3], nsurv4 = qc[Q_SURV4];
       // ---- FP64 exact pass over the first tier
       if (closest)
       {
@@ -966,6 +984,9 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     if (rc != T4C_OK)
       return rc;
     rc = exactPass(s->d_surv3.as<uint32_t>(), nsurv3, true);
+    if (rc != T4C_OK)
+      return rc;
+    rc = exactPass(s->d_surv4.as<uint32_t>(), nsurv4, true);
     if (rc != T4C_OK)
       return rc;
     P.active_shapes = all_active;
