@@ -398,3 +398,32 @@ def build_config2(n_prims=10000, margin=0.05, env_seed=42):
     b.set_active(moving)
     b.set_margin(margin)
     return b
+
+
+def build_config4(octree_leaves, plane=None, margin=0.10, robot_xyz=(0.0, -2.0, 0.0), sub_type=Octree.BOX):
+    """BASELINE.json configs[3] style: ABB IRB2400 convex-hull links vs an octomap-derived voxel environment (one box
+    or sphere per occupied leaf, bullet_utils.cpp:160-243) plus a concave workcell mesh (one triangle shape per
+    face).  octree_leaves: (n, 4) centre + size; plane: optional (vertices, faces)."""
+    b = SceneBuilder()
+    root, moving = add_robot(b, load_robot("abb_irb2400"), base_pose=pose(robot_xyz))
+    b.add_collision_object("octomap", 0, [Octree(octree_leaves, sub_type)], [identity()])
+    if plane is not None:
+        b.add_collision_object("workcell", 0, [Mesh(plane[0], plane[1])], [pose((0.0, 0.0, -0.05))])
+    b.set_active(moving)
+    b.set_margin(margin)
+    return b
+
+
+def build_config5(n_prims=2000, margin=0.05, fixtures=None):
+    """BASELINE.json configs[4] style: two iiwa (bases at y = -/+0.45 m, the second yawed by pi), 14 joints, cross-arm
+    pairs enabled, optional concave fixture meshes [(name, vertices, faces, pose)], plus the config-2 primitives."""
+    b = SceneBuilder()
+    robot = load_robot("iiwa14")
+    _, m0 = add_robot(b, robot, prefix="a_", base_pose=pose((0.0, -0.45, 0.0)))
+    _, m1 = add_robot(b, robot, prefix="b_", base_pose=pose((0.0, 0.45, 0.0), rot_z(math.pi)))
+    for name, v, f, P in fixtures or []:
+        b.add_collision_object(name, 0, [Mesh(v, f)], [identity()], pose_=P)
+    random_environment(b, n_prims, 42, keepout=0.8)
+    b.set_active(m0 + m1)
+    b.set_margin(margin)
+    return b

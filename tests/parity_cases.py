@@ -139,6 +139,52 @@ def discrete_lvs(make_checker, n_traj, n_wp, n_prims, lvs=0.05, threads=4):
     return flip_statistics(b, con_g, con_o, hit_g, hit_o, 0.05)
 
 
+def _lbracket(seed):
+    """small concave fixture: an L-bracket as a closed triangle mesh (two boxes sharing a face)"""
+    rng = np.random.default_rng(seed)
+    a, t, w = rng.uniform(0.15, 0.3), rng.uniform(0.02, 0.04), rng.uniform(0.1, 0.2)
+    boxes = [((0, 0, 0), (a, w, t)), ((0, 0, 0), (t, w, a))]
+    V, F = [], []
+    for (x0, y0, z0), (dx, dy, dz) in boxes:
+        o = len(V)
+        V += [(x0 + i * dx, y0 + j * dy, z0 + k * dz) for i in (0, 1) for j in (0, 1) for k in (0, 1)]
+        quads = [(0, 1, 3, 2), (4, 6, 7, 5), (0, 4, 5, 1), (2, 3, 7, 6), (0, 2, 6, 4), (1, 5, 7, 3)]
+        for q in quads:
+            F += [(o + q[0], o + q[1], o + q[2]), (o + q[0], o + q[2], o + q[3])]
+    return np.array(V, dtype=np.float64), np.array(F, dtype=np.int64)
+
+
+def config4_voxels(make_checker, leaves, plane, n_states, threads=4, test_type=capi.TEST_CLOSEST):
+    """configs[3]: ABB hull links vs voxels + concave mesh, distance queries at margin 0.10 (FK bypass: exact poses)"""
+    b = S.build_config4(leaves, plane, margin=0.10)
+    q = S.random_states(b, n_states, seed=99, dtype=np.float64)
+    bc = make_checker(b)
+    T = pyoracle.fk(b, q)
+    hit_g, con_g, _, stats = bc.check_link_poses(T, None, test_type)
+    hit_o, con_o, _ = pyoracle.check_discrete(b, q, test_type, n_threads=threads)
+    out = compare_batch(b, con_g, con_o, hit_g, hit_o, 0.10)
+    out["colliding"] = int(hit_g.sum())
+    return out
+
+
+def config5_dual_arm(make_checker, n_states, n_prims, threads=4, test_type=capi.TEST_CLOSEST):
+    """configs[4]: two iiwa with cross-arm pairs + concave fixtures + primitives (FK bypass: exact poses)"""
+    fixtures = []
+    for i in range(4):
+        v, f = _lbracket(5 + i)
+        fixtures.append((f"fixture_{i}", v, f, S.pose((0.45 * (1 if i % 2 else -1), 0.3 * (1 if i < 2 else -1), 0.35))))
+    b = S.build_config5(n_prims=n_prims, margin=0.05, fixtures=fixtures)
+    q = S.random_states(b, n_states, seed=2024, dtype=np.float64)
+    bc = make_checker(b)
+    T = pyoracle.fk(b, q)
+    hit_g, con_g, _, stats = bc.check_link_poses(T, None, test_type)
+    hit_o, con_o, _ = pyoracle.check_discrete(b, q, test_type, n_threads=threads)
+    out = compare_batch(b, con_g, con_o, hit_g, hit_o, 0.05)
+    out["colliding"] = int(hit_g.sum())
+    out["self_or_cross"] = int(sum(1 for c in con_g if c["link"][0] < 16 and c["link"][1] < 16))
+    return out
+
+
 def fk_parity(make_checker, robot="iiwa14", n=200):
     b = S.SceneBuilder()
     S.add_robot(b, S.load_robot(robot))

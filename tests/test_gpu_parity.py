@@ -50,3 +50,27 @@ def test_cast_lvs():
 @pytest.mark.parametrize("robot", ["iiwa14", "abb_irb2400"])
 def test_fk(robot):
     pc.fk_parity(mk, robot, n=5000)
+
+
+def test_config4_monkey_octomap():
+    """configs[3]: ABB hull links vs the 414 194 occupied leaves of blender_monkey.bt + plane_4m.stl, margin 0.10"""
+    import numpy as np
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    leaves = np.load(os.path.join(gold, "blender_monkey_octree.npz"))["leaves"].astype(np.float64)
+    pl = np.load(os.path.join(gold, "plane_4m.npz"))
+    b_kw = dict(robot_xyz=(0.0, -1.6, 0.0))
+    from tesseract_b200 import scene as S
+    orig = S.build_config4
+    try:
+        S.build_config4 = lambda l, p, margin=0.10: orig(l, p, margin=margin, **b_kw)
+        out = pc.config4_voxels(mk, leaves, (pl["vertices"], pl["faces"]), 256, threads=THREADS)
+    finally:
+        S.build_config4 = orig
+    print(out)
+    assert out["colliding"] > 0
+
+
+def test_config5_dual_arm():
+    out = pc.config5_dual_arm(mk, 4000, 10000, threads=THREADS)
+    print(out)
+    assert out["self_or_cross"] > 0

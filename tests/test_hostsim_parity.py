@@ -83,3 +83,40 @@ def test_first_in_rounds():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+def test_config4_voxels_and_mesh():
+    """configs[3] style: ABB hull links vs octomap voxels (fixture box_2m.bt) + the plane_4m.stl triangle mesh"""
+    import os
+    import numpy as np
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    leaves = np.load(os.path.join(gold, "box_2m_octree.npz"))["leaves"].astype(np.float64)
+    leaves[:, :3] += (0.0, -1.0, 0.6)
+    pl = np.load(os.path.join(gold, "plane_4m.npz"))
+    out = pc.config4_voxels(mk, leaves, (pl["vertices"], pl["faces"]), 60)
+    print(out)
+    assert out["colliding"] > 0
+
+
+def test_config5_dual_arm():
+    """configs[4] style: two iiwa (cross-arm pairs) + concave L-bracket fixtures + primitives"""
+    out = pc.config5_dual_arm(mk, 80, 2000)
+    print(out)
+    assert out["self_or_cross"] > 0
+
+
+def test_chunked_batches_with_rounds():
+    """batches larger than one chunk (default 1 Mi states; forced to 128 here) with FIRST rounds on: state indices,
+    contact offsets and per-chunk queues stay consistent"""
+    import subprocess, sys, os
+    code = ("import sys; sys.path.insert(0, 'tests'); import parity_cases as pc; from hostsim import build as h; "
+            "from tesseract_b200.managers import BatchChecker; from tesseract_b200 import capi; "
+            "mk = lambda b: BatchChecker(b, lib=h.lib()); "
+            "print(pc.discrete_config2(mk, 500, 10000, capi.TEST_FIRST)); "
+            "print(pc.discrete_config2(mk, 500, 10000, capi.TEST_CLOSEST)); "
+            "print(pc.flags_only(mk, 700, 10000)); "
+            "print(pc.cast_config3(mk, 5, 12, 10000, device_fk=True))")
+    env = dict(os.environ, T4C_ROUND_MIN_STATES="1", T4C_CHUNK_STATES="128")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout + r.stderr
