@@ -225,9 +225,10 @@ t4c_status t4c_check_cast(t4c_scene* scene, const t4c_fk_model* model, const dou
 t4c_status t4c_check_link_poses_cast(t4c_scene* scene, const double* poses0, const double* poses1, int64_t n,
                                      const t4c_request* request, t4c_result* result);
 /* LVS trajectory checks (core/utils.h:172-428): traj is n_traj x n_wp x n_q row-major doubles.
- * Work items are LVS sub-states (discrete) / sub-segments (cast); result contact.state is the
- * flat work-item index; item_traj / item_step (optional, capacity n_items_cap) map items back to
- * (trajectory, waypoint step).  n_items receives the item count. */
+ * Work items are LVS sub-states (discrete) / sub-segments (cast); result contact.state and the hit array are
+ * indexed by the flat work-item index (t4c_lvs_items maps it back to trajectory / step / sub-step).  n_items
+ * receives the item count.  lvs = +infinity disables the subdivision (CollisionEvaluatorType::DISCRETE /
+ * CONTINUOUS). */
 t4c_status t4c_check_trajectories_discrete(t4c_scene* scene, const t4c_fk_model* model, const double* traj,
                                            int64_t n_traj, int32_t n_wp, double lvs, const t4c_request* request,
                                            t4c_result* result, int64_t* n_items);
@@ -238,6 +239,15 @@ t4c_status t4c_check_trajectories_cast(t4c_scene* scene, const t4c_fk_model* mod
 /* number of LVS work items checkTrajectory would visit (core/utils.h:189-205,328-347); no device work */
 t4c_status t4c_lvs_count(const double* traj, int64_t n_traj, int32_t n_wp, int32_t n_q, double lvs, int32_t cast,
                          int64_t* n_items);
+/* Map flat work-item indices (t4c_contact::state / the hit array of t4c_check_trajectories_*) back to
+ * (trajectory, waypoint step iStep, sub-step iSubStep) in the reference's visiting order.  Each output array is
+ * optional and holds `capacity` entries; items beyond the capacity are only counted.  Host only. */
+t4c_status t4c_lvs_items(const double* traj, int64_t n_traj, int32_t n_wp, int32_t n_q, double lvs, int32_t cast,
+                         int64_t capacity, int32_t* item_traj, int32_t* item_step, int32_t* item_sub, int64_t* n_items);
+/* Joint vectors of selected work items (strictly ascending flat indices): q0, and q1 for cast sub-segments, are
+ * n_sel x n_q row-major -- the subtraj.row(iSubStep) / row(iSubStep + 1) of core/utils.h:194-205.  Host only. */
+t4c_status t4c_lvs_item_states(const double* traj, int64_t n_traj, int32_t n_wp, int32_t n_q, double lvs, int32_t cast,
+                               int64_t n_sel, const int64_t* items, double* q0, double* q1);
 
 /* Device-resident entries (inputs already in HBM; used by bench.py "value" and by multi-GPU
  * callers that gather with NCCL themselves). */

@@ -35,14 +35,16 @@ struct Epa
   struct Face
   {
     V3<T> n;
-    T d;
     int16_t v[3];
     int16_t adj[3];
     int16_t mark;
-    int16_t alive;
+    int16_t pad;
   };
   V3<T> W[MAXV], P[MAXV];
   Face F[MAXF];
+  // plane distance of every face slot, +large for a free / removed slot: the closest-face search (the most frequent
+  // memory access of an iteration) reads one dense array instead of two fields of 48-byte records
+  T Fd[MAXF];
   int nv, nf_hi;         // vertices used; high-water mark of face slots
   int16_t free_list[MAXF];
   int n_free;
@@ -125,7 +127,7 @@ struct Epa
     return false;
   }
 
-  T4_HD bool makeFace(int a, int b, int c, Face& f) const
+  T4_HD bool makeFace(int a, int b, int c, Face& f, T& d) const
   {
     f.v[0] = (int16_t)a, f.v[1] = (int16_t)b, f.v[2] = (int16_t)c;
     f.adj[0] = f.adj[1] = f.adj[2] = -1;
@@ -134,8 +136,7 @@ struct Epa
     if (!(l > T(1e-20)))
       return false;
     f.n = n * (T(1) / l);
-    f.d = f.n.dot(W[a]);
-    f.alive = 1;
+    d = f.n.dot(W[a]);
     f.mark = 0;
     return true;
   }
@@ -159,7 +160,8 @@ struct Epa
   //      EPA kernel advances every lane by ONE iteration per trip and refills finished lanes at once)
   int mark_, it_, max_iter_;
   T tol_, saved_d;
-  V3<T> saved_n, saved_w[3], saved_p[3];
+  V3<T> saved_n;
+  int16_t saved_v[3];  // vertices of the face that gave the tightest bound (W / P are append-only: indices stay valid)
   bool have_saved, deteriorated;
 
   // simplex: up to 4 points of A-B (and their A witnesses) around the origin, from the GJK that found the overlap.
@@ -205,7 +207,7 @@ struct Epa
     const int tet[4][3] = { { 0, 1, 2 }, { 1, 0, 3 }, { 2, 1, 3 }, { 0, 2, 3 } };
     for (int i = 0; i < 4; ++i)
     {
-      if (!makeFace(tet[i][0], tet[i][1], tet[i][2], F[i]))
+      if (!makeFace(tet[i][0], tet[i][1], tet[i][2], F[i], Fd[i]))
         return false;
       ++nf_hi;
     }
@@ -230,35 +232,38 @@ struct Epa
     if (it_ >= max_iter_)
       return 1;
     int best = -1;
-    for (int i = 0; i < nf_hi; ++i)
-      if (F[i].alive && (best < 0 || F[i].d < F[best].d))
-        best = i;
+    {
+      T bestd = Eps<T>::large();
+      for (int i = 0; i < nf_hi; ++i)
+        if (Fd[i] < bestd)
+        {
+          bestd = Fd[i];
+          best = i;
+        }
+    }
     if (best < 0)
       return 2;
     // The closest-face distance is a LOWER bound of the depth and can only grow.  On curved supports (cylinder /
     // cone rims) the faces shrink to rounding-noise size near convergence and the hull eventually corrupts: the
     // bound then drops.  Stop there and report the tightest bound recorded.
-    if (F[best].d + T(1e-12) < saved_d)
+    if (Fd[best] + T(1e-12) < saved_d)
     {
       deteriorated = true;
       return 1;
     }
-    if (F[best].d >= saved_d)
+    if (Fd[best] >= saved_d)
     {
-      saved_d = F[best].d;
+      saved_d = Fd[best];
       saved_n = F[best].n;
       for (int k = 0; k < 3; ++k)
-      {
-        saved_w[k] = W[F[best].v[k]];
-        saved_p[k] = P[F[best].v[k]];
-      }
+        saved_v[k] = F[best].v[k];
       have_saved = true;
     }
     if (nv >= MAXV)
       return 1;
     V3<T> w, p;
     support(F[best].n, w, p);
-    const T wdist = F[best].n.dot(w) - F[best].d;
+    const T wdist = F[best].n.dot(w) - Fd[best];
     if (wdist <= tol_)
       return 1;
     const int wi = nv;
@@ -279,7 +284,7 @@ struct Epa
         const int g = F[f].adj[e];
         if (g < 0 || F[g].mark == mark_)
           continue;
-        if (F[g].n.dot(w) - F[g].d > T(1e-14))
+        if (F[g].n.dot(w) - Fd[g] > T(1e-14))
         {
           F[g].mark = (int16_t)mark_;
           stack[sp_++] = (int16_t)g;
@@ -334,7 +339,7 @@ struct Epa
     }
     for (int k = 0; k < nvis; ++k)
     {
-      F[visible[k]].alive = 0;
+      Fd[visible[k]] = Eps<T>::large();
       free_list[n_free++] = visible[k];
     }
     // new faces (a, b, w): edge0 = horizon edge, edge1 = (b,w), edge2 = (w,a)
@@ -346,7 +351,8 @@ struct Epa
     {
       const int slot = allocFace();
       Face nf;
-      if (slot < 0 || !makeFace(hz_a[k], hz_b[k], wi, nf))
+      T nd = 0;
+      if (slot < 0 || !makeFace(hz_a[k], hz_b[k], wi, nf, nd))
       {
         bad = true;
         break;
@@ -354,6 +360,7 @@ struct Epa
       nf.adj[0] = hz_g[k];
       nf.mark = 0;
       F[slot] = nf;
+      Fd[slot] = nd;
       stack[nnew++] = (int16_t)slot;
       if (first_new < 0)
         first_new = slot;
@@ -405,39 +412,46 @@ struct Epa
     res.iterations = it_;
     // closest ALIVE face (after a break the stored `best` may have been freed)
     best = -1;
-    for (int i = 0; i < nf_hi; ++i)
-      if (F[i].alive && (best < 0 || F[i].d < F[best].d))
-        best = i;
+    {
+      T bestd = Eps<T>::large();
+      for (int i = 0; i < nf_hi; ++i)
+        if (Fd[i] < bestd)
+        {
+          bestd = Fd[i];
+          best = i;
+        }
+    }
     if (best < 0)
       return false;
-    if (have_saved && (deteriorated || F[best].d < saved_d))
+    if (have_saved && (deteriorated || Fd[best] < saved_d))
     {
       // report the recorded tightest bound; foot-point weights on its own triangle (clamped)
       const V3<T> pr = saved_n * saved_d;
-      T c0 = saved_n.dot((saved_w[1] - pr).cross(saved_w[2] - pr));
-      T c1 = saved_n.dot((saved_w[2] - pr).cross(saved_w[0] - pr));
-      T c2 = saved_n.dot((saved_w[0] - pr).cross(saved_w[1] - pr));
+      const V3<T> sw0 = W[saved_v[0]], sw1 = W[saved_v[1]], sw2 = W[saved_v[2]];
+      T c0 = saved_n.dot((sw1 - pr).cross(sw2 - pr));
+      T c1 = saved_n.dot((sw2 - pr).cross(sw0 - pr));
+      T c2 = saved_n.dot((sw0 - pr).cross(sw1 - pr));
       c0 = t4max(c0, T(0)), c1 = t4max(c1, T(0)), c2 = t4max(c2, T(0));
       const T sum = c0 + c1 + c2;
       if (!(sum > T(0)))
         return false;
       res.normal = saved_n;
       res.depth = saved_d;
-      res.pA = saved_p[0] * (c0 / sum) + saved_p[1] * (c1 / sum) + saved_p[2] * (c2 / sum);
+      res.pA = P[saved_v[0]] * (c0 / sum) + P[saved_v[1]] * (c1 / sum) + P[saved_v[2]] * (c2 / sum);
       return true;
     }
     // A flat face of A-B is usually split into several coplanar triangles with the same plane distance: take the one
     // that actually contains the foot point of the origin (signed barycentric coordinates), otherwise the witness
     // blend below would extrapolate.
-    const T dband = F[best].d + T(1e-9) * (T(1) + t4abs(F[best].d));
+    const T dband = Fd[best] + T(1e-9) * (T(1) + t4abs(Fd[best]));
     T b0 = 0, b1 = 0, b2 = 0, best_min = -Eps<T>::large();
     int pick = best;
     for (int i = 0; i < nf_hi; ++i)
     {
-      if (!F[i].alive || F[i].d > dband)
+      if (Fd[i] > dband)  // also skips free slots (+large)
         continue;
       const Face& f = F[i];
-      const V3<T> pr = f.n * f.d;
+      const V3<T> pr = f.n * Fd[i];
       const T c0 = f.n.dot((W[f.v[1]] - pr).cross(W[f.v[2]] - pr));
       const T c1 = f.n.dot((W[f.v[2]] - pr).cross(W[f.v[0]] - pr));
       const T c2 = f.n.dot((W[f.v[0]] - pr).cross(W[f.v[1]] - pr));
@@ -462,7 +476,7 @@ struct Epa
     }
     const Face& o = F[pick];
     res.normal = o.n;
-    res.depth = o.d;
+    res.depth = Fd[pick];
     res.pA = P[o.v[0]] * b0 + P[o.v[1]] * b1 + P[o.v[2]] * b2;
     return true;
   }

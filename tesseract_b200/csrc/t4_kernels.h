@@ -141,6 +141,7 @@ struct KParams
   uint32_t* first_claim;  // [n] FIRST: 0 free / 1 claimed
   t4c_contact* raw;       // staging (CLOSEST) or final buffer
   float* raw_local;       // cast: nearest_points_local [cap][6] or null
+  double* raw_d64;        // CLOSEST: FP64 distance of every raw record (the reference compares doubles) or null
   uint32_t raw_cap;
   t4c_contact* out;       // CLOSEST final
   float* out_local;
@@ -179,6 +180,10 @@ __device__ __forceinline__ uint32_t casU32(uint32_t* p, uint32_t cmp, uint32_t v
 __device__ __forceinline__ uint32_t orU32(uint32_t* p, uint32_t val) { return atomicOr(p, val); }
 __device__ __forceinline__ int32_t casI32(int32_t* p, int32_t cmp, int32_t val) { return atomicCAS(p, cmp, val); }
 __device__ __forceinline__ void minU64(unsigned long long* p, unsigned long long v) { atomicMin(p, v); }
+__device__ __forceinline__ unsigned long long casU64(unsigned long long* p, unsigned long long cmp, unsigned long long val)
+{
+  return atomicCAS(p, cmp, val);
+}
 #else
 inline uint32_t qAppend(uint32_t* ctr) { return (*ctr)++; }
 inline void statAdd(unsigned long long* stats, int k, uint32_t v) { stats[k] += v; }
@@ -206,6 +211,13 @@ inline void minU64(unsigned long long* p, unsigned long long v)
 {
   if (v < *p)
     *p = v;
+}
+inline unsigned long long casU64(unsigned long long* p, unsigned long long cmp, unsigned long long val)
+{
+  unsigned long long o = *p;
+  if (o == cmp)
+    *p = val;
+  return o;
 }
 #endif
 

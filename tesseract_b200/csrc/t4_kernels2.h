@@ -166,6 +166,22 @@ T4_KD uint32_t orderedBits(float f)
 #endif
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
+T4_KD unsigned long long orderedBits64(double d)
+{
+  unsigned long long u;
+#ifdef T4_DEVICE_BUILD
+  u = (unsigned long long)__double_as_longlong(d);
+#else
+  union
+  {
+    double d;
+    unsigned long long u;
+  } cv;
+  cv.d = d;
+  u = cv.u;
+#endif
+  return (u >> 63) ? ~u : (u | 0x8000000000000000ULL);
+}
 
 // TesseractBroadphaseBridgedManifoldResult::addContactPoint -> add{Discrete,Cast}SingleResult -> processResult
 // (bullet_utils.h:388-441,527-611,757-802 ; core/common.h:114-167)
@@ -243,6 +259,8 @@ T4_KDN void emitContact(const KParams& P, int64_t s, int a, int b, const ShapeW<
   ct.normal[0] = (float)(sg * pr.normalOnB.x), ct.normal[1] = (float)(sg * pr.normalOnB.y);
   ct.normal[2] = (float)(sg * pr.normalOnB.z);
   P.raw[slot] = ct;
+  if (P.raw_d64)
+    P.raw_d64[slot] = pr.distance;
   if (P.raw_local)
   {
     float* L = P.raw_local + (size_t)slot * 6;
@@ -692,8 +710,9 @@ T4_KD bool sameKey(const t4c_contact& x, const t4c_contact& y)
 }
 
 // ContactTestType::CLOSEST (core/common.h:151-157): keep the minimum-distance contact per (state, link pair).
-// item = raw contact index.  Pass 1 finds / claims the hash slot of the key and atomically minimises
-// (ordered distance bits, raw index); pass 2 lets every winner copy itself to the output.
+// item = raw contact index.  Pass 1 finds / claims the hash slot of the key and atomically minimises the ordered bits
+// of the FP64 distance (the reference compares doubles: two triangles of one mesh often tie in FP32); pass 2 lets the
+// first record that still finds its own distance in the slot take it (CAS to a sentinel) and copy itself out.
 T4_KD uint32_t closestSlot(const KParams& P, uint32_t i, bool insert)
 {
   const t4c_contact& c = P.raw[i];
@@ -724,8 +743,7 @@ T4_KD void closestInsertBody(int64_t i, const KParams& P)
   const uint32_t h = closestSlot(P, (uint32_t)i, true);
   if (h == 0xffffffffu)
     return;
-  const unsigned long long key = ((unsigned long long)orderedBits(P.raw[i].distance) << 32) | (uint32_t)i;
-  minU64(&P.ht_best[h], key);
+  minU64(&P.ht_best[h], orderedBits64(P.raw_d64[i]));
 }
 
 T4_KD void closestEmitBody(int64_t i, const KParams& P)
@@ -733,7 +751,8 @@ T4_KD void closestEmitBody(int64_t i, const KParams& P)
   const uint32_t h = closestSlot(P, (uint32_t)i, false);
   if (h == 0xffffffffu)
     return;
-  if ((uint32_t)(P.ht_best[h] & 0xffffffffu) != (uint32_t)i)
+  const unsigned long long key = orderedBits64(P.raw_d64[i]);
+  if (P.ht_best[h] != key || casU64(&P.ht_best[h], key, 0xfffffffffffffffeULL) != key)
     return;
   const uint32_t slot = qAppend(&P.qcount[Q_OUT]);
   if (slot >= P.out_cap)

@@ -486,7 +486,7 @@ struct t4c_scene
   // per-call workspace
   DevBuf d_q0, d_q1, d_pin0, d_pin1, d_poses0, d_poses1, d_poses0d, d_poses1d;
   DevBuf d_cand_state, d_cand_a, d_cand_b, d_surv, d_surv2, d_surv3, d_surv4, d_cull_claim, d_tasks;
-  DevBuf d_qcount, d_stats, d_hit, d_claim, d_raw, d_raw_local, d_ht_rep, d_ht_best;
+  DevBuf d_qcount, d_stats, d_hit, d_claim, d_raw, d_raw_local, d_raw_d64, d_ht_rep, d_ht_best;
   DevBuf d_out, d_out_local, d_fk_out, d_hit_full;
   DevBuf d_traj, d_lvs_counts, d_lvs_offsets, d_lvs_tmp;
   DevBuf d_sort_keys, d_sort_keys2, d_sort_vals, d_sort_idx, d_sort_tmp;
@@ -856,6 +856,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     }
     P.raw = nullptr;
     P.raw_local = nullptr;
+    P.raw_d64 = nullptr;
     P.raw_cap = 0;
     if (io.contacts && !closest)
     {
@@ -969,6 +970,8 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
         T4_TRY(s->d_raw.ensure(std::max<size_t>(nsurv, 1) * sizeof(t4c_contact)), "contact staging");
         P.raw = s->d_raw.as<t4c_contact>();
         P.raw_cap = nsurv;
+        T4_TRY(s->d_raw_d64.ensure(std::max<size_t>(nsurv, 1) * sizeof(double)), "contact staging");
+        P.raw_d64 = s->d_raw_d64.as<double>();
         if (io.cast && io.cc_local)
         {
           T4_TRY(s->d_raw_local.ensure(std::max<size_t>(nsurv, 1) * 6 * sizeof(float)), "contact staging");
@@ -1124,11 +1127,12 @@ static double linspaced(int64_t cnt, double low, double high, int64_t i)
   return (i == size1) ? high : (low + double(i) * step);
 }
 
-// LVS expansion (tesseract_environment/core/utils.h:189-205 continuous, :328-347 discrete)
-static void lvsExpand(const double* traj, int64_t n_traj, int n_wp, int n_q, double lvs, bool cast,
-                      std::vector<double>& q0, std::vector<double>& q1)
+// LVS walk (tesseract_environment/core/utils.h:189-205 continuous, :328-347 discrete): calls
+// visit(trajectory, waypoint step, sub-step, cnt, a, b) for every work item in the reference's visiting order;
+// cnt == 0 marks an undivided step (the state / segment itself)
+template <class F>
+static void lvsWalk(const double* traj, int64_t n_traj, int n_wp, int n_q, double lvs, bool cast, F&& visit)
 {
-  std::vector<double> sa((size_t)n_q), sb((size_t)n_q);
   for (int64_t t = 0; t < n_traj; ++t)
   {
     const double* tr = traj + (size_t)t * n_wp * n_q;
@@ -1149,25 +1153,26 @@ static void lvsExpand(const double* traj, int64_t n_traj, int n_wp, int n_q, dou
       {
         const int64_t cnt = (int64_t)std::ceil(dist / lvs) + 1;
         for (int64_t i = 0; i < cnt - 1; ++i)
-        {
-          for (int k = 0; k < n_q; ++k)
-          {
-            sa[k] = linspaced(cnt, a[k], b[k], i);
-            sb[k] = linspaced(cnt, a[k], b[k], i + 1);
-          }
-          q0.insert(q0.end(), sa.begin(), sa.end());
-          if (cast)
-            q1.insert(q1.end(), sb.begin(), sb.end());
-        }
+          visit(t, s, i, cnt, a, b);
       }
       else
-      {
-        q0.insert(q0.end(), a, a + n_q);
-        if (cast)
-          q1.insert(q1.end(), b, b + n_q);
-      }
+        visit(t, s, (int64_t)0, (int64_t)0, a, b);
     }
   }
+}
+
+static void lvsExpand(const double* traj, int64_t n_traj, int n_wp, int n_q, double lvs, bool cast,
+                      std::vector<double>& q0, std::vector<double>& q1)
+{
+  lvsWalk(traj, n_traj, n_wp, n_q, lvs, cast,
+          [&](int64_t, int, int64_t i, int64_t cnt, const double* a, const double* b) {
+            for (int k = 0; k < n_q; ++k)
+            {
+              q0.push_back(cnt ? linspaced(cnt, a[k], b[k], i) : a[k]);
+              if (cast)
+                q1.push_back(cnt ? linspaced(cnt, a[k], b[k], i + 1) : b[k]);
+            }
+          });
 }
 
 extern "C" {
@@ -1530,11 +1535,58 @@ static t4c_status checkTrajectories(t4c_scene* s, const t4c_fk_model* m, const d
 t4c_status t4c_lvs_count(const double* traj, int64_t n_traj, int32_t n_wp, int32_t n_q, double lvs, int32_t cast,
                          int64_t* n_items)
 {
-  if (!traj || !n_items || n_q <= 0 || !(lvs > 0))
+  return t4c_lvs_items(traj, n_traj, n_wp, n_q, lvs, cast, 0, nullptr, nullptr, nullptr, n_items);
+}
+
+t4c_status t4c_lvs_items(const double* traj, int64_t n_traj, int32_t n_wp, int32_t n_q, double lvs, int32_t cast,
+                         int64_t capacity, int32_t* item_traj, int32_t* item_step, int32_t* item_sub, int64_t* n_items)
+{
+  if (!traj || !n_items || n_q <= 0 || n_wp <= 0 || n_traj < 0 || !(lvs > 0))
     return fail(T4C_ERR_INVALID, "bad arguments");
-  std::vector<double> q0, q1;
-  lvsExpand(traj, n_traj, n_wp, n_q, lvs, cast != 0, q0, q1);
-  *n_items = (int64_t)(q0.size() / (size_t)n_q);
+  int64_t n = 0;
+  lvsWalk(traj, n_traj, n_wp, n_q, lvs, cast != 0,
+          [&](int64_t t, int s, int64_t i, int64_t, const double*, const double*) {
+            if (n < capacity)
+            {
+              if (item_traj)
+                item_traj[n] = (int32_t)t;
+              if (item_step)
+                item_step[n] = s;
+              if (item_sub)
+                item_sub[n] = (int32_t)i;
+            }
+            ++n;
+          });
+  *n_items = n;
+  return T4C_OK;
+}
+
+t4c_status t4c_lvs_item_states(const double* traj, int64_t n_traj, int32_t n_wp, int32_t n_q, double lvs, int32_t cast,
+                               int64_t n_sel, const int64_t* items, double* q0, double* q1)
+{
+  if (!traj || n_q <= 0 || n_wp <= 0 || n_traj < 0 || !(lvs > 0) || n_sel < 0 || (n_sel > 0 && (!items || !q0)) ||
+      (cast && n_sel > 0 && !q1))
+    return fail(T4C_ERR_INVALID, "bad arguments");
+  for (int64_t k = 1; k < n_sel; ++k)
+    if (items[k] <= items[k - 1])
+      return fail(T4C_ERR_INVALID, "item indices must be strictly ascending");
+  int64_t n = 0, k = 0;
+  lvsWalk(traj, n_traj, n_wp, n_q, lvs, cast != 0,
+          [&](int64_t, int, int64_t i, int64_t cnt, const double* a, const double* b) {
+            if (k < n_sel && items[k] == n)
+            {
+              for (int c = 0; c < n_q; ++c)
+              {
+                q0[(size_t)k * n_q + c] = cnt ? linspaced(cnt, a[c], b[c], i) : a[c];
+                if (cast)
+                  q1[(size_t)k * n_q + c] = cnt ? linspaced(cnt, a[c], b[c], i + 1) : b[c];
+              }
+              ++k;
+            }
+            ++n;
+          });
+  if (k != n_sel)
+    return fail(T4C_ERR_INVALID, "item index %lld outside [0,%lld)", (long long)items[k], (long long)n);
   return T4C_OK;
 }
 

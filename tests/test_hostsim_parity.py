@@ -100,7 +100,7 @@ def test_config4_voxels_and_mesh():
 
 def test_config5_dual_arm():
     """configs[4] style: two iiwa (cross-arm pairs) + concave L-bracket fixtures + primitives"""
-    out = pc.config5_dual_arm(mk, 80, 2000)
+    out = pc.config5_dual_arm(mk, 600, 6000, threads=8)
     print(out)
     assert out["self_or_cross"] > 0
 
