@@ -111,6 +111,9 @@ def load_library(path=None):
     lib.t4c_fk_model_destroy.restype = None
     lib.t4c_fk.argtypes = [VP, VP, DP, I64, DP]
     lib.t4c_lvs_count.argtypes = [DP, I64, I32, I32, C.c_double, I32, C.POINTER(I64)]
+    lib.t4c_lvs_items.argtypes = [DP, I64, I32, I32, C.c_double, I32, I64, C.POINTER(I32), C.POINTER(I32),
+                                  C.POINTER(I32), C.POINTER(I64)]
+    lib.t4c_lvs_item_states.argtypes = [DP, I64, I32, I32, C.c_double, I32, I64, C.POINTER(I64), DP, DP]
     lib.t4c_check_discrete.argtypes = [VP, VP, DP, I64, C.POINTER(Request), C.POINTER(Result)]
     lib.t4c_check_link_poses_discrete.argtypes = [VP, DP, I64, C.POINTER(Request), C.POINTER(Result)]
     lib.t4c_check_cast.argtypes = [VP, VP, DP, DP, I64, C.POINTER(Request), C.POINTER(Result)]
@@ -134,7 +137,8 @@ def load_library(path=None):
                  "t4c_fk_model_create", "t4c_fk", "t4c_check_discrete", "t4c_check_link_poses_discrete",
                  "t4c_check_cast", "t4c_check_link_poses_cast", "t4c_check_trajectories_discrete",
                  "t4c_check_trajectories_cast", "t4c_check_discrete_device", "t4c_check_cast_device",
-                 "t4c_measure_fp32_peak", "t4c_lvs_count", "t4c_debug_hull_support"):
+                 "t4c_measure_fp32_peak", "t4c_lvs_count", "t4c_lvs_items", "t4c_lvs_item_states",
+                 "t4c_debug_hull_support"):
         getattr(lib, name).restype = I32
     if path is None:
         _lib = lib

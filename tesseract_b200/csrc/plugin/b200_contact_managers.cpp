@@ -449,30 +449,50 @@ void ManagerCore::contactTest(ContactResultMap& collisions, const ContactRequest
   std::vector<t4c_contact> raw;
   std::vector<float> local;
   run(p0.data(), p1.data(), 1, request, device_type, nullptr, raw, local);
-  bool done = false;
-  for (size_t k = 0; k < raw.size() && !done; ++k)
+  std::vector<const t4c_contact*> recs(raw.size());
+  std::vector<const float*> locs(raw.size(), nullptr);
+  for (size_t k = 0; k < raw.size(); ++k)
   {
-    const t4c_contact& c = raw[k];
+    recs[k] = &raw[k];
+    if (cast_)
+      locs[k] = &local[k * 6];
+  }
+  processRecords(collisions, request, recs.data(), locs.data(), raw.size(), nullptr, nullptr);
+}
+
+bool ManagerCore::processRecords(ContactResultMap& collisions, const ContactRequest& request,
+                                 const t4c_contact* const* recs, const float* const* locals, size_t n,
+                                 const double* poses0, const double* poses1) const
+{
+  for (size_t k = 0; k < n; ++k)
+  {
+    const t4c_contact& c = *recs[k];
     ContactResult cr;
     cr.distance = c.distance;
     cr.normal = Eigen::Vector3d(c.normal[0], c.normal[1], c.normal[2]);
     for (int j = 0; j < 2; ++j)
     {
       const Object& o = objects_[(size_t)c.link[j]];
+      // only active links are moved by a state (checkTrajectoryState, core/utils.h:136-137)
+      const bool moved = poses0 && isActive(c.link[j]);
+      const Eigen::Isometry3d T0 = moved ? fromPose12(poses0 + (size_t)c.link[j] * 12) : o.pose0;
       cr.link_names[j] = o.name;
       cr.type_id[j] = o.mask_id;
       cr.shape_id[j] = c.shape_id[j];
       cr.subshape_id[j] = c.subshape_id[j];
       cr.nearest_points[j] = Eigen::Vector3d(c.point[j][0], c.point[j][1], c.point[j][2]);
-      cr.transform[j] = o.pose0;
-      cr.nearest_points_local[j] = o.pose0.inverse() * cr.nearest_points[j];
+      cr.transform[j] = T0;
+      cr.nearest_points_local[j] = T0.inverse() * cr.nearest_points[j];
       if (cast_ && c.cc_type[j] != T4C_CC_NONE)
       {
         cr.cc_time[j] = c.cc_time[j];
         cr.cc_type[j] = static_cast<ContinuousCollisionType>(c.cc_type[j]);
-        cr.cc_transform[j] = o.pose1;
-        const float* L = &local[k * 6 + 3 * (size_t)j];
-        cr.nearest_points_local[j] = Eigen::Vector3d(L[0], L[1], L[2]);
+        cr.cc_transform[j] = (moved && poses1) ? fromPose12(poses1 + (size_t)c.link[j] * 12) : o.pose1;
+        if (locals && locals[k])
+        {
+          const float* L = locals[k] + 3 * (size_t)j;
+          cr.nearest_points_local[j] = Eigen::Vector3d(L[0], L[1], L[2]);
+        }
       }
     }
     // processResult (core/common.h:114-167)
@@ -488,12 +508,153 @@ void ManagerCore::contactTest(ContactResultMap& collisions, const ContactRequest
     {
       collisions[key].push_back(cr);
       if (request.type == ContactTestType::FIRST)
-        done = true;
+        return true;
     }
     else if (request.type == ContactTestType::ALL)
       it->second.push_back(cr);
     else if (request.type == ContactTestType::CLOSEST && cr.distance < it->second[0].distance)
       it->second[0] = cr;
+  }
+  return false;
+}
+
+// checkTrajectory for many trajectories at once (tesseract_environment/core/utils.h:172-428): the LVS subdivision,
+// FK and all contact tests run as one device batch (t4c_check_trajectories_*); the host then rebuilds, only for the
+// colliding work items, what checkTrajectoryState / checkTrajectorySegment (:87-160) would have pushed.
+void ManagerCore::checkTrajectories(const t4c_fk_model* model, const double* traj, int64_t n_traj, int32_t n_wp,
+                                    int32_t n_q, double lvs, const ContactRequest& request,
+                                    std::vector<std::vector<ContactResultMap>>& contacts, std::vector<uint8_t>& found)
+{
+  if (request.type == ContactTestType::LIMITED)
+    throw std::runtime_error("tesseract_b200: ContactTestType::LIMITED is not implemented (nor in the reference, "
+                             "core/common.h:159-164)");
+  if (!model || !traj || n_traj < 0 || n_q <= 0)
+    throw std::runtime_error("tesseract_b200: checkTrajectories was given a null model / trajectory");
+  if (cast_ && n_wp == 1)
+    throw std::runtime_error("checkTrajectory was given continuous contact manager with a trajectory that only has "
+                             "one state.");  // core/utils.h:184-186
+  contacts.assign((size_t)n_traj, {});
+  found.assign((size_t)n_traj, 0);
+  if (n_traj == 0)
+    return;
+  sync();
+  int64_t n_items = 0;
+  check(t4c_lvs_count(traj, n_traj, n_wp, n_q, lvs, cast_ ? 1 : 0, &n_items), "t4c_lvs_count");
+  std::vector<int32_t> item_traj((size_t)std::max<int64_t>(n_items, 1));
+  check(t4c_lvs_items(traj, n_traj, n_wp, n_q, lvs, cast_ ? 1 : 0, n_items, item_traj.data(), nullptr, nullptr,
+                      &n_items),
+        "t4c_lvs_items");
+  t4c_request rq;
+  rq.type = request.is_valid ? (int)T4C_TEST_ALL : (int)request.type;
+  rq.calculate_penetration = request.calculate_penetration ? 1 : 0;
+  rq.calculate_distance = request.calculate_distance ? 1 : 0;
+  std::vector<uint8_t> hit((size_t)std::max<int64_t>(n_items, 1), 0);
+  std::vector<t4c_contact> raw;
+  std::vector<float> local;
+  int64_t cap = std::max<int64_t>(256, 2 * n_items);
+  for (;;)
+  {
+    raw.resize((size_t)cap);
+    if (cast_)
+      local.assign((size_t)cap * 6, 0.f);
+    t4c_result r;
+    std::memset(&r, 0, sizeof(r));
+    r.hit = hit.data();
+    r.contacts = raw.data();
+    r.capacity = cap;
+    r.cc_local = cast_ ? local.data() : nullptr;
+    int64_t ni = 0;
+    const t4c_status st = cast_ ? t4c_check_trajectories_cast(scene_, model, traj, n_traj, n_wp, lvs, &rq, &r, &ni) :
+                                  t4c_check_trajectories_discrete(scene_, model, traj, n_traj, n_wp, lvs, &rq, &r, &ni);
+    if (st == T4C_ERR_CAPACITY)
+    {
+      cap = r.n_contacts;
+      continue;
+    }
+    check(st, cast_ ? "t4c_check_trajectories_cast" : "t4c_check_trajectories_discrete");
+    raw.resize((size_t)r.n_contacts);
+    stats_ = r.stats;
+    break;
+  }
+  if (raw.empty())
+    return;
+  // records grouped by work item, items ascending (= the reference's visiting order)
+  std::vector<uint32_t> order(raw.size());
+  for (size_t k = 0; k < raw.size(); ++k)
+    order[k] = (uint32_t)k;
+  std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return raw[a].state < raw[b].state; });
+  struct Group
+  {
+    int64_t item;
+    size_t begin, end;
+  };
+  std::vector<Group> groups;
+  for (size_t k = 0; k < order.size();)
+  {
+    size_t e = k;
+    while (e < order.size() && raw[order[e]].state == raw[order[k]].state)
+      ++e;
+    groups.push_back({ raw[order[k]].state, k, e });
+    k = e;
+  }
+  const bool first = request.type == ContactTestType::FIRST;
+  if (first && !request.is_valid)
+  {
+    // only the first colliding item of a trajectory is ever reported (core/utils.h:226-231)
+    std::vector<Group> keep;
+    for (const Group& g : groups)
+      if (keep.empty() || item_traj[(size_t)keep.back().item] != item_traj[(size_t)g.item])
+        keep.push_back(g);
+    groups.swap(keep);
+  }
+  // link poses of the selected items, in blocks bounded by the size of the FK output (every scene link)
+  const size_t nl = objects_.size();
+  const size_t block = std::max<size_t>(1, (size_t)(64u << 20) / (nl * 12 * sizeof(double) * (cast_ ? 2 : 1)));
+  std::vector<int64_t> sel;
+  std::vector<double> q0, q1, T0, T1;
+  std::vector<const t4c_contact*> recs;
+  std::vector<const float*> locs;
+  for (size_t g0 = 0; g0 < groups.size(); g0 += block)
+  {
+    const size_t g1 = std::min(groups.size(), g0 + block), nb = g1 - g0;
+    sel.resize(nb);
+    for (size_t g = g0; g < g1; ++g)
+      sel[g - g0] = groups[g].item;
+    q0.resize(nb * (size_t)n_q);
+    T0.resize(nb * nl * 12);
+    if (cast_)
+    {
+      q1.resize(nb * (size_t)n_q);
+      T1.resize(nb * nl * 12);
+    }
+    check(t4c_lvs_item_states(traj, n_traj, n_wp, n_q, lvs, cast_ ? 1 : 0, (int64_t)nb, sel.data(), q0.data(),
+                              cast_ ? q1.data() : nullptr),
+          "t4c_lvs_item_states");
+    check(t4c_fk(model, scene_, q0.data(), (int64_t)nb, T0.data()), "t4c_fk");
+    if (cast_)
+      check(t4c_fk(model, scene_, q1.data(), (int64_t)nb, T1.data()), "t4c_fk");
+    for (size_t g = g0; g < g1; ++g)
+    {
+      const Group& G = groups[g];
+      const size_t t = (size_t)item_traj[(size_t)G.item];
+      if (first && found[t])
+        continue;
+      recs.clear();
+      locs.clear();
+      for (size_t k = G.begin; k < G.end; ++k)
+      {
+        recs.push_back(&raw[order[k]]);
+        locs.push_back(cast_ ? &local[(size_t)order[k] * 6] : nullptr);
+      }
+      ContactResultMap collisions;
+      processRecords(collisions, request, recs.data(), locs.data(), recs.size(), &T0[(g - g0) * nl * 12],
+                     cast_ ? &T1[(g - g0) * nl * 12] : nullptr);
+      if (!collisions.empty())
+      {
+        contacts[t].push_back(std::move(collisions));
+        found[t] = 1;
+      }
+    }
   }
 }
 

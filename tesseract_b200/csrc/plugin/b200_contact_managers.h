@@ -62,6 +62,15 @@ public:
   // returns per-state flags and raw records (t4c_contact.state = state index)
   void checkLinkPoses(const double* poses0, const double* poses1, int64_t n, const ContactRequest& request,
                       std::vector<uint8_t>& hit, std::vector<t4c_contact>& contacts);
+  // planner-facing batched validator: every LVS work item of n_traj trajectories (each n_wp x n_q row-major) in one
+  // device batch; contacts[t] receives what checkTrajectory (tesseract_environment/core/utils.h:172-428) pushes for
+  // trajectory t (one ContactResultMap per colliding state / sub-segment, in visiting order; FIRST stops after the
+  // first), found[t] its return value.  lvs = +infinity: no subdivision (DISCRETE / CONTINUOUS).
+  void checkTrajectories(const t4c_fk_model* model, const double* traj, int64_t n_traj, int32_t n_wp, int32_t n_q,
+                         double lvs, const ContactRequest& request,
+                         std::vector<std::vector<ContactResultMap>>& contacts, std::vector<uint8_t>& found);
+  int objectIndex(const std::string& name) const { return find(name); }
+  bool isCast() const { return cast_; }
   const t4c_stats& lastStats() const { return stats_; }
   t4c_scene* scene();  // synchronised device scene (for the joint-space batched entries of t4c.h)
 
@@ -81,6 +90,10 @@ private:
   void sync();  // rebuild / update the device scene to match the host state
   void run(const double* p0, const double* p1, int64_t n, const ContactRequest& request, int device_type,
            std::vector<uint8_t>* hit, std::vector<t4c_contact>& contacts, std::vector<float>& local);
+  // device records of ONE state -> ContactResult -> processResult; poses0/1 = that state's link poses (null: the
+  // objects' own); returns true when FIRST is satisfied
+  bool processRecords(ContactResultMap& collisions, const ContactRequest& request, const t4c_contact* const* recs,
+                      const float* const* locals, size_t n, const double* poses0, const double* poses1) const;
 
   bool cast_;
   int device_;

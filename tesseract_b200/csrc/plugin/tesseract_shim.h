@@ -104,6 +104,24 @@ using AlignedMap = std::map<K, V>;
 using VectorIsometry3d = AlignedVector<Eigen::Isometry3d>;
 using VectorVector3d = std::vector<Eigen::Vector3d>;
 using TransformMap = AlignedMap<std::string, Eigen::Isometry3d>;
+// Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic, Eigen::RowMajor> (tesseract_common/types.h:52-53):
+// one joint vector per row, contiguous row-major storage
+class TrajArray
+{
+public:
+  TrajArray() = default;
+  TrajArray(long rows, long cols) : rows_(rows), cols_(cols), v_((size_t)(rows * cols), 0.0) {}
+  long rows() const { return rows_; }
+  long cols() const { return cols_; }
+  double& operator()(long r, long c) { return v_[(size_t)(r * cols_ + c)]; }
+  double operator()(long r, long c) const { return v_[(size_t)(r * cols_ + c)]; }
+  const double* data() const { return v_.data(); }
+  double* data() { return v_.data(); }
+
+private:
+  long rows_ = 0, cols_ = 0;
+  std::vector<double> v_;
+};
 using LinkNamesPair = std::pair<std::string, std::string>;
 
 struct PairHash
@@ -403,6 +421,32 @@ struct ContactRequest
   long contact_limit = 0;
   IsContactResultValidFn is_valid = nullptr;
   ContactRequest(ContactTestType type = ContactTestType::ALL) : type(type) {}
+};
+
+// types.h:278-319
+enum class CollisionEvaluatorType
+{
+  DISCRETE,
+  LVS_DISCRETE,
+  CONTINUOUS,
+  LVS_CONTINUOUS
+};
+struct CollisionCheckConfig
+{
+  CollisionCheckConfig(double default_margin = 0, ContactRequest request = ContactRequest(),
+                       CollisionEvaluatorType type = CollisionEvaluatorType::DISCRETE,
+                       double longest_valid_segment_length = 0.005)
+    : collision_margin_data(default_margin)
+    , contact_request(std::move(request))
+    , type(type)
+    , longest_valid_segment_length(longest_valid_segment_length)
+  {
+  }
+  CollisionMarginOverrideType collision_margin_override_type{ CollisionMarginOverrideType::NONE };
+  CollisionMarginData collision_margin_data;
+  ContactRequest contact_request;
+  CollisionEvaluatorType type;
+  double longest_valid_segment_length{ 0.005 };
 };
 
 // discrete_contact_manager.h:65-207

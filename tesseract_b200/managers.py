@@ -252,3 +252,29 @@ class BatchChecker:
 
         return self._run(call, (self.scene.h, self.model, _dp(traj), n_traj, n_wp, float(lvs)), int(n_items.value),
                          test_type, True, True, want_contacts, capacity, cast)
+
+    def lvs_items(self, traj, lvs, cast):
+        """(item_traj, item_step, item_sub) of every LVS work item, in the reference's visiting order
+        (tesseract_environment/core/utils.h:189-205, 328-347)"""
+        traj = np.ascontiguousarray(traj, dtype=np.float64)
+        n_traj, n_wp, n_q = traj.shape
+        n = C.c_int64()
+        capi.check(self.lib.t4c_lvs_count(_dp(traj), n_traj, n_wp, n_q, float(lvs), int(cast), C.byref(n)), self.lib)
+        out = [np.zeros(max(1, n.value), dtype=np.int32) for _ in range(3)]
+        ip = [o.ctypes.data_as(C.POINTER(C.c_int32)) for o in out]
+        capi.check(self.lib.t4c_lvs_items(_dp(traj), n_traj, n_wp, n_q, float(lvs), int(cast), n.value, ip[0], ip[1],
+                                          ip[2], C.byref(n)), self.lib)
+        return tuple(o[:n.value] for o in out)
+
+    def lvs_item_states(self, traj, lvs, cast, items):
+        """joint vectors (q0, q1 or None) of the selected work items (strictly ascending flat indices)"""
+        traj = np.ascontiguousarray(traj, dtype=np.float64)
+        n_traj, n_wp, n_q = traj.shape
+        items = np.ascontiguousarray(items, dtype=np.int64)
+        q0 = np.zeros((len(items), n_q))
+        q1 = np.zeros((len(items), n_q)) if cast else None
+        capi.check(self.lib.t4c_lvs_item_states(_dp(traj), n_traj, n_wp, n_q, float(lvs), int(cast), len(items),
+                                                items.ctypes.data_as(C.POINTER(C.c_int64)), _dp(q0),
+                                                _dp(q1) if cast else None), self.lib)
+        return q0, q1
+

@@ -7,13 +7,14 @@ import subprocess
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-SRC = [os.path.join(ROOT, "tests", "cpp", "test_managers.cpp"),
-       os.path.join(ROOT, "tesseract_b200", "csrc", "plugin", "b200_contact_managers.cpp")]
+PLUGIN = [os.path.join(ROOT, "tesseract_b200", "csrc", "plugin", f)
+          for f in ("b200_contact_managers.cpp", "b200_trajectory_check.cpp")]
 
 
-def build_and_run(libdir, libname, exe):
+def build_and_run(libdir, libname, exe, test="test_managers.cpp"):
     out = os.path.join(ROOT, "tests", "cpp", exe)
-    subprocess.check_call(["g++", "-O2", "-std=c++17", "-Wall", "-Wextra", "-Werror"] + SRC +
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-Wall", "-Wextra", "-Werror",
+                           os.path.join(ROOT, "tests", "cpp", test)] + PLUGIN +
                           ["-o", out, "-L" + libdir, "-l" + libname, "-Wl,-rpath," + libdir])
     r = subprocess.run([out], capture_output=True, text=True, timeout=600)
     print(r.stdout, r.stderr)
@@ -32,6 +33,22 @@ def test_cpp_managers_gpu():
     import __graft_entry__ as g
     g.build()
     build_and_run(os.path.join(ROOT, "tesseract_b200", "csrc"), "t4c", "test_managers_gpu.bin")
+
+
+def test_cpp_trajectory_check_hostsim():
+    """checkTrajectory / checkTrajectories / isValid against the reference's per-state loop"""
+    from hostsim import build as hostsim
+    hostsim.build()
+    build_and_run(os.path.join(ROOT, "tests", "hostsim"), "t4c_hostsim", "test_trajectory_check_hostsim.bin",
+                  "test_trajectory_check.cpp")
+
+
+@pytest.mark.gpu
+def test_cpp_trajectory_check_gpu():
+    import __graft_entry__ as g
+    g.build()
+    build_and_run(os.path.join(ROOT, "tesseract_b200", "csrc"), "t4c", "test_trajectory_check_gpu.bin",
+                  "test_trajectory_check.cpp")
 
 
 def test_plugin_library_exports():
