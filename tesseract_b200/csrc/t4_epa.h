@@ -374,16 +374,23 @@ struct Epa
     }
     if (bad)
       return 1;
+    // new face k = (hz_a[k], hz_b[k], w): its edge 1 continues in the face that starts at hz_b[k], its edge 2 comes
+    // from the face that ends at hz_a[k]; matched on the dense index arrays instead of the face records
     for (int i = 0; i < nnew; ++i)
+    {
+      const int16_t ai = hz_a[i], bi = hz_b[i];
+      int16_t a1 = -1, a2 = -1;
       for (int j = 0; j < nnew; ++j)
       {
-        Face& fi = F[stack[i]];
-        const Face& fj = F[stack[j]];
-        if (fj.v[0] == fi.v[1])
-          fi.adj[1] = stack[j];
-        if (fj.v[1] == fi.v[0])
-          fi.adj[2] = stack[j];
+        if (hz_a[j] == bi)
+          a1 = stack[j];
+        if (hz_b[j] == ai)
+          a2 = stack[j];
       }
+      Face& fi = F[stack[i]];
+      fi.adj[1] = a1;
+      fi.adj[2] = a2;
+    }
     ++it_;
     return 0;
   }

@@ -206,9 +206,25 @@ static int smCount()
   return g_sm_count;
 }
 // grids are a whole number of waves: SM count x resident CTAs per SM, grid-stride over the items
-static int gridFor(int64_t n, int block, int ctas_per_sm)
+// Grid policy of the grid-stride kernels.  Default: one CTA per `block` items, so that the hardware hands the queue
+// out as CTAs retire; a grid capped at the resident CTAs gives every thread a fixed stride of the queue and the
+// slowest warp sets the time (measured r2a: fk -5 %, broad -6 %, cull -15 %, gjk -6 % uncapped; EPA alone is 2-4 %
+// faster capped and keeps the cap).  T4C_GRID_UNCAPPED=0 / T4C_EPA_UNCAPPED=1 flip the two choices.
+static bool envFlag(const char* name, bool dflt)
+{
+  const char* e = std::getenv(name);
+  return e ? (std::atoi(e) != 0) : dflt;
+}
+static bool gridUncapped()
+{
+  static const bool v = envFlag("T4C_GRID_UNCAPPED", true);
+  return v;
+}
+static int gridFor(int64_t n, int block, int ctas_per_sm, bool allow_uncapped = true)
 {
   const int64_t need = (n + block - 1) / block;
+  if (allow_uncapped && gridUncapped())
+    return (int)std::max<int64_t>(1, std::min<int64_t>(need, 0x7fffffff));
   const int64_t full = (int64_t)smCount() * ctas_per_sm;
   return (int)std::max<int64_t>(1, std::min<int64_t>(need, full));
 }
@@ -242,10 +258,10 @@ __global__ void __launch_bounds__(256, T4_CULL_MIN_CTAS) cullKernel(KParams P, i
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     cullBody(i, P);
 }
-void t4LaunchGjk(const KParams& P, int64_t n, int grid, cudaStream_t st);  // t4c_exact.cu (-fmad=false)
+void t4LaunchGjk(const KParams& P, int64_t n, int grid, int block, cudaStream_t st);  // t4c_exact.cu (-fmad=false)
 void t4LaunchLvsCount(const LvsParams& L, int64_t n, int grid, cudaStream_t st);
 void t4LaunchLvsExpand(const LvsParams& L, int64_t n, int grid, cudaStream_t st);
-void t4LaunchEpa(const KParams& P, int64_t n, int grid, cudaStream_t st);
+void t4LaunchEpa(const KParams& P, int64_t n, int grid, int block, cudaStream_t st);
 __global__ void __launch_bounds__(256) closestInsertKernel(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -373,12 +389,34 @@ static void launchBroadStatic(const KParams& P, int64_t n, t4stream st) { T4_LAU
 static void launchBroadStaticGroup(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadStaticGroupKernel, PK_BROAD_STATIC, 256, 4, P, n, st); }
 static void launchBroadActive(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadActiveKernel, PK_BROAD_ACTIVE, 256, 8, P, n, st); }
 static void launchCull(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(cullKernel, PK_CULL, 256, (T4_CULL_MIN_CTAS > 4 ? T4_CULL_MIN_CTAS : 4), P, n, st); }
+// CTA size of the exact kernels: T4C_GJK_BLOCK / T4C_EPA_BLOCK (32, 64, 128; no measurable difference, r2a)
+static int envBlock(const char* name, int dflt)
+{
+  const char* e = std::getenv(name);
+  const int v = e ? std::atoi(e) : dflt;
+  return (v == 32 || v == 64 || v == 128) ? v : dflt;
+}
+static int gjkBlock()
+{
+  static int v = envBlock("T4C_GJK_BLOCK", 128);
+  return v;
+}
+static int epaBlock()
+{
+  static int v = envBlock("T4C_EPA_BLOCK", 128);
+  return v;
+}
+static bool epaUncapped()
+{
+  static const bool v = envFlag("T4C_EPA_UNCAPPED", false);
+  return v;
+}
 static void launchGjk(const KParams& P, int64_t n, t4stream st)
 {
   if (n <= 0)
     return;
   profBegin(PK_GJK, st);
-  t4LaunchGjk(P, n, gridFor(n, 128, 4), st);
+  t4LaunchGjk(P, n, gridFor(n, gjkBlock(), 4 * (128 / gjkBlock())), gjkBlock(), st);
   profEnd(st);
   ++g_launches;
 }
@@ -390,7 +428,8 @@ static int epaCtas()
   if (!v)
   {
     const char* e = std::getenv("T4C_EPA_CTAS");
-    v = e ? std::max(1, std::min(4, std::atoi(e))) : 4;
+    const char* m = std::getenv("T4C_EPA_MINB");
+    v = e ? std::max(1, std::min(6, std::atoi(e))) : (m ? std::max(4, std::min(6, std::atoi(m))) : 4);
   }
   return v;
 }
@@ -399,7 +438,7 @@ static void launchEpa(const KParams& P, int64_t n, t4stream st)
   if (n <= 0)
     return;
   profBegin(PK_EPA, st);
-  t4LaunchEpa(P, n, gridFor(n, 128, epaCtas()), st);
+  t4LaunchEpa(P, n, gridFor(n, epaBlock(), epaCtas() * (128 / epaBlock()), epaUncapped()), epaBlock(), st);
   profEnd(st);
   ++g_launches;
 }

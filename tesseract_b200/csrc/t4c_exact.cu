@@ -39,6 +39,27 @@ __global__ void __launch_bounds__(128, 4) epaKernelR128(KParams P, int64_t n)
     epaBody(i, P, epa);
 }
 
+// experiment knobs: tighter register budgets (T4C_GJK_MINB / T4C_EPA_MINB = 5 -> 96 registers, 6 -> 80 registers)
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) gjkKernelB(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    gjkBody(i, P);
+}
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) epaKernelB(KParams P, int64_t n)
+{
+  Epa<double> epa;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    epaBody(i, P, epa);
+}
+static int envMinB(const char* name)
+{
+  const char* e = std::getenv(name);
+  const int v = e ? std::atoi(e) : 4;
+  return (v == 5 || v == 6) ? v : 4;
+}
+
 // lane-refill GJK (t4_kernels2.h gjkLaneLoop).  Measured 2x SLOWER than the pair-per-thread kernel on B200 (r1g/r1h:
 // the per-lane state machine lives in local memory and every trip reloads it), so it is opt-in: T4C_GJK_LANES=1.
 __global__ void __launch_bounds__(128, 4) gjkLaneKernel(KParams P, int64_t n)
@@ -123,22 +144,32 @@ __global__ void __launch_bounds__(256) lvsExpandKernel(LvsParams L, int64_t n)
 void t4LaunchLvsCount(const LvsParams& L, int64_t n, int grid, cudaStream_t st) { lvsCountKernel<<<grid, 256, 0, st>>>(L, n); }
 void t4LaunchLvsExpand(const LvsParams& L, int64_t n, int grid, cudaStream_t st) { lvsExpandKernel<<<grid, 256, 0, st>>>(L, n); }
 
-void t4LaunchGjk(const KParams& P, int64_t n, int grid, cudaStream_t st)
+void t4LaunchGjk(const KParams& P, int64_t n, int grid, int block, cudaStream_t st)
 {
+  static const int minb = envMinB("T4C_GJK_MINB");
   if (gjkLanes())
     gjkLaneKernel<<<grid, 128, 0, st>>>(P, n);
+  else if (minb == 5)
+    gjkKernelB<5><<<grid, block, 0, st>>>(P, n);
+  else if (minb == 6)
+    gjkKernelB<6><<<grid, block, 0, st>>>(P, n);
   else if (exactRegs() == 128)
-    gjkKernelR128<<<grid, 128, 0, st>>>(P, n);
+    gjkKernelR128<<<grid, block, 0, st>>>(P, n);
   else
-    gjkKernel<<<grid, 128, 0, st>>>(P, n);
+    gjkKernel<<<grid, block, 0, st>>>(P, n);
 }
 
-void t4LaunchEpa(const KParams& P, int64_t n, int grid, cudaStream_t st)
+void t4LaunchEpa(const KParams& P, int64_t n, int grid, int block, cudaStream_t st)
 {
+  static const int minb = envMinB("T4C_EPA_MINB");
   if (epaLanes())
     epaLaneKernel<<<grid, 128, 0, st>>>(P, n);
+  else if (minb == 5)
+    epaKernelB<5><<<grid, block, 0, st>>>(P, n);
+  else if (minb == 6)
+    epaKernelB<6><<<grid, block, 0, st>>>(P, n);
   else if (exactRegs() == 128)
-    epaKernelR128<<<grid, 128, 0, st>>>(P, n);
+    epaKernelR128<<<grid, block, 0, st>>>(P, n);
   else
-    epaKernel<<<grid, 128, 0, st>>>(P, n);
+    epaKernel<<<grid, block, 0, st>>>(P, n);
 }
