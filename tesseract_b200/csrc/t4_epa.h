@@ -36,10 +36,11 @@ struct Epa
   {
     V3<T> n;
     int16_t v[3];
-    int16_t adj[3];
+    int16_t adj[3];  // (neighbour slot << 2) | index of the twin edge in the neighbour; -1: none
     int16_t mark;
     int16_t pad;
   };
+  static constexpr int HZC = 32;  // horizon edges whose new-face plane is kept from the flood fill
   V3<T> W[MAXV], P[MAXV];
   Face F[MAXF];
   // plane distance of every face slot, +large for a free / removed slot: the closest-face search (the most frequent
@@ -49,7 +50,9 @@ struct Epa
   int16_t free_list[MAXF];
   int n_free;
   int16_t stack[MAXF], visible[MAXF];
-  int16_t hz_a[MAXF], hz_b[MAXF], hz_g[MAXF];
+  int16_t hz_a[MAXF], hz_b[MAXF], hz_g[MAXF];  // horizon edge (a -> b) and the packed adjacency entry across it
+  V3<T> hz_n[HZC];
+  T hz_d[HZC];
 
   const ShapeW<T>* A;
   const ShapeW<T>* B;
@@ -214,8 +217,12 @@ struct Epa
     for (int i = 0; i < 4; ++i)
       for (int e = 0; e < 3; ++e)
         for (int j = 0; j < 4; ++j)
-          if (j != i && edgeIndex(F[j], F[i].v[(e + 1) % 3], F[i].v[e]) >= 0)
-            F[i].adj[e] = (int16_t)j;
+          if (j != i)
+          {
+            const int ge = edgeIndex(F[j], F[i].v[(e + 1) % 3], F[i].v[e]);
+            if (ge >= 0)
+              F[i].adj[e] = (int16_t)((j << 2) | ge);
+          }
     mark_ = 0;
     it_ = 0;
     max_iter_ = max_iter;
@@ -270,9 +277,14 @@ struct Epa
     W[nv] = w;
     P[nv] = p;
     ++nv;
-    // visible set: flood fill from the closest face
+    // visible set (flood fill from the closest face) and, in the same pass, its horizon: an edge whose neighbour
+    // fails the visibility test is a horizon edge whatever is found later, and the faces are popped in the order the
+    // two-pass formulation walks them, so the horizon comes out in the same order.  The plane of the new face over
+    // each edge is computed here, while the edge's vertices are at hand, and kept for the first HZC edges.
     ++mark_;
-    int sp_ = 0, nvis = 0;
+    int sp_ = 0, nvis = 0, nh = 0, first_bad = -1;
+    bool degenerate = false;
+    const T tiny = T(1e-14) * (T(1) + w.len2());
     stack[sp_++] = (int16_t)best;
     F[best].mark = (int16_t)mark_;
     while (sp_ > 0)
@@ -281,50 +293,84 @@ struct Epa
       visible[nvis++] = (int16_t)f;
       for (int e = 0; e < 3; ++e)
       {
-        const int g = F[f].adj[e];
-        if (g < 0 || F[g].mark == mark_)
-          continue;
-        if (F[g].n.dot(w) - Fd[g] > T(1e-14))
+        const int a = F[f].adj[e];
+        if (a >= 0)
         {
-          F[g].mark = (int16_t)mark_;
-          stack[sp_++] = (int16_t)g;
+          const int g = a >> 2;
+          if (F[g].mark == mark_)
+            continue;
+          if (F[g].n.dot(w) - Fd[g] > T(1e-14))
+          {
+            F[g].mark = (int16_t)mark_;
+            stack[sp_++] = (int16_t)g;
+            continue;
+          }
+        }
+        const int va = F[f].v[e], vb = F[f].v[(e + 1) % 3];
+        const V3<T> wa = W[va];
+        const V3<T> n = (W[vb] - wa).cross(w - wa);
+        const T l = n.len();
+        if (a >= 0 && l < tiny)
+          degenerate = true;
+        if (nh < MAXF)
+        {
+          hz_a[nh] = (int16_t)va;
+          hz_b[nh] = (int16_t)vb;
+          hz_g[nh] = (int16_t)a;
+          if (nh < HZC)
+          {
+            if (l > T(1e-20))
+            {
+              const V3<T> fn = n * (T(1) / l);
+              hz_n[nh] = fn;
+              hz_d[nh] = fn.dot(wa);
+            }
+            else if (first_bad < 0)
+              first_bad = nh;
+          }
+          ++nh;
         }
       }
     }
-    // horizon; absorb outside neighbours that would give a zero-area new face
-    int nh = 0;
-    for (int guard = 0; guard < 64; ++guard)
+    bool cached = true;
+    if (degenerate)
     {
-      nh = 0;
-      bool grew = false;
-      for (int k = 0; k < nvis && !grew; ++k)
+      // rare: absorb outside neighbours that would give a zero-area new face, and rebuild the horizon
+      cached = false;
+      for (int guard = 0; guard < 64; ++guard)
       {
-        const int f = visible[k];
-        for (int e = 0; e < 3 && !grew; ++e)
+        nh = 0;
+        bool grew = false;
+        for (int k = 0; k < nvis && !grew; ++k)
         {
-          const int g = F[f].adj[e];
-          if (g >= 0 && F[g].mark == mark_)
-            continue;
-          const int va = F[f].v[e], vb = F[f].v[(e + 1) % 3];
-          const V3<T> n = (W[vb] - W[va]).cross(w - W[va]);
-          if (g >= 0 && n.len() < T(1e-14) * (T(1) + w.len2()) && nvis < MAXF)
+          const int f = visible[k];
+          for (int e = 0; e < 3 && !grew; ++e)
           {
-            F[g].mark = (int16_t)mark_;
-            visible[nvis++] = (int16_t)g;
-            grew = true;
-            break;
-          }
-          if (nh < MAXF)
-          {
-            hz_a[nh] = (int16_t)va;
-            hz_b[nh] = (int16_t)vb;
-            hz_g[nh] = (int16_t)g;
-            ++nh;
+            const int a = F[f].adj[e];
+            const int g = a >= 0 ? (a >> 2) : -1;
+            if (g >= 0 && F[g].mark == mark_)
+              continue;
+            const int va = F[f].v[e], vb = F[f].v[(e + 1) % 3];
+            const V3<T> n = (W[vb] - W[va]).cross(w - W[va]);
+            if (g >= 0 && n.len() < tiny && nvis < MAXF)
+            {
+              F[g].mark = (int16_t)mark_;
+              visible[nvis++] = (int16_t)g;
+              grew = true;
+              break;
+            }
+            if (nh < MAXF)
+            {
+              hz_a[nh] = (int16_t)va;
+              hz_b[nh] = (int16_t)vb;
+              hz_g[nh] = (int16_t)a;
+              ++nh;
+            }
           }
         }
+        if (!grew)
+          break;
       }
-      if (!grew)
-        break;
     }
     if (nh < 3)
     {
@@ -352,25 +398,33 @@ struct Epa
       const int slot = allocFace();
       Face nf;
       T nd = 0;
-      if (slot < 0 || !makeFace(hz_a[k], hz_b[k], wi, nf, nd))
+      if (cached && k < HZC)
+      {
+        if (slot < 0 || k == first_bad)
+        {
+          bad = true;
+          break;
+        }
+        nf.v[0] = hz_a[k], nf.v[1] = hz_b[k], nf.v[2] = (int16_t)wi;
+        nf.n = hz_n[k];
+        nd = hz_d[k];
+      }
+      else if (slot < 0 || !makeFace(hz_a[k], hz_b[k], wi, nf, nd))
       {
         bad = true;
         break;
       }
-      nf.adj[0] = hz_g[k];
+      const int a = hz_g[k];
+      nf.adj[0] = (int16_t)a;
+      nf.adj[1] = nf.adj[2] = -1;
       nf.mark = 0;
       F[slot] = nf;
       Fd[slot] = nd;
       stack[nnew++] = (int16_t)slot;
       if (first_new < 0)
         first_new = slot;
-      const int g = hz_g[k];
-      if (g >= 0)
-      {
-        const int ge = edgeIndex(F[g], hz_b[k], hz_a[k]);
-        if (ge >= 0)
-          F[g].adj[ge] = (int16_t)slot;
-      }
+      if (a >= 0)
+        F[a >> 2].adj[a & 3] = (int16_t)(slot << 2);  // twin of the new face's edge 0
     }
     if (bad)
       return 1;
@@ -383,9 +437,9 @@ struct Epa
       for (int j = 0; j < nnew; ++j)
       {
         if (hz_a[j] == bi)
-          a1 = stack[j];
+          a1 = (int16_t)((stack[j] << 2) | 2);  // (b, w) is the twin of that face's (w, a)
         if (hz_b[j] == ai)
-          a2 = stack[j];
+          a2 = (int16_t)((stack[j] << 2) | 1);  // (w, a) is the twin of that face's (b, w)
       }
       Face& fi = F[stack[i]];
       fi.adj[1] = a1;

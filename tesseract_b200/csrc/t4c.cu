@@ -240,6 +240,13 @@ __global__ void __launch_bounds__(256) broadStaticKernel(KParams P, int64_t n)
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     broadStaticBody(i, P);
 }
+// experiment knob T4C_BROAD_MINB = 5 | 6 | 8: tighter register budgets (48 / 40 / 32) for more resident warps
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB) broadStaticKernelB(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    broadStaticBody(i, P);
+}
 __global__ void __launch_bounds__(256) broadStaticGroupKernel(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -385,7 +392,21 @@ static void launchFk(const KParams& P, int64_t n, t4stream st)
   ++g_launches;
 }
 static void launchConvert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(convertPosesKernel, PK_CONVERT, 256, 8, P, n, st); }
-static void launchBroadStatic(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadStaticKernel, PK_BROAD_STATIC, 256, 8, P, n, st); }
+static void launchBroadStatic(const KParams& P, int64_t n, t4stream st)
+{
+  static const int minb = [] {
+    const char* e = std::getenv("T4C_BROAD_MINB");
+    return e ? std::atoi(e) : 0;
+  }();
+  if (minb == 5)
+    T4_LAUNCH(broadStaticKernelB<5>, PK_BROAD_STATIC, 256, 8, P, n, st);
+  else if (minb == 6)
+    T4_LAUNCH(broadStaticKernelB<6>, PK_BROAD_STATIC, 256, 8, P, n, st);
+  else if (minb == 8)
+    T4_LAUNCH(broadStaticKernelB<8>, PK_BROAD_STATIC, 256, 8, P, n, st);
+  else
+    T4_LAUNCH(broadStaticKernel, PK_BROAD_STATIC, 256, 8, P, n, st);
+}
 static void launchBroadStaticGroup(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadStaticGroupKernel, PK_BROAD_STATIC, 256, 4, P, n, st); }
 static void launchBroadActive(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadActiveKernel, PK_BROAD_ACTIVE, 256, 8, P, n, st); }
 static void launchCull(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(cullKernel, PK_CULL, 256, (T4_CULL_MIN_CTAS > 4 ? T4_CULL_MIN_CTAS : 4), P, n, st); }
