@@ -37,8 +37,7 @@ struct Epa
     V3<T> n;
     int16_t v[3];
     int16_t adj[3];  // (neighbour slot << 2) | index of the twin edge in the neighbour; -1: none
-    int16_t mark;
-    int16_t pad;
+    int16_t pad[2];
   };
   static constexpr int HZC = 32;  // horizon edges whose new-face plane is kept from the flood fill
   V3<T> W[MAXV], P[MAXV];
@@ -46,6 +45,8 @@ struct Epa
   // plane distance of every face slot, +large for a free / removed slot: the closest-face search (the most frequent
   // memory access of an iteration) reads one dense array instead of two fields of 48-byte records
   T Fd[MAXF];
+  // visit stamp of every face slot (dense for the same reason: three look-ups per face of the flood fill)
+  int16_t Fm[MAXF];
   int nv, nf_hi;         // vertices used; high-water mark of face slots
   int16_t free_list[MAXF];
   int n_free;
@@ -140,7 +141,6 @@ struct Epa
       return false;
     f.n = n * (T(1) / l);
     d = f.n.dot(W[a]);
-    f.mark = 0;
     return true;
   }
   T4_HD int allocFace()
@@ -212,6 +212,7 @@ struct Epa
     {
       if (!makeFace(tet[i][0], tet[i][1], tet[i][2], F[i], Fd[i]))
         return false;
+      Fm[i] = 0;
       ++nf_hi;
     }
     for (int i = 0; i < 4; ++i)
@@ -286,7 +287,7 @@ struct Epa
     bool degenerate = false;
     const T tiny = T(1e-14) * (T(1) + w.len2());
     stack[sp_++] = (int16_t)best;
-    F[best].mark = (int16_t)mark_;
+    Fm[best] = (int16_t)mark_;
     while (sp_ > 0)
     {
       const int f = stack[--sp_];
@@ -297,11 +298,11 @@ struct Epa
         if (a >= 0)
         {
           const int g = a >> 2;
-          if (F[g].mark == mark_)
+          if (Fm[g] == mark_)
             continue;
           if (F[g].n.dot(w) - Fd[g] > T(1e-14))
           {
-            F[g].mark = (int16_t)mark_;
+            Fm[g] = (int16_t)mark_;
             stack[sp_++] = (int16_t)g;
             continue;
           }
@@ -348,13 +349,13 @@ struct Epa
           {
             const int a = F[f].adj[e];
             const int g = a >= 0 ? (a >> 2) : -1;
-            if (g >= 0 && F[g].mark == mark_)
+            if (g >= 0 && Fm[g] == mark_)
               continue;
             const int va = F[f].v[e], vb = F[f].v[(e + 1) % 3];
             const V3<T> n = (W[vb] - W[va]).cross(w - W[va]);
             if (g >= 0 && n.len() < tiny && nvis < MAXF)
             {
-              F[g].mark = (int16_t)mark_;
+              Fm[g] = (int16_t)mark_;
               visible[nvis++] = (int16_t)g;
               grew = true;
               break;
@@ -417,8 +418,8 @@ struct Epa
       const int a = hz_g[k];
       nf.adj[0] = (int16_t)a;
       nf.adj[1] = nf.adj[2] = -1;
-      nf.mark = 0;
       F[slot] = nf;
+      Fm[slot] = 0;
       Fd[slot] = nd;
       stack[nnew++] = (int16_t)slot;
       if (first_new < 0)
