@@ -59,6 +59,7 @@ static bool zero(void* d, size_t n, t4stream) { std::memset(d, 0, n); return tru
 static bool fill(void* d, int v, size_t n, t4stream) { std::memset(d, v, n); return true; }
 static bool sync(t4stream) { return true; }
 static t4stream newStream() { return nullptr; }
+static bool isPinned(const void*) { return true; }  // exercises the progressive-copy logic in the host simulator
 static void freeStream(t4stream) {}
 static const char* lastError() { return "hostsim"; }
 }  // namespace plat
@@ -114,6 +115,17 @@ static void freeStream(t4stream s)
 {
   if (s)
     cudaStreamDestroy(s);
+}
+// page-locked host memory: the only kind an asynchronous copy does not stage through the launching thread
+static bool isPinned(const void* p)
+{
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess)
+  {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeHost;
 }
 static const char* lastError() { return cudaGetErrorString(g_last); }
 }  // namespace plat
@@ -541,6 +553,7 @@ struct t4c_scene
   unsigned long long uploaded = 0;  // rev of the device copy
   CompiledScene comp;
   t4stream stream = nullptr;
+  t4stream copy_stream = nullptr;  // progressive download of finished contact records (hostRun)
   // device scene
   DevBuf d_shapes, d_statics, d_verts, d_sup_cells, d_sup_cand, d_bvh, d_active, d_aa, d_acm, d_margin, d_shape_d, d_statics_d;
   // per-call workspace
@@ -557,6 +570,7 @@ struct t4c_scene
   {
     fk.clear();
     plat::freeStream(stream);
+    plat::freeStream(copy_stream);
   }
 };
 
@@ -708,6 +722,10 @@ struct BatchIO
   t4c_contact* contacts = nullptr;
   float* cc_local = nullptr;
   int64_t capacity = 0;
+  // host-buffer entries with a page-locked result buffer: records are downloaded on the scene's copy stream as soon
+  // as they are final, while later rounds / chunks compute; host_copied = records already on their way
+  t4c_contact* host_contacts = nullptr;
+  int64_t host_copied = 0;
   // results
   int64_t n_contacts = 0;
   t4c_stats stats{};
@@ -835,6 +853,23 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
   const int64_t CH = chunkStates();
   int64_t total = 0;
   const size_t qelem = io.q_layout == T4C_Q_F64_ROWMAJOR ? sizeof(double) : sizeof(float);
+  // records [0, upto) are final on the device (the compute stream has just been synchronised): send what is new to
+  // the caller's page-locked buffer on the copy stream, under the kernels that follow
+  auto drain = [&](int64_t upto) -> bool {
+    if (!io.host_contacts || !io.contacts)
+      return true;
+    upto = std::min<int64_t>(upto, io.capacity);
+    static const int64_t min_records = [] {
+      const char* e = std::getenv("T4C_DRAIN_MIN");  // tests: 1 = copy after every round / chunk
+      return e ? std::max<long long>(1, std::atoll(e)) : 4096;
+    }();
+    if (upto - io.host_copied < min_records)
+      return true;
+    const bool ok = plat::d2h(io.host_contacts + io.host_copied, io.contacts + io.host_copied,
+                              (size_t)(upto - io.host_copied) * sizeof(t4c_contact), s->copy_stream);
+    io.host_copied = upto;
+    return ok;
+  };
   for (int64_t base = 0; base < io.n; base += CH)
   {
     const int64_t nc = std::min<int64_t>(CH, io.n - base);
@@ -1021,6 +1056,8 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       P.cull_base = cand_begin;
       launchCull(P, ncand - cand_begin, st);
       T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "cull");
+      if (!closest)
+        T4_TRY(drain(total + qc[Q_RAW]), "contact download");  // the records of the earlier rounds
       cand_begin = ncand;
       const uint32_t nsurv = qc[Q_SURV];
       nsurv2 = qc[Q_SURV2], nsurv3 = qc[Q_SURV3], nsurv4 = qc[Q_SURV4];
@@ -1079,6 +1116,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     }
     else
       total += nraw;
+    T4_TRY(drain(total), "contact download");  // this chunk's records, under the next chunk
     launchCountHit(P, nc, st);
     T4_TRY(launchOk() && plat::d2h(stats_host, P.stats, sizeof(stats_host), st) && plat::sync(st), "stats");
   }
@@ -1153,6 +1191,8 @@ static t4c_status hostRun(t4c_scene* s, BatchIO& io, const double* hq0, const do
     T4_TRY(s->d_out.ensure((size_t)std::max<int64_t>(r->capacity, 1) * sizeof(t4c_contact)), "workspace");
     io.contacts = s->d_out.as<t4c_contact>();
     io.capacity = r->capacity;
+    if (s->copy_stream || !s->stream)
+      io.host_contacts = plat::isPinned(r->contacts) ? r->contacts : nullptr;
     if (r->cc_local && io.cast)
     {
       T4_TRY(s->d_out_local.ensure((size_t)std::max<int64_t>(r->capacity, 1) * 6 * sizeof(float)), "workspace");
@@ -1163,13 +1203,20 @@ static t4c_status hostRun(t4c_scene* s, BatchIO& io, const double* hq0, const do
   r->n_contacts = io.n_contacts;
   r->stats = io.stats;
   if (rc != T4C_OK && rc != T4C_ERR_CAPACITY)
+  {
+    if (io.host_copied > 0)
+      plat::sync(s->copy_stream);  // nothing may still be writing into the caller's buffer after the return
     return rc;
+  }
   const int64_t ncopy = std::min<int64_t>(io.n_contacts, r->capacity);
   bool ok = true;
   if (r->hit)
     ok = ok && plat::d2h(r->hit, io.hit, (size_t)io.n, st);
-  if (r->contacts)
-    ok = ok && plat::d2h(r->contacts, io.contacts, (size_t)ncopy * sizeof(t4c_contact), st);
+  if (r->contacts && ncopy > io.host_copied)
+    ok = ok && plat::d2h(r->contacts + io.host_copied, io.contacts + io.host_copied,
+                         (size_t)(ncopy - io.host_copied) * sizeof(t4c_contact), st);
+  if (io.host_copied > 0)
+    ok = ok && plat::sync(s->copy_stream);
   if (r->contacts && r->cc_local && io.cast)
     ok = ok && plat::d2h(r->cc_local, io.cc_local, (size_t)ncopy * 6 * sizeof(float), st);
   T4_TRY(ok && plat::sync(st), "download results");
@@ -1306,6 +1353,7 @@ t4c_status t4c_scene_create(const t4c_scene_desc* d, int32_t device, t4c_scene**
   for (int i = 0; i < d->n_margin_pairs; ++i)
     H.pair_margins[hostPairKey(d->margin_pairs[2 * i], d->margin_pairs[2 * i + 1])] = d->margin_values[i];
   s->stream = plat::newStream();
+  s->copy_stream = plat::newStream();
   t4c_status rc = syncScene(s.get());
   if (rc != T4C_OK)
     return rc;
@@ -1323,6 +1371,7 @@ t4c_status t4c_scene_clone(const t4c_scene* src, t4c_scene** out)
   if (!plat::setDevice(s->device))
     return fail(T4C_ERR_CUDA, "cudaSetDevice(%d): %s", s->device, plat::lastError());
   s->stream = plat::newStream();
+  s->copy_stream = plat::newStream();
   t4c_status rc = syncScene(s.get());
   if (rc != T4C_OK)
     return rc;
