@@ -60,6 +60,11 @@ static bool fill(void* d, int v, size_t n, t4stream) { std::memset(d, v, n); ret
 static bool sync(t4stream) { return true; }
 static t4stream newStream() { return nullptr; }
 static bool isPinned(const void*) { return true; }  // exercises the progressive-copy logic in the host simulator
+typedef void* t4event;
+static t4event newEvent() { return nullptr; }
+static void freeEvent(t4event) {}
+static bool record(t4event, t4stream) { return true; }
+static bool wait(t4stream, t4event) { return true; }
 static void freeStream(t4stream) {}
 static const char* lastError() { return "hostsim"; }
 }  // namespace plat
@@ -116,6 +121,21 @@ static void freeStream(t4stream s)
   if (s)
     cudaStreamDestroy(s);
 }
+typedef cudaEvent_t t4event;
+static t4event newEvent()
+{
+  cudaEvent_t e = nullptr;
+  if (!chk(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)))
+    return nullptr;
+  return e;
+}
+static void freeEvent(t4event e)
+{
+  if (e)
+    cudaEventDestroy(e);
+}
+static bool record(t4event e, t4stream st) { return chk(cudaEventRecord(e, st)); }
+static bool wait(t4stream st, t4event e) { return chk(cudaStreamWaitEvent(st, e, 0)); }
 // page-locked host memory: the only kind an asynchronous copy does not stage through the launching thread
 static bool isPinned(const void* p)
 {
@@ -241,7 +261,7 @@ static int gridFor(int64_t n, int block, int ctas_per_sm, bool allow_uncapped = 
   return (int)std::max<int64_t>(1, std::min<int64_t>(need, full));
 }
 
-void t4LaunchFk(const KParams& P, int64_t n, int grid, cudaStream_t st);  // t4c_exact.cu (-fmad=false)
+void t4LaunchFk(const KParams& P, int64_t first, int64_t n, int grid, cudaStream_t st);  // t4c_exact.cu (-fmad=false)
 __global__ void __launch_bounds__(256) convertPosesKernel(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -394,12 +414,12 @@ static void profResolve()
     }                                                                                                                  \
   } while (0)
 static bool launchOk() { return plat::chk(cudaGetLastError()); }
-static void launchFk(const KParams& P, int64_t n, t4stream st)
+static void launchFk(const KParams& P, int64_t first, int64_t n, t4stream st)
 {
   if (n <= 0)
     return;
   profBegin(PK_FK, st);
-  t4LaunchFk(P, n, gridFor(n, 128, 8), st);
+  t4LaunchFk(P, first, n, gridFor(n, 128, 8), st);
   profEnd(st);
   ++g_launches;
 }
@@ -488,7 +508,11 @@ static void launchCountHit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH
       ++g_launches;                                                                                                    \
   } while (0)
 static bool launchOk() { return true; }
-static void launchFk(const KParams& P, int64_t n, t4stream) { T4_SERIAL(fkBody, P, n); }
+static void launchFk(const KParams& P, int64_t first, int64_t n, t4stream)
+{
+  for (int64_t i = 0; i < n; ++i)
+    fkBody(first + i, P);
+}
 static void launchConvert(const KParams& P, int64_t n, t4stream) { T4_SERIAL(convertPosesBody, P, n); }
 static void launchBroadStatic(const KParams& P, int64_t n, t4stream) { T4_SERIAL(broadStaticBody, P, n); }
 static void launchBroadStaticGroup(const KParams& P, int64_t n, t4stream) { T4_SERIAL(broadStaticGroupBody, P, n); }
@@ -554,6 +578,7 @@ struct t4c_scene
   CompiledScene comp;
   t4stream stream = nullptr;
   t4stream copy_stream = nullptr;  // progressive download of finished contact records (hostRun)
+  plat::t4event q_events[4] = { nullptr, nullptr, nullptr, nullptr };  // piecewise upload of q (hostRun)
   // device scene
   DevBuf d_shapes, d_statics, d_verts, d_sup_cells, d_sup_cand, d_bvh, d_active, d_aa, d_acm, d_margin, d_shape_d, d_statics_d;
   // per-call workspace
@@ -571,6 +596,8 @@ struct t4c_scene
     fk.clear();
     plat::freeStream(stream);
     plat::freeStream(copy_stream);
+    for (auto& e : q_events)
+      plat::freeEvent(e);
   }
 };
 
@@ -726,6 +753,10 @@ struct BatchIO
   // as they are final, while later rounds / chunks compute; host_copied = records already on their way
   t4c_contact* host_contacts = nullptr;
   int64_t host_copied = 0;
+  // q arrives in q_pieces uploads of q_piece_states states each on the copy stream (event k = piece k is resident):
+  // FK runs piece by piece under the rest of the upload
+  int q_pieces = 0;
+  int64_t q_piece_states = 0;
   // results
   int64_t n_contacts = 0;
   t4c_stats stats{};
@@ -894,7 +925,20 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       const size_t qoff = io.q_layout == T4C_Q_F32_SOA ? (size_t)base : (size_t)base * (size_t)io.model->n_q;
       P.q0 = (const char*)io.q0 + qoff * qelem;
       P.q1 = io.q1 ? (const char*)io.q1 + qoff * qelem : nullptr;
-      launchFk(P, nc, st);
+      if (io.q_pieces > 0)
+      {
+        for (int k = 0; k < io.q_pieces; ++k)
+        {
+          const int64_t a = std::max<int64_t>(base, (int64_t)k * io.q_piece_states);
+          const int64_t b = std::min<int64_t>(base + nc, (int64_t)(k + 1) * io.q_piece_states);
+          if (a >= b)
+            continue;
+          T4_TRY(plat::wait(st, s->q_events[k]), "upload q");
+          launchFk(P, a - base, b - a, st);
+        }
+      }
+      else
+        launchFk(P, 0, nc, st);
     }
     else if (na > 0)
     {
@@ -1160,13 +1204,44 @@ static t4c_status hostRun(t4c_scene* s, BatchIO& io, const double* hq0, const do
   }
   else if (io.model)
   {
-    const size_t qb = (size_t)io.n * (size_t)io.model->n_q * sizeof(double);
-    T4_TRY(s->d_q0.ensure(qb) && plat::h2d(s->d_q0.p, hq0, qb, st), "upload q");
+    const size_t row = (size_t)io.model->n_q * sizeof(double);
+    const size_t qb = (size_t)io.n * row;
+    T4_TRY(s->d_q0.ensure(qb) && (!io.cast || s->d_q1.ensure(qb)), "workspace");
     io.q0 = s->d_q0.p;
     if (io.cast)
-    {
-      T4_TRY(s->d_q1.ensure(qb) && plat::h2d(s->d_q1.p, hq1, qb, st), "upload q1");
       io.q1 = s->d_q1.p;
+    static const int64_t piece_min = [] {
+      const char* e = std::getenv("T4C_UPLOAD_PIECE_MIN");  // tests: small values force the piecewise path
+      return e ? std::max<long long>(1, std::atoll(e)) : 65536;
+    }();
+    const bool pieces = io.n >= 4 * piece_min && ((s->copy_stream && s->q_events[3]) || !s->stream) &&
+                        plat::isPinned(hq0) && (!io.cast || plat::isPinned(hq1));
+    if (pieces)
+    {
+      // four uploads on the copy stream; FK of piece k starts when piece k is resident (runBatch)
+      io.q_pieces = 4;
+      io.q_piece_states = (io.n + 3) / 4;
+      for (int k = 0; k < 4; ++k)
+      {
+        const int64_t a = (int64_t)k * io.q_piece_states, b = std::min<int64_t>(io.n, a + io.q_piece_states);
+        if (a >= b)
+        {
+          io.q_pieces = k;
+          break;
+        }
+        bool ok = plat::h2d((char*)s->d_q0.p + (size_t)a * row, (const char*)hq0 + (size_t)a * row,
+                            (size_t)(b - a) * row, s->copy_stream);
+        if (io.cast)
+          ok = ok && plat::h2d((char*)s->d_q1.p + (size_t)a * row, (const char*)hq1 + (size_t)a * row,
+                               (size_t)(b - a) * row, s->copy_stream);
+        T4_TRY(ok && plat::record(s->q_events[k], s->copy_stream), "upload q");
+      }
+    }
+    else
+    {
+      T4_TRY(plat::h2d(s->d_q0.p, hq0, qb, st), "upload q");
+      if (io.cast)
+        T4_TRY(plat::h2d(s->d_q1.p, hq1, qb, st), "upload q1");
     }
     io.q_layout = T4C_Q_F64_ROWMAJOR;
   }
@@ -1354,6 +1429,8 @@ t4c_status t4c_scene_create(const t4c_scene_desc* d, int32_t device, t4c_scene**
     H.pair_margins[hostPairKey(d->margin_pairs[2 * i], d->margin_pairs[2 * i + 1])] = d->margin_values[i];
   s->stream = plat::newStream();
   s->copy_stream = plat::newStream();
+  for (auto& e : s->q_events)
+    e = plat::newEvent();
   t4c_status rc = syncScene(s.get());
   if (rc != T4C_OK)
     return rc;
@@ -1372,6 +1449,8 @@ t4c_status t4c_scene_clone(const t4c_scene* src, t4c_scene** out)
     return fail(T4C_ERR_CUDA, "cudaSetDevice(%d): %s", s->device, plat::lastError());
   s->stream = plat::newStream();
   s->copy_stream = plat::newStream();
+  for (auto& e : s->q_events)
+    e = plat::newEvent();
   t4c_status rc = syncScene(s.get());
   if (rc != T4C_OK)
     return rc;
@@ -1512,7 +1591,7 @@ t4c_status t4c_fk(const t4c_fk_model* m, const t4c_scene* scene_c, const double*
     P.q_stride_n = nc;
     P.cast = 0;
     P.fk_out = s->d_fk_out.as<double>();
-    launchFk(P, nc, st);
+    launchFk(P, 0, nc, st);
     T4_TRY(launchOk() && plat::d2h(link_poses + (size_t)base * nl * 12, P.fk_out, ob, st) && plat::sync(st), "FK");
   }
   return T4C_OK;

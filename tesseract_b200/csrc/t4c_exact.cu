@@ -109,25 +109,26 @@ static int exactRegs()
 }
 
 // FK feeds the exact pass: same two-rounding arithmetic so that link poses equal the reference's FP64 FK
-__global__ void __launch_bounds__(128) fkKernel(KParams P, int64_t n)
+// states [first, first + n) of the chunk (the host-buffer entries run FK piecewise under the upload of q)
+__global__ void __launch_bounds__(128) fkKernel(KParams P, int64_t first, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    fkBody(i, P);
+    fkBody(first + i, P);
 }
 
 // robots with at most 16 joints (iiwa: 9, IRB2400: 8) keep the joint frames in a 1.5 KB frame instead of 6 KB
-__global__ void __launch_bounds__(128) fkKernel16(KParams P, int64_t n)
+__global__ void __launch_bounds__(128) fkKernel16(KParams P, int64_t first, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    fkBodyT<16>(i, P);
+    fkBodyT<16>(first + i, P);
 }
 
-void t4LaunchFk(const KParams& P, int64_t n, int grid, cudaStream_t st)
+void t4LaunchFk(const KParams& P, int64_t first, int64_t n, int grid, cudaStream_t st)
 {
   if (P.n_joints <= 16)
-    fkKernel16<<<grid, 128, 0, st>>>(P, n);
+    fkKernel16<<<grid, 128, 0, st>>>(P, first, n);
   else
-    fkKernel<<<grid, 128, 0, st>>>(P, n);
+    fkKernel<<<grid, 128, 0, st>>>(P, first, n);
 }
 
 // LVS subdivision: FP64, two roundings per a*b+c like the host formula it restates (Eigen LinSpaced)
