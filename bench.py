@@ -62,6 +62,25 @@ class ClockSampler:
         self.t = threading.Thread(target=self.run, daemon=True)
 
     def run(self):
+        # in-process NVML first: spawning nvidia-smi every 200 ms initialises NVML on every GPU of the box each time
+        # and was measured to skew the ranks of a multi-GPU run by ~5 ms per step (profiles/README, r2f)
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            bits = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20),
+                    ("sw_power_cap", 0x4))
+            get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            while not self.stop_flag:
+                r = int(get_reasons(h))
+                self.rows.append([str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(mx), "0"] +
+                                 ["Active" if r & b else "Not Active" for _, b in bits])
+                time.sleep(0.05)
+            return
+        except Exception:
+            pass
         q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
              "clocks_event_reasons.sw_power_cap")
@@ -195,26 +214,34 @@ def main():
             if gather:
                 gather()
         total_ms, last = 0.0, None
+        gather_ms[0] = 0.0
         for _ in range(steps):
             flush.zero_()
             barrier()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0, em, e1 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
             e0.record()
             last = fn()          # synchronous C-ABI call: kernels run on the library's stream and are joined here
+            em.record()
             if gather:
                 gather()
             e1.record()
             torch.cuda.synchronize()
-            ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+            ms = torch.tensor([e0.elapsed_time(e1), em.elapsed_time(e1)], device=dev)
             if world > 1:
                 dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-            total_ms += float(ms.item())
+            total_ms += float(ms[0].item())
+            gather_ms[0] += float(ms[1].item()) / steps  # result exchange incl. waiting for the slowest rank
         return total_ms / steps, last
 
+    gather_ms = [0.0]
+    gather_kind = os.environ.get("T4_BENCH_GATHER", "gather")
     gathered = [torch.empty(n, dtype=torch.uint8, device=dev) for _ in range(world)] if (world > 1 and rank == 0) else None
+    gathered_all = torch.empty(world * n, dtype=torch.uint8, device=dev) if (world > 1 and gather_kind == "allgather") else None
 
     def gather_hits():
-        if world > 1:
+        if world > 1 and gather_kind == "allgather":
+            dist.all_gather_into_tensor(gathered_all, hit_dev)
+        elif world > 1:
             dist.gather(hit_dev, gathered, dst=0)  # the single result exchange (north_star): flags to rank 0 over NVLink
 
     sampler = ClockSampler(local_rank)
@@ -227,6 +254,18 @@ def main():
     launches0 = lib.t4c_kernel_launch_count()
     sampler.start()
     ms_dev, io = timed(step_device, args.steps, 0, gather_hits)
+    exchange_ms = gather_ms[0]
+    collective_ms = None
+    if world > 1:
+        # the collective alone, ranks aligned by a barrier: separates its own cost from the wait for the slowest rank
+        barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        for _ in range(10):
+            gather_hits()
+        c1.record()
+        torch.cuda.synchronize()
+        collective_ms = c0.elapsed_time(c1) / 10
     clocks = sampler.stop()
     launches = int(lib.t4c_kernel_launch_count() - launches0)
     prof = capi.profile_get(lib)
@@ -294,7 +333,10 @@ def main():
                "config": workload(args), "clocks": clocks, "gpu_launches": launches,
                "e2e": {"value": world * n / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                        "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
-               "roofline": roof, "cpu_baseline": cpu, "stats_per_step": stats, "mode": args.mode}
+               "roofline": roof, "cpu_baseline": cpu, "stats_per_step": stats, "mode": args.mode,
+               "exchange": {"kind": ("none" if world == 1 else gather_kind), "ms_per_step": exchange_ms,
+                            "collective_only_ms": collective_ms,
+                            "note": "hit flags to rank 0; includes waiting for the slowest rank"}}
         print(json.dumps(out))
     lib.t4c_fk_model_destroy(model)
     lib.t4c_scene_destroy(scene)

@@ -123,6 +123,7 @@ struct KParams
   uint32_t* cand_state;
   uint32_t* cand_a;
   uint32_t* cand_b;
+  uint8_t* cand_class;    // per candidate: iterations the FP32 cull needed (sort key of the exact queues) or null
   uint32_t cand_cap;
   uint32_t cull_base;  // first candidate of the range the cull kernel works on (FIRST in rounds: candidates append)
   uint32_t* surv;      // queue read by the GJK kernel in this launch

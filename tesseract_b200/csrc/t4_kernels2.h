@@ -86,6 +86,8 @@ T4_KD void cullBody(int64_t item, const KParams& P)
   loadPairShapes<float>(P, s, a, b, A, B);
   if (!A.cast && !B.cast && analyticPair(A.type, B.type))
   {
+    if (P.cand_class)
+      P.cand_class[c] = 0;
     pushSurvivor(P, (uint32_t)c, first_rec ? 3 : 0);
     return;
   }
@@ -117,6 +119,8 @@ T4_KD void cullBody(int64_t item, const KParams& P)
   statAdd(P.stats, ST_GJK_ITERS, (uint32_t)g.iters);
   if (st == GJK_FAR)
     return;
+  if (P.cand_class)  // the exact pass of this pair will need about as many iterations: keeps a warp's lanes in step
+    P.cand_class[c] = (uint8_t)(g.iters < 63 ? g.iters : 63);
   if (st == GJK_SEPARATED && !P.calc_dist)
     return;
   if (P.hit_only)

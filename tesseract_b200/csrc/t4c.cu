@@ -319,7 +319,7 @@ __global__ void __launch_bounds__(256) countHitKernel(KParams P, int64_t n)
 // sort key of a queued pair: (type of shape A, type of shape B).  Sorting the survivor / EPA task queues by it puts
 // pairs that take the same branches of the support mapping (and similar iteration counts: EPA needs ~7 iterations
 // against boxes and spheres, 15-75 against cylinders) into the same warps.
-__global__ void __launch_bounds__(256) typeKeyKernel(KParams P, const uint32_t* queue, int from_tasks, uint8_t* keys,
+__global__ void __launch_bounds__(256) typeKeyKernel(KParams P, const uint32_t* queue, int from_tasks, uint16_t* keys,
                                                     uint32_t* idx, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -328,7 +328,9 @@ __global__ void __launch_bounds__(256) typeKeyKernel(KParams P, const uint32_t* 
     // major: type of B (the environment primitive in robot-vs-environment pairs), then type of A, then which shape A is
     // (same hull vertices / support table inside a warp)
     const uint32_t a = P.cand_a[c];
-    keys[i] = (uint8_t)(((P.shapes[P.cand_b[c]].type & 7) << 5) | ((P.shapes[a].type & 3) << 3) | (a & 7u));
+    // minor (survivor queues only): the iteration count of the FP32 cull, a predictor of the exact pass's
+    const uint32_t cls = (!from_tasks && P.cand_class) ? P.cand_class[c] : 0u;
+    keys[i] = (uint16_t)(((((P.shapes[P.cand_b[c]].type & 7) << 5) | ((P.shapes[a].type & 3) << 3) | (a & 7u)) << 6) | cls);
     if (from_tasks)
       idx[i] = (uint32_t)i;
   }
@@ -583,7 +585,7 @@ struct t4c_scene
   DevBuf d_shapes, d_statics, d_verts, d_sup_cells, d_sup_cand, d_bvh, d_active, d_aa, d_acm, d_margin, d_shape_d, d_statics_d;
   // per-call workspace
   DevBuf d_q0, d_q1, d_pin0, d_pin1, d_poses0, d_poses1, d_poses0d, d_poses1d;
-  DevBuf d_cand_state, d_cand_a, d_cand_b, d_surv, d_surv2, d_surv3, d_surv4, d_cull_claim, d_tasks;
+  DevBuf d_cand_state, d_cand_a, d_cand_b, d_cand_class, d_surv, d_surv2, d_surv3, d_surv4, d_cull_claim, d_tasks;
   DevBuf d_qcount, d_stats, d_hit, d_claim, d_raw, d_raw_local, d_raw_d64, d_ht_rep, d_ht_best;
   DevBuf d_out, d_out_local, d_fk_out, d_hit_full;
   DevBuf d_traj, d_lvs_counts, d_lvs_offsets, d_lvs_tmp;
@@ -769,6 +771,17 @@ static int64_t roundMinStates()
   return e ? std::max<long long>(1, std::atoll(e)) : 16384;
 }
 
+// survivor queues are sorted by (types, iteration count of the FP32 cull): the exact pass of a pair needs about as many
+// iterations as its cull did, so a warp's lanes finish together (GJK -6 %, r2g).  T4C_SORT_CLASS=0: types alone
+static bool sortClass()
+{
+  static const bool v = [] {
+    const char* e = std::getenv("T4C_SORT_CLASS");
+    return !e || std::atoi(e) != 0;
+  }();
+  return v;
+}
+
 static int maxRounds()
 {
   const char* e = std::getenv("T4C_ROUNDS");
@@ -827,19 +840,21 @@ static const uint32_t* sortByType(t4c_scene* s, const KParams& P, const uint32_t
   if (!sortQueues() || n < 4096)
     return nullptr;
   t4stream st = s->stream;
-  if (!(s->d_sort_keys.ensure(n) && s->d_sort_keys2.ensure(n) && s->d_sort_vals.ensure((size_t)n * 4) &&
+  if (!(s->d_sort_keys.ensure((size_t)n * 2) && s->d_sort_keys2.ensure((size_t)n * 2) && s->d_sort_vals.ensure((size_t)n * 4) &&
         s->d_sort_idx.ensure((size_t)n * 4)))
     return nullptr;
-  typeKeyKernel<<<gridFor(n, 256, 8), 256, 0, st>>>(P, queue, from_tasks, s->d_sort_keys.as<uint8_t>(),
+  typeKeyKernel<<<gridFor(n, 256, 8), 256, 0, st>>>(P, queue, from_tasks, s->d_sort_keys.as<uint16_t>(),
                                                     s->d_sort_idx.as<uint32_t>(), (int64_t)n);
   ++g_launches;
   const uint32_t* vals_in = from_tasks ? s->d_sort_idx.as<uint32_t>() : queue;
   size_t tmp = 0;
-  if (cub::DeviceRadixSort::SortPairs(nullptr, tmp, s->d_sort_keys.as<uint8_t>(), s->d_sort_keys2.as<uint8_t>(), vals_in,
-                                      s->d_sort_vals.as<uint32_t>(), (int)n, 0, 8, st) != cudaSuccess ||
+  // task queues and class-less runs have zero low bits: one 8-bit digit is enough for them
+  const int bit0 = (!from_tasks && P.cand_class) ? 0 : 6;
+  if (cub::DeviceRadixSort::SortPairs(nullptr, tmp, s->d_sort_keys.as<uint16_t>(), s->d_sort_keys2.as<uint16_t>(), vals_in,
+                                      s->d_sort_vals.as<uint32_t>(), (int)n, bit0, 14, st) != cudaSuccess ||
       !s->d_sort_tmp.ensure(tmp) ||
-      cub::DeviceRadixSort::SortPairs(s->d_sort_tmp.p, tmp, s->d_sort_keys.as<uint8_t>(), s->d_sort_keys2.as<uint8_t>(),
-                                      vals_in, s->d_sort_vals.as<uint32_t>(), (int)n, 0, 8, st) != cudaSuccess)
+      cub::DeviceRadixSort::SortPairs(s->d_sort_tmp.p, tmp, s->d_sort_keys.as<uint16_t>(), s->d_sort_keys2.as<uint16_t>(),
+                                      vals_in, s->d_sort_vals.as<uint32_t>(), (int)n, bit0, 14, st) != cudaSuccess)
     return nullptr;
   return s->d_sort_vals.as<uint32_t>();
 }
@@ -1015,6 +1030,13 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       P.cand_state = s->d_cand_state.as<uint32_t>();
       P.cand_a = s->d_cand_a.as<uint32_t>();
       P.cand_b = s->d_cand_b.as<uint32_t>();
+      P.cand_class = nullptr;
+      if (sortClass())
+      {
+        if (!s->d_cand_class.ensureKeep((size_t)s->cand_cap, (size_t)cand_begin, st))
+          return false;
+        P.cand_class = s->d_cand_class.as<uint8_t>();
+      }
       P.cand_cap = s->cand_cap;
       P.surv_w = s->d_surv.as<uint32_t>();
       P.surv_cap = s->cand_cap;
