@@ -172,7 +172,7 @@ def main():
     capi.check(lib.t4c_fk_model_create(C.byref(fkd), scene, C.byref(model)), lib)
     nq = fkd.n_q
     # ---- synthetic inputs: this rank's shard of the joint states
-    q_host = S.random_states(b, n, seed=1234 + rank, dtype=np.float64)  # (n, nq)
+    q_host = S.random_states(b, n, seed=1234 + rank + int(os.environ.get("T4_BENCH_SEED_OFFSET", "0")), dtype=np.float64)  # (n, nq)
     dev = torch.device("cuda", local_rank)
     q_soa = torch.from_numpy(np.ascontiguousarray(q_host.T.astype(np.float32))).to(dev)  # FP32 SoA q[j][i] in HBM
     q_pin = torch.from_numpy(q_host).pin_memory()
@@ -226,6 +226,10 @@ def main():
                 gather()
             e1.record()
             torch.cuda.synchronize()
+            if os.environ.get("T4_BENCH_DEBUG"):
+                print(f"[rank {rank}] fn {e0.elapsed_time(em):.2f} ms, exchange {em.elapsed_time(e1):.2f} ms, "
+                      f"kernels {sum(v[0] for v in capi.profile_get(lib).values()):.2f} ms (cumulative)",
+                      file=sys.stderr, flush=True)
             ms = torch.tensor([e0.elapsed_time(e1), em.elapsed_time(e1)], device=dev)
             if world > 1:
                 dist.all_reduce(ms, op=dist.ReduceOp.MAX)

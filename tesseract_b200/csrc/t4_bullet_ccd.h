@@ -342,7 +342,9 @@ T4_HDN bool phase1Step(Phase1State<T>& st, const V3<T>& w)
 
 // phase 1 driver: 0 = cores intersect, -1 = separated (tesseract_gjk_pair_detector.cpp:732-821)
 template <class T>
-T4_HDN int booleanGjk(const ShapeW<T>& A, const ShapeW<T>& B, int& iters)
+// budget: give up (return -3, nothing decided) after that many support pairs -- the caller queues the pair for a
+// run without a budget (t4_kernels2.h gjkBody); the default never triggers (phase 1 stops at 1000 by itself)
+T4_HDN int booleanGjk(const ShapeW<T>& A, const ShapeW<T>& B, int& iters, int budget = 1 << 30)
 {
   Phase1State<T> st;
   st.reset();
@@ -353,6 +355,8 @@ T4_HDN int booleanGjk(const ShapeW<T>& A, const ShapeW<T>& B, int& iters)
     ++iters;
     if (phase1Step(st, w))
       break;
+    if (iters >= budget)
+      return -3;
   }
   return st.status;
 }

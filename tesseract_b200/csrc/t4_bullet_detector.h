@@ -46,7 +46,8 @@ enum
 {
   DET_DONE = 0,    // finished: `out` is final (possibly out.has == false)
   DET_PHASE4 = 1,  // phases 1-2 produced the answer: run phase 4
-  DET_PHASE3 = 2   // penetration / degenerate: run phase 3, then phase 4
+  DET_PHASE3 = 2,  // penetration / degenerate: run phase 3, then phase 4
+  DET_BUDGET = 3   // the iteration budget ran out before phases 1-2 were decided: nothing is valid, run again without
 };
 
 // recentre both shapes about the midpoint of their origins (:694-698); returns the offset
@@ -189,7 +190,7 @@ T4_HDN int phase2Finish(Phase2State<T>& st, T marginA, T marginB, DetectorState<
 // phases 1 and 2 on RECENTRED shapes
 template <class T>
 T4_HDN int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& positionOffset, T maxDist2, bool calc_pen,
-                        bool calc_dist, DetectorState<T>& S, DetectorOut<T>& out)
+                        bool calc_dist, DetectorState<T>& S, DetectorOut<T>& out, int budget = 1 << 30)
 {
   out.has = false;
   out.gjk_iters = 0;
@@ -197,9 +198,11 @@ T4_HDN int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& po
   out.used_epa = false;
   resetDetectorState(S);
   int it1 = 0;
-  const int status = booleanGjk(A, B, it1);
+  const int status = booleanGjk(A, B, it1, budget);
   S.status = status;
   out.gjk_iters += it1;
+  if (status == -3)
+    return DET_BUDGET;
 
   if (status == 0 && !calc_pen)
   {
@@ -223,6 +226,8 @@ T4_HDN int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& po
     ++out.gjk_iters;
     if (phase2Step(st, pWorld, qWorld, maxDist2))
       break;
+    if (out.gjk_iters >= budget)
+      return DET_BUDGET;
   }
   return phase2Finish(st, A.margin(), B.margin(), S);
 }

@@ -49,6 +49,8 @@ enum
   Q_FETCH_EPA,  // next EPA task to hand to a lane of the EPA kernel (lane-refill loop)
   Q_RAW,        // raw contacts (CLOSEST staging) or final contacts (ALL / FIRST)
   Q_OUT,        // final contacts emitted by the CLOSEST reduction
+  Q_LONG,       // survivors whose GJK ran out of its iteration budget: run again, without one, beside the later passes
+  Q_TASK_LONG,  // EPA tasks of the long-pair pass (it runs on its own stream: own task queue)
   Q_COUNT
 };
 
@@ -123,6 +125,10 @@ struct KParams
   uint32_t* cand_state;
   uint32_t* cand_a;
   uint32_t* cand_b;
+  uint32_t* long_w;       // Q_LONG queue (candidate indices) or null: no budget
+  uint32_t long_cap;
+  int task_q;             // Q_TASK, or Q_TASK_LONG in the long-pair pass
+  int gjk_budget;         // support pairs a pair may spend in phases 1-2 before it is deferred (0: unlimited)
   uint8_t* cand_class;    // per candidate: iterations the FP32 cull needed (sort key of the exact queues) or null
   uint32_t cand_cap;
   uint32_t cull_base;  // first candidate of the range the cull kernel works on (FIRST in rounds: candidates append)

@@ -296,11 +296,22 @@ T4_KD void gjkBody(int64_t k, const KParams& P)
   const V3<double> offset = bt::recentre(A, B);
   bt::DetectorState<double> S;
   bt::DetectorOut<double> d;
-  const int r = bt::detectPhase12(A, B, offset, maxDist2, P.calc_pen != 0, P.calc_dist != 0, S, d);
+  const bool budgeted = P.gjk_budget > 0 && P.long_w;
+  const int r = bt::detectPhase12(A, B, offset, maxDist2, P.calc_pen != 0, P.calc_dist != 0, S, d,
+                                  budgeted ? P.gjk_budget : (1 << 30));
   statAdd(P.stats, ST_GJK_ITERS, (uint32_t)d.gjk_iters);
+  if (r == bt::DET_BUDGET)
+  {
+    // a pair that cycles towards the detector's 1000-iteration caps would hold its whole launch for milliseconds
+    // with one active lane: such pairs are collected and run together at the end of the chunk
+    const uint32_t t = qAppend(&P.qcount[Q_LONG]);
+    if (t < P.long_cap)
+      P.long_w[t] = c;
+    return;
+  }
   if (r == bt::DET_PHASE3)
   {
-    const uint32_t t = qAppend(&P.qcount[Q_TASK]);
+    const uint32_t t = qAppend(&P.qcount[P.task_q]);
     if (t < P.task_cap)
     {
       EpaTask& T = P.tasks[t];

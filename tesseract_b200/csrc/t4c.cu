@@ -580,12 +580,13 @@ struct t4c_scene
   CompiledScene comp;
   t4stream stream = nullptr;
   t4stream copy_stream = nullptr;  // progressive download of finished contact records (hostRun)
+  t4stream aux_stream = nullptr;   // long-pair GJK pass, beside the deferred tiers / EPA on the main stream
   plat::t4event q_events[4] = { nullptr, nullptr, nullptr, nullptr };  // piecewise upload of q (hostRun)
   // device scene
   DevBuf d_shapes, d_statics, d_verts, d_sup_cells, d_sup_cand, d_bvh, d_active, d_aa, d_acm, d_margin, d_shape_d, d_statics_d;
   // per-call workspace
   DevBuf d_q0, d_q1, d_pin0, d_pin1, d_poses0, d_poses1, d_poses0d, d_poses1d;
-  DevBuf d_cand_state, d_cand_a, d_cand_b, d_cand_class, d_surv, d_surv2, d_surv3, d_surv4, d_cull_claim, d_tasks;
+  DevBuf d_cand_state, d_cand_a, d_cand_b, d_cand_class, d_long, d_tasks_long, d_surv, d_surv2, d_surv3, d_surv4, d_cull_claim, d_tasks;
   DevBuf d_qcount, d_stats, d_hit, d_claim, d_raw, d_raw_local, d_raw_d64, d_ht_rep, d_ht_best;
   DevBuf d_out, d_out_local, d_fk_out, d_hit_full;
   DevBuf d_traj, d_lvs_counts, d_lvs_offsets, d_lvs_tmp;
@@ -598,6 +599,7 @@ struct t4c_scene
     fk.clear();
     plat::freeStream(stream);
     plat::freeStream(copy_stream);
+    plat::freeStream(aux_stream);
     for (auto& e : q_events)
       plat::freeEvent(e);
   }
@@ -778,6 +780,18 @@ static bool sortClass()
   static const bool v = [] {
     const char* e = std::getenv("T4C_SORT_CLASS");
     return !e || std::atoi(e) != 0;
+  }();
+  return v;
+}
+
+// support pairs a survivor may spend in phases 1-2 of the exact pass before it is deferred to the long-pair pass
+// (T4C_GJK_BUDGET, 0 = no budget).  One pair in a million cycles towards the detector's 1000-iteration caps; alone in
+// its warp it holds the launch it is in for milliseconds.
+static int gjkBudget()
+{
+  static const int v = [] {
+    const char* e = std::getenv("T4C_GJK_BUDGET");
+    return e ? std::max(0, std::atoi(e)) : 0;
   }();
   return v;
 }
@@ -980,7 +994,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     //      active shapes at a time, and states that already have a contact take no part in the later rounds.  This
     //      is the reference's early exit (ContactTestData::done, core/common.h:129-133: Bullet stops dispatching
     //      pairs once the first contact is stored) applied per state across the batch.
-    uint32_t qc[Q_COUNT];
+    uint32_t qc[Q_COUNT] = {};
     const bool first_rec = io.req.type == T4C_TEST_FIRST && io.contacts;
     const bool closest = io.req.type == T4C_TEST_CLOSEST && io.contacts;
     const int64_t room = std::max<int64_t>(0, io.capacity - total);
@@ -1019,6 +1033,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       P.raw_local = (io.cast && io.cc_local) ? io.cc_local + (size_t)std::min<int64_t>(total, io.capacity) * 6 : nullptr;
     }
     uint32_t cand_begin = 0, nsurv2 = 0, nsurv3 = 0, nsurv4 = 0;
+    uint32_t long_cap_bound = 0, long_done = 0;
     auto bindQueues = [&]() -> bool {
       const size_t cb = (size_t)s->cand_cap * sizeof(uint32_t), keep = (size_t)cand_begin * sizeof(uint32_t);
       if (!(s->d_cand_state.ensureKeep(cb, keep, st) && s->d_cand_a.ensureKeep(cb, keep, st) &&
@@ -1038,6 +1053,18 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
         P.cand_class = s->d_cand_class.as<uint8_t>();
       }
       P.cand_cap = s->cand_cap;
+      P.long_w = nullptr;
+      P.long_cap = 0;
+      P.task_q = Q_TASK;
+      P.gjk_budget = gjkBudget();
+      if (P.gjk_budget > 0)
+      {
+        if (!s->d_long.ensureKeep(cb, (size_t)std::min(qc[Q_LONG], long_cap_bound) * sizeof(uint32_t), st))
+          return false;
+        long_cap_bound = s->cand_cap;
+        P.long_w = s->d_long.as<uint32_t>();
+        P.long_cap = s->cand_cap;
+      }
       P.surv_w = s->d_surv.as<uint32_t>();
       P.surv_cap = s->cand_cap;
       if (first_rec)
@@ -1077,6 +1104,19 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
         T4_TRY(plat::zero(P.qcount + Q_TASK, sizeof(uint32_t), st), "memset");
       }
       return T4C_OK;
+    };
+    // pairs whose GJK ran out of its iteration budget (Q_LONG): all of them together, without a budget
+    auto longPass = [&](bool run_epa) -> t4c_status {
+      if (!P.long_w)
+        return run_epa ? exactPass(nullptr, 0, true) : T4C_OK;
+      T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (GJK)");
+      const uint32_t nlong = std::min(qc[Q_LONG], P.long_cap);
+      const int budget = P.gjk_budget;
+      P.gjk_budget = 0;
+      const t4c_status r = exactPass(P.long_w + long_done, nlong - long_done, run_epa);
+      P.gjk_budget = budget;
+      long_done = nlong;
+      return r;
     };
     for (int round = 0; round < n_rounds; ++round)
     {
@@ -1141,9 +1181,32 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
           P.raw_local = s->d_raw_local.as<float>();
         }
       }
-      rc = exactPass(s->d_surv.as<uint32_t>(), nsurv, round == n_rounds - 1);
+      // with a long-pair queue the EPA launch waits until the long pairs' GJK has been started beside it
+      rc = exactPass(s->d_surv.as<uint32_t>(), nsurv, round == n_rounds - 1 && !P.long_w);
       if (rc != T4C_OK)
         return rc;
+    }
+    // ---- long pairs of the rounds: their GJK (milliseconds with a handful of active lanes) starts now on its own
+    //      stream, beside the deferred tiers and the EPA launch of the main stream; joined below
+    uint32_t n_long_async = 0;
+    if (P.long_w)
+    {
+      T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (GJK)");
+      const uint32_t nlong = std::min(qc[Q_LONG], P.long_cap);
+      if (nlong > long_done)
+      {
+        n_long_async = nlong - long_done;
+        T4_TRY(s->d_tasks_long.ensure((size_t)n_long_async * sizeof(EpaTask)), "EPA task queue");
+        KParams PL = P;
+        PL.gjk_budget = 0;
+        PL.long_w = nullptr;
+        PL.surv = P.long_w + long_done;
+        PL.tasks = s->d_tasks_long.as<EpaTask>();
+        PL.task_cap = n_long_async;
+        PL.task_q = Q_TASK_LONG;
+        launchGjk(PL, n_long_async, s->aux_stream ? s->aux_stream : st);
+        long_done = nlong;
+      }
     }
     // ---- deferred tiers, for the states that are still without a contact
     rc = exactPass(s->d_surv2.as<uint32_t>(), nsurv2, true);
@@ -1153,6 +1216,25 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     if (rc != T4C_OK)
       return rc;
     rc = exactPass(s->d_surv4.as<uint32_t>(), nsurv4, true);
+    if (rc != T4C_OK)
+      return rc;
+    if (n_long_async > 0)
+    {
+      // join the long-pair pass; its penetrating pairs go through EPA now
+      T4_TRY(launchOk() && plat::sync(s->aux_stream ? s->aux_stream : st) &&
+                 plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st),
+             "narrowphase (long pairs)");
+      const uint32_t ntl = std::min(qc[Q_TASK_LONG], n_long_async);
+      if (ntl > 0)
+      {
+        EpaTask* const keep_tasks = P.tasks;
+        P.tasks = s->d_tasks_long.as<EpaTask>();
+        P.task_order = nullptr;
+        launchEpa(P, ntl, st);
+        P.tasks = keep_tasks;
+      }
+    }
+    rc = longPass(true);  // long pairs that came out of the deferred tiers
     if (rc != T4C_OK)
       return rc;
     P.active_shapes = all_active;
@@ -1451,6 +1533,7 @@ t4c_status t4c_scene_create(const t4c_scene_desc* d, int32_t device, t4c_scene**
     H.pair_margins[hostPairKey(d->margin_pairs[2 * i], d->margin_pairs[2 * i + 1])] = d->margin_values[i];
   s->stream = plat::newStream();
   s->copy_stream = plat::newStream();
+  s->aux_stream = plat::newStream();
   for (auto& e : s->q_events)
     e = plat::newEvent();
   t4c_status rc = syncScene(s.get());
@@ -1471,6 +1554,7 @@ t4c_status t4c_scene_clone(const t4c_scene* src, t4c_scene** out)
     return fail(T4C_ERR_CUDA, "cudaSetDevice(%d): %s", s->device, plat::lastError());
   s->stream = plat::newStream();
   s->copy_stream = plat::newStream();
+  s->aux_stream = plat::newStream();
   for (auto& e : s->q_events)
     e = plat::newEvent();
   t4c_status rc = syncScene(s.get());

@@ -109,7 +109,8 @@ def test_chunked_batches_with_rounds():
     """batches larger than one chunk (default 1 Mi states; forced to 128 here) with FIRST rounds on: state indices,
     contact offsets and per-chunk queues stay consistent; T4C_DRAIN_MIN=1 makes the host-buffer entries download the
     finished records after every round and chunk (the progressive copy of hostRun) and T4C_UPLOAD_PIECE_MIN=16 the
-    piecewise q upload / FK"""
+    piecewise q upload / FK; T4C_GJK_BUDGET=4 sends most pairs through the deferred long-pair pass (results must not
+    change: a deferred pair is run again from the start)"""
     import subprocess, sys, os
     code = ("import sys; sys.path.insert(0, 'tests'); import parity_cases as pc; from hostsim import build as h; "
             "from tesseract_b200.managers import BatchChecker; from tesseract_b200 import capi; "
@@ -119,7 +120,7 @@ def test_chunked_batches_with_rounds():
             "print(pc.flags_only(mk, 700, 10000)); "
             "print(pc.cast_config3(mk, 5, 12, 10000, device_fk=True))")
     env = dict(os.environ, T4C_ROUND_MIN_STATES="1", T4C_CHUNK_STATES="128", T4C_DRAIN_MIN="1",
-               T4C_UPLOAD_PIECE_MIN="16")
+               T4C_UPLOAD_PIECE_MIN="16", T4C_GJK_BUDGET="4")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout + r.stderr
