@@ -787,11 +787,13 @@ static bool sortClass()
 // support pairs a survivor may spend in phases 1-2 of the exact pass before it is deferred to the long-pair pass
 // (T4C_GJK_BUDGET, 0 = no budget).  One pair in a million cycles towards the detector's 1000-iteration caps; alone in
 // its warp it holds the launch it is in for milliseconds.
+// Default (r2k, profiles/r2k_sweep_gjk_budget_async.txt): 64 for FIRST queries (+8 % on batches that contain such pairs,
+// no change on batches that do not), none for CLOSEST / ALL (there the extra pass costs 5 %).
 static int gjkBudget()
 {
   static const int v = [] {
     const char* e = std::getenv("T4C_GJK_BUDGET");
-    return e ? std::max(0, std::atoi(e)) : 0;
+    return e ? std::max(0, std::atoi(e)) : -1;
   }();
   return v;
 }
@@ -1056,7 +1058,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       P.long_w = nullptr;
       P.long_cap = 0;
       P.task_q = Q_TASK;
-      P.gjk_budget = gjkBudget();
+      P.gjk_budget = gjkBudget() >= 0 ? gjkBudget() : (io.req.type == T4C_TEST_FIRST ? 64 : 0);
       if (P.gjk_budget > 0)
       {
         if (!s->d_long.ensureKeep(cb, (size_t)std::min(qc[Q_LONG], long_cap_bound) * sizeof(uint32_t), st))
