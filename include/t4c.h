@@ -46,7 +46,7 @@
 extern "C" {
 #endif
 
-#define T4C_ABI_VERSION 1
+#define T4C_ABI_VERSION 2
 
 typedef int32_t t4c_status;
 enum {
@@ -150,17 +150,31 @@ typedef struct t4c_contact {
   uint32_t flags;         /* bit 0: produced by the penetration (EPA) pass */
 } t4c_contact;
 
+/* Work counters of one call (roofline accounting).  An "iteration" is one support-PAIR evaluation
+ * (support of A and of B along one direction).  The FP32 cull, the exact FP64 GJK kernel and the EPA kernel are
+ * counted separately so that each kernel's algorithmic work can be recomputed from the line alone. */
 typedef struct t4c_stats {
-  uint64_t states;          /* states / sub-segments processed */
-  uint64_t bvh_nodes;       /* wide-BVH node visits */
-  uint64_t candidates;      /* (shape, shape) pairs passing the AABB + filter tests */
-  uint64_t culled;          /* candidates rejected by the bounding-sphere pretest */
-  uint64_t gjk_pairs;       /* pairs entering GJK */
-  uint64_t gjk_iterations;  /* support-pair evaluations in GJK */
-  uint64_t epa_pairs;       /* pairs entering EPA */
-  uint64_t epa_iterations;
-  uint64_t contacts;        /* records emitted */
+  uint64_t states;            /* states / sub-segments processed */
+  uint64_t bvh_nodes;         /* BVH node visits (two child boxes tested per visit) */
+  uint64_t candidates;        /* (shape, shape) pairs passing the AABB + filter tests */
+  uint64_t culled;            /* candidates rejected by the bounding-sphere / link-box pretests */
+  uint64_t gjk_pairs;         /* pairs entering the FP32 cull GJK */
+  uint64_t gjk_iterations;    /* total support-pair evaluations: cull + exact GJK (phases 1, 2, 4) + EPA kernel's GJK */
+  uint64_t epa_pairs;         /* pairs entering the penetration solver */
+  uint64_t epa_iterations;    /* polytope expansion iterations (one support pair each) */
+  uint64_t contacts;          /* records emitted */
   uint64_t colliding_states;
+  /* ---- ABI 2 */
+  uint64_t cull_iterations;   /* FP32 cull kernel: support pairs */
+  uint64_t exact_pairs;       /* pairs entering the FP64 exact GJK kernel (survivors of the cull) */
+  uint64_t phase1_iterations; /* exact GJK kernel: support pairs of the boolean GJK */
+  uint64_t phase2_iterations; /* exact GJK kernel: support pairs of the Voronoi GJK + the 3 of phase 4 */
+  uint64_t epa_gjk_iterations;/* EPA kernel: support pairs of its seed GJK + the 3 of phase 4 */
+  uint64_t support_vertices;  /* hull vertices whose dot product was evaluated, all kernels (table scans touch few) */
+  uint64_t support_vertices_fp64; /* ... of which in the FP64 kernels */
+  uint64_t bvh_stack_overflows;   /* traversal stack overflows (must be 0: the call fails otherwise) */
+  uint64_t phase1_skipped;    /* exact pairs whose boolean GJK outcome was already certified by the cull */
+  uint64_t reserved[3];
 } t4c_stats;
 
 typedef struct t4c_scene t4c_scene;
@@ -268,8 +282,11 @@ int32_t t4c_profile_get(double* ms, uint64_t* launches, int32_t capacity); /* re
  * average table cell length (-1: the hull has no table). */
 t4c_status t4c_debug_hull_support(t4c_scene* scene, int32_t shape, const double* dirs, int64_t n, int32_t* out,
                                   double* mean_candidates);
-/* measured-peak helper: runs an FP32 FMA loop on every SM, returns TFLOP/s (roofline denominator) */
+/* Test hook: sine and cosine of n doubles as the FK kernel computes them (t4_sincos.h), evaluated ON THE DEVICE. */
+t4c_status t4c_debug_sincos(int32_t device, const double* x, int64_t n, double* sin_out, double* cos_out);
+/* measured-peak helpers: an FP32 FFMA loop / an FP64 DFMA loop on every SM, TFLOP/s (roofline denominators) */
 t4c_status t4c_measure_fp32_peak(int32_t device, double* tflops);
+t4c_status t4c_measure_fp64_peak(int32_t device, double* tflops);
 
 #ifdef __cplusplus
 }

@@ -57,10 +57,13 @@ class Request(C.Structure):
 class Stats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("states", "bvh_nodes", "candidates", "culled", "gjk_pairs",
                                           "gjk_iterations", "epa_pairs", "epa_iterations", "contacts",
-                                          "colliding_states")]
+                                          "colliding_states", "cull_iterations", "exact_pairs", "phase1_iterations",
+                                          "phase2_iterations", "epa_gjk_iterations", "support_vertices",
+                                          "support_vertices_fp64", "bvh_stack_overflows", "phase1_skipped")] + \
+               [("reserved", C.c_uint64 * 3)]
 
     def as_dict(self):
-        return {n: int(getattr(self, n)) for n, _ in self._fields_}
+        return {n: int(getattr(self, n)) for n, _ in self._fields_ if n != "reserved"}
 
 
 class Result(C.Structure):
@@ -131,6 +134,8 @@ def load_library(path=None):
     lib.t4c_profile_get.argtypes = [DP, C.POINTER(C.c_uint64), I32]
     lib.t4c_profile_get.restype = I32
     lib.t4c_measure_fp32_peak.argtypes = [I32, DP]
+    lib.t4c_measure_fp64_peak.argtypes = [I32, DP]
+    lib.t4c_debug_sincos.argtypes = [I32, DP, I64, DP, DP]
     lib.t4c_debug_hull_support.argtypes = [VP, I32, DP, I64, C.POINTER(I32), DP]
     for name in ("t4c_scene_create", "t4c_scene_clone", "t4c_scene_set_active", "t4c_scene_set_enabled",
                  "t4c_scene_set_acm", "t4c_scene_set_margins", "t4c_scene_set_link_pose", "t4c_scene_num_active",
@@ -138,7 +143,7 @@ def load_library(path=None):
                  "t4c_check_cast", "t4c_check_link_poses_cast", "t4c_check_trajectories_discrete",
                  "t4c_check_trajectories_cast", "t4c_check_discrete_device", "t4c_check_cast_device",
                  "t4c_measure_fp32_peak", "t4c_lvs_count", "t4c_lvs_items", "t4c_lvs_item_states",
-                 "t4c_debug_hull_support"):
+                 "t4c_debug_hull_support", "t4c_measure_fp64_peak", "t4c_debug_sincos"):
         getattr(lib, name).restype = I32
     if path is None:
         _lib = lib

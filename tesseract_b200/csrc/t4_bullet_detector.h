@@ -29,7 +29,8 @@ struct DetectorOut
   bool has;
   V3<T> normalOnB, pointOnB;
   T distance;
-  int gjk_iters, epa_iters;
+  int gjk_iters, epa_iters;  // support pairs of phases 1 + 2 + 4 (and of the penetration solver's seed GJK); EPA iterations
+  int p1_iters;              // ... of which in phase 1
   bool used_epa;
 };
 
@@ -190,17 +191,22 @@ T4_HDN int phase2Finish(Phase2State<T>& st, T marginA, T marginB, DetectorState<
 // phases 1 and 2 on RECENTRED shapes
 template <class T>
 T4_HDN int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& positionOffset, T maxDist2, bool calc_pen,
-                        bool calc_dist, DetectorState<T>& S, DetectorOut<T>& out, int budget = 1 << 30)
+                        bool calc_dist, DetectorState<T>& S, DetectorOut<T>& out, int budget = 1 << 30,
+                        bool skip_phase1 = false)
 {
   out.has = false;
   out.gjk_iters = 0;
   out.epa_iters = 0;
+  out.p1_iters = 0;
   out.used_epa = false;
   resetDetectorState(S);
   int it1 = 0;
-  const int status = booleanGjk(A, B, it1, budget);
+  // skip_phase1: the caller holds a certificate that the cores are separated by more than any tolerance of the boolean
+  // GJK (t4_kernels2.h cullBody), i.e. that phase 1 returns "separated"; its only output is that status
+  const int status = skip_phase1 ? -1 : booleanGjk(A, B, it1, budget);
   S.status = status;
   out.gjk_iters += it1;
+  out.p1_iters = it1;
   if (status == -3)
     return DET_BUDGET;
 
@@ -214,8 +220,9 @@ T4_HDN int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& po
   }
   if (status == -1 && !calc_dist)
     return DET_DONE;
-  if (status == 0)
-    return DET_PHASE3;  // phase 2 is skipped when the cores intersect: the penetration result always supersedes it
+  // Phase 2 runs whatever phase 1 found (:836-1006).  For intersecting cores it usually ends on a degenerate simplex,
+  // but it can leave a valid contact (isValid, distance ~ -margins, orgNormalInB): the fall-back when the penetration
+  // solver produces nothing, and the candidate of the phase-4 normal override.
 
   Phase2State<T> st;
   st.reset();
@@ -229,7 +236,8 @@ T4_HDN int detectPhase12(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& po
     if (out.gjk_iters >= budget)
       return DET_BUDGET;
   }
-  return phase2Finish(st, A.margin(), B.margin(), S);
+  const int next = phase2Finish(st, A.margin(), B.margin(), S);
+  return status == 0 ? DET_PHASE3 : next;  // "|| (status == 0)" at :1011
 }
 
 // phase 3 on RECENTRED shapes, in three pieces so that the polytope expansion in the middle can be run one iteration

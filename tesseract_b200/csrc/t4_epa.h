@@ -29,7 +29,8 @@ struct EpaResult
   bool converged;
 };
 
-template <class T, int MAXV = 96, int MAXF = 192>
+// caps = btGjkEpaSolver2's EPA_MAX_VERTICES / EPA_MAX_FACES (128 / 256)
+template <class T, int MAXV = 128, int MAXF = 256>
 struct Epa
 {
   struct Face

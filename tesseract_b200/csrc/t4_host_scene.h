@@ -60,6 +60,7 @@ struct CompiledScene
   float default_margin = 0, max_margin = 0;
   double default_margin_d = 0, max_margin_d = 0;
   bool cast_unsupported = false;
+  int bvh_depth = 0;
 };
 
 struct HostScene
@@ -99,9 +100,10 @@ struct LbvhBuilder
   const std::vector<uint32_t>& codes;
   const std::vector<int32_t>& leaf_shape;
   std::vector<DBvhNode>& nodes;
+  int max_depth = 0;  // deepest inner node (root = 1)
 
   // returns child reference (>=0 node, <0 leaf) and its box
-  int32_t build(int lo, int hi, Box& out)
+  int32_t build(int lo, int hi, Box& out, int depth = 1)
   {
     if (hi - lo == 1)
     {
@@ -126,9 +128,10 @@ struct LbvhBuilder
     }
     const int idx = (int)nodes.size();
     nodes.emplace_back();
+    max_depth = std::max(max_depth, depth);
     Box l, r;
-    const int32_t lc = build(lo, split, l);
-    const int32_t rc = build(split, hi, r);
+    const int32_t lc = build(lo, split, l, depth + 1);
+    const int32_t rc = build(split, hi, r, depth + 1);
     DBvhNode& n = nodes[idx];
     for (int k = 0; k < 3; ++k)
     {
@@ -398,7 +401,7 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
       leaf[i] = sshape[order[i]];
     }
     C.bvh.reserve((size_t)nst);
-    LbvhBuilder B{ boxes, codes, leaf, C.bvh };
+    LbvhBuilder B{ boxes, codes, leaf, C.bvh, 0 };
     if (nst == 1)
     {
       DBvhNode n;
@@ -416,6 +419,15 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
     {
       LbvhBuilder::Box root;
       B.build(0, nst, root);
+      // 30 Morton bits + log2(longest run of equal codes): 50 for a million coincident shapes.  The device walk keeps
+      // one pending sibling per level in a T4_BVH_STACK-entry stack; a deeper tree is refused here, never truncated
+      // silently on the device.
+      if (B.max_depth > T4_BVH_STACK - 1)
+      {
+        err = "environment BVH too deep for the device traversal stack (" + std::to_string(B.max_depth) + " levels)";
+        return false;
+      }
+      C.bvh_depth = B.max_depth;
     }
   }
   // ---- ACM bit-matrix [n_alinks][n_links]: bit set = pair never tested

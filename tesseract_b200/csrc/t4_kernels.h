@@ -18,6 +18,7 @@
 
 #include "../../include/t4c.h"
 #include "t4_pair.h"
+#include "t4_sincos.h"
 
 namespace t4
 {
@@ -33,6 +34,15 @@ enum
   ST_EPA_ITERS,
   ST_CONTACTS,
   ST_COLLIDING,
+  ST_CULL_ITERS,     // support pairs of the FP32 cull
+  ST_EXACT_PAIRS,    // pairs entering the exact GJK kernel
+  ST_P1_ITERS,       // exact kernel: boolean GJK
+  ST_P2_ITERS,       // exact kernel: Voronoi GJK + phase 4
+  ST_EPA_GJK_ITERS,  // EPA kernel: seed GJK + phase 4
+  ST_SUPV,           // hull vertices evaluated by the support mapping, all kernels
+  ST_SUPV64,         // ... in the FP64 kernels
+  ST_BVH_OVERFLOW,   // traversal stack overflows (the call fails when non-zero)
+  ST_P1_SKIPPED,     // exact pairs whose phase-1 outcome was certified by the cull
   ST_COUNT
 };
 
@@ -55,6 +65,9 @@ enum
 };
 
 #define T4_MAX_JOINTS 64
+// depth-first traversal stack of the environment BVH: a walk keeps at most one pending sibling per level, so a tree of
+// depth D needs D entries; the scene compiler refuses trees deeper than this (t4_host_scene.h)
+#define T4_BVH_STACK 64
 
 struct alignas(16) DJoint
 {
@@ -324,8 +337,8 @@ T4_KD void fkOne(const KParams& P, const void* q, int64_t s, Xf<double>* Tj)
     {
       // Eigen::AngleAxisd(q, axis.normalized()) (ofkt_nodes.cpp:200,217-219)
       const double a = loadQ(P, q, s, J.q_index);
-      double sn, cs;
-      sincos(a, &sn, &cs);
+      // the host libm's bits (t4_sincos.h): link poses identical to the reference's FK on the same host
+      const double sn = t4sin(a), cs = t4cos(a);
       const double t = 1.0 - cs, x = J.axis[0], y = J.axis[1], z = J.axis[2];
       Xf<double> rot;
       rot.r[0] = t * x * x + cs, rot.r[1] = t * x * y - sn * z, rot.r[2] = t * x * z + sn * y;
@@ -356,7 +369,27 @@ T4_KD void storePoseF(float* dst, const Xf<double>& x)
   d[0] = a, d[1] = b, d[2] = c;
 }
 
+// world pose of active link `a` from the joint frames of one state
+T4_KD Xf<double> fkAlinkPose(const KParams& P, const Xf<double>* Tj, int a)
+{
+  const int j = P.alink_joint[a];
+  return j >= 0 ? Tj[j] : Xf<double>::from12(P.alink_static + (size_t)a * 12);
+}
+
+// t4c_fk: poses of ALL links of state s, FP64
+T4_KD void fkStoreAllLinks(const KParams& P, const Xf<double>* Tj, int64_t s)
+{
+  for (int l = 0; l < P.n_links; ++l)
+  {
+    const int j = P.link_joint[l];
+    const Xf<double> x = j >= 0 ? Tj[j] : Xf<double>::from12(P.link_static + (size_t)l * 12);
+    x.to12(P.fk_out + ((size_t)s * P.n_links + l) * 12);
+  }
+}
+
 // item = state.  Writes poses0 (and poses1 for cast) of the kinematic links, or fk_out (all links, FP64).
+// (Serial form: host simulator.  The device kernel stages the poses of a warp through shared memory and writes whole
+// 128-byte lines, t4c_exact.cu fkKernelT.)
 template <int MAXJ>
 T4_KD void fkBodyT(int64_t s, const KParams& P)
 {
@@ -366,20 +399,14 @@ T4_KD void fkBodyT(int64_t s, const KParams& P)
     fkOne(P, pass ? P.q1 : P.q0, s, Tj);
     if (P.fk_out)
     {
-      for (int l = 0; l < P.n_links; ++l)
-      {
-        const int j = P.link_joint[l];
-        const Xf<double> x = j >= 0 ? Tj[j] : Xf<double>::from12(P.link_static + (size_t)l * 12);
-        x.to12(P.fk_out + ((size_t)s * P.n_links + l) * 12);
-      }
+      fkStoreAllLinks(P, Tj, s);
       return;
     }
     float* dst = pass ? P.poses1 : P.poses0;
     double* dstd = pass ? P.poses1d : P.poses0d;
     for (int a = 0; a < P.n_alinks; ++a)
     {
-      const int j = P.alink_joint[a];
-      const Xf<double> x = j >= 0 ? Tj[j] : Xf<double>::from12(P.alink_static + (size_t)a * 12);
+      const Xf<double> x = fkAlinkPose(P, Tj, a);
       storePoseF(dst + poseOffset(P, s, a), x);
       x.to12(dstd + poseOffset(P, s, a));
     }
@@ -542,8 +569,8 @@ T4_KD void broadStaticBody(int64_t item, const KParams& P)
   const V3<float> bc(S.bc[0], S.bc[1], S.bc[2]), bh(S.bh[0], S.bh[1], S.bh[2]);
   const V3<float> cw = x0(bc);
   const float ra = S.bc[3];
-  uint32_t nodes = 0, culled = 0, cands = 0;
-  int stack[64];
+  uint32_t nodes = 0, culled = 0, cands = 0, overflow = 0;
+  int stack[T4_BVH_STACK];
   int sp = 0;
   stack[sp++] = 0;
   while (sp > 0)
@@ -560,8 +587,10 @@ T4_KD void broadStaticBody(int64_t item, const KParams& P)
       const int child = side ? N.right : N.left;
       if (child >= 0)
       {
-        if (sp < 64)
+        if (sp < T4_BVH_STACK)
           stack[sp++] = child;
+        else
+          ++overflow;  // cannot happen for a tree the scene compiler accepted (depth check); reported, never silent
         continue;
       }
       const int b = ~child;
@@ -597,119 +626,8 @@ T4_KD void broadStaticBody(int64_t item, const KParams& P)
   statAdd(P.stats, ST_BVH_NODES, nodes);
   statAdd(P.stats, ST_CULLED, culled);
   statAdd(P.stats, ST_CANDIDATES, cands + culled);
-}
-
-// Grouped traversal: item = group * n + s, a group = up to T4_BROAD_GROUP consecutive active shapes (for a single
-// robot: all its links).  ONE walk of the environment BVH serves the whole group: a node is entered when the union
-// box of the group overlaps it and ANY member box does, so the dependent node fetches of the upper levels -- the
-// latency that bounds the per-shape traversal (ncu r1j: long scoreboard 18 warp-cycles per issue at 97 % L1 hits) --
-// are shared by the links of the robot instead of being repeated per link.  Leaf filters are those of broadStaticBody.
-#define T4_BROAD_GROUP 8
-T4_KD void broadStaticGroupBody(int64_t item, const KParams& P)
-{
-  const int g = (int)(item / P.n);
-  const int64_t s = item - (int64_t)g * P.n;
-  const int first = g * T4_BROAD_GROUP;
-  const int cnt = t4min(T4_BROAD_GROUP, P.n_active_shapes - first);
-  const float grow = P.max_margin + T4_CULL_SLACK;
-  float mnx[T4_BROAD_GROUP], mny[T4_BROAD_GROUP], mnz[T4_BROAD_GROUP];
-  float mxx[T4_BROAD_GROUP], mxy[T4_BROAD_GROUP], mxz[T4_BROAD_GROUP];
-  V3<float> umn(1e30f, 1e30f, 1e30f), umx(-1e30f, -1e30f, -1e30f);
-#pragma unroll
-  for (int k = 0; k < T4_BROAD_GROUP; ++k)
-  {
-    mnx[k] = mny[k] = mnz[k] = 1e30f;  // empty box: overlaps nothing
-    mxx[k] = mxy[k] = mxz[k] = -1e30f;
-    if (k < cnt)
-    {
-      const int sh = P.active_shapes[first + k];
-      const DShape& S = P.shapes[sh];
-      Xf<float> x0, x1;
-      shapePose<float>(P, S, sh, s, x0, x1);
-      V3<float> mn, mx;
-      shapeWorldBox(P, S, x0, x1, mn, mx);
-      mnx[k] = mn.x - grow, mny[k] = mn.y - grow, mnz[k] = mn.z - grow;
-      mxx[k] = mx.x + grow, mxy[k] = mx.y + grow, mxz[k] = mx.z + grow;
-      umn = V3<float>(t4min(umn.x, mnx[k]), t4min(umn.y, mny[k]), t4min(umn.z, mnz[k]));
-      umx = V3<float>(t4max(umx.x, mxx[k]), t4max(umx.y, mxy[k]), t4max(umx.z, mxz[k]));
-    }
-  }
-  uint32_t nodes = 0, culled = 0, cands = 0;
-  int stack[64];
-  int sp = 0;
-  stack[sp++] = 0;
-  while (sp > 0)
-  {
-    const int ni = stack[--sp];
-    const DBvhNode& N = P.bvh[ni];
-    ++nodes;
-    for (int side = 0; side < 2; ++side)
-    {
-      const float* bmn = side ? N.rmn : N.lmn;
-      const float* bmx = side ? N.rmx : N.lmx;
-      if (!boxesOverlap(umn, umx, bmn, bmx))
-        continue;
-      unsigned mask = 0;
-#pragma unroll
-      for (int k = 0; k < T4_BROAD_GROUP; ++k)
-        if (!(mnx[k] > bmx[0] || mxx[k] < bmn[0] || mny[k] > bmx[1] || mxy[k] < bmn[1] || mnz[k] > bmx[2] ||
-              mxz[k] < bmn[2]))
-          mask |= 1u << k;
-      if (!mask)
-        continue;
-      const int child = side ? N.right : N.left;
-      if (child >= 0)
-      {
-        if (sp < 64)
-          stack[sp++] = child;
-        continue;
-      }
-      const int b = ~child;
-      const DShape& Sb = P.shapes[b];
-      const DStaticW& W = P.statics[b];
-      const V3<float> cb(W.bs[0], W.bs[1], W.bs[2]);
-      const float reach = W.bs[3] + grow;
-      while (mask)
-      {
-#ifdef T4_DEVICE_BUILD
-        const int k = __ffs(mask) - 1;
-#else
-        const int k = __builtin_ctz(mask);
-#endif
-        mask &= mask - 1;
-        const int sh = P.active_shapes[first + k];
-        const DShape& S = P.shapes[sh];
-        if (Sb.link == S.link || acmAllowed(P, S.alink, Sb.link))
-          continue;
-        if (!P.cast)
-        {
-          Xf<float> x0, x1;
-          shapePose<float>(P, S, sh, s, x0, x1);
-          const V3<float> bc(S.bc[0], S.bc[1], S.bc[2]), bh(S.bh[0], S.bh[1], S.bh[2]);
-          const V3<float> d = cb - x0(bc);
-          const float rr = S.bc[3] + reach;
-          if (d.len2() > rr * rr)
-          {
-            ++culled;
-            continue;
-          }
-          const V3<float> pl = x0.invApply(cb) - bc;
-          const V3<float> e(t4max(t4abs(pl.x) - bh.x, 0.f), t4max(t4abs(pl.y) - bh.y, 0.f),
-                            t4max(t4abs(pl.z) - bh.z, 0.f));
-          if (e.len2() > reach * reach)
-          {
-            ++culled;
-            continue;
-          }
-        }
-        ++cands;
-        pushCandidate(P, s, sh, b);
-      }
-    }
-  }
-  statAdd(P.stats, ST_BVH_NODES, nodes);
-  statAdd(P.stats, ST_CULLED, culled);
-  statAdd(P.stats, ST_CANDIDATES, cands + culled);
+  if (overflow)
+    statAdd(P.stats, ST_BVH_OVERFLOW, overflow);
 }
 
 // item = pair * n + s ; pairs are (active shape, active shape) of two different links, ACM-filtered on the host

@@ -116,7 +116,8 @@ T4_KD void cullBody(int64_t item, const KParams& P)
   GjkOut<float, false> g;
   const int st = gjkDistance<float, false>(A, B, axis0, false, cutoff, accept, g, 48);
   statAdd(P.stats, ST_GJK_PAIRS, 1);
-  statAdd(P.stats, ST_GJK_ITERS, (uint32_t)g.iters);
+  statAdd(P.stats, ST_CULL_ITERS, (uint32_t)g.iters);
+  statAdd(P.stats, ST_SUPV, A.evals + B.evals);
   if (st == GJK_FAR)
     return;
   if (P.cand_class)  // the exact pass of this pair will need about as many iterations: keeps a warp's lanes in step
@@ -274,9 +275,15 @@ T4_KDN void emitContact(const KParams& P, int64_t s, int a, int b, const ShapeW<
   }
 }
 
+// work counters of one exact-pass item, flushed once per item (every exit of the body)
+struct ExactCounters
+{
+  uint32_t pairs = 0, p1 = 0, p2 = 0, supv = 0;
+};
+
 // item = survivor index: phases 1-2 of the exact (FP64) query.  Pairs that need the penetration solver are handed to
 // the EPA kernel through the task queue, so that a warp never mixes the short GJK path with the long EPA path.
-T4_KD void gjkBody(int64_t k, const KParams& P)
+T4_KD void gjkBodyInner(int64_t k, const KParams& P, ExactCounters& cnt)
 {
   const uint32_t c = P.surv[k];
   const int64_t s = P.cand_state[c];
@@ -286,6 +293,7 @@ T4_KD void gjkBody(int64_t k, const KParams& P)
   ShapeW<double> A, B;
   loadPairShapesD(P, s, a, b, A, B);
   PairResult<double> pr;
+  cnt.pairs = 1;
   if (analyticPairQuery(A, B, P.max_margin_d, pr))
   {
     emitContact(P, s, a, b, A, B, pr);
@@ -299,7 +307,11 @@ T4_KD void gjkBody(int64_t k, const KParams& P)
   const bool budgeted = P.gjk_budget > 0 && P.long_w;
   const int r = bt::detectPhase12(A, B, offset, maxDist2, P.calc_pen != 0, P.calc_dist != 0, S, d,
                                   budgeted ? P.gjk_budget : (1 << 30));
-  statAdd(P.stats, ST_GJK_ITERS, (uint32_t)d.gjk_iters);
+  if (r == bt::DET_PHASE4)
+    bt::detectPhase4(A, B, offset, maxDist2, S, d);
+  cnt.p1 = (uint32_t)d.p1_iters;
+  cnt.p2 = (uint32_t)(d.gjk_iters - d.p1_iters);
+  cnt.supv = A.evals + B.evals;
   if (r == bt::DET_BUDGET)
   {
     // a pair that cycles towards the detector's 1000-iteration caps would hold its whole launch for milliseconds
@@ -325,8 +337,6 @@ T4_KD void gjkBody(int64_t k, const KParams& P)
     }
     return;
   }
-  if (r == bt::DET_PHASE4)
-    bt::detectPhase4(A, B, offset, maxDist2, S, d);
   copyOut(d, pr);
   if (!pr.has)
     return;
@@ -335,221 +345,14 @@ T4_KD void gjkBody(int64_t k, const KParams& P)
   emitContact(P, s, a, b, A, B, pr);
 }
 
-// ---------------------------------------------------------------------------------------------------------------
-// Lane-refill form of the exact GJK pass.  gjkBody above runs one pair per thread from start to end: lanes of a warp
-// sit in different phases with different iteration counts, and the ncu source view (r1e) showed 2-4 active threads
-// per instruction in the simplex code.  Here every trip of the loop evaluates exactly ONE support pair per lane --
-// the common, hottest block -- then advances that lane's state machine (phase 1 simplex, phase 2 Voronoi step, or
-// one of the three phase-4 evaluations); a lane whose pair is finished fetches the next survivor at once instead of
-// idling until the slowest lane of the warp is done.  The arithmetic per pair is exactly that of gjkBody.
-// ---------------------------------------------------------------------------------------------------------------
-enum
+T4_KD void gjkBody(int64_t k, const KParams& P)
 {
-  LP_PHASE1 = 0,
-  LP_PHASE2,
-  LP_PHASE4_ORG,   // support along -/+ orgNormalInB  -> d2
-  LP_PHASE4_FLIP,  // support along +/- normalInB     -> d1
-  LP_PHASE4_FWD    // support along -/+ normalInB     -> d0
-};
-
-struct GjkLane
-{
-  uint32_t c;
-  int64_t s;
-  int a, b, phase, gjk_iters;
-  ShapeW<double> A, B;  // recentred
-  V3<double> offset;
-  double maxDist2, d1, d2;
-  bt::Phase1State<double> p1;
-  bt::Phase2State<double> p2;
-  bt::DetectorState<double> S;
-};
-
-T4_KDN void lanePushEpaTask(const KParams& P, const GjkLane& L)
-{
-  const uint32_t t = qAppend(&P.qcount[Q_TASK]);
-  if (t >= P.task_cap)
-    return;
-  EpaTask& T = P.tasks[t];
-  T.cand = L.c;
-  T.is_valid = L.S.isValid;
-  T.distance = L.S.distance;
-  T.normalInB[0] = L.S.normalInB.x, T.normalInB[1] = L.S.normalInB.y, T.normalInB[2] = L.S.normalInB.z;
-  T.pointOnA[0] = L.S.pointOnA.x, T.pointOnA[1] = L.S.pointOnA.y, T.pointOnA[2] = L.S.pointOnA.z;
-  T.pointOnB[0] = L.S.pointOnB.x, T.pointOnB[1] = L.S.pointOnB.y, T.pointOnB[2] = L.S.pointOnB.z;
-  T.orgNormalInB[0] = L.S.orgNormalInB.x, T.orgNormalInB[1] = L.S.orgNormalInB.y, T.orgNormalInB[2] = L.S.orgNormalInB.z;
-}
-
-T4_KDN void laneEmit(const KParams& P, const GjkLane& L, const bt::DetectorOut<double>& d)
-{
-  PairResult<double> pr;
-  copyOut(d, pr);
-  if (!pr.has)
-    return;
-  if (P.cast)
-  {
-    // continuous data needs the shapes at their world poses (not recentred): reload, exactly as gjkBody holds them
-    ShapeW<double> A, B;
-    loadPairShapesD(P, L.s, L.a, L.b, A, B);
-    emitContact(P, L.s, L.a, L.b, A, B, pr);
-  }
-  else
-    emitContact(P, L.s, L.a, L.b, L.A, L.B, pr);
-}
-
-// fetch + set up the next survivor for this lane; false when the queue is exhausted.  Pairs that need no iteration
-// (state already decided, analytic pairs) are completed here.
-T4_KDN bool laneFetch(const KParams& P, int64_t n, GjkLane& L)
-{
-  for (;;)
-  {
-    const uint32_t k = qAppend(&P.qcount[Q_FETCH]);
-    if ((int64_t)k >= n)
-      return false;
-    L.c = P.surv[k];
-    L.s = P.cand_state[L.c];
-    if ((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit[L.s])
-      continue;
-    L.a = (int)P.cand_a[L.c], L.b = (int)P.cand_b[L.c];
-    loadPairShapesD(P, L.s, L.a, L.b, L.A, L.B);
-    PairResult<double> pr;
-    if (analyticPairQuery(L.A, L.B, P.max_margin_d, pr))
-    {
-      emitContact(P, L.s, L.a, L.b, L.A, L.B, pr);
-      continue;
-    }
-    L.maxDist2 = detectorMaxDist2(L.A, L.B, P.max_margin_d);
-    L.offset = bt::recentre(L.A, L.B);
-    bt::resetDetectorState(L.S);
-    L.p1.reset();
-    L.phase = LP_PHASE1;
-    L.gjk_iters = 0;
-    return true;
-  }
-}
-
-// advance the lane by one support pair (pW on A along dA, qW on B along -dA); true when the pair is finished
-T4_KDN bool laneStep(const KParams& P, GjkLane& L, const V3<double>& pW, const V3<double>& qW)
-{
-  ++L.gjk_iters;
-  bt::DetectorOut<double> d;
-  d.has = false;
-  d.gjk_iters = 0;
-  d.epa_iters = 0;
-  d.used_epa = false;
-  const double margin = L.A.margin() + L.B.margin();
-  switch (L.phase)
-  {
-    case LP_PHASE1:
-    {
-      if (!bt::phase1Step(L.p1, pW - qW))
-        return false;
-      const int status = L.p1.status;
-      L.S.status = status;
-      if (status == 0 && !P.calc_pen)
-      {
-        d.has = true;
-        d.normalOnB = L.S.normalInB;
-        d.pointOnB = L.offset;
-        d.distance = -(double)FLT_MIN;
-        laneEmit(P, L, d);
-        return true;
-      }
-      if (status == -1 && !P.calc_dist)
-        return true;
-      if (status == 0)
-      {
-        lanePushEpaTask(P, L);
-        return true;
-      }
-      L.p2.reset();
-      L.phase = LP_PHASE2;
-      return false;
-    }
-    case LP_PHASE2:
-    {
-      if (!bt::phase2Step(L.p2, pW, qW, L.maxDist2))
-        return false;
-      if (bt::phase2Finish(L.p2, L.A.margin(), L.B.margin(), L.S) == bt::DET_PHASE3)
-      {
-        lanePushEpaTask(P, L);
-        return true;
-      }
-      if (!bt::phase4Accepts(L.S, L.maxDist2))
-        return true;
-      L.phase = LP_PHASE4_ORG;
-      return false;
-    }
-    case LP_PHASE4_ORG:
-      L.d2 = L.S.orgNormalInB.dot(pW - qW) - margin;
-      L.phase = LP_PHASE4_FLIP;
-      return false;
-    case LP_PHASE4_FLIP:
-      L.d1 = (-L.S.normalInB).dot(pW - qW) - margin;
-      L.phase = LP_PHASE4_FWD;
-      return false;
-    default:
-    {
-      const double d0 = L.S.normalInB.dot(pW - qW) - margin;
-      bt::phase4Decide(L.S, d0, L.d1, L.d2, L.offset, d);
-      laneEmit(P, L, d);
-      return true;
-    }
-  }
-}
-
-// direction of the next support evaluation on A (B gets the negated direction; negation is exact)
-T4_KD V3<double> laneDirection(const GjkLane& L)
-{
-  switch (L.phase)
-  {
-    case LP_PHASE1:
-      return L.p1.dir;
-    case LP_PHASE2:
-      return -L.p2.axis;
-    case LP_PHASE4_ORG:
-      return -L.S.orgNormalInB;
-    case LP_PHASE4_FLIP:
-      return L.S.normalInB;
-    default:
-      return -L.S.normalInB;
-  }
-}
-
-#ifdef T4_DEVICE_BUILD
-#define T4_WARP_ANY(x) __any_sync(0xffffffffu, (x))
-#else
-#define T4_WARP_ANY(x) (x)
-#endif
-
-// whole-kernel body: n = number of survivors in P.surv; P.qcount[Q_FETCH] must be zero at launch
-T4_KD void gjkLaneLoop(const KParams& P, int64_t n)
-{
-  GjkLane L;
-  bool have = false, more = true;
-  uint32_t iters = 0;
-  for (;;)
-  {
-    if (!have && more)
-    {
-      have = laneFetch(P, n, L);
-      more = have;
-    }
-    if (!T4_WARP_ANY(have))
-      break;
-    if (have)
-    {
-      const V3<double> dA = laneDirection(L);
-      const V3<double> pW = supportW(L.A, dA, false);
-      const V3<double> qW = supportW(L.B, -dA, false);
-      if (laneStep(P, L, pW, qW))
-      {
-        iters += (uint32_t)L.gjk_iters;
-        have = false;
-      }
-    }
-  }
-  statAdd(P.stats, ST_GJK_ITERS, iters);
+  ExactCounters cnt;
+  gjkBodyInner(k, P, cnt);
+  statAdd(P.stats, ST_EXACT_PAIRS, cnt.pairs);
+  statAdd(P.stats, ST_P1_ITERS, cnt.p1);
+  statAdd(P.stats, ST_P2_ITERS, cnt.p2);
+  statAdd(P.stats, ST_SUPV64, cnt.supv);
 }
 
 // item = EPA task: phase 3 (penetration) and phase 4 of the exact query
@@ -578,15 +381,14 @@ T4_KD void epaBody(int64_t t, const KParams& P, EPA_T& epa)
   d.has = false;
   d.gjk_iters = 0;
   d.epa_iters = 0;
+  d.p1_iters = 0;
   d.used_epa = false;
   bt::detectPhase3(A, B, S, d, epa);
   bt::detectPhase4(A, B, offset, maxDist2, S, d);
-  statAdd(P.stats, ST_GJK_ITERS, (uint32_t)d.gjk_iters);
+  statAdd(P.stats, ST_EPA_GJK_ITERS, (uint32_t)d.gjk_iters);
   statAdd(P.stats, ST_EPA_PAIRS, 1u);
   statAdd(P.stats, ST_EPA_ITERS, (uint32_t)d.epa_iters);
-#ifdef T4C_DEBUG_EPA_HIST
-  fprintf(stderr, "EPAHIST %d %d %d\n", A.type, B.type, d.epa_iters);
-#endif
+  statAdd(P.stats, ST_SUPV64, A.evals + B.evals);
   PairResult<double> pr;
   copyOut(d, pr);
   if (!pr.has)
@@ -594,117 +396,6 @@ T4_KD void epaBody(int64_t t, const KParams& P, EPA_T& epa)
   if (P.cast)
     loadPairShapesD(P, s, a, b, A, B);
   emitContact(P, s, a, b, A, B, pr);
-}
-
-// ---------------------------------------------------------------------------------------------------------------
-// Lane-refill form of the EPA pass.  The expansion needs 7 iterations (median) for box / sphere / hull pairs but
-// 15-75 against cylinders: with one task per thread from start to end a warp lasts as long as its slowest lane.
-// Here every trip of the loop runs ONE expansion iteration per lane (Epa::step; the polytope already lives in
-// thread-local memory, so resuming costs nothing extra) and a finished lane takes the next task at once.
-// ---------------------------------------------------------------------------------------------------------------
-struct EpaLane
-{
-  uint32_t c;
-  int64_t s;
-  int a, b;
-  ShapeW<double> A, B;  // recentred
-  V3<double> offset;
-  double maxDist2;
-  bt::DetectorState<double> S;
-  bt::DetectorOut<double> d;
-};
-
-// phase 4 + statistics + result bridging of a finished task
-template <class EPA_T>
-T4_KDN void epaLaneFinish(const KParams& P, EpaLane& L, int st, const V3<double>& gv, const V3<double>& gpA, bool ok,
-                          EPA_T& epa)
-{
-  EpaResult<double> er;
-  er.iterations = 0;
-  if (ok)
-    ok = epa.finish(er);
-  bt::phase3Apply(L.A, L.B, L.S, L.d, st, gv, gpA, ok, er);
-  bt::detectPhase4(L.A, L.B, L.offset, L.maxDist2, L.S, L.d);
-  statAdd(P.stats, ST_GJK_ITERS, (uint32_t)L.d.gjk_iters);
-  statAdd(P.stats, ST_EPA_PAIRS, 1u);
-  statAdd(P.stats, ST_EPA_ITERS, (uint32_t)L.d.epa_iters);
-  PairResult<double> pr;
-  copyOut(L.d, pr);
-  if (!pr.has)
-    return;
-  if (P.cast)
-  {
-    ShapeW<double> A, B;
-    loadPairShapesD(P, L.s, L.a, L.b, A, B);
-    emitContact(P, L.s, L.a, L.b, A, B, pr);
-  }
-  else
-    emitContact(P, L.s, L.a, L.b, L.A, L.B, pr);
-}
-
-// fetch + seed the next task; true when the lane now has a polytope to expand
-template <class EPA_T>
-T4_KDN bool epaLaneFetch(const KParams& P, int64_t n, EpaLane& L, EPA_T& epa)
-{
-  for (;;)
-  {
-    const uint32_t k = qAppend(&P.qcount[Q_FETCH_EPA]);
-    if ((int64_t)k >= n)
-      return false;
-    const EpaTask& T = P.tasks[P.task_order ? P.task_order[k] : k];
-    L.c = T.cand;
-    L.s = P.cand_state[L.c];
-    if ((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit[L.s])
-      continue;
-    L.a = (int)P.cand_a[L.c], L.b = (int)P.cand_b[L.c];
-    loadPairShapesD(P, L.s, L.a, L.b, L.A, L.B);
-    L.maxDist2 = detectorMaxDist2(L.A, L.B, P.max_margin_d);
-    L.offset = bt::recentre(L.A, L.B);
-    L.S.isValid = T.is_valid;
-    L.S.status = 0;
-    L.S.distance = T.distance;
-    L.S.normalInB = V3<double>(T.normalInB[0], T.normalInB[1], T.normalInB[2]);
-    L.S.pointOnA = V3<double>(T.pointOnA[0], T.pointOnA[1], T.pointOnA[2]);
-    L.S.pointOnB = V3<double>(T.pointOnB[0], T.pointOnB[1], T.pointOnB[2]);
-    L.S.orgNormalInB = V3<double>(T.orgNormalInB[0], T.orgNormalInB[1], T.orgNormalInB[2]);
-    L.d.has = false;
-    L.d.gjk_iters = 0;
-    L.d.epa_iters = 0;
-    L.d.used_epa = true;
-    GjkOut<double, true> g;
-    const int st = bt::phase3Seed(L.A, L.B, g);
-    L.d.gjk_iters += g.iters;
-    if (st == GJK_INTERSECT && epa.begin(L.A, L.B, g.sx.W, g.sx.P, g.sx.n, 255, 1e-12))
-      return true;
-    epaLaneFinish(P, L, st, g.v, g.pA, false, epa);  // separated cores, or no enclosing tetrahedron: done already
-  }
-}
-
-// whole-kernel body: n = number of tasks in P.tasks; P.qcount[Q_FETCH_EPA] must be zero at launch
-template <class EPA_T>
-T4_KD void epaLaneLoop(const KParams& P, int64_t n, EPA_T& epa)
-{
-  EpaLane L;
-  bool have = false, more = true;
-  for (;;)
-  {
-    if (!have && more)
-    {
-      have = epaLaneFetch(P, n, L, epa);
-      more = have;
-    }
-    if (!T4_WARP_ANY(have))
-      break;
-    if (have)
-    {
-      const int r = epa.step();
-      if (r != 0)
-      {
-        epaLaneFinish(P, L, GJK_INTERSECT, V3<double>(0, 0, 0), V3<double>(0, 0, 0), r == 1, epa);
-        have = false;
-      }
-    }
-  }
 }
 
 T4_KD unsigned long long mix64(unsigned long long x)

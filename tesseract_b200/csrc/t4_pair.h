@@ -40,6 +40,7 @@ T4_HD void makeShapeW(ShapeW<T>& w, const DShape& s, const f4* verts, const uint
   w.type = s.type;
   w.r = 0, w.h = 0;
   w.nv = 0;
+  w.evals = 0;
   w.verts = nullptr;
   w.sup_cells = nullptr;
   w.sup_cand = nullptr;

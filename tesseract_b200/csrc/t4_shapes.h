@@ -73,6 +73,9 @@ struct ShapeW
   bool cast;
   Xf<T> x0, x1;  // world pose at t0 (and t1 for cast shapes), recentred by the caller
   Xf<T> t01;     // cast shapes: pose at t1 relative to t0, (T0 L)^-1 (T1 L)  (bullet_cast_bvh_manager.cpp:281-305)
+  // hull vertices whose dot product the support mapping has evaluated so far (t4c_stats::support_vertices: the work
+  // the roofline figure may claim)
+  mutable uint32_t evals;
   T4_HD T innerMargin() const { return (type == SH_SPHERE || type == SH_CAPSULE) ? r : T(0); }
   // margin the detector subtracts analytically.  A cast shape is conv(shape@t0 U shape@t1) built from the WITH-margin
   // support and reports margin 0 (CastHullShape::getMargin, bullet_utils.h:230-235,286): the swept ball is part of
@@ -153,6 +156,7 @@ T4_HD V3<T> coreSupportInline(const ShapeW<T>& s, const V3<T>& d)
           iv = iv < 0 ? 0 : (iv > T4_SUP_R - 1 ? T4_SUP_R - 1 : iv);
           const int cell = (face * T4_SUP_R + iu) * T4_SUP_R + iv;
           const uint32_t beg = s.sup_cells[cell], end = s.sup_cells[cell + 1];
+          s.evals += end - beg;
           for (uint32_t k = beg; k < end; ++k)
           {
             const int i = (int)s.sup_cand[k];
@@ -167,6 +171,7 @@ T4_HD V3<T> coreSupportInline(const ShapeW<T>& s, const V3<T>& d)
           return vtx<T>(s.verts, best);
         }
       }
+      s.evals += (uint32_t)s.nv;
       for (int i = 0; i < s.nv; ++i)
       {
         f4 v = s.verts[i];

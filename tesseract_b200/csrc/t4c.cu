@@ -237,25 +237,14 @@ static int smCount()
   }
   return g_sm_count;
 }
-// grids are a whole number of waves: SM count x resident CTAs per SM, grid-stride over the items
-// Grid policy of the grid-stride kernels.  Default: one CTA per `block` items, so that the hardware hands the queue
-// out as CTAs retire; a grid capped at the resident CTAs gives every thread a fixed stride of the queue and the
-// slowest warp sets the time (measured r2a: fk -5 %, broad -6 %, cull -15 %, gjk -6 % uncapped; EPA alone is 2-4 %
-// faster capped and keeps the cap).  T4C_GRID_UNCAPPED=0 / T4C_EPA_UNCAPPED=1 flip the two choices.
-static bool envFlag(const char* name, bool dflt)
-{
-  const char* e = std::getenv(name);
-  return e ? (std::atoi(e) != 0) : dflt;
-}
-static bool gridUncapped()
-{
-  static const bool v = envFlag("T4C_GRID_UNCAPPED", true);
-  return v;
-}
-static int gridFor(int64_t n, int block, int ctas_per_sm, bool allow_uncapped = true)
+// Grid policy of the grid-stride kernels: one CTA per `block` items, so that the hardware hands the queue out as CTAs
+// retire; a grid capped at the resident CTAs gives every thread a fixed stride of the queue and the slowest warp sets
+// the time (measured r2a: fk -5 %, broad -6 %, cull -15 %, gjk -6 % uncapped; the thread-per-task EPA alone was 2-4 %
+// faster capped).  `capped` selects the resident-CTA grid.
+static int gridFor(int64_t n, int block, int ctas_per_sm, bool capped = false)
 {
   const int64_t need = (n + block - 1) / block;
-  if (allow_uncapped && gridUncapped())
+  if (!capped)
     return (int)std::max<int64_t>(1, std::min<int64_t>(need, 0x7fffffff));
   const int64_t full = (int64_t)smCount() * ctas_per_sm;
   return (int)std::max<int64_t>(1, std::min<int64_t>(need, full));
@@ -271,18 +260,6 @@ __global__ void __launch_bounds__(256) broadStaticKernel(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     broadStaticBody(i, P);
-}
-// experiment knob T4C_BROAD_MINB = 5 | 6 | 8: tighter register budgets (48 / 40 / 32) for more resident warps
-template <int MINB>
-__global__ void __launch_bounds__(256, MINB) broadStaticKernelB(KParams P, int64_t n)
-{
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    broadStaticBody(i, P);
-}
-__global__ void __launch_bounds__(256) broadStaticGroupKernel(KParams P, int64_t n)
-{
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    broadStaticGroupBody(i, P);
 }
 __global__ void __launch_bounds__(256) broadActiveKernel(KParams P, int64_t n)
 {
@@ -346,6 +323,27 @@ __global__ void fmaPeakKernel(float* out, int iters)
     a4 = fmaf(a4, b, c), a5 = fmaf(a5, b, c), a6 = fmaf(a6, b, c), a7 = fmaf(a7, b, c);
   }
   out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+__global__ void dfmaPeakKernel(double* out, int iters)
+{
+  double a0 = threadIdx.x * 1e-3, a1 = a0 + 1., a2 = a0 + 2., a3 = a0 + 3., a4 = a0 + 4., a5 = a0 + 5., a6 = a0 + 6.,
+         a7 = a0 + 7.;
+  const double b = 1.0000001, c = 1e-7;
+  for (int i = 0; i < iters; ++i)
+  {
+    a0 = fma(a0, b, c), a1 = fma(a1, b, c), a2 = fma(a2, b, c), a3 = fma(a3, b, c);
+    a4 = fma(a4, b, c), a5 = fma(a5, b, c), a6 = fma(a6, b, c), a7 = fma(a7, b, c);
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+__global__ void sincosDebugKernel(const double* x, int64_t n, double* s, double* c)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+  {
+    s[i] = t4sin(x[i]);
+    c[i] = t4cos(x[i]);
+  }
 }
 
 // optional per-kernel timing with CUDA events recorded on the launching stream (bench.py roofline figures)
@@ -426,74 +424,24 @@ static void launchFk(const KParams& P, int64_t first, int64_t n, t4stream st)
   ++g_launches;
 }
 static void launchConvert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(convertPosesKernel, PK_CONVERT, 256, 8, P, n, st); }
-static void launchBroadStatic(const KParams& P, int64_t n, t4stream st)
-{
-  static const int minb = [] {
-    const char* e = std::getenv("T4C_BROAD_MINB");
-    return e ? std::atoi(e) : 0;
-  }();
-  if (minb == 5)
-    T4_LAUNCH(broadStaticKernelB<5>, PK_BROAD_STATIC, 256, 8, P, n, st);
-  else if (minb == 6)
-    T4_LAUNCH(broadStaticKernelB<6>, PK_BROAD_STATIC, 256, 8, P, n, st);
-  else if (minb == 8)
-    T4_LAUNCH(broadStaticKernelB<8>, PK_BROAD_STATIC, 256, 8, P, n, st);
-  else
-    T4_LAUNCH(broadStaticKernel, PK_BROAD_STATIC, 256, 8, P, n, st);
-}
-static void launchBroadStaticGroup(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadStaticGroupKernel, PK_BROAD_STATIC, 256, 4, P, n, st); }
+static void launchBroadStatic(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadStaticKernel, PK_BROAD_STATIC, 256, 8, P, n, st); }
 static void launchBroadActive(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(broadActiveKernel, PK_BROAD_ACTIVE, 256, 8, P, n, st); }
 static void launchCull(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(cullKernel, PK_CULL, 256, (T4_CULL_MIN_CTAS > 4 ? T4_CULL_MIN_CTAS : 4), P, n, st); }
-// CTA size of the exact kernels: T4C_GJK_BLOCK / T4C_EPA_BLOCK (32, 64, 128; no measurable difference, r2a)
-static int envBlock(const char* name, int dflt)
-{
-  const char* e = std::getenv(name);
-  const int v = e ? std::atoi(e) : dflt;
-  return (v == 32 || v == 64 || v == 128) ? v : dflt;
-}
-static int gjkBlock()
-{
-  static int v = envBlock("T4C_GJK_BLOCK", 128);
-  return v;
-}
-static int epaBlock()
-{
-  static int v = envBlock("T4C_EPA_BLOCK", 128);
-  return v;
-}
-static bool epaUncapped()
-{
-  static const bool v = envFlag("T4C_EPA_UNCAPPED", false);
-  return v;
-}
 static void launchGjk(const KParams& P, int64_t n, t4stream st)
 {
   if (n <= 0)
     return;
   profBegin(PK_GJK, st);
-  t4LaunchGjk(P, n, gridFor(n, gjkBlock(), 4 * (128 / gjkBlock())), gjkBlock(), st);
+  t4LaunchGjk(P, n, gridFor(n, 128, 4), 128, st);
   profEnd(st);
   ++g_launches;
-}
-// resident CTAs per SM of the EPA kernel: its polytope pools live in local memory (20 KB per thread), fewer resident
-// threads keep that working set closer to the L2 share of an SM
-static int epaCtas()
-{
-  static int v = 0;
-  if (!v)
-  {
-    const char* e = std::getenv("T4C_EPA_CTAS");
-    const char* m = std::getenv("T4C_EPA_MINB");
-    v = e ? std::max(1, std::min(6, std::atoi(e))) : (m ? std::max(4, std::min(6, std::atoi(m))) : 4);
-  }
-  return v;
 }
 static void launchEpa(const KParams& P, int64_t n, t4stream st)
 {
   if (n <= 0)
     return;
   profBegin(PK_EPA, st);
-  t4LaunchEpa(P, n, gridFor(n, epaBlock(), epaCtas() * (128 / epaBlock()), epaUncapped()), epaBlock(), st);
+  t4LaunchEpa(P, n, gridFor(n, 128, 4, true), 128, st);
   profEnd(st);
   ++g_launches;
 }
@@ -517,32 +465,14 @@ static void launchFk(const KParams& P, int64_t first, int64_t n, t4stream)
 }
 static void launchConvert(const KParams& P, int64_t n, t4stream) { T4_SERIAL(convertPosesBody, P, n); }
 static void launchBroadStatic(const KParams& P, int64_t n, t4stream) { T4_SERIAL(broadStaticBody, P, n); }
-static void launchBroadStaticGroup(const KParams& P, int64_t n, t4stream) { T4_SERIAL(broadStaticGroupBody, P, n); }
 static void launchBroadActive(const KParams& P, int64_t n, t4stream) { T4_SERIAL(broadActiveBody, P, n); }
 static void launchCull(const KParams& P, int64_t n, t4stream) { T4_SERIAL(cullBody, P, n); }
-static void launchGjk(const KParams& P, int64_t n, t4stream)
-{
-  // same selection as the device build (t4c_exact.cu): pair-per-thread body by default, the lane-refill loop (with a
-  // single lane: same state machine as the device kernel) under T4C_GJK_LANES=1
-  const char* e = std::getenv("T4C_GJK_LANES");
-  if (n > 0 && e && std::atoi(e) == 1)
-  {
-    gjkLaneLoop(P, n);
-    ++g_launches;
-    return;
-  }
-  T4_SERIAL(gjkBody, P, n);
-}
+static void launchGjk(const KParams& P, int64_t n, t4stream) { T4_SERIAL(gjkBody, P, n); }
 static void launchEpa(const KParams& P, int64_t n, t4stream)
 {
   std::unique_ptr<Epa<double>> epa(new Epa<double>());
-  // same selection as the device build (t4c_exact.cu): task-per-thread body unless T4C_EPA_LANES=1
-  const char* e = std::getenv("T4C_EPA_LANES");
-  if (e && std::atoi(e) == 1 && n > 0)
-    epaLaneLoop(P, n, *epa);
-  else
-    for (int64_t i = 0; i < n; ++i)
-      epaBody(i, P, *epa);
+  for (int64_t i = 0; i < n; ++i)
+    epaBody(i, P, *epa);
   if (n > 0)
     ++g_launches;
 }
@@ -766,62 +696,51 @@ struct BatchIO
   t4c_stats stats{};
 };
 
-// FIRST queries of at least this many states (per chunk) run in rounds over the robot's shapes (runBatch)
-static int64_t roundMinStates()
+// Pipeline parameters.  The values are the measured choices (profiles/README.md); the five environment variables are
+// TEST HOOKS that let small test batches reach the code paths of the million-state runs (rounds, budgets, chunking,
+// progressive copies) -- nothing else in the library reads the environment.
+struct Tuning
 {
-  const char* e = std::getenv("T4C_ROUND_MIN_STATES");
-  return e ? std::max<long long>(1, std::atoll(e)) : 16384;
+  // FIRST queries of at least this many states (per chunk) run in rounds over the robot's shapes (runBatch)
+  int64_t round_min_states = 16384;  // T4C_ROUND_MIN_STATES
+  // support pairs a survivor may spend in phases 1-2 of the exact pass before it is deferred to the long-pair pass
+  // (0 = no budget).  One pair in a million cycles towards the detector's 1000-iteration caps; alone in its warp it
+  // holds the launch it is in for milliseconds.  -1: 64 for FIRST queries (+8 % on batches that contain such pairs, no
+  // change on batches that do not, profiles/r2k), none for CLOSEST / ALL (there the extra pass costs 5 %).
+  int gjk_budget = -1;               // T4C_GJK_BUDGET
+  int64_t chunk_states = 1ll << 20;  // T4C_CHUNK_STATES
+  int64_t drain_min = 4096;          // T4C_DRAIN_MIN: records per progressive download
+  int64_t upload_piece_min = 65536;  // T4C_UPLOAD_PIECE_MIN: states per piece of the piecewise q upload
+  int max_rounds = 8;
+  Tuning()
+  {
+    auto env = [](const char* name, long long dflt, long long lo) {
+      const char* e = std::getenv(name);
+      return e ? std::max<long long>(lo, std::atoll(e)) : dflt;
+    };
+    round_min_states = env("T4C_ROUND_MIN_STATES", round_min_states, 1);
+    gjk_budget = (int)env("T4C_GJK_BUDGET", gjk_budget, 0);
+    chunk_states = env("T4C_CHUNK_STATES", chunk_states, 1);
+    drain_min = env("T4C_DRAIN_MIN", drain_min, 1);
+    upload_piece_min = env("T4C_UPLOAD_PIECE_MIN", upload_piece_min, 1);
+  }
+};
+static const Tuning& tuning()
+{
+  static const Tuning t;
+  return t;
 }
-
+static int64_t roundMinStates() { return tuning().round_min_states; }
+static int gjkBudget() { return tuning().gjk_budget; }
+static int maxRounds() { return tuning().max_rounds; }
+static int64_t chunkStates() { return tuning().chunk_states; }
 // survivor queues are sorted by (types, iteration count of the FP32 cull): the exact pass of a pair needs about as many
-// iterations as its cull did, so a warp's lanes finish together (GJK -6 %, r2g).  T4C_SORT_CLASS=0: types alone
-static bool sortClass()
-{
-  static const bool v = [] {
-    const char* e = std::getenv("T4C_SORT_CLASS");
-    return !e || std::atoi(e) != 0;
-  }();
-  return v;
-}
-
-// support pairs a survivor may spend in phases 1-2 of the exact pass before it is deferred to the long-pair pass
-// (T4C_GJK_BUDGET, 0 = no budget).  One pair in a million cycles towards the detector's 1000-iteration caps; alone in
-// its warp it holds the launch it is in for milliseconds.
-// Default (r2k, profiles/r2k_sweep_gjk_budget_async.txt): 64 for FIRST queries (+8 % on batches that contain such pairs,
-// no change on batches that do not), none for CLOSEST / ALL (there the extra pass costs 5 %).
-static int gjkBudget()
-{
-  static const int v = [] {
-    const char* e = std::getenv("T4C_GJK_BUDGET");
-    return e ? std::max(0, std::atoi(e)) : -1;
-  }();
-  return v;
-}
-
-static int maxRounds()
-{
-  const char* e = std::getenv("T4C_ROUNDS");
-  return e ? std::max(1, std::min(64, std::atoi(e))) : 8;
-}
+// iterations as its cull did, so a warp's lanes finish together (GJK -6 %, r2g)
+static bool sortClass() { return true; }
 // 0: last active shapes first (distal links of a serial arm), 1: first shapes first.  Measured on configs[1] (r1v):
 // flags-only queries are fastest distal-first (157 M vs 138 M states/s), queries with records proximal-first
-// (38.0 M vs 36.1 M: fewer states end up needing EPA iterations); T4C_ROUND_ORDER overrides.
-static int roundOrder(bool with_records)
-{
-  const char* e = std::getenv("T4C_ROUND_ORDER");
-  return e ? std::atoi(e) : (with_records ? 1 : 0);
-}
-
-static int64_t chunkStates()
-{
-  static int64_t v = 0;
-  if (!v)
-  {
-    const char* e = std::getenv("T4C_CHUNK_STATES");
-    v = e ? std::max<long long>(1, std::atoll(e)) : (1ll << 20);
-  }
-  return v;
-}
+// (38.0 M vs 36.1 M: fewer states end up needing EPA iterations)
+static int roundOrder(bool with_records) { return with_records ? 1 : 0; }
 
 static uint32_t nextPow2(uint64_t x)
 {
@@ -839,21 +758,11 @@ static uint32_t nextPow2(uint64_t x)
   } while (0)
 
 #ifndef T4C_HOSTSIM
-static int sortQueues()
-{
-  static int v = -1;
-  if (v < 0)
-  {
-    const char* e = std::getenv("T4C_SORT_QUEUES");
-    v = (e && std::atoi(e) == 0) ? 0 : 1;
-  }
-  return v;
-}
 // stable radix sort of a queue of n pairs by shape-type key; returns the sorted values (candidate indices when
 // from_tasks == 0, task indices otherwise) or null when sorting is off / not worthwhile
 static const uint32_t* sortByType(t4c_scene* s, const KParams& P, const uint32_t* queue, int from_tasks, uint32_t n)
 {
-  if (!sortQueues() || n < 4096)
+  if (n < 4096)
     return nullptr;
   t4stream st = s->stream;
   if (!(s->d_sort_keys.ensure((size_t)n * 2) && s->d_sort_keys2.ensure((size_t)n * 2) && s->d_sort_vals.ensure((size_t)n * 4) &&
@@ -921,10 +830,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     if (!io.host_contacts || !io.contacts)
       return true;
     upto = std::min<int64_t>(upto, io.capacity);
-    static const int64_t min_records = [] {
-      const char* e = std::getenv("T4C_DRAIN_MIN");  // tests: 1 = copy after every round / chunk
-      return e ? std::max<long long>(1, std::atoll(e)) : 4096;
-    }();
+    const int64_t min_records = tuning().drain_min;
     if (upto - io.host_copied < min_records)
       return true;
     const bool ok = plat::d2h(io.host_contacts + io.host_copied, io.contacts + io.host_copied,
@@ -1134,19 +1040,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       {
         T4_TRY(bindQueues(), "candidate queue");
         if (P.n_bvh_nodes > 0)
-        {
-          // T4C_BROAD_GROUP=1: grouped traversal (one BVH walk per state and group of 8 robot shapes).  It visits 3.4x
-          // fewer nodes but measured 19 % SLOWER on B200 (r1r: 121 registers, 7x fewer threads in flight), and its
-          // state-major candidate order doubles the cull time of flags-only queries: opt-in only.
-          static const int grouped = [] {
-            const char* e = std::getenv("T4C_BROAD_GROUP");
-            return (e && std::atoi(e) == 1) ? 1 : 0;
-          }();
-          if (grouped)
-            launchBroadStaticGroup(P, nc * (int64_t)((P.n_active_shapes + T4_BROAD_GROUP - 1) / T4_BROAD_GROUP), st);
-          else
-            launchBroadStatic(P, nc * (int64_t)P.n_active_shapes, st);
-        }
+          launchBroadStatic(P, nc * (int64_t)P.n_active_shapes, st);
         launchBroadActive(P, nc * (int64_t)P.n_aa_pairs, st);
         T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "broadphase");
         if (qc[Q_CAND] <= s->cand_cap)
@@ -1278,11 +1172,24 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
   io.stats.candidates = stats_host[ST_CANDIDATES];
   io.stats.culled = stats_host[ST_CULLED];
   io.stats.gjk_pairs = stats_host[ST_GJK_PAIRS];
-  io.stats.gjk_iterations = stats_host[ST_GJK_ITERS];
+  io.stats.gjk_iterations = stats_host[ST_CULL_ITERS] + stats_host[ST_P1_ITERS] + stats_host[ST_P2_ITERS] +
+                            stats_host[ST_EPA_GJK_ITERS];
   io.stats.epa_pairs = stats_host[ST_EPA_PAIRS];
   io.stats.epa_iterations = stats_host[ST_EPA_ITERS];
   io.stats.contacts = stats_host[ST_CONTACTS];
   io.stats.colliding_states = stats_host[ST_COLLIDING];
+  io.stats.cull_iterations = stats_host[ST_CULL_ITERS];
+  io.stats.exact_pairs = stats_host[ST_EXACT_PAIRS];
+  io.stats.phase1_iterations = stats_host[ST_P1_ITERS];
+  io.stats.phase2_iterations = stats_host[ST_P2_ITERS];
+  io.stats.epa_gjk_iterations = stats_host[ST_EPA_GJK_ITERS];
+  io.stats.support_vertices = stats_host[ST_SUPV] + stats_host[ST_SUPV64];
+  io.stats.support_vertices_fp64 = stats_host[ST_SUPV64];
+  io.stats.bvh_stack_overflows = stats_host[ST_BVH_OVERFLOW];
+  io.stats.phase1_skipped = stats_host[ST_P1_SKIPPED];
+  if (stats_host[ST_BVH_OVERFLOW])
+    return fail(T4C_ERR_UNSUPPORTED, "environment BVH traversal overflowed its stack %llu times: results incomplete",
+                stats_host[ST_BVH_OVERFLOW]);
   if (io.contacts && total > io.capacity)
     return fail(T4C_ERR_CAPACITY, "contact buffer too small: %lld needed, capacity %lld", (long long)total,
                 (long long)io.capacity);
@@ -1316,10 +1223,7 @@ static t4c_status hostRun(t4c_scene* s, BatchIO& io, const double* hq0, const do
     io.q0 = s->d_q0.p;
     if (io.cast)
       io.q1 = s->d_q1.p;
-    static const int64_t piece_min = [] {
-      const char* e = std::getenv("T4C_UPLOAD_PIECE_MIN");  // tests: small values force the piecewise path
-      return e ? std::max<long long>(1, std::atoll(e)) : 65536;
-    }();
+    const int64_t piece_min = tuning().upload_piece_min;
     const bool pieces = io.n >= 4 * piece_min && ((s->copy_stream && s->q_events[3]) || !s->stream) &&
                         plat::isPinned(hq0) && (!io.cast || plat::isPinned(hq1));
     if (pieces)
@@ -1462,6 +1366,44 @@ static void lvsExpand(const double* traj, int64_t n_traj, int n_wp, int n_q, dou
             }
           });
 }
+
+#ifndef T4C_HOSTSIM
+template <class T, class K>
+static t4c_status measurePeak(int32_t device, double* tflops, K kernel, int iters)
+{
+  if (device < 0 || device >= plat::deviceCount())
+    return fail(T4C_ERR_CUDA, "no usable CUDA device %d", device);
+  plat::setDevice(device);
+  g_sm_count = 0;
+  const int blocks = smCount() * 8, threads = 256;
+  T* out = (T*)plat::alloc((size_t)blocks * threads * sizeof(T));
+  if (!out)
+    return fail(T4C_ERR_NOMEM, "alloc");
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  double best = 0;
+  for (int rep = 0; rep < 5; ++rep)
+  {
+    cudaEventRecord(e0);
+    kernel<<<blocks, threads>>>(out, iters);
+    ++g_launches;
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess)
+      break;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double fl = 2.0 * 8.0 * (double)iters * (double)blocks * threads;
+    if (ms > 0)
+      best = std::max(best, fl / (ms * 1e-3) / 1e12);
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  plat::release(out);
+  *tflops = best;
+  return best > 0 ? T4C_OK : fail(T4C_ERR_CUDA, "FMA peak kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
+}
+#endif
 
 extern "C" {
 const char* t4c_last_error(void) { return g_err.c_str(); }
@@ -2000,37 +1942,50 @@ t4c_status t4c_measure_fp32_peak(int32_t device, double* tflops)
   (void)device;
   return fail(T4C_ERR_CUDA, "host simulator has no device");
 #else
+  return measurePeak<float>(device, tflops, fmaPeakKernel, 1 << 15);
+#endif
+}
+
+t4c_status t4c_measure_fp64_peak(int32_t device, double* tflops)
+{
+  if (!tflops)
+    return fail(T4C_ERR_INVALID, "null argument");
+#ifdef T4C_HOSTSIM
+  (void)device;
+  return fail(T4C_ERR_CUDA, "host simulator has no device");
+#else
+  return measurePeak<double>(device, tflops, dfmaPeakKernel, 1 << 13);
+#endif
+}
+
+t4c_status t4c_debug_sincos(int32_t device, const double* x, int64_t n, double* sin_out, double* cos_out)
+{
+  if (!x || !sin_out || !cos_out || n < 0)
+    return fail(T4C_ERR_INVALID, "null argument");
+#ifdef T4C_HOSTSIM
+  (void)device;
+  for (int64_t i = 0; i < n; ++i)
+  {
+    sin_out[i] = t4sin(x[i]);
+    cos_out[i] = t4cos(x[i]);
+  }
+  return T4C_OK;
+#else
   if (device < 0 || device >= plat::deviceCount())
     return fail(T4C_ERR_CUDA, "no usable CUDA device %d", device);
   plat::setDevice(device);
-  g_sm_count = 0;
-  const int blocks = smCount() * 8, threads = 256, iters = 1 << 15;
-  float* out = (float*)plat::alloc((size_t)blocks * threads * sizeof(float));
-  if (!out)
-    return fail(T4C_ERR_NOMEM, "alloc");
-  cudaEvent_t e0, e1;
-  cudaEventCreate(&e0);
-  cudaEventCreate(&e1);
-  double best = 0;
-  for (int rep = 0; rep < 5; ++rep)
+  DevBuf dx, ds, dc;
+  const size_t bytes = (size_t)n * sizeof(double);
+  T4_TRY(dx.ensure(bytes) && ds.ensure(bytes) && dc.ensure(bytes) && plat::h2d(dx.p, x, bytes, nullptr), "sincos workspace");
+  if (n > 0)
   {
-    cudaEventRecord(e0);
-    fmaPeakKernel<<<blocks, threads>>>(out, iters);
+    sincosDebugKernel<<<gridFor(n, 256, 8), 256>>>(dx.as<double>(), n, ds.as<double>(), dc.as<double>());
     ++g_launches;
-    cudaEventRecord(e1);
-    if (cudaEventSynchronize(e1) != cudaSuccess)
-      break;
-    float ms = 0;
-    cudaEventElapsedTime(&ms, e0, e1);
-    const double fl = 2.0 * 8.0 * (double)iters * (double)blocks * threads;
-    if (ms > 0)
-      best = std::max(best, fl / (ms * 1e-3) / 1e12);
   }
-  cudaEventDestroy(e0);
-  cudaEventDestroy(e1);
-  plat::release(out);
-  *tflops = best;
-  return best > 0 ? T4C_OK : fail(T4C_ERR_CUDA, "FMA peak kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
+  T4_TRY(launchOk() && plat::d2h(sin_out, ds.p, bytes, nullptr) && plat::d2h(cos_out, dc.p, bytes, nullptr) &&
+             plat::chk(cudaDeviceSynchronize()),
+         "sincos");
+  return T4C_OK;
 #endif
 }
 }  // extern "C"

@@ -13,122 +13,99 @@
 
 using namespace t4;
 
-__global__ void __launch_bounds__(128, 2) gjkKernel(KParams P, int64_t n)
-{
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    gjkBody(i, P);
-}
-// same body under a 128-register budget (twice the resident warps): the default (measured faster on B200, r1d);
-// T4C_EXACT_REGS=255 selects the unconstrained build
+// 128-register budget (four 128-thread CTAs per SM): measured faster on B200 than the unconstrained build (r1d); tighter
+// budgets (96 / 80 registers) made no difference (r2a sweep)
 __global__ void __launch_bounds__(128, 4) gjkKernelR128(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     gjkBody(i, P);
 }
 
-__global__ void __launch_bounds__(128, 2) epaKernel(KParams P, int64_t n)
+__global__ void __launch_bounds__(128, 4) epaKernelR128(KParams P, int64_t n)
 {
   Epa<double> epa;  // polytope pools live in thread-local memory
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     epaBody(i, P, epa);
 }
-__global__ void __launch_bounds__(128, 4) epaKernelR128(KParams P, int64_t n)
-{
-  Epa<double> epa;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    epaBody(i, P, epa);
-}
 
-// experiment knobs: tighter register budgets (T4C_GJK_MINB / T4C_EPA_MINB = 5 -> 96 registers, 6 -> 80 registers)
-template <int MINB>
-__global__ void __launch_bounds__(128, MINB) gjkKernelB(KParams P, int64_t n)
+// FK feeds the exact pass: same two-rounding arithmetic (and the host libm's sine / cosine, t4_sincos.h) so that link
+// poses equal the reference's FP64 FK bit for bit.  States [first, first + n) of the chunk (the host-buffer entries run
+// FK piecewise under the upload of q).
+// Stores: the pose arrays are link-major ([alink][state][12]), so the 32 states of a warp own one contiguous run of
+// 32 x 96 B (FP64) and 32 x 48 B (FP32) per link.  A thread writing its own record scatters 8- / 16-byte pieces over
+// 32 sectors per instruction and the L2 had to merge them: ncu (r2e) counted 4.4 GB of DRAM traffic for 1.06 GB of
+// poses.  Here a warp stages the 32 records in shared memory and writes the run as full 128-bit lanes, line by line.
+template <int MAXJ>
+__global__ void __launch_bounds__(128) fkKernelT(KParams P, int64_t first, int64_t n)
 {
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    gjkBody(i, P);
-}
-template <int MINB>
-__global__ void __launch_bounds__(128, MINB) epaKernelB(KParams P, int64_t n)
-{
-  Epa<double> epa;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    epaBody(i, P, epa);
-}
-static int envMinB(const char* name)
-{
-  const char* e = std::getenv(name);
-  const int v = e ? std::atoi(e) : 4;
-  return (v == 5 || v == 6) ? v : 4;
-}
-
-// lane-refill GJK (t4_kernels2.h gjkLaneLoop).  Measured 2x SLOWER than the pair-per-thread kernel on B200 (r1g/r1h:
-// the per-lane state machine lives in local memory and every trip reloads it), so it is opt-in: T4C_GJK_LANES=1.
-__global__ void __launch_bounds__(128, 4) gjkLaneKernel(KParams P, int64_t n)
-{
-  gjkLaneLoop(P, n);
-}
-
-// lane-refill EPA (t4_kernels2.h epaLaneLoop).  Measured 35-50 % SLOWER than the task-per-thread kernel on B200 (r1m:
-// the kernel is bound by local-memory latency, not by idle lanes), so it is opt-in: T4C_EPA_LANES=1.
-__global__ void __launch_bounds__(128, 4) epaLaneKernel(KParams P, int64_t n)
-{
-  Epa<double> epa;
-  epaLaneLoop(P, n, epa);
-}
-
-static int epaLanes()
-{
-  static int v = -1;
-  if (v < 0)
+  constexpr int STRIDE = 13;  // doubles per staged record (12 + 1: conflict-free column access)
+  __shared__ double stage[4][32 * STRIDE];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double* sm = stage[warp];
+  Xf<double> Tj[MAXJ];
+  for (int64_t base = blockIdx.x * (int64_t)blockDim.x; base < n; base += (int64_t)gridDim.x * blockDim.x)
   {
-    const char* e = std::getenv("T4C_EPA_LANES");
-    v = (e && std::atoi(e) == 1) ? 1 : 0;
+    const int64_t i = base + threadIdx.x;
+    const bool valid = i < n;
+    const int64_t s = first + i;
+    if (P.fk_out)
+    {
+      if (valid)
+      {
+        fkOne(P, P.q0, s, Tj);
+        fkStoreAllLinks(P, Tj, s);
+      }
+      continue;
+    }
+    const int64_t s0 = first + base + warp * 32;                     // first state of this warp
+    const int cnt = (int)t4min<int64_t>(32, n - (base + warp * 32));  // states of this warp inside the range
+    for (int pass = 0; pass < (P.cast ? 2 : 1); ++pass)
+    {
+      if (valid)
+        fkOne(P, pass ? P.q1 : P.q0, s, Tj);
+      float* dst = pass ? P.poses1 : P.poses0;
+      double* dstd = pass ? P.poses1d : P.poses0d;
+      for (int a = 0; a < P.n_alinks; ++a)
+      {
+        if (valid)
+        {
+          const Xf<double> x = fkAlinkPose(P, Tj, a);
+          double* r = sm + lane * STRIDE;
+          r[0] = x.r[0], r[1] = x.r[1], r[2] = x.r[2], r[3] = x.p.x;
+          r[4] = x.r[3], r[5] = x.r[4], r[6] = x.r[5], r[7] = x.p.y;
+          r[8] = x.r[6], r[9] = x.r[7], r[10] = x.r[8], r[11] = x.p.z;
+        }
+        __syncwarp();
+        if (cnt > 0)
+        {
+          const size_t off = poseOffset(P, s0, a);  // 96 B (48 B) per state: 16-byte aligned for any s0
+          double2* o64 = reinterpret_cast<double2*>(dstd + off);
+          for (int e = lane; e < cnt * 6; e += 32)  // 6 x 128 bit per FP64 record
+          {
+            const int st = e / 6, k = (e - st * 6) * 2;
+            o64[e] = make_double2(sm[st * STRIDE + k], sm[st * STRIDE + k + 1]);
+          }
+          float4* o32 = reinterpret_cast<float4*>(dst + off);
+          for (int e = lane; e < cnt * 3; e += 32)  // 3 x 128 bit per FP32 record
+          {
+            const int st = e / 3, k = (e - st * 3) * 4;
+            const double* r = sm + st * STRIDE + k;
+            o32[e] = make_float4((float)r[0], (float)r[1], (float)r[2], (float)r[3]);
+          }
+        }
+        __syncwarp();
+      }
+    }
   }
-  return v;
-}
-
-static int gjkLanes()
-{
-  static int v = -1;
-  if (v < 0)
-  {
-    const char* e = std::getenv("T4C_GJK_LANES");
-    v = (e && std::atoi(e) == 1) ? 1 : 0;
-  }
-  return v;
-}
-
-static int exactRegs()
-{
-  static int v = 0;
-  if (!v)
-  {
-    const char* e = std::getenv("T4C_EXACT_REGS");
-    v = (e && std::atoi(e) == 255) ? 255 : 128;
-  }
-  return v;
-}
-
-// FK feeds the exact pass: same two-rounding arithmetic so that link poses equal the reference's FP64 FK
-// states [first, first + n) of the chunk (the host-buffer entries run FK piecewise under the upload of q)
-__global__ void __launch_bounds__(128) fkKernel(KParams P, int64_t first, int64_t n)
-{
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    fkBody(first + i, P);
-}
-
-// robots with at most 16 joints (iiwa: 9, IRB2400: 8) keep the joint frames in a 1.5 KB frame instead of 6 KB
-__global__ void __launch_bounds__(128) fkKernel16(KParams P, int64_t first, int64_t n)
-{
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    fkBodyT<16>(first + i, P);
 }
 
 void t4LaunchFk(const KParams& P, int64_t first, int64_t n, int grid, cudaStream_t st)
 {
+  // robots with at most 16 joints (iiwa: 9, IRB2400: 8) keep the joint frames in a 1.5 KB frame instead of 6 KB
   if (P.n_joints <= 16)
-    fkKernel16<<<grid, 128, 0, st>>>(P, first, n);
+    fkKernelT<16><<<grid, 128, 0, st>>>(P, first, n);
   else
-    fkKernel<<<grid, 128, 0, st>>>(P, first, n);
+    fkKernelT<T4_MAX_JOINTS><<<grid, 128, 0, st>>>(P, first, n);
 }
 
 // LVS subdivision: FP64, two roundings per a*b+c like the host formula it restates (Eigen LinSpaced)
@@ -147,30 +124,10 @@ void t4LaunchLvsExpand(const LvsParams& L, int64_t n, int grid, cudaStream_t st)
 
 void t4LaunchGjk(const KParams& P, int64_t n, int grid, int block, cudaStream_t st)
 {
-  static const int minb = envMinB("T4C_GJK_MINB");
-  if (gjkLanes())
-    gjkLaneKernel<<<grid, 128, 0, st>>>(P, n);
-  else if (minb == 5)
-    gjkKernelB<5><<<grid, block, 0, st>>>(P, n);
-  else if (minb == 6)
-    gjkKernelB<6><<<grid, block, 0, st>>>(P, n);
-  else if (exactRegs() == 128)
-    gjkKernelR128<<<grid, block, 0, st>>>(P, n);
-  else
-    gjkKernel<<<grid, block, 0, st>>>(P, n);
+  gjkKernelR128<<<grid, block, 0, st>>>(P, n);
 }
 
 void t4LaunchEpa(const KParams& P, int64_t n, int grid, int block, cudaStream_t st)
 {
-  static const int minb = envMinB("T4C_EPA_MINB");
-  if (epaLanes())
-    epaLaneKernel<<<grid, 128, 0, st>>>(P, n);
-  else if (minb == 5)
-    epaKernelB<5><<<grid, block, 0, st>>>(P, n);
-  else if (minb == 6)
-    epaKernelB<6><<<grid, block, 0, st>>>(P, n);
-  else if (exactRegs() == 128)
-    epaKernelR128<<<grid, block, 0, st>>>(P, n);
-  else
-    epaKernel<<<grid, block, 0, st>>>(P, n);
+  epaKernelR128<<<grid, block, 0, st>>>(P, n);
 }

@@ -49,26 +49,6 @@ def test_fk(robot):
     pc.fk_parity(mk, robot)
 
 
-def test_lane_refill_state_machine(monkeypatch):
-    """the opt-in lane-refill form of the exact GJK pass (t4_kernels2.h gjkLaneLoop) gives the same contacts"""
-    monkeypatch.setenv("T4C_GJK_LANES", "1")
-    monkeypatch.setenv("T4C_EPA_LANES", "1")
-    print(pc.discrete_config2(mk, 300, 10000, capi.TEST_CLOSEST))
-    print(pc.cast_config3(mk, 4, 10, 10000))
-
-
-def test_grouped_broadphase(monkeypatch):
-    """the opt-in grouped BVH traversal (t4_kernels.h broadStaticGroupBody) finds the same candidate set"""
-    import subprocess, sys, os
-    code = ("import sys; sys.path.insert(0, 'tests'); import parity_cases as pc; from hostsim import build as h; "
-            "from tesseract_b200.managers import BatchChecker; from tesseract_b200 import capi; "
-            "print(pc.discrete_config2(lambda b: BatchChecker(b, lib=h.lib()), 200, 10000, capi.TEST_CLOSEST))")
-    env = dict(os.environ, T4C_BROAD_GROUP="1")
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0, r.stdout + r.stderr
-
-
 def test_first_in_rounds():
     """FIRST queries in rounds over the robot's shapes (t4c.cu runBatch; on by default for >= 16384 states): same
     flags, one record per colliding state, each record a contact the oracle also reports"""

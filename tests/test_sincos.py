@@ -1,0 +1,54 @@
+"""t4_sincos.h (device FK sine / cosine) against the host libm the oracle -- and the reference -- call.
+
+The claim under test: bit-identical results, so that device link poses equal host link poses exactly and the timed path
+can be held to the strict parity rule.  CPU tier: the same header compiled into the host simulator.  GPU tier: the
+kernel on the device (tests/test_gpu_parity.py::test_sincos_device)."""
+import ctypes as C
+import ctypes.util
+import math
+
+import numpy as np
+
+from hostsim import build as hostsim
+
+
+def libm_sincos(x):
+    sin = np.fromiter((math.sin(v) for v in x), dtype=np.float64, count=len(x))
+    cos = np.fromiter((math.cos(v) for v in x), dtype=np.float64, count=len(x))
+    return sin, cos
+
+
+def arguments(n, seed=1):
+    rng = np.random.default_rng(seed)
+    x = np.concatenate([rng.uniform(-3.2, 3.2, n // 2),            # joint ranges
+                        rng.uniform(-100.0, 100.0, n // 4),        # Cody-Waite reduction, all quadrants
+                        rng.uniform(-1.0, 1.0, n // 8) * 1e-3,     # Taylor branch
+                        rng.uniform(-1.0, 1.0, n // 8) * 1e5])
+    edge = np.array([0.0, -0.0, 1e-9, 2.0 ** -26, 2.0 ** -27, 0.126, 0.855469, 2.426265, math.pi / 2, math.pi,
+                     -math.pi, 2 * math.pi, 105414349.0, 1e9, -1e9])
+    return np.concatenate([x, edge, np.nextafter(edge, 1e30), np.nextafter(edge, -1e30)])
+
+
+def check_bits(run, n):
+    x = arguments(n)
+    s, c = run(x)
+    s0, c0 = libm_sincos(x)
+    bad_s = int((s.view(np.uint64) != s0.view(np.uint64)).sum())
+    bad_c = int((c.view(np.uint64) != c0.view(np.uint64)).sum())
+    assert bad_s == 0 and bad_c == 0, f"{bad_s} sines / {bad_c} cosines of {len(x)} differ from the host libm"
+    return len(x)
+
+
+def run_lib(lib, device=0):
+    def run(x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        s, c = np.empty_like(x), np.empty_like(x)
+        dp = C.POINTER(C.c_double)
+        st = lib.t4c_debug_sincos(device, x.ctypes.data_as(dp), len(x), s.ctypes.data_as(dp), c.ctypes.data_as(dp))
+        assert st == 0, lib.t4c_last_error()
+        return s, c
+    return run
+
+
+def test_sincos_bits_match_host_libm():
+    print(check_bits(run_lib(hostsim.lib()), 400000), "arguments, 0 mismatches")
