@@ -67,7 +67,7 @@ def lib():
                                      C.POINTER(I32), I64]
         L.t4o_pair_distance.restype = C.c_int
         L.t4o_pair_distance.argtypes = [C.POINTER(capi.Shape), DP, C.POINTER(capi.Shape), DP, DP, C.c_double,
-                                        C.c_int, C.c_int, DP, DP, DP]
+                                        C.c_int, C.c_int, DP, DP, DP]  # noqa
         _lib = L
     return _lib
 
@@ -144,6 +144,23 @@ class OracleManager:
         c = (C.c_uint64 * 6)()
         self.L.t4o_manager_get_counters(self.h, c)
         return dict(zip(COUNTER_NAMES, [int(x) for x in c]))
+
+
+def pair_distance(builder, shape_a, pose_a, shape_b, pose_b, threshold, calculate_penetration=True,
+                  calculate_distance=True):
+    """One convex-convex query of the restated detector (collideConvexConvex): shapes are indices into builder.shapes,
+    poses 3x4 WORLD poses of the shapes.  Returns (distance, normal_on_b, point_on_b) or None."""
+    L = lib()
+    sd = builder.scene_desc()
+    pa = np.ascontiguousarray(pose_a, dtype=np.float64).reshape(12)
+    pb = np.ascontiguousarray(pose_b, dtype=np.float64).reshape(12)
+    d = C.c_double()
+    n = np.zeros(3)
+    p = np.zeros(3)
+    ok = L.t4o_pair_distance(C.byref(sd.shapes[shape_a]), _dp(pa), C.byref(sd.shapes[shape_b]), _dp(pb), sd.vertices,
+                             float(threshold), int(calculate_penetration), int(calculate_distance), C.byref(d), _dp(n),
+                             _dp(p))
+    return (float(d.value), n, p) if ok else None
 
 
 def fk(builder, q):

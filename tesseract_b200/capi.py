@@ -59,8 +59,9 @@ class Stats(C.Structure):
                                           "gjk_iterations", "epa_pairs", "epa_iterations", "contacts",
                                           "colliding_states", "cull_iterations", "exact_pairs", "phase1_iterations",
                                           "phase2_iterations", "epa_gjk_iterations", "support_vertices",
-                                          "support_vertices_fp64", "bvh_stack_overflows", "phase1_skipped")] + \
-               [("reserved", C.c_uint64 * 3)]
+                                          "support_vertices_fp64", "bvh_stack_overflows", "phase1_skipped",
+                                          "support_vertices_epa")] + \
+               [("reserved", C.c_uint64 * 2)]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_ if n != "reserved"}

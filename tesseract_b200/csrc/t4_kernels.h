@@ -43,6 +43,7 @@ enum
   ST_SUPV64,         // ... in the FP64 kernels
   ST_BVH_OVERFLOW,   // traversal stack overflows (the call fails when non-zero)
   ST_P1_SKIPPED,     // exact pairs whose phase-1 outcome was certified by the cull
+  ST_SUPV_EPA,       // part of ST_SUPV64 evaluated in the EPA kernel
   ST_COUNT
 };
 

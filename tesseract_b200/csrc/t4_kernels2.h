@@ -389,6 +389,7 @@ T4_KD void epaBody(int64_t t, const KParams& P, EPA_T& epa)
   statAdd(P.stats, ST_EPA_PAIRS, 1u);
   statAdd(P.stats, ST_EPA_ITERS, (uint32_t)d.epa_iters);
   statAdd(P.stats, ST_SUPV64, A.evals + B.evals);
+  statAdd(P.stats, ST_SUPV_EPA, A.evals + B.evals);
   PairResult<double> pr;
   copyOut(d, pr);
   if (!pr.has)

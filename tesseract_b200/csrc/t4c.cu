@@ -1187,6 +1187,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
   io.stats.support_vertices_fp64 = stats_host[ST_SUPV64];
   io.stats.bvh_stack_overflows = stats_host[ST_BVH_OVERFLOW];
   io.stats.phase1_skipped = stats_host[ST_P1_SKIPPED];
+  io.stats.support_vertices_epa = stats_host[ST_SUPV_EPA];
   if (stats_host[ST_BVH_OVERFLOW])
     return fail(T4C_ERR_UNSUPPORTED, "environment BVH traversal overflowed its stack %llu times: results incomplete",
                 stats_host[ST_BVH_OVERFLOW]);

@@ -23,6 +23,11 @@ DATA_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data")
 
 
 # --------------------------------------------------------------------------- geometry PODs
+SHAPE_DTYPE = np.dtype([("type", "<i4"), ("link", "<i4"), ("shape_id", "<i4"), ("subshape_id", "<i4"),
+                        ("params", "<f8", 3), ("vertex_offset", "<i4"), ("vertex_count", "<i4"), ("pose", "<f8", 12)])
+assert SHAPE_DTYPE.itemsize == C.sizeof(capi.Shape)
+
+
 class Geometry:
     pass
 
@@ -175,14 +180,20 @@ class SceneBuilder:
                 for f in range(len(g.faces)):
                     self._shape(capi.TRIANGLE, li, j, f, (0, 0, 0), P, off + 3 * f, 3)
             elif isinstance(g, Octree):
-                for v, (x, y, z, size) in enumerate(g.leaves):  # bullet_utils.cpp:160-243
-                    Pv = compose(P, pose((x, y, z)))
+                # bullet_utils.cpp:160-243: one box (half = size/2) / inscribed sphere / circumscribed-in-plane sphere
+                # (r = sqrt(2) size/2) per occupied leaf; child pose = P * Translation(centre)
+                centres = g.leaves[:, :3] @ P[:, :3].T + P[:, 3]
+                half = g.leaves[:, 3] * 0.5
+                for v in range(len(g.leaves)):
+                    Pv = P.copy()
+                    Pv[:, 3] = centres[v]
+                    h = float(half[v])
                     if g.sub_type == Octree.BOX:
-                        self._shape(capi.BOX, li, j, v, (size / 2, size / 2, size / 2), Pv)
+                        self._shape(capi.BOX, li, j, v, (h, h, h), Pv)
                     elif g.sub_type == Octree.SPHERE_INSIDE:
-                        self._shape(capi.SPHERE, li, j, v, (size / 2, 0, 0), Pv)
+                        self._shape(capi.SPHERE, li, j, v, (h, 0, 0), Pv)
                     else:
-                        self._shape(capi.SPHERE, li, j, v, (math.sqrt(2 * ((size / 2) * (size / 2))), 0, 0), Pv)
+                        self._shape(capi.SPHERE, li, j, v, (math.sqrt(2 * (h * h)), 0, 0), Pv)
             else:
                 raise TypeError(f"unsupported geometry {type(g)}")
         return True
@@ -239,13 +250,15 @@ class SceneBuilder:
             links[i].enabled = self.link_enabled[i]
             links[i].active = self.link_active[i]
             links[i].pose[:] = self.link_pose[i].reshape(-1).tolist()
-        shapes = (capi.Shape * max(len(self.shapes), 1))()
-        for i, s in enumerate(self.shapes):
-            sh = shapes[i]
-            sh.type, sh.link, sh.shape_id, sh.subshape_id = s["type"], s["link"], s["shape_id"], s["subshape_id"]
-            sh.params[:] = [float(x) for x in s["params"]]
-            sh.vertex_offset, sh.vertex_count = s["vertex_offset"], s["vertex_count"]
-            sh.pose[:] = s["pose"].reshape(-1).tolist()
+        # t4c_shape records through a numpy mirror of the struct (a million voxels fill in seconds, not minutes)
+        ns = len(self.shapes)
+        arr = np.zeros(max(ns, 1), dtype=SHAPE_DTYPE)
+        if ns:
+            for f in ("type", "link", "shape_id", "subshape_id", "vertex_offset", "vertex_count"):
+                arr[f][:ns] = np.fromiter((s[f] for s in self.shapes), dtype=np.int32, count=ns)
+            arr["params"][:ns] = np.array([s["params"] for s in self.shapes], dtype=np.float64).reshape(ns, 3)
+            arr["pose"][:ns] = np.array([s["pose"] for s in self.shapes], dtype=np.float64).reshape(ns, 12)
+        shapes = (capi.Shape * max(ns, 1)).from_buffer(arr)
         verts = np.ascontiguousarray(np.vstack(self.vertices) if self.vertices else np.zeros((0, 3)))
         acm = np.ascontiguousarray(np.array(sorted(self.acm), dtype=np.int32).reshape(-1, 2))
         mp = np.ascontiguousarray(np.array(sorted(self.pair_margins.keys()), dtype=np.int32).reshape(-1, 2))
@@ -260,7 +273,7 @@ class SceneBuilder:
         d.n_margin_pairs = len(mp)
         d.margin_pairs = mp.ctypes.data_as(C.POINTER(C.c_int32))
         d.margin_values = mv.ctypes.data_as(C.POINTER(C.c_double))
-        self._keep.append((links, names, shapes, verts, acm, mp, mv))
+        self._keep.append((links, names, shapes, arr, verts, acm, mp, mv))
         return d
 
     def fk_desc(self, root=None):
@@ -412,6 +425,70 @@ def build_config4(octree_leaves, plane=None, margin=0.10, robot_xyz=(0.0, -2.0, 
     b.set_active(moving)
     b.set_margin(margin)
     return b
+
+
+def synthetic_room_voxels(n_voxels=1000000, res=0.02, seed=99):
+    """SURVEY 8(d) config 4 occupancy: voxels of `res` on the inside of a 4 x 4 x 2.5 m room (shell five voxels thick:
+    a real octomap wall is one voxel thick, five layers are what it takes to reach a million leaves at this size)
+    plus six solid box fixtures around the robot, thinned at random (seed) to exactly n_voxels.  Returns (n, 4)
+    centre + edge, sorted in Morton order of the cell index like an octomap leaf iterator (depth first)."""
+    rng = np.random.Generator(np.random.MT19937(seed))
+    nx, ny, nz = int(round(4.0 / res)), int(round(4.0 / res)), int(round(2.5 / res))
+    ix, iy, iz = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz), indexing="ij")
+    t = 5
+    shell = (ix < t) | (ix >= nx - t) | (iy < t) | (iy >= ny - t) | (iz < t) | (iz >= nz - t)
+    occ = shell.copy()
+    centre = lambda a, n: (a + 0.5) * res - (n * res) / 2.0
+    X, Y, Z = centre(ix, nx), centre(iy, ny), (iz + 0.5) * res
+    fixtures = [((1.05, 0.0), (0.6, 0.7, 0.9)), ((-1.0, 0.3), (0.7, 0.6, 0.8)), ((0.2, 1.1), (0.8, 0.5, 1.0)),
+                ((0.0, -1.15), (0.7, 0.7, 0.7)), ((1.2, 1.2), (0.6, 0.6, 1.2)), ((-1.2, -1.1), (0.7, 0.7, 1.1))]
+    for (cx, cy), (sx, sy, sz) in fixtures:
+        occ |= (np.abs(X - cx) <= sx / 2) & (np.abs(Y - cy) <= sy / 2) & (Z <= sz + t * res)
+    idx = np.flatnonzero(occ.reshape(-1))
+    if len(idx) < n_voxels:
+        raise ValueError(f"only {len(idx)} occupied cells")
+    idx = np.sort(rng.choice(idx, size=n_voxels, replace=False))
+    cx, cy, cz = X.reshape(-1)[idx], Y.reshape(-1)[idx], Z.reshape(-1)[idx]
+    return np.stack([cx, cy, cz, np.full(len(idx), res)], axis=1)
+
+
+def build_config4_synthetic(n_voxels=1000000, margin=0.10, plane=None, seed=99):
+    """BASELINE.json configs[3]: ABB IRB2400 hull links vs n_voxels synthetic octomap voxels -- half as boxes, half as
+    SPHERE_OUTSIDE (bullet_utils.cpp:182-183,228) -- plus the concave workcell mesh (one triangle per face)."""
+    leaves = synthetic_room_voxels(n_voxels, seed=seed)
+    b = SceneBuilder()
+    root, moving = add_robot(b, load_robot("abb_irb2400"), base_pose=pose((0.0, 0.0, 5 * 0.02)))
+    b.add_collision_object("octomap_boxes", 0, [Octree(leaves[0::2], Octree.BOX)], [identity()])
+    b.add_collision_object("octomap_spheres", 0, [Octree(leaves[1::2], Octree.SPHERE_OUTSIDE)], [identity()])
+    if plane is not None:
+        b.add_collision_object("workcell", 0, [Mesh(plane[0], plane[1])], [pose((0.0, 0.0, 5 * 0.02 + 0.001))])
+    b.set_active(moving)
+    b.set_margin(margin)
+    return b
+
+
+def lbracket_mesh(seed):
+    """small concave fixture: an L-bracket as a closed triangle mesh (two boxes sharing an edge), ~24 triangles"""
+    rng = np.random.default_rng(seed)
+    a, t, w = rng.uniform(0.15, 0.3), rng.uniform(0.02, 0.04), rng.uniform(0.1, 0.2)
+    boxes = [((0, 0, 0), (a, w, t)), ((0, 0, 0), (t, w, a))]
+    V, F = [], []
+    for (x0, y0, z0), (dx, dy, dz) in boxes:
+        o = len(V)
+        V += [(x0 + i * dx, y0 + j * dy, z0 + k * dz) for i in (0, 1) for j in (0, 1) for k in (0, 1)]
+        quads = [(0, 1, 3, 2), (4, 6, 7, 5), (0, 4, 5, 1), (2, 3, 7, 6), (0, 2, 6, 4), (1, 5, 7, 3)]
+        for q in quads:
+            F += [(o + q[0], o + q[1], o + q[2]), (o + q[0], o + q[2], o + q[3])]
+    return np.array(V, dtype=np.float64), np.array(F, dtype=np.int64)
+
+
+def config5_fixtures():
+    """the four concave fixtures of configs[4] (seed 5.., between the two arms)"""
+    out = []
+    for i in range(4):
+        v, f = lbracket_mesh(5 + i)
+        out.append((f"fixture_{i}", v, f, pose((0.45 * (1 if i % 2 else -1), 0.3 * (1 if i < 2 else -1), 0.35))))
+    return out
 
 
 def build_config5(n_prims=2000, margin=0.05, fixtures=None):

@@ -22,7 +22,7 @@ def test_every_declared_symbol_is_exported():
     lib = capi.load_library()
     missing = [n for n in declared_functions() if not hasattr(lib, n)]
     assert not missing, missing
-    assert lib.t4c_abi_version() == 1
+    assert lib.t4c_abi_version() == 2
 
 
 def test_no_cpu_fallback_without_device():

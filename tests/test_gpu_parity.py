@@ -21,10 +21,34 @@ def test_discrete_config2(tt):
     print(pc.discrete_config2(mk, 20000, 10000, tt, threads=THREADS))
 
 
-@pytest.mark.parametrize("tt", [capi.TEST_FIRST, capi.TEST_CLOSEST])
+@pytest.mark.parametrize("tt", [capi.TEST_FIRST, capi.TEST_CLOSEST, capi.TEST_ALL])
 def test_discrete_config2_device_fk(tt):
-    """full path: FK on the device (see parity_cases.flip_statistics)"""
+    """the timed path -- joint vectors in, FK on the device -- under the same strict rule as the FK-bypass entries"""
     print(pc.discrete_config2(mk, 20000, 10000, tt, device_fk=True, threads=THREADS))
+
+
+def test_sincos_device():
+    """t4_sincos.h evaluated by a kernel on the device: the host libm's bits on 2e6 arguments"""
+    import test_sincos as ts
+    print(ts.check_bits(ts.run_lib(capi.load_library()), 2000000), "arguments, 0 mismatches")
+
+
+def test_budgeted_gjk_async_pass():
+    """FIRST rounds + a GJK budget of 4 support pairs on 32 768 states: most pairs are deferred to the long-pair pass,
+    which runs on its own stream beside the deferred tiers and the EPA launch; results must not change (a deferred
+    pair is run again from the start)"""
+    import subprocess, sys
+    code = ("import sys, os; sys.path.insert(0, 'tests'); import parity_cases as pc; "
+            "from tesseract_b200.managers import BatchChecker; from tesseract_b200 import capi; "
+            "mk = lambda b: BatchChecker(b); t = os.cpu_count(); "
+            "print(pc.discrete_config2(mk, 32768, 10000, capi.TEST_FIRST, device_fk=True, threads=t)); "
+            "print(pc.discrete_config2(mk, 32768, 10000, capi.TEST_CLOSEST, device_fk=True, threads=t)); "
+            "print(pc.flags_only(mk, 32768, 10000, threads=t))")
+    env = dict(os.environ, T4C_GJK_BUDGET="4", T4C_DRAIN_MIN="1", T4C_UPLOAD_PIECE_MIN="4096")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=1800)
+    print(r.stdout[-2000:])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
 
 
 def test_cast_trajectories_device_fk():
