@@ -297,21 +297,6 @@ T4_HDN void phase3Apply(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T>
   }
 }
 
-template <class T, class EPA_T>
-T4_HDN void detectPhase3(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T>& S, DetectorOut<T>& out, EPA_T& epa)
-{
-  out.used_epa = true;
-  GjkOut<T, true> g;
-  const int st = phase3Seed(A, B, g);
-  out.gjk_iters += g.iters;
-  EpaResult<T> er;
-  er.iterations = 0;
-  bool ok = false;
-  if (st == GJK_INTERSECT)
-    ok = epa.run(A, B, g.sx.W, g.sx.P, g.sx.n, 255, T(1e-12), er);
-  phase3Apply(A, B, S, out, st, g.v, g.pA, ok, er);
-}
-
 // phase 4 (:1111-1179): acceptance test ...
 template <class T>
 T4_HD bool phase4Accepts(const DetectorState<T>& S, T maxDist2)
@@ -355,23 +340,6 @@ T4_HDN void detectPhase4(const ShapeW<T>& A, const ShapeW<T>& B, const V3<T>& po
   const T d0 = normalInB.dot(supportW(A, -normalInB, false) - supportW(B, normalInB, false)) - margin;
   out.gjk_iters += 3;
   phase4Decide(S, d0, d1, d2, positionOffset, out);
-}
-
-// A, B: shapes with WORLD poses.  maxDist2 = (marginA + marginB + contactBreakingThreshold + max margin)^2  (:435-440 of
-// tesseract_convex_convex_algorithm.cpp).  Single-call form (all phases in one thread).
-template <class T, class EPA_T>
-T4_HD void gjkPairDetector(const ShapeW<T>& A0, const ShapeW<T>& B0, T maxDist2, bool calc_pen, bool calc_dist,
-                           DetectorOut<T>& out, EPA_T& epa)
-{
-  ShapeW<T> A = A0, B = B0;
-  const V3<T> positionOffset = recentre(A, B);
-  DetectorState<T> S;
-  const int r = detectPhase12(A, B, positionOffset, maxDist2, calc_pen, calc_dist, S, out);
-  if (r == DET_DONE)
-    return;
-  if (r == DET_PHASE3)
-    detectPhase3(A, B, S, out, epa);
-  detectPhase4(A, B, positionOffset, maxDist2, S, out);
 }
 
 }  // namespace bt

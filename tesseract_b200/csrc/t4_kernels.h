@@ -56,12 +56,13 @@ enum
   Q_SURV3,      // FIRST with records: one certainly penetrating pair per state against a CURVED primitive (slow EPA)
   Q_SURV4,      // FIRST with records: every other survivor (looked at only if still no contact after the others)
   Q_TASK,       // pairs handed from the GJK kernel to the EPA kernel
-  Q_FETCH,      // next survivor to hand to a lane of the GJK kernel (lane-refill loop)
-  Q_FETCH_EPA,  // next EPA task to hand to a lane of the EPA kernel (lane-refill loop)
+  Q_FETCH,      // EPA kernel, small-polytope tier: next task to hand to a group
+  Q_FETCH_EPA,  // EPA kernel, full-size tier: next entry of the retry queue to hand to a warp
   Q_RAW,        // raw contacts (CLOSEST staging) or final contacts (ALL / FIRST)
   Q_OUT,        // final contacts emitted by the CLOSEST reduction
   Q_LONG,       // survivors whose GJK ran out of its iteration budget: run again, without one, beside the later passes
   Q_TASK_LONG,  // EPA tasks of the long-pair pass (it runs on its own stream: own task queue)
+  Q_RETRY,      // EPA tasks forwarded from the small-polytope tier to the full-size tier (curved cores, pool overflow)
   Q_COUNT
 };
 
@@ -156,6 +157,8 @@ struct KParams
   EpaTask* tasks;
   const uint32_t* task_order;  // EPA tasks sorted by shape-type pair (null: queue order)
   uint32_t task_cap;
+  uint32_t* epa_retry;         // task indices forwarded to the full-size EPA tier (Q_RETRY entries)
+  double* epa_scratch;         // A-side witnesses of the polytope vertices, 3 doubles x pool size per resident group
   uint32_t* qcount;       // [Q_COUNT]
   unsigned long long* stats;  // [ST_COUNT]
   uint8_t* hit;           // [n] (chunk-relative) or null

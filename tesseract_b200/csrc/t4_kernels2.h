@@ -355,48 +355,112 @@ T4_KD void gjkBody(int64_t k, const KParams& P)
   statAdd(P.stats, ST_SUPV64, cnt.supv);
 }
 
-// item = EPA task: phase 3 (penetration) and phase 4 of the exact query
-template <class EPA_T>
-T4_KD void epaBody(int64_t t, const KParams& P, EPA_T& epa)
+// One EPA task -- phase 3 (penetration) and phase 4 of the exact query -- worked on by a group of G lanes with the
+// polytope in the shared-memory pool S (t4_epa.h).  The group's first lane does the scalar parts (seed GJK, support
+// mapping, phase 4, result bridging); all lanes share the data-parallel parts of the expansion.
+// FORWARD: this is the small-polytope tier -- tasks with a curved core (cylinder / cone: 15-75 iterations, 100+ faces)
+// and tasks that run into the pool capacity are forwarded to the full-size tier through the retry queue.  A forwarded
+// task is run again from the start there, so the result does not depend on the tiering.
+template <int G, int MAXV, int MAXF, bool FORWARD>
+T4_KD void epaTaskBody(uint32_t t, const KParams& P, EpaPool<MAXV, MAXF>& S, V3<double>* Pw)
 {
-  const EpaTask& T = P.tasks[P.task_order ? P.task_order[t] : (uint32_t)t];
-  const uint32_t c = T.cand;
-  const int64_t s = P.cand_state[c];
-  if ((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit[s])
-    return;
-  const int a = (int)P.cand_a[c], b = (int)P.cand_b[c];
-  ShapeW<double> A, B;
-  loadPairShapesD(P, s, a, b, A, B);
-  const double maxDist2 = detectorMaxDist2(A, B, P.max_margin_d);
-  const V3<double> offset = bt::recentre(A, B);
-  bt::DetectorState<double> S;
-  S.isValid = T.is_valid;
-  S.status = 0;
-  S.distance = T.distance;
-  S.normalInB = V3<double>(T.normalInB[0], T.normalInB[1], T.normalInB[2]);
-  S.pointOnA = V3<double>(T.pointOnA[0], T.pointOnA[1], T.pointOnA[2]);
-  S.pointOnB = V3<double>(T.pointOnB[0], T.pointOnB[1], T.pointOnB[2]);
-  S.orgNormalInB = V3<double>(T.orgNormalInB[0], T.orgNormalInB[1], T.orgNormalInB[2]);
+  EpaCoop<G, MAXV, MAXF> epa(S, Pw);
+  const bool leader = epa.g.lane == 0;
+  // leader state
+  uint32_t c = 0;
+  int64_t s = 0;
+  int a = 0, b = 0, st = GJK_SEPARATED;
+  double maxDist2 = 0;
+  V3<double> offset;
+  bt::DetectorState<double> St;
   bt::DetectorOut<double> d;
-  d.has = false;
-  d.gjk_iters = 0;
-  d.epa_iters = 0;
-  d.p1_iters = 0;
-  d.used_epa = false;
-  bt::detectPhase3(A, B, S, d, epa);
-  bt::detectPhase4(A, B, offset, maxDist2, S, d);
-  statAdd(P.stats, ST_EPA_GJK_ITERS, (uint32_t)d.gjk_iters);
-  statAdd(P.stats, ST_EPA_PAIRS, 1u);
-  statAdd(P.stats, ST_EPA_ITERS, (uint32_t)d.epa_iters);
-  statAdd(P.stats, ST_SUPV64, A.evals + B.evals);
-  statAdd(P.stats, ST_SUPV_EPA, A.evals + B.evals);
-  PairResult<double> pr;
-  copyOut(d, pr);
-  if (!pr.has)
-    return;
-  if (P.cast)
-    loadPairShapesD(P, s, a, b, A, B);
-  emitContact(P, s, a, b, A, B, pr);
+  GjkOut<double, true> gj;
+  gj.sx.n = 0;
+  if (leader)
+  {
+    int run = 0;  // 0: nothing to do, 1: expand the polytope, 2: no expansion (the seed GJK decided), 3: forward
+    const EpaTask& T = P.tasks[P.task_order ? P.task_order[t] : t];
+    c = T.cand;
+    s = P.cand_state[c];
+    if (!((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit[s]))
+    {
+      a = (int)P.cand_a[c], b = (int)P.cand_b[c];
+      loadPairShapesD(P, s, a, b, S.A, S.B);
+      if (FORWARD && (S.A.curvedCore() || S.B.curvedCore()))
+        run = 3;
+      else
+      {
+        maxDist2 = detectorMaxDist2(S.A, S.B, P.max_margin_d);
+        offset = bt::recentre(S.A, S.B);
+        St.isValid = T.is_valid;
+        St.status = 0;
+        St.distance = T.distance;
+        St.normalInB = V3<double>(T.normalInB[0], T.normalInB[1], T.normalInB[2]);
+        St.pointOnA = V3<double>(T.pointOnA[0], T.pointOnA[1], T.pointOnA[2]);
+        St.pointOnB = V3<double>(T.pointOnB[0], T.pointOnB[1], T.pointOnB[2]);
+        St.orgNormalInB = V3<double>(T.orgNormalInB[0], T.orgNormalInB[1], T.orgNormalInB[2]);
+        d.has = false;
+        d.gjk_iters = 0;
+        d.epa_iters = 0;
+        d.p1_iters = 0;
+        d.used_epa = true;
+        st = bt::phase3Seed(S.A, S.B, gj);
+        d.gjk_iters += gj.iters;
+        run = st == GJK_INTERSECT ? 1 : 2;
+      }
+    }
+    S.ctl = run;
+  }
+  epa.g.sync();
+  int run = S.ctl;
+  epa.g.sync();
+  EpaResult<double> er;
+  er.iterations = 0;
+  er.capped = false;
+  bool ok = false;
+  if (run == 1)
+  {
+    if (epa.begin(gj.sx.W, gj.sx.P, gj.sx.n, 255, 1e-12))
+    {
+      int r;
+      while ((r = epa.step()) == 0)
+      {
+      }
+      ok = r != 2 && epa.finish(er);
+    }
+    if (FORWARD && epa.capped)
+      run = 3;
+  }
+  if (leader && run == 3)
+  {
+    const uint32_t k = qAppend(&P.qcount[Q_RETRY]);
+    P.epa_retry[k] = t;  // sized for every task of the launch
+  }
+  else if (leader && run != 0)
+  {
+    bt::phase3Apply(S.A, S.B, St, d, st, gj.v, gj.pA, ok, er);
+    bt::detectPhase4(S.A, S.B, offset, maxDist2, St, d);
+    statAdd(P.stats, ST_EPA_GJK_ITERS, (uint32_t)d.gjk_iters);
+    statAdd(P.stats, ST_EPA_PAIRS, 1u);
+    statAdd(P.stats, ST_EPA_ITERS, (uint32_t)d.epa_iters);
+    statAdd(P.stats, ST_SUPV64, S.A.evals + S.B.evals);
+    statAdd(P.stats, ST_SUPV_EPA, S.A.evals + S.B.evals);
+    PairResult<double> pr;
+    copyOut(d, pr);
+    if (pr.has)
+    {
+      if (P.cast)
+      {
+        // continuous data needs the shapes at their world poses (not recentred)
+        ShapeW<double> A, B;
+        loadPairShapesD(P, s, a, b, A, B);
+        emitContact(P, s, a, b, A, B, pr);
+      }
+      else
+        emitContact(P, s, a, b, S.A, S.B, pr);
+    }
+  }
+  epa.g.sync();  // the pool is reused by the group's next task
 }
 
 T4_KD unsigned long long mix64(unsigned long long x)

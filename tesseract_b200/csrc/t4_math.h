@@ -19,12 +19,16 @@
 #define T4_HDN __host__ __device__ __noinline__
 #define T4_KD __device__ __forceinline__ /* kernel bodies: may use device-only primitives */
 #define T4_KDN static __device__ __noinline__
+#define T4_KM __device__ __forceinline__ /* member functions of device-only classes */
+#define T4_KMN __device__ __noinline__
 #define T4_DEVICE_BUILD 1
 #else
 #define T4_HD inline
 #define T4_HDN
 #define T4_KD inline
 #define T4_KDN inline
+#define T4_KM inline
+#define T4_KMN
 #endif
 
 namespace t4

@@ -339,22 +339,6 @@ T4_HD void copyOut(const bt::DetectorOut<T>& d, PairResult<T>& out)
   out.used_epa = d.used_epa;
 }
 
-/*
- * One exact convex-convex query in a single call (the thing TesseractConvexConvexAlgorithm::processCollision does for
- * one pair, tesseract_convex_convex_algorithm.cpp:289-444,764).  The kernels run the same phases split over two
- * launches (t4_kernels2.h: gjkBody / epaBody).
- */
-template <class T, class EPA_T>
-T4_HDN void exactPair(const ShapeW<T>& A0, const ShapeW<T>& B0, T threshold, bool calc_pen, bool calc_dist,
-                      PairResult<T>& out, EPA_T& epa)
-{
-  if (analyticPairQuery(A0, B0, threshold, out))
-    return;
-  bt::DetectorOut<T> d;
-  bt::gjkPairDetector<T>(A0, B0, detectorMaxDist2(A0, B0, threshold), calc_pen, calc_dist, d, epa);
-  copyOut(d, out);
-}
-
 // ---- continuous collision data (bullet_utils.h:306-349 GetAverageSupport, :452-525 calculateContinuousData) ------
 template <class T>
 T4_HDN void averageSupport(const ShapeW<T>& s, const V3<T>& n, T& outsupport, V3<T>& outpt)

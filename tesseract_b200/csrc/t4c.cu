@@ -277,7 +277,8 @@ __global__ void __launch_bounds__(256, T4_CULL_MIN_CTAS) cullKernel(KParams P, i
 void t4LaunchGjk(const KParams& P, int64_t n, int grid, int block, cudaStream_t st);  // t4c_exact.cu (-fmad=false)
 void t4LaunchLvsCount(const LvsParams& L, int64_t n, int grid, cudaStream_t st);
 void t4LaunchLvsExpand(const LvsParams& L, int64_t n, int grid, cudaStream_t st);
-void t4LaunchEpa(const KParams& P, int64_t n, int grid, int block, cudaStream_t st);
+int t4LaunchEpa(const KParams& P, int64_t n, int sm_count, cudaStream_t st);
+size_t t4EpaScratchBytes(int sm_count);
 __global__ void __launch_bounds__(256) closestInsertKernel(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -441,9 +442,8 @@ static void launchEpa(const KParams& P, int64_t n, t4stream st)
   if (n <= 0)
     return;
   profBegin(PK_EPA, st);
-  t4LaunchEpa(P, n, gridFor(n, 128, 4, true), 128, st);
+  g_launches += (unsigned long long)t4LaunchEpa(P, n, smCount(), st);
   profEnd(st);
-  ++g_launches;
 }
 static void launchClosestInsert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestInsertKernel, PK_CLOSEST_INSERT, 256, 8, P, n, st); }
 static void launchClosestEmit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestEmitKernel, PK_CLOSEST_EMIT, 256, 8, P, n, st); }
@@ -470,9 +470,12 @@ static void launchCull(const KParams& P, int64_t n, t4stream) { T4_SERIAL(cullBo
 static void launchGjk(const KParams& P, int64_t n, t4stream) { T4_SERIAL(gjkBody, P, n); }
 static void launchEpa(const KParams& P, int64_t n, t4stream)
 {
-  std::unique_ptr<Epa<double>> epa(new Epa<double>());
+  // the same task body as the device kernels, as a group of ONE lane with Bullet's full pool: results do not depend
+  // on the group size or on the tiering (t4_epa.h)
+  std::unique_ptr<EpaPool<128, 256>> pool(new EpaPool<128, 256>());
+  std::vector<V3<double>> witnesses(128);
   for (int64_t i = 0; i < n; ++i)
-    epaBody(i, P, *epa);
+    epaTaskBody<1, 128, 256, false>((uint32_t)i, P, *pool, witnesses.data());
   if (n > 0)
     ++g_launches;
 }
@@ -521,6 +524,7 @@ struct t4c_scene
   DevBuf d_out, d_out_local, d_fk_out, d_hit_full;
   DevBuf d_traj, d_lvs_counts, d_lvs_offsets, d_lvs_tmp;
   DevBuf d_sort_keys, d_sort_keys2, d_sort_vals, d_sort_idx, d_sort_tmp;
+  DevBuf d_epa_retry, d_epa_scratch;
   uint32_t cand_cap = 0;
   std::unordered_map<const t4c_fk_model*, std::unique_ptr<FkCache>> fk;
 
@@ -987,6 +991,20 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     // tasks stay queued (and the next pass appends to them): a launch of a few hundred EPA tasks lasts as long as its
     // slowest task, so the rounds share ONE EPA launch instead of paying that tail once per round.
     uint32_t ntask_pending = 0;
+    // EPA over P.tasks[0, ntask): the two tiers of t4_epa.h need a zeroed fetch / retry counter each, a retry queue of
+    // ntask entries and the witness scratch
+    auto runEpa = [&](uint32_t ntask) -> t4c_status {
+#ifndef T4C_HOSTSIM
+      T4_TRY(s->d_epa_retry.ensure((size_t)ntask * sizeof(uint32_t)) && s->d_epa_scratch.ensure(t4EpaScratchBytes(smCount())),
+             "EPA workspace");
+      P.epa_retry = s->d_epa_retry.as<uint32_t>();
+      P.epa_scratch = s->d_epa_scratch.as<double>();
+      T4_TRY(plat::zero(P.qcount + Q_FETCH, 2 * sizeof(uint32_t), st) && plat::zero(P.qcount + Q_RETRY, sizeof(uint32_t), st),
+             "memset");
+#endif
+      launchEpa(P, ntask, st);
+      return T4C_OK;
+    };
     auto exactPass = [&](uint32_t* queue, uint32_t nq, bool run_epa) -> t4c_status {
       if (nq > 0)
       {
@@ -996,7 +1014,6 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
         P.tasks = s->d_tasks.as<EpaTask>();
         P.task_cap = ntask_pending + nq;
         P.surv = queue;
-        T4_TRY(plat::zero(P.qcount + Q_FETCH, 2 * sizeof(uint32_t), st), "memset");  // Q_FETCH, Q_FETCH_EPA
         P.task_order = nullptr;
         if (const uint32_t* sorted = sortByType(s, P, P.surv, 0, nq))
           P.surv = const_cast<uint32_t*>(sorted);
@@ -1007,7 +1024,9 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       if (run_epa && ntask_pending > 0)
       {
         P.task_order = sortByType(s, P, nullptr, 1, ntask_pending);
-        launchEpa(P, ntask_pending, st);
+        const t4c_status re = runEpa(ntask_pending);
+        if (re != T4C_OK)
+          return re;
         ntask_pending = 0;
         T4_TRY(plat::zero(P.qcount + Q_TASK, sizeof(uint32_t), st), "memset");
       }
@@ -1126,8 +1145,10 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
         EpaTask* const keep_tasks = P.tasks;
         P.tasks = s->d_tasks_long.as<EpaTask>();
         P.task_order = nullptr;
-        launchEpa(P, ntl, st);
+        const t4c_status re = runEpa(ntl);
         P.tasks = keep_tasks;
+        if (re != T4C_OK)
+          return re;
       }
     }
     rc = longPass(true);  // long pairs that came out of the deferred tiers

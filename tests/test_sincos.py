@@ -18,7 +18,7 @@ def libm_sincos(x):
     return sin, cos
 
 
-def arguments(n, seed=1):
+def arguments(n, seed=1, table_range_only=False):
     rng = np.random.default_rng(seed)
     x = np.concatenate([rng.uniform(-3.2, 3.2, n // 2),            # joint ranges
                         rng.uniform(-100.0, 100.0, n // 4),        # Cody-Waite reduction, all quadrants
@@ -26,11 +26,14 @@ def arguments(n, seed=1):
                         rng.uniform(-1.0, 1.0, n // 8) * 1e5])
     edge = np.array([0.0, -0.0, 1e-9, 2.0 ** -26, 2.0 ** -27, 0.126, 0.855469, 2.426265, math.pi / 2, math.pi,
                      -math.pi, 2 * math.pi, 105414349.0, 1e9, -1e9])
-    return np.concatenate([x, edge, np.nextafter(edge, 1e30), np.nextafter(edge, -1e30)])
+    x = np.concatenate([x, edge, np.nextafter(edge, 1e30), np.nextafter(edge, -1e30)])
+    # beyond 105414350 glibc switches to a Payne-Hanek reduction and the header to the platform's sin / cos: the host
+    # simulator (glibc itself) still matches there, the device is only specified inside the table / Cody-Waite range
+    return x[np.abs(x) < 105414350.0] if table_range_only else x
 
 
-def check_bits(run, n):
-    x = arguments(n)
+def check_bits(run, n, table_range_only=False):
+    x = arguments(n, table_range_only=table_range_only)
     s, c = run(x)
     s0, c0 = libm_sincos(x)
     bad_s = int((s.view(np.uint64) != s0.view(np.uint64)).sum())
