@@ -70,6 +70,9 @@ def parse():
     ap.add_argument("--secondary", default="", help="comma list of secondary entries to run (default: all that apply)")
     ap.add_argument("--cast-traj", type=int, default=65536)
     ap.add_argument("--voxels", type=int, default=1000000)
+    ap.add_argument("--voxel-states", type=int, default=1 << 17,
+                    help="configs[3] states per GPU (the configuration names 1 Mi; a state has ~1 600 voxel pairs inside "
+                         "the 0.10 m margin, so the default bench line times a 128 Ki-state slice of it)")
     ap.add_argument("--dual-states", type=int, default=1 << 21, help="configs[4] states per GPU")
     return ap.parse_args()
 
@@ -675,8 +678,9 @@ def main():
         pl = np.load(os.path.join(ROOT, "tests", "golden", "plane_4m.npz"))
         b4 = S.build_config4_synthetic(args.voxels, margin=0.10, plane=(pl["vertices"], pl["faces"]))
         eng = Engine(lib, b4, local_rank, ctx)
-        q4 = S.random_states(b4, n, seed=99 + rank, dtype=np.float64)
-        r2 = eng.discrete(q4, 1, True, 2, 1, 1, 24, chunk=1 << 18)
+        n4 = args.voxel_states
+        q4 = S.random_states(b4, n4, seed=99 + rank, dtype=np.float64)
+        r2 = eng.discrete(q4, 1, True, 1, 1, 1, 24, chunk=1 << 16)
         ps = c2 = None
         if check:
             # chunked batches keep no single contact buffer: run the sample through the host entry once more
@@ -685,10 +689,11 @@ def main():
             hit_s, con_s, _ = bc.check_discrete(q4[:256], 1)
             ps, c2 = parity_discrete(b4, q4, 1, dict(hit=hit_s, contacts=con_s), 256, 0.10, cores)
             del bc
-        finish("config3_voxels", r2, b4, UNIT, n, True,
-               f"configs[3]: ABB IRB2400 hull links vs {args.voxels} synthetic octomap voxels (half boxes, half "
-               f"SPHERE_OUTSIDE, 0.02 m) + plane_4m.stl as a triangle mesh, {n} states, CLOSEST, margin 0.10", ps, c2,
-               nq2=6)
+        finish("config3_voxels", r2, b4, UNIT, n4, True,
+               f"configs[3]: ABB IRB2400 hull links vs {args.voxels} synthetic octomap voxels (one layer of 0.01 m cells "
+               f"on the walls of a 4.4 x 4.4 x 2.6 m room and on six box fixtures; half boxes, half SPHERE_OUTSIDE) + "
+               f"plane_4m.stl as a triangle mesh, {n4} states (slice of the 1 Mi-state configuration), CLOSEST, "
+               f"margin 0.10", ps, c2, nq2=6)
         eng.close()
     if on("config4_dual_arm", not single):
         b5 = S.build_config5(n_prims=args.prims, margin=0.05, fixtures=S.config5_fixtures())

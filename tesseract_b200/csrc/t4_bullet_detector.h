@@ -297,6 +297,21 @@ T4_HDN void phase3Apply(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T>
   }
 }
 
+template <class T, class EPA_T>
+T4_HDN void detectPhase3(const ShapeW<T>& A, const ShapeW<T>& B, DetectorState<T>& S, DetectorOut<T>& out, EPA_T& epa)
+{
+  out.used_epa = true;
+  GjkOut<T, true> g;
+  const int st = phase3Seed(A, B, g);
+  out.gjk_iters += g.iters;
+  EpaResult<T> er;
+  er.iterations = 0;
+  bool ok = false;
+  if (st == GJK_INTERSECT)
+    ok = epa.run(A, B, g.sx.W, g.sx.P, g.sx.n, 255, T(1e-12), er);
+  phase3Apply(A, B, S, out, st, g.v, g.pA, ok, er);
+}
+
 // phase 4 (:1111-1179): acceptance test ...
 template <class T>
 T4_HD bool phase4Accepts(const DetectorState<T>& S, T maxDist2)

@@ -1,38 +1,19 @@
 /*
- * t4_epa.h -- penetration depth (minimum translation) of two intersecting convex cores by polytope expansion, written
- * for a GROUP of G lanes that work on one task in lock step with the polytope in SHARED memory.
+ * t4_epa.h -- penetration depth (minimum translation) of two intersecting convex cores by polytope expansion.
  *
  * Computes what btGjkEpaPenetrationDepthSolver::calcPenDepth / btGjkEpaSolver2::Penetration converge to
  * (called at tesseract_collision/src/bullet/tesseract_gjk_pair_detector.cpp:1024-1032; Bullet itself is an
- * un-vendored dependency): the face of the Minkowski difference A-B closest to the origin.  Caps are
- * Bullet's (128 vertices, 256 faces, 255 iterations).  Differences from a literal port, all result-preserving at
- * convergence:
+ * un-vendored dependency): the face of the Minkowski difference A-B closest to the origin.
+ * Differences from a literal port, all result-preserving at convergence:
  *   - margins (sphere / capsule radii, also of cast shapes) are NOT put into the support: the penetration depth of
  *     two ball-inflated cores is depth(cores) + rA + rB along the same normal, so the polytope stays finite and the
  *     expansion terminates exactly for sphere / capsule / box / hull / triangle pairs;
- *   - visible-set flood fill with an explicit horizon instead of Bullet's recursive silhouette walk.
- *
- * Why a group and shared memory.  With one task per thread and the pools in thread-local memory (round 1) the kernel
- * ran at 5.7 % of the FP64 pipe: 17 KB of pools per thread, 10 GB of DRAM traffic per million states, 18 warp-cycles of
- * long-scoreboard stall per issued instruction.  Here the pools of a task live in shared memory and the lanes of its
- * group share the parts of an iteration that are data parallel:
- *     closest-face search      every lane scans a stride of the plane distances, arg-min by shuffle (ties -> lowest
- *                              slot, the answer of the serial scan)
- *     visibility               every lane tests a stride of the faces against the new vertex
- *     flood fill + horizon     ONE lane, integer work on the flags (order of the horizon = order of the new faces)
- *     new faces                one horizon edge per lane: plane, slot, twin links
- * while the support mapping -- the scalar part -- runs on the group's first lane.  A warp instruction costs the same
- * issue slot whatever its number of active lanes and the B200 issues 64 FP64 lane-operations per SM and clock, so the
- * group is kept SMALL where the polytope is small (flat-faced pairs, median 7 iterations, ~20 faces: several tasks
- * per warp) and a full warp only where it is large (curved cores: 15-75 iterations, 100+ faces).
- *
- * Every result is independent of G: reductions are exact (min / max with index tie-break, no floating-point sums
- * across lanes), and the serial sections run on one lane.  The host simulator runs the same code with G = 1.
+ *   - iterative visible-set marking with an explicit horizon instead of Bullet's recursive silhouette walk
+ *     (no device recursion, bounded stack);
+ *   - fixed-capacity vertex / face pools in thread-local memory with slot reuse.
  */
 #ifndef T4_EPA_H_
 #define T4_EPA_H_
-
-#include <limits.h>
 
 #include "t4_gjk.h"
 
@@ -46,150 +27,74 @@ struct EpaResult
   V3<T> pA;      // witness on core A (world frame of the inputs)
   int iterations;
   bool converged;
-  bool capped;   // stopped on a pool capacity (vertices / faces): a larger pool could have gone on
 };
 
-// ---------------------------------------------------------------------------------------------------------------
-// lock-step group of G lanes.  G = 1: serial (host simulator).
-// ---------------------------------------------------------------------------------------------------------------
-template <int G>
-struct Coop;
-
-template <>
-struct Coop<1>
+// caps = btGjkEpaSolver2's EPA_MAX_VERTICES / EPA_MAX_FACES (128 / 256)
+template <class T, int MAXV = 128, int MAXF = 256>
+struct Epa
 {
-  static constexpr int lanes = 1;
-  int lane = 0;
-  T4_HD void sync() const {}
-  T4_HD void argMin(double&, int&) const {}
-  T4_HD void argMax(double&, int&) const {}
-  T4_HD bool any(bool p) const { return p; }
-  T4_HD uint32_t bcast(uint32_t v) const { return v; }
-};
-
-#ifdef T4_DEVICE_BUILD
-template <int G>
-struct Coop
-{
-  static constexpr int lanes = G;
-  int lane;
-  unsigned mask;
-  __device__ __forceinline__ Coop()
+  struct Face
   {
-    const int wl = threadIdx.x & 31;
-    lane = wl % G;
-    mask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (wl - lane));
-  }
-  __device__ __forceinline__ void sync() const { __syncwarp(mask); }
-  // (key, index) of the smallest key; equal keys: the lowest index -- what a serial ascending scan with '<' finds
-  __device__ __forceinline__ void argMin(double& k, int& i) const
-  {
-#pragma unroll
-    for (int off = G / 2; off > 0; off >>= 1)
-    {
-      const double ok = __shfl_xor_sync(mask, k, off, G);
-      const int oi = __shfl_xor_sync(mask, i, off, G);
-      if (ok < k || (ok == k && oi < i))
-        k = ok, i = oi;
-    }
-  }
-  __device__ __forceinline__ void argMax(double& k, int& i) const
-  {
-#pragma unroll
-    for (int off = G / 2; off > 0; off >>= 1)
-    {
-      const double ok = __shfl_xor_sync(mask, k, off, G);
-      const int oi = __shfl_xor_sync(mask, i, off, G);
-      if (ok > k || (ok == k && oi < i))
-        k = ok, i = oi;
-    }
-  }
-  __device__ __forceinline__ bool any(bool p) const { return __any_sync(mask, p) != 0; }
-  __device__ __forceinline__ uint32_t bcast(uint32_t v) const { return __shfl_sync(mask, v, 0, G); }  // from lane 0
-};
-#endif
-
-// ---------------------------------------------------------------------------------------------------------------
-// storage of one task (shared memory on the device)
-// ---------------------------------------------------------------------------------------------------------------
-template <int MAXV, int MAXF>
-struct EpaPool
-{
-  static_assert(MAXV <= 255 && MAXF <= 4096, "index widths");
-  V3<double> W[MAXV];     // vertices of the polytope (points of A-B)
-  V3<double> Fn[MAXF];    // unit face normals
-  double Fd[MAXF];        // plane distances; +large marks a free slot (the closest-face search reads only this array)
-  uint8_t Fv[MAXF][4];    // vertex indices
-  int16_t Fadj[MAXF][4];  // (neighbour slot << 2) | index of the twin edge in the neighbour; -1: none
-  uint8_t vis[MAXF];      // per iteration: 1 = sees the new vertex, 2 = visited by the flood fill
-  int16_t free_list[MAXF];
-  int16_t visible[MAXF], stack[MAXF];
-  uint8_t hz_a[MAXF], hz_b[MAXF];     // horizon edge a -> b
-  int16_t hz_g[MAXF], hz_slot[MAXF];  // packed adjacency entry across the edge; slot of the new face over it
-  int32_t nvis, nh, ctl, pad;
-  ShapeW<double> A, B;  // the pair, recentred (read by the support mapping of every iteration)
-};
-
-template <int G, int MAXV, int MAXF>
-struct EpaCoop
-{
-  typedef double T;
-  EpaPool<MAXV, MAXF>& S;
-  V3<T>* Pw;  // witness on A of every vertex (global scratch: written once per vertex, three entries read at the end)
-  Coop<G> g;
-  // replicated in every lane
-  int nv, nf_hi, n_free, it, max_iter;
-  T tol;
-  bool capped;
-  // lane 0 only
-  T saved_d;
-  V3<T> saved_n;
-  int saved_v[3];
-  bool have_saved, deteriorated;
-
-  T4_KM EpaCoop(EpaPool<MAXV, MAXF>& pool, V3<T>* witnesses) : S(pool), Pw(witnesses) {}
-
-  T4_KMN void support(const V3<T>& d, V3<T>& w, V3<T>& p) const
-  {
-    p = supportW(S.A, d, false);
-    w = p - supportW(S.B, -d, false);
-  }
-  T4_KM static T det3(const V3<T>& a, const V3<T>& b, const V3<T>& c) { return a.dot(b.cross(c)); }
-
-  // ---- btGjkEpaSolver2 GJK::EncloseOrigin on a local simplex: grow it to a non-degenerate tetrahedron (lane 0)
-  struct Seed
-  {
-    V3<T> w[4], p[4];
-    int n;
+    V3<T> n;
+    int16_t v[3];
+    int16_t adj[3];  // (neighbour slot << 2) | index of the twin edge in the neighbour; -1: none
+    int16_t pad[2];
   };
-  T4_KMN void push(Seed& sd, const V3<T>& d) const
+  static constexpr int HZC = 32;  // horizon edges whose new-face plane is kept from the flood fill
+  V3<T> W[MAXV], P[MAXV];
+  Face F[MAXF];
+  // plane distance of every face slot, +large for a free / removed slot: the closest-face search (the most frequent
+  // memory access of an iteration) reads one dense array instead of two fields of 48-byte records
+  T Fd[MAXF];
+  // visit stamp of every face slot (dense for the same reason: three look-ups per face of the flood fill)
+  int16_t Fm[MAXF];
+  int nv, nf_hi;         // vertices used; high-water mark of face slots
+  int16_t free_list[MAXF];
+  int n_free;
+  int16_t stack[MAXF], visible[MAXF];
+  int16_t hz_a[MAXF], hz_b[MAXF], hz_g[MAXF];  // horizon edge (a -> b) and the packed adjacency entry across it
+  V3<T> hz_n[HZC];
+  T hz_d[HZC];
+
+  const ShapeW<T>* A;
+  const ShapeW<T>* B;
+
+  T4_HDN void support(const V3<T>& d, V3<T>& w, V3<T>& p) const
   {
-    support(d, sd.w[sd.n], sd.p[sd.n]);
-    ++sd.n;
+    p = supportW(*A, d, false);
+    w = p - supportW(*B, -d, false);
   }
-  T4_KM static bool enclose4(const Seed& sd)
+  T4_HD static T det3(const V3<T>& a, const V3<T>& b, const V3<T>& c) { return a.dot(b.cross(c)); }
+
+  T4_HDN bool pushSupport(const V3<T>& d)
   {
-    return t4abs(det3(sd.w[0] - sd.w[3], sd.w[1] - sd.w[3], sd.w[2] - sd.w[3])) > T(0);
+    if (nv >= MAXV)
+      return false;
+    support(d, W[nv], P[nv]);
+    ++nv;
+    return true;
   }
-  T4_KMN bool enclose3(Seed& sd) const
+  // btGjkEpaSolver2 GJK::EncloseOrigin: grow the simplex (W[0..nv)) to a non-degenerate tetrahedron
+  T4_HD bool enclose4() const { return t4abs(det3(W[0] - W[3], W[1] - W[3], W[2] - W[3])) > T(0); }
+  T4_HDN bool enclose3()
   {
-    const V3<T> n = (sd.w[1] - sd.w[0]).cross(sd.w[2] - sd.w[0]);
+    const V3<T> n = (W[1] - W[0]).cross(W[2] - W[0]);
     if (n.len2() > T(0))
     {
-      push(sd, n);
-      if (enclose4(sd))
+      pushSupport(n);
+      if (enclose4())
         return true;
-      --sd.n;
-      push(sd, -n);
-      if (enclose4(sd))
+      --nv;
+      pushSupport(-n);
+      if (enclose4())
         return true;
-      --sd.n;
+      --nv;
     }
     return false;
   }
-  T4_KMN bool enclose2(Seed& sd) const
+  T4_HDN bool enclose2()
   {
-    const V3<T> d = sd.w[1] - sd.w[0];
+    const V3<T> d = W[1] - W[0];
     for (int i = 0; i < 3; ++i)
     {
       V3<T> axis(0, 0, 0);
@@ -197,452 +102,422 @@ struct EpaCoop
       const V3<T> p = d.cross(axis);
       if (p.len2() > T(0))
       {
-        push(sd, p);
-        if (enclose3(sd))
+        pushSupport(p);
+        if (enclose3())
           return true;
-        --sd.n;
-        push(sd, -p);
-        if (enclose3(sd))
+        --nv;
+        pushSupport(-p);
+        if (enclose3())
           return true;
-        --sd.n;
+        --nv;
       }
     }
     return false;
   }
-  T4_KMN bool enclose1(Seed& sd) const
+  T4_HDN bool enclose1()
   {
     for (int i = 0; i < 3; ++i)
     {
       V3<T> axis(0, 0, 0);
       axis.set(i, 1);
-      push(sd, axis);
-      if (enclose2(sd))
+      pushSupport(axis);
+      if (enclose2())
         return true;
-      --sd.n;
-      push(sd, -axis);
-      if (enclose2(sd))
+      --nv;
+      pushSupport(-axis);
+      if (enclose2())
         return true;
-      --sd.n;
+      --nv;
     }
     return false;
   }
 
-  T4_KM bool planeOf(int a, int b, int c, V3<T>& n, T& d) const
+  T4_HD bool makeFace(int a, int b, int c, Face& f, T& d) const
   {
-    const V3<T> wa = S.W[a];
-    const V3<T> r = (S.W[b] - wa).cross(S.W[c] - wa);
-    const T l = r.len();
+    f.v[0] = (int16_t)a, f.v[1] = (int16_t)b, f.v[2] = (int16_t)c;
+    f.adj[0] = f.adj[1] = f.adj[2] = -1;
+    const V3<T> n = (W[b] - W[a]).cross(W[c] - W[a]);
+    const T l = n.len();
     if (!(l > T(1e-20)))
       return false;
-    n = r * (T(1) / l);
-    d = n.dot(wa);
+    f.n = n * (T(1) / l);
+    d = f.n.dot(W[a]);
+    return true;
+  }
+  T4_HD int allocFace()
+  {
+    if (n_free > 0)
+      return free_list[--n_free];
+    if (nf_hi < MAXF)
+      return nf_hi++;
+    return -1;
+  }
+  T4_HD static int edgeIndex(const Face& g, int from, int to)
+  {
+    for (int e = 0; e < 3; ++e)
+      if (g.v[e] == from && g.v[(e + 1) % 3] == to)
+        return e;
+    return -1;
+  }
+
+  // ---- iteration state (members, so that the expansion can be resumed one iteration at a time: the lane-refill
+  //      EPA kernel advances every lane by ONE iteration per trip and refills finished lanes at once)
+  int mark_, it_, max_iter_;
+  T tol_, saved_d;
+  V3<T> saved_n;
+  int16_t saved_v[3];  // vertices of the face that gave the tightest bound (W / P are append-only: indices stay valid)
+  bool have_saved, deteriorated;
+
+  // simplex: up to 4 points of A-B (and their A witnesses) around the origin, from the GJK that found the overlap.
+  // false: no enclosing tetrahedron could be built (no penetration result)
+  T4_HDN bool begin(const ShapeW<T>& a, const ShapeW<T>& b, const V3<T>* sw, const V3<T>* sp, int rank, int max_iter,
+                    T tol)
+  {
+    A = &a;
+    B = &b;
+    nv = 0;
+    for (int i = 0; i < rank && i < 4; ++i)
+    {
+      W[i] = sw[i];
+      P[i] = sp[i];
+      ++nv;
+    }
+    bool ok = false;
+    if (nv == 0)
+    {
+      pushSupport(V3<T>(1, 0, 0));
+    }
+    if (nv == 1)
+      ok = enclose1();
+    else if (nv == 2)
+      ok = enclose2();
+    else if (nv == 3)
+      ok = enclose3();
+    else
+      ok = enclose4();
+    if (!ok || nv != 4)
+      return false;
+    if (det3(W[0] - W[3], W[1] - W[3], W[2] - W[3]) < T(0))
+    {
+      V3<T> t = W[0];
+      W[0] = W[1];
+      W[1] = t;
+      t = P[0];
+      P[0] = P[1];
+      P[1] = t;
+    }
+    nf_hi = 0;
+    n_free = 0;
+    const int tet[4][3] = { { 0, 1, 2 }, { 1, 0, 3 }, { 2, 1, 3 }, { 0, 2, 3 } };
+    for (int i = 0; i < 4; ++i)
+    {
+      if (!makeFace(tet[i][0], tet[i][1], tet[i][2], F[i], Fd[i]))
+        return false;
+      Fm[i] = 0;
+      ++nf_hi;
+    }
+    for (int i = 0; i < 4; ++i)
+      for (int e = 0; e < 3; ++e)
+        for (int j = 0; j < 4; ++j)
+          if (j != i)
+          {
+            const int ge = edgeIndex(F[j], F[i].v[(e + 1) % 3], F[i].v[e]);
+            if (ge >= 0)
+              F[i].adj[e] = (int16_t)((j << 2) | ge);
+          }
+    mark_ = 0;
+    it_ = 0;
+    max_iter_ = max_iter;
+    tol_ = tol;
+    saved_d = -Eps<T>::large();
+    have_saved = false;
+    deteriorated = false;
     return true;
   }
 
-  // simplex: up to 4 points of A-B (and their A witnesses) around the origin, from the GJK that found the overlap
-  // (lane 0 holds them).  false: no enclosing tetrahedron could be built (no penetration result).  Collective.
-  T4_KMN bool begin(const V3<T>* sw, const V3<T>* sp, int rank, int max_iterations, T tolerance)
+  // one expansion iteration: 0 = continue, 1 = finished (call finish), 2 = failed (no result)
+  T4_HDN int step()
   {
-    if (g.lane == 0)
-    {
-      Seed sd;
-      sd.n = 0;
-      for (int i = 0; i < rank && i < 4; ++i)
-      {
-        sd.w[i] = sw[i];
-        sd.p[i] = sp[i];
-        ++sd.n;
-      }
-      bool ok = false;
-      if (sd.n == 0)
-        push(sd, V3<T>(1, 0, 0));
-      if (sd.n == 1)
-        ok = enclose1(sd);
-      else if (sd.n == 2)
-        ok = enclose2(sd);
-      else if (sd.n == 3)
-        ok = enclose3(sd);
-      else
-        ok = enclose4(sd);
-      ok = ok && sd.n == 4;
-      if (ok)
-      {
-        if (det3(sd.w[0] - sd.w[3], sd.w[1] - sd.w[3], sd.w[2] - sd.w[3]) < T(0))
-        {
-          V3<T> t = sd.w[0];
-          sd.w[0] = sd.w[1];
-          sd.w[1] = t;
-          t = sd.p[0];
-          sd.p[0] = sd.p[1];
-          sd.p[1] = t;
-        }
-        for (int i = 0; i < 4; ++i)
-        {
-          S.W[i] = sd.w[i];
-          Pw[i] = sd.p[i];
-        }
-        const int tet[4][3] = { { 0, 1, 2 }, { 1, 0, 3 }, { 2, 1, 3 }, { 0, 2, 3 } };
-        for (int i = 0; i < 4 && ok; ++i)
-        {
-          ok = planeOf(tet[i][0], tet[i][1], tet[i][2], S.Fn[i], S.Fd[i]);
-          for (int e = 0; e < 3; ++e)
-          {
-            S.Fv[i][e] = (uint8_t)tet[i][e];
-            S.Fadj[i][e] = -1;
-          }
-        }
-        for (int i = 0; i < 4; ++i)
-          for (int e = 0; e < 3; ++e)
-            for (int j = 0; j < 4; ++j)
-              if (j != i)
-                for (int ge = 0; ge < 3; ++ge)  // twin edge: same vertices, opposite direction
-                  if (tet[j][ge] == tet[i][(e + 1) % 3] && tet[j][(ge + 1) % 3] == tet[i][e])
-                    S.Fadj[i][e] = (int16_t)((j << 2) | ge);
-      }
-      S.ctl = ok ? 1 : 0;
-      S.pad = 0;
-      saved_d = -Eps<T>::large();
-      have_saved = false;
-      deteriorated = false;
-    }
-    g.sync();
-    const bool ok = S.ctl != 0;
-    nv = 4;
-    nf_hi = 4;
-    n_free = 0;
-    it = 0;
-    max_iter = max_iterations;
-    tol = tolerance;
-    capped = false;
-    g.sync();
-    return ok;
-  }
-
-  // the closest alive face: plane distance and slot (INT_MAX: none).  Collective; the same answer in every lane.
-  T4_KM void closestFace(T& bd, int& bi) const
-  {
-    bd = Eps<T>::large();
-    bi = INT_MAX;
-    for (int i = g.lane; i < nf_hi; i += G)
-    {
-      const T d = S.Fd[i];
-      if (d < bd)
-      {
-        bd = d;
-        bi = i;
-      }
-    }
-    g.argMin(bd, bi);
-  }
-
-  // one expansion iteration: 0 = continue, 1 = finished (call finish), 2 = failed (no result).  Collective.
-  T4_KMN int step()
-  {
-    if (it >= max_iter)
+    if (it_ >= max_iter_)
       return 1;
-    T bd;
-    int bi;
-    closestFace(bd, bi);
-    if (bi == INT_MAX)
+    int best = -1;
+    {
+      T bestd = Eps<T>::large();
+      for (int i = 0; i < nf_hi; ++i)
+        if (Fd[i] < bestd)
+        {
+          bestd = Fd[i];
+          best = i;
+        }
+    }
+    if (best < 0)
       return 2;
-    if (g.lane == 0)
+    // The closest-face distance is a LOWER bound of the depth and can only grow.  On curved supports (cylinder /
+    // cone rims) the faces shrink to rounding-noise size near convergence and the hull eventually corrupts: the
+    // bound then drops.  Stop there and report the tightest bound recorded.
+    if (Fd[best] + T(1e-12) < saved_d)
     {
-      int ctl = 0;
-      // The closest-face distance is a LOWER bound of the depth and can only grow.  On curved supports (cylinder /
-      // cone rims) the faces shrink to rounding-noise size near convergence and the hull eventually corrupts: the
-      // bound then drops.  Stop there and report the tightest bound recorded.
-      if (bd + T(1e-12) < saved_d)
-      {
-        deteriorated = true;
-        ctl = 1;
-      }
-      else
-      {
-        if (bd >= saved_d)
-        {
-          saved_d = bd;
-          saved_n = S.Fn[bi];
-          for (int k = 0; k < 3; ++k)
-            saved_v[k] = S.Fv[bi][k];
-          have_saved = true;
-        }
-        if (nv >= MAXV)
-          ctl = 3;  // vertex pool full
-        else
-        {
-          const V3<T> n = S.Fn[bi];
-          V3<T> w, p;
-          support(n, w, p);
-          if (n.dot(w) - bd <= tol)
-            ctl = 1;
-          else
-          {
-            S.W[nv] = w;
-            Pw[nv] = p;
-          }
-        }
-      }
-      S.ctl = ctl;
-    }
-    g.sync();
-    const int ctl = S.ctl;
-    if (ctl)
-    {
-      capped = capped || ctl == 3;
+      deteriorated = true;
       return 1;
     }
+    if (Fd[best] >= saved_d)
+    {
+      saved_d = Fd[best];
+      saved_n = F[best].n;
+      for (int k = 0; k < 3; ++k)
+        saved_v[k] = F[best].v[k];
+      have_saved = true;
+    }
+    if (nv >= MAXV)
+      return 1;
+    V3<T> w, p;
+    support(F[best].n, w, p);
+    const T wdist = F[best].n.dot(w) - Fd[best];
+    if (wdist <= tol_)
+      return 1;
     const int wi = nv;
-    const V3<T> w = S.W[wi];
+    W[nv] = w;
+    P[nv] = p;
     ++nv;
-    const T tiny = T(1e-14) * (T(1) + w.len2());
-    // ---- which faces see the new vertex
-    for (int i = g.lane; i < nf_hi; i += G)
-    {
-      const T d = S.Fd[i];
-      S.vis[i] = (d < Eps<T>::large() && S.Fn[i].dot(w) - d > T(1e-14)) ? 1 : 0;
-    }
-    g.sync();
-    // ---- flood fill from the closest face over the visible faces; an edge whose neighbour does not see the vertex is
-    //      a horizon edge.  The order in which the horizon comes out fixes the slots of the new faces: one lane.
-    if (g.lane == 0)
-    {
-      int sp = 0, nvis = 0, nh = 0;
-      S.stack[sp++] = (int16_t)bi;
-      S.vis[bi] = 2;
-      while (sp > 0)
-      {
-        const int f = S.stack[--sp];
-        S.visible[nvis++] = (int16_t)f;
-        for (int e = 0; e < 3; ++e)
-        {
-          const int a = S.Fadj[f][e];
-          if (a >= 0)
-          {
-            const int q = a >> 2;
-            if (S.vis[q] == 2)
-              continue;
-            if (S.vis[q] == 1)
-            {
-              S.vis[q] = 2;
-              S.stack[sp++] = (int16_t)q;
-              continue;
-            }
-          }
-          if (nh < MAXF)
-          {
-            S.hz_a[nh] = S.Fv[f][e];
-            S.hz_b[nh] = S.Fv[f][(e + 1) % 3];
-            S.hz_g[nh] = (int16_t)a;
-            ++nh;
-          }
-          else
-            nh = MAXF + 1;  // horizon longer than the pool: reported as a capacity stop below
-        }
-      }
-      S.nvis = nvis;
-      S.nh = nh;
-    }
-    g.sync();
-    int nvis = S.nvis, nh = S.nh;
-    if (nh > MAXF)
-    {
-      --nv;
-      capped = true;
-      return 1;
-    }
-    // ---- geometry of the new faces (one horizon edge per lane): zero-area faces over an edge that has a neighbour
-    //      mean the neighbour is coplanar with the new vertex and must be absorbed (rare, serial)
+    // visible set (flood fill from the closest face) and, in the same pass, its horizon: an edge whose neighbour
+    // fails the visibility test is a horizon edge whatever is found later, and the faces are popped in the order the
+    // two-pass formulation walks them, so the horizon comes out in the same order.  The plane of the new face over
+    // each edge is computed here, while the edge's vertices are at hand, and kept for the first HZC edges.
+    ++mark_;
+    int sp_ = 0, nvis = 0, nh = 0, first_bad = -1;
     bool degenerate = false;
-    for (int k = g.lane; k < nh; k += G)
+    const T tiny = T(1e-14) * (T(1) + w.len2());
+    stack[sp_++] = (int16_t)best;
+    Fm[best] = (int16_t)mark_;
+    while (sp_ > 0)
     {
-      const V3<T> wa = S.W[S.hz_a[k]];
-      const T l = (S.W[S.hz_b[k]] - wa).cross(w - wa).len();
-      if (S.hz_g[k] >= 0 && l < tiny)
-        degenerate = true;
-    }
-    if (g.any(degenerate))
-    {
-      if (g.lane == 0)
+      const int f = stack[--sp_];
+      visible[nvis++] = (int16_t)f;
+      for (int e = 0; e < 3; ++e)
       {
-        for (int guard = 0; guard < 64; ++guard)
+        const int a = F[f].adj[e];
+        if (a >= 0)
         {
-          nh = 0;
-          bool grew = false;
-          for (int k = 0; k < nvis && !grew; ++k)
+          const int g = a >> 2;
+          if (Fm[g] == mark_)
+            continue;
+          if (F[g].n.dot(w) - Fd[g] > T(1e-14))
           {
-            const int f = S.visible[k];
-            for (int e = 0; e < 3 && !grew; ++e)
+            Fm[g] = (int16_t)mark_;
+            stack[sp_++] = (int16_t)g;
+            continue;
+          }
+        }
+        const int va = F[f].v[e], vb = F[f].v[(e + 1) % 3];
+        const V3<T> wa = W[va];
+        const V3<T> n = (W[vb] - wa).cross(w - wa);
+        const T l = n.len();
+        if (a >= 0 && l < tiny)
+          degenerate = true;
+        if (nh < MAXF)
+        {
+          hz_a[nh] = (int16_t)va;
+          hz_b[nh] = (int16_t)vb;
+          hz_g[nh] = (int16_t)a;
+          if (nh < HZC)
+          {
+            if (l > T(1e-20))
             {
-              const int a = S.Fadj[f][e];
-              const int q = a >= 0 ? (a >> 2) : -1;
-              if (q >= 0 && S.vis[q] == 2)
-                continue;
-              const int va = S.Fv[f][e], vb = S.Fv[f][(e + 1) % 3];
-              const V3<T> n = (S.W[vb] - S.W[va]).cross(w - S.W[va]);
-              if (q >= 0 && n.len() < tiny && nvis >= MAXF)
-                S.pad = 1;  // cannot absorb: pool full
-              if (q >= 0 && n.len() < tiny && nvis < MAXF)
-              {
-                S.vis[q] = 2;
-                S.visible[nvis++] = (int16_t)q;
-                grew = true;
-                break;
-              }
-              if (nh < MAXF)
-              {
-                S.hz_a[nh] = (uint8_t)va;
-                S.hz_b[nh] = (uint8_t)vb;
-                S.hz_g[nh] = (int16_t)a;
-                ++nh;
-              }
+              const V3<T> fn = n * (T(1) / l);
+              hz_n[nh] = fn;
+              hz_d[nh] = fn.dot(wa);
+            }
+            else if (first_bad < 0)
+              first_bad = nh;
+          }
+          ++nh;
+        }
+      }
+    }
+    bool cached = true;
+    if (degenerate)
+    {
+      // rare: absorb outside neighbours that would give a zero-area new face, and rebuild the horizon
+      cached = false;
+      for (int guard = 0; guard < 64; ++guard)
+      {
+        nh = 0;
+        bool grew = false;
+        for (int k = 0; k < nvis && !grew; ++k)
+        {
+          const int f = visible[k];
+          for (int e = 0; e < 3 && !grew; ++e)
+          {
+            const int a = F[f].adj[e];
+            const int g = a >= 0 ? (a >> 2) : -1;
+            if (g >= 0 && Fm[g] == mark_)
+              continue;
+            const int va = F[f].v[e], vb = F[f].v[(e + 1) % 3];
+            const V3<T> n = (W[vb] - W[va]).cross(w - W[va]);
+            if (g >= 0 && n.len() < tiny && nvis < MAXF)
+            {
+              Fm[g] = (int16_t)mark_;
+              visible[nvis++] = (int16_t)g;
+              grew = true;
+              break;
+            }
+            if (nh < MAXF)
+            {
+              hz_a[nh] = (int16_t)va;
+              hz_b[nh] = (int16_t)vb;
+              hz_g[nh] = (int16_t)a;
+              ++nh;
             }
           }
-          if (!grew)
-            break;
         }
-        S.nvis = nvis;
-        S.nh = nh;
+        if (!grew)
+          break;
       }
-      g.sync();
-      nvis = S.nvis;
-      nh = S.nh;
-      capped = capped || S.pad != 0;
     }
-    bool bad = false;
-    for (int k = g.lane; k < nh; k += G)
-    {
-      const V3<T> wa = S.W[S.hz_a[k]];
-      const T l = (S.W[S.hz_b[k]] - wa).cross(w - wa).len();
-      if (!(l > T(1e-20)))
-        bad = true;
-    }
-    bad = g.any(bad);
-    // nothing has been modified so far: a horizon that cannot be closed, or does not fit, ends the expansion with the
-    // hull of the previous iteration intact
-    const int nfree_tot = n_free + nvis;
-    const bool no_room = nh > (MAXF - nf_hi) + nfree_tot;
-    if (nh < 3 || bad || no_room)
+    if (nh < 3)
     {
       --nv;
-      capped = capped || no_room;
       return 1;
     }
-    // ---- commit: the visible faces become free slots ...
-    for (int k = g.lane; k < nvis; k += G)
+    // capacity check before touching the hull
+    if (nh > (MAXF - nf_hi) + n_free + nvis)
     {
-      const int f = S.visible[k];
-      S.Fd[f] = Eps<T>::large();
-      S.free_list[n_free + k] = (int16_t)f;
+      --nv;
+      return 1;
     }
-    g.sync();
-    // ... and every horizon edge (a, b) gets its face (a, b, w): edge 0 = the horizon edge, edge 1 = (b, w), edge 2 =
-    // (w, a).  Slots are handed out in horizon order: the free list last-in first-out, then the high-water mark.
-    for (int k = g.lane; k < nh; k += G)
+    for (int k = 0; k < nvis; ++k)
     {
-      const int slot = k < nfree_tot ? S.free_list[nfree_tot - 1 - k] : nf_hi + (k - nfree_tot);
-      S.hz_slot[k] = (int16_t)slot;
-      const int va = S.hz_a[k], vb = S.hz_b[k];
-      const V3<T> wa = S.W[va];
-      const V3<T> r = (S.W[vb] - wa).cross(w - wa);
-      const V3<T> fn = r * (T(1) / r.len());
-      S.Fn[slot] = fn;
-      S.Fd[slot] = fn.dot(wa);
-      S.Fv[slot][0] = (uint8_t)va, S.Fv[slot][1] = (uint8_t)vb, S.Fv[slot][2] = (uint8_t)wi;
-      const int a = S.hz_g[k];
-      S.Fadj[slot][0] = (int16_t)a;
-      if (a >= 0)
-        S.Fadj[a >> 2][a & 3] = (int16_t)(slot << 2);  // twin of the new face's edge 0
+      Fd[visible[k]] = Eps<T>::large();
+      free_list[n_free++] = visible[k];
     }
-    if (nh <= nfree_tot)
-      n_free = nfree_tot - nh;
-    else
+    // new faces (a, b, w): edge0 = horizon edge, edge1 = (b,w), edge2 = (w,a)
+    bool bad = false;
+    int first_new = -1;
+    // remember the slots of the new faces in `stack` (free again at this point)
+    int nnew = 0;
+    for (int k = 0; k < nh; ++k)
     {
-      n_free = 0;
-      nf_hi += nh - nfree_tot;
-    }
-    g.sync();
-    // new face k = (a_k, b_k, w): its edge 1 continues in the face that starts at b_k, its edge 2 comes from the face
-    // that ends at a_k
-    for (int k = g.lane; k < nh; k += G)
-    {
-      const int ai = S.hz_a[k], bk = S.hz_b[k];
-      int16_t a1 = -1, a2 = -1;
-      for (int j = 0; j < nh; ++j)
+      const int slot = allocFace();
+      Face nf;
+      T nd = 0;
+      if (cached && k < HZC)
       {
-        if (S.hz_a[j] == bk)
-          a1 = (int16_t)((S.hz_slot[j] << 2) | 2);  // (b, w) is the twin of that face's (w, a)
-        if (S.hz_b[j] == ai)
-          a2 = (int16_t)((S.hz_slot[j] << 2) | 1);  // (w, a) is the twin of that face's (b, w)
+        if (slot < 0 || k == first_bad)
+        {
+          bad = true;
+          break;
+        }
+        nf.v[0] = hz_a[k], nf.v[1] = hz_b[k], nf.v[2] = (int16_t)wi;
+        nf.n = hz_n[k];
+        nd = hz_d[k];
       }
-      const int slot = S.hz_slot[k];
-      S.Fadj[slot][1] = a1;
-      S.Fadj[slot][2] = a2;
+      else if (slot < 0 || !makeFace(hz_a[k], hz_b[k], wi, nf, nd))
+      {
+        bad = true;
+        break;
+      }
+      const int a = hz_g[k];
+      nf.adj[0] = (int16_t)a;
+      nf.adj[1] = nf.adj[2] = -1;
+      F[slot] = nf;
+      Fm[slot] = 0;
+      Fd[slot] = nd;
+      stack[nnew++] = (int16_t)slot;
+      if (first_new < 0)
+        first_new = slot;
+      if (a >= 0)
+        F[a >> 2].adj[a & 3] = (int16_t)(slot << 2);  // twin of the new face's edge 0
     }
-    g.sync();
-    ++it;
+    if (bad)
+      return 1;
+    // new face k = (hz_a[k], hz_b[k], w): its edge 1 continues in the face that starts at hz_b[k], its edge 2 comes
+    // from the face that ends at hz_a[k]; matched on the dense index arrays instead of the face records
+    for (int i = 0; i < nnew; ++i)
+    {
+      const int16_t ai = hz_a[i], bi = hz_b[i];
+      int16_t a1 = -1, a2 = -1;
+      for (int j = 0; j < nnew; ++j)
+      {
+        if (hz_a[j] == bi)
+          a1 = (int16_t)((stack[j] << 2) | 2);  // (b, w) is the twin of that face's (w, a)
+        if (hz_b[j] == ai)
+          a2 = (int16_t)((stack[j] << 2) | 1);  // (w, a) is the twin of that face's (b, w)
+      }
+      Face& fi = F[stack[i]];
+      fi.adj[1] = a1;
+      fi.adj[2] = a2;
+    }
+    ++it_;
     return 0;
   }
 
-  // result after the expansion stopped.  Collective; `res` is meaningful in lane 0.
-  T4_KMN bool finish(EpaResult<T>& res)
+  T4_HDN bool run(const ShapeW<T>& a, const ShapeW<T>& b, const V3<T>* sw, const V3<T>* sp, int rank, int max_iter,
+                 T tol, EpaResult<T>& res)
   {
     res.converged = false;
-    res.iterations = it;
-    res.capped = capped;
-    T bd;
-    int best;
-    closestFace(bd, best);
-    if (best == INT_MAX)
+    res.iterations = 0;
+    if (!begin(a, b, sw, sp, rank, max_iter, tol))
       return false;
-    if (g.lane == 0)
-      S.ctl = (have_saved && (deteriorated || bd < saved_d)) ? 1 : 0;
-    g.sync();
-    const bool use_saved = S.ctl != 0;
-    g.sync();
-    if (use_saved)
+    int r;
+    while ((r = step()) == 0)
     {
-      if (g.lane == 0)
-      {
-        // report the recorded tightest bound; foot-point weights on its own triangle (clamped)
-        bool ok = false;
-        const V3<T> pr = saved_n * saved_d;
-        const V3<T> sw0 = S.W[saved_v[0]], sw1 = S.W[saved_v[1]], sw2 = S.W[saved_v[2]];
-        T c0 = saved_n.dot((sw1 - pr).cross(sw2 - pr));
-        T c1 = saved_n.dot((sw2 - pr).cross(sw0 - pr));
-        T c2 = saved_n.dot((sw0 - pr).cross(sw1 - pr));
-        c0 = t4max(c0, T(0)), c1 = t4max(c1, T(0)), c2 = t4max(c2, T(0));
-        const T sum = c0 + c1 + c2;
-        if (sum > T(0))
+    }
+    if (r == 2)
+      return false;
+    return finish(res);
+  }
+
+  // result after the expansion stopped
+  T4_HDN bool finish(EpaResult<T>& res)
+  {
+    res.converged = false;
+    int best = -1;
+    res.iterations = it_;
+    // closest ALIVE face (after a break the stored `best` may have been freed)
+    best = -1;
+    {
+      T bestd = Eps<T>::large();
+      for (int i = 0; i < nf_hi; ++i)
+        if (Fd[i] < bestd)
         {
-          res.normal = saved_n;
-          res.depth = saved_d;
-          res.pA = Pw[saved_v[0]] * (c0 / sum) + Pw[saved_v[1]] * (c1 / sum) + Pw[saved_v[2]] * (c2 / sum);
-          ok = true;
+          bestd = Fd[i];
+          best = i;
         }
-        S.ctl = ok ? 1 : 0;
-      }
-      g.sync();
-      const bool ok = S.ctl != 0;
-      g.sync();
-      return ok;
+    }
+    if (best < 0)
+      return false;
+    if (have_saved && (deteriorated || Fd[best] < saved_d))
+    {
+      // report the recorded tightest bound; foot-point weights on its own triangle (clamped)
+      const V3<T> pr = saved_n * saved_d;
+      const V3<T> sw0 = W[saved_v[0]], sw1 = W[saved_v[1]], sw2 = W[saved_v[2]];
+      T c0 = saved_n.dot((sw1 - pr).cross(sw2 - pr));
+      T c1 = saved_n.dot((sw2 - pr).cross(sw0 - pr));
+      T c2 = saved_n.dot((sw0 - pr).cross(sw1 - pr));
+      c0 = t4max(c0, T(0)), c1 = t4max(c1, T(0)), c2 = t4max(c2, T(0));
+      const T sum = c0 + c1 + c2;
+      if (!(sum > T(0)))
+        return false;
+      res.normal = saved_n;
+      res.depth = saved_d;
+      res.pA = P[saved_v[0]] * (c0 / sum) + P[saved_v[1]] * (c1 / sum) + P[saved_v[2]] * (c2 / sum);
+      return true;
     }
     // A flat face of A-B is usually split into several coplanar triangles with the same plane distance: take the one
-    // that actually contains the foot point of the origin (largest minimum barycentric coordinate; ties -> lowest
-    // slot), otherwise the witness blend below would extrapolate.
-    const T dband = bd + T(1e-9) * (T(1) + t4abs(bd));
-    T best_min = -Eps<T>::large();
-    int pick = INT_MAX;
-    for (int i = g.lane; i < nf_hi; i += G)
+    // that actually contains the foot point of the origin (signed barycentric coordinates), otherwise the witness
+    // blend below would extrapolate.
+    const T dband = Fd[best] + T(1e-9) * (T(1) + t4abs(Fd[best]));
+    T b0 = 0, b1 = 0, b2 = 0, best_min = -Eps<T>::large();
+    int pick = best;
+    for (int i = 0; i < nf_hi; ++i)
     {
-      const T d = S.Fd[i];
-      if (d > dband)  // also skips free slots (+large)
+      if (Fd[i] > dband)  // also skips free slots (+large)
         continue;
-      const V3<T> n = S.Fn[i];
-      const V3<T> pr = n * d;
-      const V3<T> w0 = S.W[S.Fv[i][0]], w1 = S.W[S.Fv[i][1]], w2 = S.W[S.Fv[i][2]];
-      const T c0 = n.dot((w1 - pr).cross(w2 - pr));
-      const T c1 = n.dot((w2 - pr).cross(w0 - pr));
-      const T c2 = n.dot((w0 - pr).cross(w1 - pr));
+      const Face& f = F[i];
+      const V3<T> pr = f.n * Fd[i];
+      const T c0 = f.n.dot((W[f.v[1]] - pr).cross(W[f.v[2]] - pr));
+      const T c1 = f.n.dot((W[f.v[2]] - pr).cross(W[f.v[0]] - pr));
+      const T c2 = f.n.dot((W[f.v[0]] - pr).cross(W[f.v[1]] - pr));
       const T sum = c0 + c1 + c2;
       if (!(sum > T(0)))
         continue;
@@ -651,30 +526,21 @@ struct EpaCoop
       {
         best_min = m;
         pick = i;
+        b0 = c0 / sum, b1 = c1 / sum, b2 = c2 / sum;
       }
     }
-    g.argMax(best_min, pick);
-    if (pick == INT_MAX)
+    if (best_min == -Eps<T>::large())
       return false;
-    if (g.lane == 0)
+    // clamp tiny negative weights (foot point on an edge) and renormalise
+    b0 = t4max(b0, T(0)), b1 = t4max(b1, T(0)), b2 = t4max(b2, T(0));
     {
-      const T d = S.Fd[pick];
-      const V3<T> n = S.Fn[pick];
-      const V3<T> pr = n * d;
-      const int v0 = S.Fv[pick][0], v1 = S.Fv[pick][1], v2 = S.Fv[pick][2];
-      const V3<T> w0 = S.W[v0], w1 = S.W[v1], w2 = S.W[v2];
-      const T c0 = n.dot((w1 - pr).cross(w2 - pr));
-      const T c1 = n.dot((w2 - pr).cross(w0 - pr));
-      const T c2 = n.dot((w0 - pr).cross(w1 - pr));
-      const T sum = c0 + c1 + c2;
-      // clamp tiny negative weights (foot point on an edge) and renormalise
-      T b0 = t4max(c0 / sum, T(0)), b1 = t4max(c1 / sum, T(0)), b2 = t4max(c2 / sum, T(0));
-      const T bs = b0 + b1 + b2;
-      b0 /= bs, b1 /= bs, b2 /= bs;
-      res.normal = n;
-      res.depth = d;
-      res.pA = Pw[v0] * b0 + Pw[v1] * b1 + Pw[v2] * b2;
+      const T sum = b0 + b1 + b2;
+      b0 /= sum, b1 /= sum, b2 /= sum;
     }
+    const Face& o = F[pick];
+    res.normal = o.n;
+    res.depth = Fd[pick];
+    res.pA = P[o.v[0]] * b0 + P[o.v[1]] * b1 + P[o.v[2]] * b2;
     return true;
   }
 };

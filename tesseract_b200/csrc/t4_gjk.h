@@ -314,6 +314,7 @@ struct GjkOut
   V3<T> v;     // closest vector of the cores, from B to A
   V3<T> pA;    // witness on core A (WITNESS only)
   int iters;
+  bool separated_by_1mm;  // some support plane proved the cores more than 1e-3 apart (a lower bound, not the distance)
   Simplex<T, WITNESS> sx;
 };
 
@@ -336,6 +337,7 @@ T4_HD int gjkDistance(const ShapeW<T>& A, const ShapeW<T>& B, V3<T> axis, bool w
   bool have_v = false;  // v is a point of the Minkowski difference (after the first closest())
   int status = GJK_SEPARATED;
   int it = 0;
+  out.separated_by_1mm = false;
   for (; it < max_iter; ++it)
   {
     const V3<T> p = supportW(A, -v, with_margin);
@@ -343,6 +345,9 @@ T4_HD int gjkDistance(const ShapeW<T>& A, const ShapeW<T>& B, V3<T> axis, bool w
     const V3<T> w = p - q;
     const T delta = v.dot(w);
     const T vv = v.len2();
+    // v.x >= delta for every point x of A - B: the cores are at least delta / |v| apart
+    if (delta > T(0) && delta * delta > vv * T(1e-6))
+      out.separated_by_1mm = true;
     if (delta > T(0) && delta * delta > vv * cutoff * cutoff)
     {
       status = GJK_FAR;

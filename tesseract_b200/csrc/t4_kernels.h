@@ -44,6 +44,7 @@ enum
   ST_BVH_OVERFLOW,   // traversal stack overflows (the call fails when non-zero)
   ST_P1_SKIPPED,     // exact pairs whose phase-1 outcome was certified by the cull
   ST_SUPV_EPA,       // part of ST_SUPV64 evaluated in the EPA kernel
+  ST_P1_VIOLATIONS,  // verify mode: certified pairs whose boolean GJK said "intersect" (must be 0)
   ST_COUNT
 };
 
@@ -56,13 +57,12 @@ enum
   Q_SURV3,      // FIRST with records: one certainly penetrating pair per state against a CURVED primitive (slow EPA)
   Q_SURV4,      // FIRST with records: every other survivor (looked at only if still no contact after the others)
   Q_TASK,       // pairs handed from the GJK kernel to the EPA kernel
-  Q_FETCH,      // EPA kernel, small-polytope tier: next task to hand to a group
-  Q_FETCH_EPA,  // EPA kernel, full-size tier: next entry of the retry queue to hand to a warp
+  Q_FETCH,      // (unused)
+  Q_FETCH_EPA,  // (unused)
   Q_RAW,        // raw contacts (CLOSEST staging) or final contacts (ALL / FIRST)
   Q_OUT,        // final contacts emitted by the CLOSEST reduction
   Q_LONG,       // survivors whose GJK ran out of its iteration budget: run again, without one, beside the later passes
   Q_TASK_LONG,  // EPA tasks of the long-pair pass (it runs on its own stream: own task queue)
-  Q_RETRY,      // EPA tasks forwarded from the small-polytope tier to the full-size tier (curved cores, pool overflow)
   Q_COUNT
 };
 
@@ -144,6 +144,7 @@ struct KParams
   uint32_t long_cap;
   int task_q;             // Q_TASK, or Q_TASK_LONG in the long-pair pass
   int gjk_budget;         // support pairs a pair may spend in phases 1-2 before it is deferred (0: unlimited)
+  int verify_skip;        // test hook: run phase 1 for certified pairs too and count contradictions
   uint8_t* cand_class;    // per candidate: iterations the FP32 cull needed (sort key of the exact queues) or null
   uint32_t cand_cap;
   uint32_t cull_base;  // first candidate of the range the cull kernel works on (FIRST in rounds: candidates append)
@@ -157,8 +158,6 @@ struct KParams
   EpaTask* tasks;
   const uint32_t* task_order;  // EPA tasks sorted by shape-type pair (null: queue order)
   uint32_t task_cap;
-  uint32_t* epa_retry;         // task indices forwarded to the full-size EPA tier (Q_RETRY entries)
-  double* epa_scratch;         // A-side witnesses of the polytope vertices, 3 doubles x pool size per resident group
   uint32_t* qcount;       // [Q_COUNT]
   unsigned long long* stats;  // [ST_COUNT]
   uint8_t* hit;           // [n] (chunk-relative) or null

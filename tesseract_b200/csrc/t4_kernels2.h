@@ -120,8 +120,10 @@ T4_KD void cullBody(int64_t item, const KParams& P)
   statAdd(P.stats, ST_SUPV, A.evals + B.evals);
   if (st == GJK_FAR)
     return;
-  if (P.cand_class)  // the exact pass of this pair will need about as many iterations: keeps a warp's lanes in step
-    P.cand_class[c] = (uint8_t)(g.iters < 63 ? g.iters : 63);
+  // low 6 bits: the exact pass of this pair will need about as many iterations (sort key: keeps a warp's lanes in
+  // step); bit 7: the cores are certainly separated (see gjkBodyInner)
+  if (P.cand_class)
+    P.cand_class[c] = (uint8_t)((g.iters < 63 ? g.iters : 63) | (g.separated_by_1mm ? 0x80 : 0));
   if (st == GJK_SEPARATED && !P.calc_dist)
     return;
   if (P.hit_only)
@@ -278,7 +280,7 @@ T4_KDN void emitContact(const KParams& P, int64_t s, int a, int b, const ShapeW<
 // work counters of one exact-pass item, flushed once per item (every exit of the body)
 struct ExactCounters
 {
-  uint32_t pairs = 0, p1 = 0, p2 = 0, supv = 0;
+  uint32_t pairs = 0, p1 = 0, p2 = 0, supv = 0, skipped = 0, violations = 0;
 };
 
 // item = survivor index: phases 1-2 of the exact (FP64) query.  Pairs that need the penetration solver are handed to
@@ -305,8 +307,22 @@ T4_KD void gjkBodyInner(int64_t k, const KParams& P, ExactCounters& cnt)
   bt::DetectorState<double> S;
   bt::DetectorOut<double> d;
   const bool budgeted = P.gjk_budget > 0 && P.long_w;
+  // Phase 1 (the boolean GJK) has ONE output: "the cores intersect" or not.  When the FP32 cull found a support plane
+  // that puts the cores more than 1 mm apart -- a thousand times its own rounding error and far beyond every tolerance
+  // of the boolean GJK (its "touching" exits need the origin within ~1e-8 of a simplex of A - B, or, for a segment,
+  // within 1.5e-8 / |AB| with |AB| >= the separation) -- that output is known and the 3-4 support pairs are not spent.
+  // Only with calculate_distance on: without it the reference tells "separated" (-1) from "undecided after 1000
+  // iterations" (-2).  P.verify_skip (test hook) runs phase 1 anyway and counts the pairs whose outcome contradicts the
+  // certificate.
+  const bool certified = P.calc_dist && P.cand_class && (P.cand_class[c] & 0x80);
   const int r = bt::detectPhase12(A, B, offset, maxDist2, P.calc_pen != 0, P.calc_dist != 0, S, d,
-                                  budgeted ? P.gjk_budget : (1 << 30));
+                                  budgeted ? P.gjk_budget : (1 << 30), certified && !P.verify_skip);
+  if (certified)
+  {
+    cnt.skipped = 1;
+    if (P.verify_skip && S.status == 0 && r != bt::DET_BUDGET)
+      cnt.violations = 1;
+  }
   if (r == bt::DET_PHASE4)
     bt::detectPhase4(A, B, offset, maxDist2, S, d);
   cnt.p1 = (uint32_t)d.p1_iters;
@@ -353,114 +369,53 @@ T4_KD void gjkBody(int64_t k, const KParams& P)
   statAdd(P.stats, ST_P1_ITERS, cnt.p1);
   statAdd(P.stats, ST_P2_ITERS, cnt.p2);
   statAdd(P.stats, ST_SUPV64, cnt.supv);
+  statAdd(P.stats, ST_P1_SKIPPED, cnt.skipped);
+  if (cnt.violations)
+    statAdd(P.stats, ST_P1_VIOLATIONS, cnt.violations);
 }
 
-// One EPA task -- phase 3 (penetration) and phase 4 of the exact query -- worked on by a group of G lanes with the
-// polytope in the shared-memory pool S (t4_epa.h).  The group's first lane does the scalar parts (seed GJK, support
-// mapping, phase 4, result bridging); all lanes share the data-parallel parts of the expansion.
-// FORWARD: this is the small-polytope tier -- tasks with a curved core (cylinder / cone: 15-75 iterations, 100+ faces)
-// and tasks that run into the pool capacity are forwarded to the full-size tier through the retry queue.  A forwarded
-// task is run again from the start there, so the result does not depend on the tiering.
-template <int G, int MAXV, int MAXF, bool FORWARD>
-T4_KD void epaTaskBody(uint32_t t, const KParams& P, EpaPool<MAXV, MAXF>& S, V3<double>* Pw)
+// item = EPA task: phase 3 (penetration) and phase 4 of the exact query
+template <class EPA_T>
+T4_KD void epaBody(int64_t t, const KParams& P, EPA_T& epa)
 {
-  EpaCoop<G, MAXV, MAXF> epa(S, Pw);
-  const bool leader = epa.g.lane == 0;
-  // leader state
-  uint32_t c = 0;
-  int64_t s = 0;
-  int a = 0, b = 0, st = GJK_SEPARATED;
-  double maxDist2 = 0;
-  V3<double> offset;
-  bt::DetectorState<double> St;
+  const EpaTask& T = P.tasks[P.task_order ? P.task_order[t] : (uint32_t)t];
+  const uint32_t c = T.cand;
+  const int64_t s = P.cand_state[c];
+  if ((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit[s])
+    return;
+  const int a = (int)P.cand_a[c], b = (int)P.cand_b[c];
+  ShapeW<double> A, B;
+  loadPairShapesD(P, s, a, b, A, B);
+  const double maxDist2 = detectorMaxDist2(A, B, P.max_margin_d);
+  const V3<double> offset = bt::recentre(A, B);
+  bt::DetectorState<double> S;
+  S.isValid = T.is_valid;
+  S.status = 0;
+  S.distance = T.distance;
+  S.normalInB = V3<double>(T.normalInB[0], T.normalInB[1], T.normalInB[2]);
+  S.pointOnA = V3<double>(T.pointOnA[0], T.pointOnA[1], T.pointOnA[2]);
+  S.pointOnB = V3<double>(T.pointOnB[0], T.pointOnB[1], T.pointOnB[2]);
+  S.orgNormalInB = V3<double>(T.orgNormalInB[0], T.orgNormalInB[1], T.orgNormalInB[2]);
   bt::DetectorOut<double> d;
-  GjkOut<double, true> gj;
-  gj.sx.n = 0;
-  if (leader)
-  {
-    int run = 0;  // 0: nothing to do, 1: expand the polytope, 2: no expansion (the seed GJK decided), 3: forward
-    const EpaTask& T = P.tasks[P.task_order ? P.task_order[t] : t];
-    c = T.cand;
-    s = P.cand_state[c];
-    if (!((P.test_type == T4C_TEST_FIRST || P.hit_only) && P.hit[s]))
-    {
-      a = (int)P.cand_a[c], b = (int)P.cand_b[c];
-      loadPairShapesD(P, s, a, b, S.A, S.B);
-      if (FORWARD && (S.A.curvedCore() || S.B.curvedCore()))
-        run = 3;
-      else
-      {
-        maxDist2 = detectorMaxDist2(S.A, S.B, P.max_margin_d);
-        offset = bt::recentre(S.A, S.B);
-        St.isValid = T.is_valid;
-        St.status = 0;
-        St.distance = T.distance;
-        St.normalInB = V3<double>(T.normalInB[0], T.normalInB[1], T.normalInB[2]);
-        St.pointOnA = V3<double>(T.pointOnA[0], T.pointOnA[1], T.pointOnA[2]);
-        St.pointOnB = V3<double>(T.pointOnB[0], T.pointOnB[1], T.pointOnB[2]);
-        St.orgNormalInB = V3<double>(T.orgNormalInB[0], T.orgNormalInB[1], T.orgNormalInB[2]);
-        d.has = false;
-        d.gjk_iters = 0;
-        d.epa_iters = 0;
-        d.p1_iters = 0;
-        d.used_epa = true;
-        st = bt::phase3Seed(S.A, S.B, gj);
-        d.gjk_iters += gj.iters;
-        run = st == GJK_INTERSECT ? 1 : 2;
-      }
-    }
-    S.ctl = run;
-  }
-  epa.g.sync();
-  int run = S.ctl;
-  epa.g.sync();
-  EpaResult<double> er;
-  er.iterations = 0;
-  er.capped = false;
-  bool ok = false;
-  if (run == 1)
-  {
-    if (epa.begin(gj.sx.W, gj.sx.P, gj.sx.n, 255, 1e-12))
-    {
-      int r;
-      while ((r = epa.step()) == 0)
-      {
-      }
-      ok = r != 2 && epa.finish(er);
-    }
-    if (FORWARD && epa.capped)
-      run = 3;
-  }
-  if (leader && run == 3)
-  {
-    const uint32_t k = qAppend(&P.qcount[Q_RETRY]);
-    P.epa_retry[k] = t;  // sized for every task of the launch
-  }
-  else if (leader && run != 0)
-  {
-    bt::phase3Apply(S.A, S.B, St, d, st, gj.v, gj.pA, ok, er);
-    bt::detectPhase4(S.A, S.B, offset, maxDist2, St, d);
-    statAdd(P.stats, ST_EPA_GJK_ITERS, (uint32_t)d.gjk_iters);
-    statAdd(P.stats, ST_EPA_PAIRS, 1u);
-    statAdd(P.stats, ST_EPA_ITERS, (uint32_t)d.epa_iters);
-    statAdd(P.stats, ST_SUPV64, S.A.evals + S.B.evals);
-    statAdd(P.stats, ST_SUPV_EPA, S.A.evals + S.B.evals);
-    PairResult<double> pr;
-    copyOut(d, pr);
-    if (pr.has)
-    {
-      if (P.cast)
-      {
-        // continuous data needs the shapes at their world poses (not recentred)
-        ShapeW<double> A, B;
-        loadPairShapesD(P, s, a, b, A, B);
-        emitContact(P, s, a, b, A, B, pr);
-      }
-      else
-        emitContact(P, s, a, b, S.A, S.B, pr);
-    }
-  }
-  epa.g.sync();  // the pool is reused by the group's next task
+  d.has = false;
+  d.gjk_iters = 0;
+  d.epa_iters = 0;
+  d.p1_iters = 0;
+  d.used_epa = false;
+  bt::detectPhase3(A, B, S, d, epa);
+  bt::detectPhase4(A, B, offset, maxDist2, S, d);
+  statAdd(P.stats, ST_EPA_GJK_ITERS, (uint32_t)d.gjk_iters);
+  statAdd(P.stats, ST_EPA_PAIRS, 1u);
+  statAdd(P.stats, ST_EPA_ITERS, (uint32_t)d.epa_iters);
+  statAdd(P.stats, ST_SUPV64, A.evals + B.evals);
+  statAdd(P.stats, ST_SUPV_EPA, A.evals + B.evals);
+  PairResult<double> pr;
+  copyOut(d, pr);
+  if (!pr.has)
+    return;
+  if (P.cast)
+    loadPairShapesD(P, s, a, b, A, B);
+  emitContact(P, s, a, b, A, B, pr);
 }
 
 T4_KD unsigned long long mix64(unsigned long long x)

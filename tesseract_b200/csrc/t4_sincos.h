@@ -14,7 +14,7 @@
  * -fmad=false, the host simulator and the oracle with -ffp-contract=off).  Verified bit for bit against the host libm on
  * 2e7 random arguments in [-100, 100] (tests/test_sincos.py; 0 mismatches) -- a correctly rounded sine differs from
  * glibc's in 0.13 % of the arguments, CUDA's in far more.
- * Range: |x| < 105414350 (glibc's table / Cody-Waite path).  Larger arguments, infinities and NaNs take the platform's
+ * Range: |x| < 105414336 (glibc's table / Cody-Waite path).  Larger arguments, infinities and NaNs take the platform's
  * sin / cos (glibc uses a Payne-Hanek reduction there): joint angles never get there.
  * The 110 x 4 table is glibc's __sincostab (sin(k/128) hi, lo, cos(k/128) hi, lo), see tools/make_sincos_table.py.
  */
@@ -273,7 +273,7 @@ T4_HD double t4sin(double x)
     const double t = sc::hp0() - fabs(x);
     return copysign(sc::doCos(t, sc::hp1()), x);
   }
-  if (k < 0x419921fbu)  // |x| < 105414350
+  if (k < 0x419921fbu)  // |x| < 105414336
   {
     double a, da;
     const int n = sc::reduce(x, a, da);

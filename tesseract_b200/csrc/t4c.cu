@@ -31,6 +31,7 @@ using namespace t4;
 // platform layer
 // ===================================================================================================================
 static thread_local std::string g_err;
+static thread_local bool g_alloc_failed = false;  // a device allocation failed since the flag was last cleared
 static std::atomic<unsigned long long> g_launches{ 0 };
 
 static t4c_status fail(t4c_status st, const char* fmt, ...)
@@ -94,7 +95,11 @@ static void* alloc(size_t n)
 {
   void* p = nullptr;
   if (!chk(cudaMalloc(&p, n ? n : 1)))
+  {
+    g_alloc_failed = true;
+    cudaGetLastError();  // out of memory is not sticky: clear it so that the next call starts clean
     return nullptr;
+  }
   return p;
 }
 static void release(void* p) { cudaFree(p); }
@@ -277,8 +282,7 @@ __global__ void __launch_bounds__(256, T4_CULL_MIN_CTAS) cullKernel(KParams P, i
 void t4LaunchGjk(const KParams& P, int64_t n, int grid, int block, cudaStream_t st);  // t4c_exact.cu (-fmad=false)
 void t4LaunchLvsCount(const LvsParams& L, int64_t n, int grid, cudaStream_t st);
 void t4LaunchLvsExpand(const LvsParams& L, int64_t n, int grid, cudaStream_t st);
-int t4LaunchEpa(const KParams& P, int64_t n, int sm_count, cudaStream_t st);
-size_t t4EpaScratchBytes(int sm_count);
+void t4LaunchEpa(const KParams& P, int64_t n, int grid, int block, cudaStream_t st);
 __global__ void __launch_bounds__(256) closestInsertKernel(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -307,7 +311,7 @@ __global__ void __launch_bounds__(256) typeKeyKernel(KParams P, const uint32_t* 
     // (same hull vertices / support table inside a warp)
     const uint32_t a = P.cand_a[c];
     // minor (survivor queues only): the iteration count of the FP32 cull, a predictor of the exact pass's
-    const uint32_t cls = (!from_tasks && P.cand_class) ? P.cand_class[c] : 0u;
+    const uint32_t cls = (!from_tasks && P.cand_class) ? (P.cand_class[c] & 63u) : 0u;
     keys[i] = (uint16_t)(((((P.shapes[P.cand_b[c]].type & 7) << 5) | ((P.shapes[a].type & 3) << 3) | (a & 7u)) << 6) | cls);
     if (from_tasks)
       idx[i] = (uint32_t)i;
@@ -442,8 +446,9 @@ static void launchEpa(const KParams& P, int64_t n, t4stream st)
   if (n <= 0)
     return;
   profBegin(PK_EPA, st);
-  g_launches += (unsigned long long)t4LaunchEpa(P, n, smCount(), st);
+  t4LaunchEpa(P, n, gridFor(n, 128, 4, true), 128, st);
   profEnd(st);
+  ++g_launches;
 }
 static void launchClosestInsert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestInsertKernel, PK_CLOSEST_INSERT, 256, 8, P, n, st); }
 static void launchClosestEmit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestEmitKernel, PK_CLOSEST_EMIT, 256, 8, P, n, st); }
@@ -470,12 +475,9 @@ static void launchCull(const KParams& P, int64_t n, t4stream) { T4_SERIAL(cullBo
 static void launchGjk(const KParams& P, int64_t n, t4stream) { T4_SERIAL(gjkBody, P, n); }
 static void launchEpa(const KParams& P, int64_t n, t4stream)
 {
-  // the same task body as the device kernels, as a group of ONE lane with Bullet's full pool: results do not depend
-  // on the group size or on the tiering (t4_epa.h)
-  std::unique_ptr<EpaPool<128, 256>> pool(new EpaPool<128, 256>());
-  std::vector<V3<double>> witnesses(128);
+  std::unique_ptr<Epa<double>> epa(new Epa<double>());
   for (int64_t i = 0; i < n; ++i)
-    epaTaskBody<1, 128, 256, false>((uint32_t)i, P, *pool, witnesses.data());
+    epaBody(i, P, *epa);
   if (n > 0)
     ++g_launches;
 }
@@ -524,9 +526,21 @@ struct t4c_scene
   DevBuf d_out, d_out_local, d_fk_out, d_hit_full;
   DevBuf d_traj, d_lvs_counts, d_lvs_offsets, d_lvs_tmp;
   DevBuf d_sort_keys, d_sort_keys2, d_sort_vals, d_sort_idx, d_sort_tmp;
-  DevBuf d_epa_retry, d_epa_scratch;
   uint32_t cand_cap = 0;
+  int64_t chunk_hint = 0;  // states per chunk that fitted the device memory (0: the default)
   std::unordered_map<const t4c_fk_model*, std::unique_ptr<FkCache>> fk;
+
+  // frees what runBatch allocates per chunk (not the caller-facing staging buffers of the host entries)
+  void releaseWorkspace()
+  {
+    DevBuf* bufs[] = { &d_poses0, &d_poses1, &d_poses0d, &d_poses1d, &d_cand_state, &d_cand_a, &d_cand_b, &d_cand_class,
+                       &d_long, &d_tasks_long, &d_surv, &d_surv2, &d_surv3, &d_surv4, &d_cull_claim, &d_tasks, &d_hit,
+                       &d_claim, &d_raw, &d_raw_local, &d_raw_d64, &d_ht_rep, &d_ht_best, &d_sort_keys, &d_sort_keys2,
+                       &d_sort_vals, &d_sort_idx, &d_sort_tmp };
+    for (DevBuf* b : bufs)
+      b->reset();
+    cand_cap = 0;
+  }
 
   ~t4c_scene()
   {
@@ -700,7 +714,7 @@ struct BatchIO
   t4c_stats stats{};
 };
 
-// Pipeline parameters.  The values are the measured choices (profiles/README.md); the five environment variables are
+// Pipeline parameters.  The values are the measured choices (profiles/README.md); the six environment variables are
 // TEST HOOKS that let small test batches reach the code paths of the million-state runs (rounds, budgets, chunking,
 // progressive copies) -- nothing else in the library reads the environment.
 struct Tuning
@@ -716,6 +730,7 @@ struct Tuning
   int64_t drain_min = 4096;          // T4C_DRAIN_MIN: records per progressive download
   int64_t upload_piece_min = 65536;  // T4C_UPLOAD_PIECE_MIN: states per piece of the piecewise q upload
   int max_rounds = 8;
+  int verify_skip = 0;               // T4C_VERIFY_SKIP: run phase 1 for certified pairs too, count contradictions
   Tuning()
   {
     auto env = [](const char* name, long long dflt, long long lo) {
@@ -727,6 +742,7 @@ struct Tuning
     chunk_states = env("T4C_CHUNK_STATES", chunk_states, 1);
     drain_min = env("T4C_DRAIN_MIN", drain_min, 1);
     upload_piece_min = env("T4C_UPLOAD_PIECE_MIN", upload_piece_min, 1);
+    verify_skip = (int)env("T4C_VERIFY_SKIP", 0, 0);
   }
 };
 static const Tuning& tuning()
@@ -791,7 +807,41 @@ static const uint32_t* sortByType(t4c_scene* s, const KParams& P, const uint32_t
 static const uint32_t* sortByType(t4c_scene*, const KParams&, const uint32_t*, int, uint32_t) { return nullptr; }
 #endif
 
+static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH);
+
+// The per-chunk workspace (pose arrays, candidate / survivor queues, raw-contact staging, CLOSEST hash table) scales with
+// the states of a chunk times the pairs per state, which the caller cannot know in advance: 1 Mi states against ten
+// thousand primitives need 2 GB, against a million voxels at a 0.10 m margin a hundred times that.  When a device
+// allocation fails, the workspace is released and the batch is run again in chunks of half the size; the scene remembers
+// the size that worked.
 static t4c_status runBatch(t4c_scene* s, BatchIO& io)
+{
+  int64_t ch = s->chunk_hint > 0 ? s->chunk_hint : chunkStates();
+  for (;;)
+  {
+    BatchIO attempt = io;
+    g_alloc_failed = false;
+    const t4c_status rc = runBatchChunked(s, attempt, ch);
+    const bool nomem = rc == T4C_ERR_NOMEM || (rc == T4C_ERR_CUDA && g_alloc_failed);
+    if (!nomem || ch <= 2048)
+    {
+      io = attempt;
+      if (nomem)
+        return fail(T4C_ERR_NOMEM, "out of device memory even in chunks of %lld states", (long long)ch);
+      return rc;
+    }
+    plat::sync(s->stream);
+    if (s->aux_stream)
+      plat::sync(s->aux_stream);
+    if (s->copy_stream)
+      plat::sync(s->copy_stream);
+    s->releaseWorkspace();
+    ch = std::max<int64_t>(2048, ch / 2);
+    s->chunk_hint = ch;
+  }
+}
+
+static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
 {
   t4c_status rc = syncScene(s);
   if (rc != T4C_OK)
@@ -825,7 +875,6 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
   unsigned long long stats_host[ST_COUNT];
   std::memset(stats_host, 0, sizeof(stats_host));
   const int na = P.n_alinks;
-  const int64_t CH = chunkStates();
   int64_t total = 0;
   const size_t qelem = io.q_layout == T4C_Q_F64_ROWMAJOR ? sizeof(double) : sizeof(float);
   // records [0, upto) are final on the device (the compute stream has just been synchronised): send what is new to
@@ -969,6 +1018,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
       P.long_cap = 0;
       P.task_q = Q_TASK;
       P.gjk_budget = gjkBudget() >= 0 ? gjkBudget() : (io.req.type == T4C_TEST_FIRST ? 64 : 0);
+      P.verify_skip = tuning().verify_skip;
       if (P.gjk_budget > 0)
       {
         if (!s->d_long.ensureKeep(cb, (size_t)std::min(qc[Q_LONG], long_cap_bound) * sizeof(uint32_t), st))
@@ -991,17 +1041,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     // tasks stay queued (and the next pass appends to them): a launch of a few hundred EPA tasks lasts as long as its
     // slowest task, so the rounds share ONE EPA launch instead of paying that tail once per round.
     uint32_t ntask_pending = 0;
-    // EPA over P.tasks[0, ntask): the two tiers of t4_epa.h need a zeroed fetch / retry counter each, a retry queue of
-    // ntask entries and the witness scratch
     auto runEpa = [&](uint32_t ntask) -> t4c_status {
-#ifndef T4C_HOSTSIM
-      T4_TRY(s->d_epa_retry.ensure((size_t)ntask * sizeof(uint32_t)) && s->d_epa_scratch.ensure(t4EpaScratchBytes(smCount())),
-             "EPA workspace");
-      P.epa_retry = s->d_epa_retry.as<uint32_t>();
-      P.epa_scratch = s->d_epa_scratch.as<double>();
-      T4_TRY(plat::zero(P.qcount + Q_FETCH, 2 * sizeof(uint32_t), st) && plat::zero(P.qcount + Q_RETRY, sizeof(uint32_t), st),
-             "memset");
-#endif
       launchEpa(P, ntask, st);
       return T4C_OK;
     };
@@ -1209,6 +1249,7 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
   io.stats.bvh_stack_overflows = stats_host[ST_BVH_OVERFLOW];
   io.stats.phase1_skipped = stats_host[ST_P1_SKIPPED];
   io.stats.support_vertices_epa = stats_host[ST_SUPV_EPA];
+  io.stats.phase1_skip_violations = stats_host[ST_P1_VIOLATIONS];
   if (stats_host[ST_BVH_OVERFLOW])
     return fail(T4C_ERR_UNSUPPORTED, "environment BVH traversal overflowed its stack %llu times: results incomplete",
                 stats_host[ST_BVH_OVERFLOW]);

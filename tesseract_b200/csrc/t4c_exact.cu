@@ -21,105 +21,16 @@ __global__ void __launch_bounds__(128, 4) gjkKernelR128(KParams P, int64_t n)
     gjkBody(i, P);
 }
 
-// ---- EPA: groups of G lanes per task, polytope pools in shared memory (t4_epa.h).  Persistent grid: a group takes the
-//      next task from a device counter as soon as it is done with the last one.
-//      tier 1 (FORWARD): small pools, small groups -- flat-faced pairs (median 7 iterations, ~20 faces);
-//      tier 2: Bullet's full caps (128 vertices / 256 faces), one warp per task -- curved cores and whatever overflowed
-//      tier 1, read from the retry queue (or every task directly when there is no retry queue).
-#ifndef T4_EPA_SMALL_G
-#define T4_EPA_SMALL_G 4
-#endif
-#define T4_EPA_SMALL_V 20
-#define T4_EPA_SMALL_F 36
-#define T4_EPA_SMALL_THREADS 64
-#define T4_EPA_BIG_THREADS 128
-
-template <int G, int MAXV, int MAXF, bool FORWARD, int THREADS>
-__global__ void __launch_bounds__(THREADS) epaCoopKernel(KParams P, int64_t n)
+// One EPA task per thread, polytope pools in thread-local memory (t4_epa.h).  A group-cooperative version with the pools
+// in shared memory was built and measured 3.7x SLOWER (experiments/t4_epa_coop.h): the scalar part
+// of a task -- seed GJK, support mapping, phase 4 -- is most of its instructions, a warp instruction costs the same
+// issue slot for one active lane as for 32, and shared memory holds 64 tasks per SM where this kernel keeps 512 in
+// flight to hide the FP64 dependency latency.
+__global__ void __launch_bounds__(128, 4) epaKernelR128(KParams P, int64_t n)
 {
-  extern __shared__ __align__(16) unsigned char epa_smem[];
-  typedef EpaPool<MAXV, MAXF> Pool;
-  constexpr int GROUPS = THREADS / G;
-  const int grp = threadIdx.x / G;
-  Pool& S = reinterpret_cast<Pool*>(epa_smem)[grp];
-  V3<double>* Pw = reinterpret_cast<V3<double>*>(P.epa_scratch) + ((size_t)blockIdx.x * GROUPS + grp) * MAXV;
-  Coop<G> g;
-  const bool from_retry = !FORWARD && P.epa_retry != nullptr;
-  const uint32_t count = from_retry ? P.qcount[Q_RETRY] : (uint32_t)n;
-  for (;;)
-  {
-    uint32_t i = 0;
-    if (g.lane == 0)
-      i = atomicAdd(&P.qcount[FORWARD ? Q_FETCH : Q_FETCH_EPA], 1u);
-    i = g.bcast(i);
-    if (i >= count)
-      break;
-    epaTaskBody<G, MAXV, MAXF, FORWARD>(from_retry ? P.epa_retry[i] : i, P, S, Pw);
-  }
-}
-
-typedef void (*EpaKernelFn)(KParams, int64_t);
-struct EpaLaunchCfg
-{
-  EpaKernelFn fn;
-  int threads, groups, maxv, blocks_per_sm;
-  size_t smem;
-};
-static EpaLaunchCfg epaCfg(bool small)
-{
-  static EpaLaunchCfg cfg[2];
-  static bool ready = false;
-  if (!ready)
-  {
-    cfg[0].fn = epaCoopKernel<T4_EPA_SMALL_G, T4_EPA_SMALL_V, T4_EPA_SMALL_F, true, T4_EPA_SMALL_THREADS>;
-    cfg[0].threads = T4_EPA_SMALL_THREADS, cfg[0].groups = T4_EPA_SMALL_THREADS / T4_EPA_SMALL_G;
-    cfg[0].maxv = T4_EPA_SMALL_V;
-    cfg[0].smem = cfg[0].groups * sizeof(EpaPool<T4_EPA_SMALL_V, T4_EPA_SMALL_F>);
-    cfg[1].fn = epaCoopKernel<32, 128, 256, false, T4_EPA_BIG_THREADS>;
-    cfg[1].threads = T4_EPA_BIG_THREADS, cfg[1].groups = T4_EPA_BIG_THREADS / 32, cfg[1].maxv = 128;
-    cfg[1].smem = cfg[1].groups * sizeof(EpaPool<128, 256>);
-    for (auto& c : cfg)
-    {
-      cudaFuncSetAttribute(c.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c.smem);
-      int nb = 0;
-      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, c.fn, c.threads, c.smem) != cudaSuccess || nb < 1)
-        nb = 1;
-      c.blocks_per_sm = nb;
-    }
-    ready = true;
-  }
-  return cfg[small ? 0 : 1];
-}
-
-// bytes of witness scratch the two tiers need (tier 1 first, tier 2 behind it)
-size_t t4EpaScratchBytes(int sm_count)
-{
-  const EpaLaunchCfg a = epaCfg(true), b = epaCfg(false);
-  return ((size_t)sm_count * a.blocks_per_sm * a.groups * a.maxv + (size_t)sm_count * b.blocks_per_sm * b.groups * b.maxv) *
-         sizeof(V3<double>);
-}
-
-// P.qcount[Q_FETCH], [Q_FETCH_EPA] and [Q_RETRY] must be zero; P.epa_retry holds n entries (null: tier 2 only);
-// P.epa_scratch holds t4EpaScratchBytes().  Returns the number of launches.
-int t4LaunchEpa(const KParams& P, int64_t n, int sm_count, cudaStream_t st)
-{
-  const EpaLaunchCfg a = epaCfg(true), b = epaCfg(false);
-  KParams Q = P;
-  int launches = 0;
-  if (P.epa_retry)
-  {
-    const int64_t want = (n + a.groups - 1) / a.groups;
-    const int grid = (int)t4max<int64_t>(1, t4min<int64_t>(want, (int64_t)sm_count * a.blocks_per_sm));
-    a.fn<<<grid, a.threads, a.smem, st>>>(Q, n);
-    ++launches;
-  }
-  Q.epa_scratch = P.epa_scratch + (size_t)sm_count * a.blocks_per_sm * a.groups * a.maxv * 3;
-  // tier 2 does not know its task count on the host (it is the retry counter): a full persistent grid unless the
-  // whole launch is smaller
-  const int64_t want = (n + b.groups - 1) / b.groups;
-  const int grid = (int)t4max<int64_t>(1, t4min<int64_t>(want, (int64_t)sm_count * b.blocks_per_sm));
-  b.fn<<<grid, b.threads, b.smem, st>>>(Q, n);
-  return launches + 1;
+  Epa<double> epa;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    epaBody(i, P, epa);
 }
 
 // FK feeds the exact pass: same two-rounding arithmetic (and the host libm's sine / cosine, t4_sincos.h) so that link
@@ -221,3 +132,7 @@ void t4LaunchGjk(const KParams& P, int64_t n, int grid, int block, cudaStream_t 
   gjkKernelR128<<<grid, block, 0, st>>>(P, n);
 }
 
+void t4LaunchEpa(const KParams& P, int64_t n, int grid, int block, cudaStream_t st)
+{
+  epaKernelR128<<<grid, block, 0, st>>>(P, n);
+}

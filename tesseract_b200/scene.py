@@ -427,29 +427,45 @@ def build_config4(octree_leaves, plane=None, margin=0.10, robot_xyz=(0.0, -2.0, 
     return b
 
 
-def synthetic_room_voxels(n_voxels=1000000, res=0.02, seed=99):
-    """SURVEY 8(d) config 4 occupancy: voxels of `res` on the inside of a 4 x 4 x 2.5 m room (shell five voxels thick:
-    a real octomap wall is one voxel thick, five layers are what it takes to reach a million leaves at this size)
-    plus six solid box fixtures around the robot, thinned at random (seed) to exactly n_voxels.  Returns (n, 4)
-    centre + edge, sorted in Morton order of the cell index like an octomap leaf iterator (depth first)."""
+def synthetic_room_voxels(n_voxels=1000000, res=0.01, seed=99):
+    """SURVEY 8(d) config 4 occupancy: ONE layer of voxels on the inner surfaces of a room plus the surfaces of six box
+    fixtures around the robot -- what an octomap of a scanned workcell holds -- thinned at random (seed) to exactly
+    n_voxels.  The survey's 4 x 4 x 2.5 m room has 180 k surface cells at its 0.02 m: a million leaves need 0.01 m
+    cells and a 4.4 x 4.4 x 2.6 m room (1.04 M cells before thinning).  Returns (n, 4) centre + edge."""
     rng = np.random.Generator(np.random.MT19937(seed))
-    nx, ny, nz = int(round(4.0 / res)), int(round(4.0 / res)), int(round(2.5 / res))
-    ix, iy, iz = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz), indexing="ij")
-    t = 5
-    shell = (ix < t) | (ix >= nx - t) | (iy < t) | (iy >= ny - t) | (iz < t) | (iz >= nz - t)
-    occ = shell.copy()
-    centre = lambda a, n: (a + 0.5) * res - (n * res) / 2.0
-    X, Y, Z = centre(ix, nx), centre(iy, ny), (iz + 0.5) * res
+    sx, sy, sz = 4.4, 4.4, 2.6
+    cells = []
+
+    def face(u0, u1, v0, v1, fixed, axis):
+        """cell centres of an axis-aligned rectangle: axis = the constant coordinate"""
+        nu, nv = int(round((u1 - u0) / res)), int(round((v1 - v0) / res))
+        u = u0 + (np.arange(nu) + 0.5) * res
+        v = v0 + (np.arange(nv) + 0.5) * res
+        U, V = np.meshgrid(u, v, indexing="ij")
+        W = np.full_like(U, fixed)
+        order = {0: (W, U, V), 1: (U, W, V), 2: (U, V, W)}[axis]
+        cells.append(np.stack([a.reshape(-1) for a in order], axis=1))
+
+    h = res / 2
+    face(-sx / 2, sx / 2, -sy / 2, sy / 2, -h, 2)          # floor (top of the cells at z = 0)
+    face(-sx / 2, sx / 2, -sy / 2, sy / 2, sz + h, 2)      # ceiling
+    face(-sy / 2, sy / 2, 0.0, sz, -sx / 2 - h, 0)         # walls
+    face(-sy / 2, sy / 2, 0.0, sz, sx / 2 + h, 0)
+    face(-sx / 2, sx / 2, 0.0, sz, -sy / 2 - h, 1)
+    face(-sx / 2, sx / 2, 0.0, sz, sy / 2 + h, 1)
     fixtures = [((1.05, 0.0), (0.6, 0.7, 0.9)), ((-1.0, 0.3), (0.7, 0.6, 0.8)), ((0.2, 1.1), (0.8, 0.5, 1.0)),
                 ((0.0, -1.15), (0.7, 0.7, 0.7)), ((1.2, 1.2), (0.6, 0.6, 1.2)), ((-1.2, -1.1), (0.7, 0.7, 1.1))]
-    for (cx, cy), (sx, sy, sz) in fixtures:
-        occ |= (np.abs(X - cx) <= sx / 2) & (np.abs(Y - cy) <= sy / 2) & (Z <= sz + t * res)
-    idx = np.flatnonzero(occ.reshape(-1))
-    if len(idx) < n_voxels:
-        raise ValueError(f"only {len(idx)} occupied cells")
-    idx = np.sort(rng.choice(idx, size=n_voxels, replace=False))
-    cx, cy, cz = X.reshape(-1)[idx], Y.reshape(-1)[idx], Z.reshape(-1)[idx]
-    return np.stack([cx, cy, cz, np.full(len(idx), res)], axis=1)
+    for (cx, cy), (fx, fy, fz) in fixtures:
+        face(cx - fx / 2, cx + fx / 2, cy - fy / 2, cy + fy / 2, fz - h, 2)   # top
+        face(cy - fy / 2, cy + fy / 2, 0.0, fz, cx - fx / 2 + h, 0)           # four sides
+        face(cy - fy / 2, cy + fy / 2, 0.0, fz, cx + fx / 2 - h, 0)
+        face(cx - fx / 2, cx + fx / 2, 0.0, fz, cy - fy / 2 + h, 1)
+        face(cx - fx / 2, cx + fx / 2, 0.0, fz, cy + fy / 2 - h, 1)
+    allc = np.concatenate(cells)
+    if len(allc) < n_voxels:
+        raise ValueError(f"only {len(allc)} occupied cells")
+    idx = np.sort(rng.choice(len(allc), size=n_voxels, replace=False))
+    return np.concatenate([allc[idx], np.full((n_voxels, 1), res)], axis=1)
 
 
 def build_config4_synthetic(n_voxels=1000000, margin=0.10, plane=None, seed=99):
@@ -457,11 +473,11 @@ def build_config4_synthetic(n_voxels=1000000, margin=0.10, plane=None, seed=99):
     SPHERE_OUTSIDE (bullet_utils.cpp:182-183,228) -- plus the concave workcell mesh (one triangle per face)."""
     leaves = synthetic_room_voxels(n_voxels, seed=seed)
     b = SceneBuilder()
-    root, moving = add_robot(b, load_robot("abb_irb2400"), base_pose=pose((0.0, 0.0, 5 * 0.02)))
+    root, moving = add_robot(b, load_robot("abb_irb2400"), base_pose=pose((0.0, 0.0, 0.0)))
     b.add_collision_object("octomap_boxes", 0, [Octree(leaves[0::2], Octree.BOX)], [identity()])
     b.add_collision_object("octomap_spheres", 0, [Octree(leaves[1::2], Octree.SPHERE_OUTSIDE)], [identity()])
     if plane is not None:
-        b.add_collision_object("workcell", 0, [Mesh(plane[0], plane[1])], [pose((0.0, 0.0, 5 * 0.02 + 0.001))])
+        b.add_collision_object("workcell", 0, [Mesh(plane[0], plane[1])], [pose((0.0, 0.0, 0.001))])
     b.set_active(moving)
     b.set_margin(margin)
     return b

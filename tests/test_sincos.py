@@ -27,9 +27,9 @@ def arguments(n, seed=1, table_range_only=False):
     edge = np.array([0.0, -0.0, 1e-9, 2.0 ** -26, 2.0 ** -27, 0.126, 0.855469, 2.426265, math.pi / 2, math.pi,
                      -math.pi, 2 * math.pi, 105414349.0, 1e9, -1e9])
     x = np.concatenate([x, edge, np.nextafter(edge, 1e30), np.nextafter(edge, -1e30)])
-    # beyond 105414350 glibc switches to a Payne-Hanek reduction and the header to the platform's sin / cos: the host
+    # beyond 105414336 (high word 0x419921fb) glibc switches to a Payne-Hanek reduction and the header to the platform's sin / cos: the host
     # simulator (glibc itself) still matches there, the device is only specified inside the table / Cody-Waite range
-    return x[np.abs(x) < 105414350.0] if table_range_only else x
+    return x[np.abs(x) < 105414336.0] if table_range_only else x  # high word < 0x419921fb
 
 
 def check_bits(run, n, table_range_only=False):
