@@ -193,8 +193,22 @@ class Engine:
         capi.check(lib.t4c_fk_model_create(C.byref(self.fkd), self.scene, C.byref(self.model)), lib)
         self.nq = self.fkd.n_q
         self.flush = torch.empty(512 << 20, dtype=torch.uint8, device=self.dev)
+        # multi-GPU: the library's own communicator (t4_multi.h); torch.distributed only carries the 128-byte id
+        self.comm = None
+        if self.world > 1:
+            idt = torch.zeros(128, dtype=torch.uint8, device=self.dev)
+            if self.rank == 0:
+                buf = (C.c_uint8 * 128)()
+                capi.check(lib.t4c_comm_unique_id(buf), lib)
+                idt.copy_(torch.tensor(list(buf), dtype=torch.uint8))
+            self.dist.broadcast(idt, src=0)
+            buf = (C.c_uint8 * 128)(*idt.cpu().tolist())
+            self.comm = C.c_void_p()
+            capi.check(lib.t4c_comm_create(buf, self.rank, self.world, device, C.byref(self.comm)), lib)
 
     def close(self):
+        if self.comm is not None:
+            self.lib.t4c_comm_destroy(self.comm)
         self.lib.t4c_fk_model_destroy(self.model)
         self.lib.t4c_scene_destroy(self.scene)
 
@@ -245,10 +259,33 @@ class Engine:
         con_pin = torch.empty((cap if want else 1) * 80, dtype=torch.uint8).pin_memory()
         req = capi.Request(tt, 1, 1)
         acc = {}
+        sharded = self.comm is not None
+        root = self.rank == 0
+        g_hit = g_con = g_hit_pin = g_con_pin = None
+        if sharded and root:
+            # the root's gathered buffers: flags of the whole batch, records of every shard
+            g_hit = torch.zeros(self.world * n, dtype=torch.uint8, device=self.dev)
+            g_con = torch.empty(self.world * (cap if want else 1) * 80, dtype=torch.uint8, device=self.dev)
+            g_hit_pin = torch.zeros(self.world * n, dtype=torch.uint8).pin_memory()
+            g_con_pin = torch.empty(self.world * (cap if want else 1) * 80, dtype=torch.uint8).pin_memory()
+        q_dev64 = torch.empty((n, self.nq), dtype=torch.float64, device=self.dev) if sharded else None
+        gathered_n = [0]
 
         def add_stats(st):
             for k, v in st.as_dict().items():
                 acc[k] = acc.get(k, 0) + v
+
+        def call_sharded(io, m, a):
+            """this rank's shard [a, a + m) of its n states; one gather to rank 0 inside the entry"""
+            g = capi.Gathered()
+            if root:
+                g.hit = g_hit.data_ptr()
+                g.contacts = g_con.data_ptr() if want else None
+                g.capacity = self.world * cap if want else 0
+            capi.check(lib.t4c_check_discrete_sharded(self.scene, self.model, self.comm, 0, m, self.rank * n + a,
+                                                      C.byref(req), C.byref(io), C.byref(g) if root else None), lib)
+            if root:
+                gathered_n[0] = int(g.n_contacts)
 
         def step_device():
             acc.clear()
@@ -265,12 +302,39 @@ class Engine:
                 io.hit = hit_dev.data_ptr() + a
                 io.contacts = con_dev.data_ptr() if want else None
                 io.capacity = cap if want else 0
-                capi.check(lib.t4c_check_discrete_device(self.scene, self.model, m, C.byref(req), C.byref(io)), lib)
+                if sharded:
+                    call_sharded(io, m, a)
+                else:
+                    capi.check(lib.t4c_check_discrete_device(self.scene, self.model, m, C.byref(req), C.byref(io)), lib)
                 add_stats(io.stats)
                 ncon += int(io.n_contacts)
             return ncon
 
+        def step_host_sharded():
+            """end to end at N GPUs: pinned host q -> H2D, sharded check with its gather, D2H of the gathered flags
+            and records on rank 0"""
+            q_dev64.copy_(q_pin, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            ncon = 0
+            for a in range(0, n, chunk):
+                m = min(chunk, n - a)
+                io = capi.DeviceIO()
+                io.q, io.q_layout = q_dev64.data_ptr() + a * self.nq * 8, capi.Q_F64_ROWMAJOR
+                io.hit = hit_dev.data_ptr() + a
+                io.contacts = con_dev.data_ptr() if want else None
+                io.capacity = cap if want else 0
+                call_sharded(io, m, a)
+                ncon += int(io.n_contacts)
+                if root:
+                    g_hit_pin.copy_(g_hit, non_blocking=True)
+                    if want and gathered_n[0] > 0:
+                        g_con_pin[:gathered_n[0] * 80].copy_(g_con[:gathered_n[0] * 80], non_blocking=True)
+                    torch.cuda.current_stream().synchronize()
+            return ncon
+
         def step_host():
+            if sharded:
+                return step_host_sharded()
             ncon = 0
             for a in range(0, n, chunk):
                 m = min(chunk, n - a)
@@ -287,7 +351,7 @@ class Engine:
         q_rm = None
         if chunk < n:
             q_rm = torch.from_numpy(np.ascontiguousarray(q_host.astype(np.float32))).to(self.dev)
-        after = (lambda: gather(hit_dev)) if gather else None
+        after = (lambda: gather(hit_dev)) if (gather and not sharded) else None
         lib.t4c_profile_enable(1)
         for _ in range(warmup):
             step_device()
@@ -305,11 +369,15 @@ class Engine:
         con_view = None
         if want and chunk >= n:
             con_view = np.frombuffer(con_pin.numpy(), dtype=capi.CONTACT_DTYPE)[:ncon_h]
+        if sharded and root:
+            hit_pin, want_view = g_hit_pin, False  # gathered flags of the whole batch
         return dict(ms=ms_dev, ms_e2e=ms_e2e, exchange_ms=ms_tail, stats=stats, n_contacts=ncon, launches=launches,
+                    gathered_contacts=gathered_n[0],
                     kernels={k: v[0] / max(1, steps) for k, v in prof.items() if v[1]},
                     kernel_launches={k: v[1] // max(1, steps) for k, v in prof.items() if v[1]},
                     hit=hit_pin.numpy().copy(), contacts=con_view, h2d=n * self.nq * 8,
-                    d2h=n + (ncon_h * 80 if want else 0))
+                    d2h=(self.world * n + (gathered_n[0] * 80 if want else 0)) if sharded
+                    else n + (ncon_h * 80 if want else 0))
 
     # ---- cast trajectories -----------------------------------------------------------------------------------------
     def cast(self, traj, lvs, tt, steps, warmup, e2e_steps, contacts_per_item, traj_chunk):
@@ -724,9 +792,11 @@ def main():
                        "d2h_bytes_per_step": r["d2h"], "ms_per_step": r["ms_e2e"]},
                "roofline": roof, "cpu_baseline": cpu, "parity_sample": psample, "stats_per_step": r["stats"],
                "mode": args.mode,
-               "exchange": {"kind": ("none" if world == 1 else "gather"), "ms_per_step": r["exchange_ms"],
+               "exchange": {"kind": ("none" if world == 1 else "t4c_check_discrete_sharded: one grouped ncclSend/ncclRecv "
+                                     "of hit flags + contact records + counters to rank 0, inside the C-ABI entry"),
+                            "gathered_contacts_per_step": r.get("gathered_contacts"),
                             "collective_only_ms": collective_ms,
-                            "note": "hit flags to rank 0; includes waiting for the slowest rank"},
+                            "note": "the exchange is part of the timed entry (value and e2e)"},
                "per_rank": per_rank, "secondary": secondary}
         print(json.dumps(out))
     if world > 1:

@@ -271,6 +271,41 @@ t4c_status t4c_check_discrete_device(t4c_scene* scene, const t4c_fk_model* model
                                      const t4c_request* request, t4c_device_io* io);
 t4c_status t4c_check_cast_device(t4c_scene* scene, const t4c_fk_model* model, int64_t n /* segments */,
                                  const void* q1, const t4c_request* request, t4c_device_io* io);
+/* ---- multi-GPU: contiguous shard of the state batch per GPU, scene replicated, ONE gather of the
+ * per-GPU results (hit flags + contact records + counters) to the root GPU over NVLink:
+ *     ncclGroupStart(); ncclSend (ranks != root) / ncclRecv (root); ncclGroupEnd();
+ * Replaces the reference's clone-per-thread parallelism (discrete_contact_manager.h:59-65;
+ * test_suite/collision_multi_threaded_unit.hpp:79-127).  NCCL is loaded with dlopen("libnccl.so.2"). */
+typedef struct t4c_comm t4c_comm;
+/* rank 0 makes the 128-byte id (ncclUniqueId) and hands it to the other ranks by any transport */
+t4c_status t4c_comm_unique_id(uint8_t* id128);
+t4c_status t4c_comm_create(const uint8_t* id128, int32_t rank, int32_t world, int32_t device, t4c_comm** out);
+/* one process driving n devices: out receives n communicators, out[i] for devices[i] (ncclCommInitAll) */
+t4c_status t4c_comm_create_local(const int32_t* devices, int32_t n, t4c_comm** out);
+void t4c_comm_destroy(t4c_comm* comm);
+/* gathered results on the root (device buffers on the root's device, caller-owned; hit / contacts optional) */
+typedef struct t4c_gathered {
+  uint8_t* hit;          /* one byte per state of the WHOLE batch, indexed by state_offset + local index */
+  t4c_contact* contacts; /* shards concatenated in rank order; t4c_contact::state is the global state index */
+  int64_t capacity;
+  int64_t n_contacts;    /* out */
+  int64_t n_states;      /* out: states of all shards */
+  t4c_stats stats;       /* out: counters summed over the ranks */
+} t4c_gathered;
+/* Every rank calls with ITS shard (io: device buffers of this rank; io->q holds n_local joint vectors, records are
+ * also left in io->contacts); state_offset = global index of the shard's first state.  `gathered` on the root only. */
+t4c_status t4c_check_discrete_sharded(t4c_scene* scene, const t4c_fk_model* model, t4c_comm* comm, int32_t root,
+                                      int64_t n_local, int64_t state_offset, const t4c_request* request,
+                                      t4c_device_io* io, t4c_gathered* gathered);
+t4c_status t4c_check_cast_sharded(t4c_scene* scene, const t4c_fk_model* model, t4c_comm* comm, int32_t root,
+                                  int64_t n_local, int64_t state_offset, const void* q1, const t4c_request* request,
+                                  t4c_device_io* io, t4c_gathered* gathered);
+/* One process, one host thread per device: scenes[i] / comms[i] live on device i of t4c_comm_create_local; q is the
+ * whole batch (n x n_q doubles, host); the result (host buffers) is what t4c_check_discrete would return for it. */
+t4c_status t4c_check_discrete_multi(t4c_scene* const* scenes, const t4c_fk_model* model, t4c_comm* const* comms,
+                                    int32_t n_devices, const double* q, int64_t n, const t4c_request* request,
+                                    t4c_result* result);
+
 /* number of this library's kernel launches since load (bench.py "gpu_launches") */
 uint64_t t4c_kernel_launch_count(void);
 /* Per-kernel device timing (CUDA events recorded on the launching stream around every launch of this library).

@@ -77,6 +77,11 @@ class DeviceIO(C.Structure):
                 ("capacity", C.c_int64), ("cc_local", C.c_void_p), ("n_contacts", C.c_int64), ("stats", Stats)]
 
 
+class Gathered(C.Structure):
+    _fields_ = [("hit", C.c_void_p), ("contacts", C.c_void_p), ("capacity", C.c_int64), ("n_contacts", C.c_int64),
+                ("n_states", C.c_int64), ("stats", Stats)]
+
+
 # numpy view of t4c_contact (80 bytes)
 CONTACT_DTYPE = np.dtype([("state", "<i4"), ("link", "<i4", 2), ("subshape_id", "<i4", 2), ("shape_id", "<i2", 2),
                           ("distance", "<f4"), ("point", "<f4", (2, 3)), ("normal", "<f4", 3), ("cc_time", "<f4", 2),
@@ -128,6 +133,18 @@ def load_library(path=None):
                                                 C.POINTER(Result), C.POINTER(I64)]
     lib.t4c_check_discrete_device.argtypes = [VP, VP, I64, C.POINTER(Request), C.POINTER(DeviceIO)]
     lib.t4c_check_cast_device.argtypes = [VP, VP, I64, VP, C.POINTER(Request), C.POINTER(DeviceIO)]
+    U8P = C.POINTER(C.c_uint8)
+    lib.t4c_comm_unique_id.argtypes = [U8P]
+    lib.t4c_comm_create.argtypes = [U8P, I32, I32, I32, C.POINTER(VP)]
+    lib.t4c_comm_create_local.argtypes = [C.POINTER(I32), I32, C.POINTER(VP)]
+    lib.t4c_comm_destroy.argtypes = [VP]
+    lib.t4c_comm_destroy.restype = None
+    lib.t4c_check_discrete_sharded.argtypes = [VP, VP, VP, I32, I64, I64, C.POINTER(Request), C.POINTER(DeviceIO),
+                                               C.POINTER(Gathered)]
+    lib.t4c_check_cast_sharded.argtypes = [VP, VP, VP, I32, I64, I64, VP, C.POINTER(Request), C.POINTER(DeviceIO),
+                                           C.POINTER(Gathered)]
+    lib.t4c_check_discrete_multi.argtypes = [C.POINTER(VP), VP, C.POINTER(VP), I32, DP, I64, C.POINTER(Request),
+                                             C.POINTER(Result)]
     lib.t4c_kernel_launch_count.restype = C.c_uint64
     lib.t4c_profile_enable.argtypes = [I32]
     lib.t4c_profile_enable.restype = None
@@ -144,7 +161,9 @@ def load_library(path=None):
                  "t4c_check_cast", "t4c_check_link_poses_cast", "t4c_check_trajectories_discrete",
                  "t4c_check_trajectories_cast", "t4c_check_discrete_device", "t4c_check_cast_device",
                  "t4c_measure_fp32_peak", "t4c_lvs_count", "t4c_lvs_items", "t4c_lvs_item_states",
-                 "t4c_debug_hull_support", "t4c_measure_fp64_peak", "t4c_debug_sincos"):
+                 "t4c_debug_hull_support", "t4c_measure_fp64_peak", "t4c_debug_sincos", "t4c_comm_unique_id",
+                 "t4c_comm_create", "t4c_comm_create_local", "t4c_check_discrete_sharded", "t4c_check_cast_sharded",
+                 "t4c_check_discrete_multi"):
         getattr(lib, name).restype = I32
     if path is None:
         _lib = lib

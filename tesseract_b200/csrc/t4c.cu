@@ -524,6 +524,7 @@ struct t4c_scene
   DevBuf d_cand_state, d_cand_a, d_cand_b, d_cand_class, d_long, d_tasks_long, d_surv, d_surv2, d_surv3, d_surv4, d_cull_claim, d_tasks;
   DevBuf d_qcount, d_stats, d_hit, d_claim, d_raw, d_raw_local, d_raw_d64, d_ht_rep, d_ht_best;
   DevBuf d_out, d_out_local, d_fk_out, d_hit_full;
+  DevBuf d_hit_send, d_shard_out, d_gather_hit, d_gather_out;  // multi-GPU entries (t4_multi.h)
   DevBuf d_traj, d_lvs_counts, d_lvs_offsets, d_lvs_tmp;
   DevBuf d_sort_keys, d_sort_keys2, d_sort_vals, d_sort_idx, d_sort_tmp;
   uint32_t cand_cap = 0;
@@ -696,6 +697,7 @@ struct BatchIO
   const double* poses0 = nullptr;
   const double* poses1 = nullptr;
   t4c_request req{ T4C_TEST_FIRST, 1, 1 };
+  int64_t state_offset = 0;  // added to the state index of every record (shard of a larger batch, t4_multi.h)
   // outputs (device pointers, may be null)
   uint8_t* hit = nullptr;
   t4c_contact* contacts = nullptr;
@@ -895,7 +897,7 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
   {
     const int64_t nc = std::min<int64_t>(CH, io.n - base);
     P.n = nc;
-    P.state_base = base;
+    P.state_base = base + io.state_offset;
     // ---- poses of the kinematic links
     const size_t pose_elems = (size_t)nc * (size_t)std::max(na, 1) * 12;
     T4_TRY(s->d_poses0.ensure(pose_elems * sizeof(float)) && s->d_poses0d.ensure(pose_elems * sizeof(double)),
@@ -2052,3 +2054,5 @@ t4c_status t4c_debug_sincos(int32_t device, const double* x, int64_t n, double* 
 #endif
 }
 }  // extern "C"
+
+#include "t4_multi.h"
