@@ -229,6 +229,20 @@ void t4c_fk_model_destroy(t4c_fk_model* model);
  * (every scene link; links no joint reaches keep their scene pose). */
 t4c_status t4c_fk(const t4c_fk_model* model, const t4c_scene* scene, const double* q, int64_t n, double* link_poses);
 
+/* Geometric Jacobian of `link` for n joint vectors (host buffers): J is n x 6 x n_q row-major, rows 0-2 linear and 3-5
+ * angular velocity of the link per unit joint velocity, world frame, taken at the link origin or at point_local (a
+ * point fixed in the link frame; may be NULL).  ForwardKinematics::calcJacobian
+ * (tesseract_kinematics/src/kdl/kdl_fwd_kin_chain.cpp:127-178) + jacobianChangeRefPoint. */
+t4c_status t4c_jacobian(const t4c_fk_model* model, const t4c_scene* scene, const double* q, int64_t n, int32_t link,
+                        const double* point_local, double* J);
+/* d(distance)/dq of contact records: grad is n_contacts x n_q, grad[i] = n_i . (J_lin,link1(p1) - J_lin,link0(p0)) with
+ * the record's world points and normal (TrajOpt's collision-term gradient).  contacts[i].state indexes q.  The device
+ * variant takes device pointers (q in any t4c_device_io layout) so that records never leave the GPU. */
+t4c_status t4c_contact_gradients(t4c_scene* scene, const t4c_fk_model* model, const double* q, int64_t n,
+                                 const t4c_contact* contacts, int64_t n_contacts, double* grad);
+t4c_status t4c_contact_gradients_device(t4c_scene* scene, const t4c_fk_model* model, const void* q, int32_t q_layout,
+                                        int64_t n, const t4c_contact* contacts, int64_t n_contacts, double* grad);
+
 /* Discrete batched check: FK + self + environment test of n joint vectors (host buffers). */
 t4c_status t4c_check_discrete(t4c_scene* scene, const t4c_fk_model* model, const double* q, int64_t n,
                               const t4c_request* request, t4c_result* result);

@@ -2193,6 +2193,10 @@ void gjkPairDetector(const Convex& A, const Xf& transA, const Convex& B, const X
       d0 = normalInB.dot(pW - qW) - margin;
     }
     cnt.gjk_iterations += 3;
+    if (getenv("T4O_DEBUG"))
+      fprintf(stderr, "[t4o] phase4 status=%d distance=%.9g d0=%.9g d1=%.9g d2=%.9g n=(%.6f %.6f %.6f) org=(%.6f %.6f %.6f)\n",
+              status, distance, d0, d1, d2, normalInB.x, normalInB.y, normalInB.z, orgNormalInB.x, orgNormalInB.y,
+              orgNormalInB.z);
     if (d1 > d0)
       normalInB *= -1;
     if (orgNormalInB.length2() > 0)

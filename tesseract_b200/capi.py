@@ -145,6 +145,9 @@ def load_library(path=None):
                                            C.POINTER(Gathered)]
     lib.t4c_check_discrete_multi.argtypes = [C.POINTER(VP), VP, C.POINTER(VP), I32, DP, I64, C.POINTER(Request),
                                              C.POINTER(Result)]
+    lib.t4c_jacobian.argtypes = [VP, VP, DP, I64, I32, DP, DP]
+    lib.t4c_contact_gradients.argtypes = [VP, VP, DP, I64, VP, I64, DP]
+    lib.t4c_contact_gradients_device.argtypes = [VP, VP, VP, I32, I64, VP, I64, VP]
     lib.t4c_kernel_launch_count.restype = C.c_uint64
     lib.t4c_profile_enable.argtypes = [I32]
     lib.t4c_profile_enable.restype = None
@@ -163,7 +166,8 @@ def load_library(path=None):
                  "t4c_measure_fp32_peak", "t4c_lvs_count", "t4c_lvs_items", "t4c_lvs_item_states",
                  "t4c_debug_hull_support", "t4c_measure_fp64_peak", "t4c_debug_sincos", "t4c_comm_unique_id",
                  "t4c_comm_create", "t4c_comm_create_local", "t4c_check_discrete_sharded", "t4c_check_cast_sharded",
-                 "t4c_check_discrete_multi"):
+                 "t4c_check_discrete_multi", "t4c_jacobian", "t4c_contact_gradients",
+                 "t4c_contact_gradients_device"):
         getattr(lib, name).restype = I32
     if path is None:
         _lib = lib

@@ -15,6 +15,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <unordered_map>
 #include <unordered_set>
@@ -51,7 +52,11 @@ struct CompiledScene
   std::vector<uint16_t> sup_cand;
   std::vector<DBvhNode> bvh;
   std::vector<int32_t> active_shapes;
-  std::vector<int32_t> aa_pairs;
+  // kinematic-kinematic broadphase (a9): per kinematic link a child tree over its shapes in the LINK frame, and one item
+  // per (child shape of the smaller link, other link) of every admissible link pair
+  std::vector<int32_t> aa_pairs;   // [3 * items]: shape, active ordinal of the other link, 1 if the shape's link is the higher one
+  std::vector<DBvhNode> link_bvh;  // child trees of all kinematic links, boxes in the link frame
+  std::vector<int32_t> link_root;  // [n_alinks] root node in link_bvh, -1: the link has no shapes
   std::vector<uint32_t> acm_bits;
   int acm_words = 0;
   std::vector<double> pair_margin;  // empty: default only
@@ -63,11 +68,19 @@ struct CompiledScene
   int bvh_depth = 0;
 };
 
+// Geometry (shape records + vertex pool) is immutable once a scene exists and is shared by its clones -- the
+// reference shares shared_ptr<const Geometry> between manager clones the same way (types.h:52, bullet_utils.h:183-198);
+// adding / removing an object makes a private copy first (t4c.cu).
+struct HostGeometry
+{
+  std::vector<t4c_shape> shapes;
+  std::vector<double> vertices;
+};
+
 struct HostScene
 {
   std::vector<HostLink> links;
-  std::vector<t4c_shape> shapes;
-  std::vector<double> vertices;
+  std::shared_ptr<HostGeometry> geom = std::make_shared<HostGeometry>();
   std::unordered_set<uint64_t> acm;
   double default_margin = 0;
   std::unordered_map<uint64_t, double> pair_margins;
@@ -247,12 +260,10 @@ inline void buildSupportTable(const f4* v, int nv, std::vector<uint32_t>& cells,
   cells.push_back((uint32_t)cand.size());
 }
 
-// max number of flattened (active shape, active shape) pairs handled by the brute-force active-active kernel
-#define T4_MAX_AA_PAIRS (64ll << 20)
-
 inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
 {
-  const int nl = (int)H.links.size(), ns = (int)H.shapes.size();
+  const HostGeometry& G = *H.geom;
+  const int nl = (int)H.links.size(), ns = (int)G.shapes.size();
   C = CompiledScene();
   C.default_margin_d = H.default_margin;
   C.max_margin_d = H.maxMargin();
@@ -266,11 +277,11 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
       C.alinks.push_back(i);
     }
   const int na = (int)C.alinks.size();
-  C.verts.resize(H.vertices.size() / 3);
+  C.verts.resize(G.vertices.size() / 3);
   for (size_t i = 0; i < C.verts.size(); ++i)
   {
-    C.verts[i].x = (float)H.vertices[3 * i], C.verts[i].y = (float)H.vertices[3 * i + 1];
-    C.verts[i].z = (float)H.vertices[3 * i + 2], C.verts[i].w = 0.f;
+    C.verts[i].x = (float)G.vertices[3 * i], C.verts[i].y = (float)G.vertices[3 * i + 1];
+    C.verts[i].z = (float)G.vertices[3 * i + 2], C.verts[i].w = 0.f;
   }
   C.shapes.resize((size_t)ns);
   C.statics.resize((size_t)ns);
@@ -281,7 +292,7 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
   std::vector<std::vector<int32_t>> link_active_shapes((size_t)nl);
   for (int i = 0; i < ns; ++i)
   {
-    const t4c_shape& s = H.shapes[i];
+    const t4c_shape& s = G.shapes[i];
     if (s.link < 0 || s.link >= nl)
     {
       err = "shape refers to an unknown link";
@@ -304,7 +315,7 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
     for (int k = 0; k < 12; ++k)
       C.shape_d[(size_t)i * 16 + 4 + k] = s.pose[k];
     double c[3], h[3];
-    shapeLocalBox(s, H.vertices.data(), c, h);
+    shapeLocalBox(s, G.vertices.data(), c, h);
     const double rad = s.type == T4C_SPHERE ? s.params[0] : std::sqrt(h[0] * h[0] + h[1] * h[1] + h[2] * h[2]);
     for (int k = 0; k < 3; ++k)
     {
@@ -463,8 +474,85 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
         C.pair_margin[(size_t)C.link_alink[b] * nl + a] = kv.second;
     }
   }
-  // ---- active x active shape pairs (enabled, different links, not allowed by the ACM)
-  long long n_pairs = 0;
+  // ---- child trees of the kinematic links (TesseractCompoundCollisionAlgorithm walks the compound's btDbvt with the
+  //      other shape's box, tesseract_compound_collision_algorithm.cpp:323-338; compound x compound is a dual-tree walk,
+  //      tesseract_compound_compound_collision_algorithm.cpp:256-325).  Boxes are the children's boxes in the LINK frame.
+  C.link_root.assign((size_t)std::max(na, 1), -1);
+  for (int a = 0; a < na; ++a)
+  {
+    const std::vector<int32_t>& kids = link_active_shapes[C.alinks[a]];
+    if (kids.empty())
+      continue;
+    std::vector<LbvhBuilder::Box> kb(kids.size());
+    float lo[3] = { 1e30f, 1e30f, 1e30f }, hi[3] = { -1e30f, -1e30f, -1e30f };
+    for (size_t k = 0; k < kids.size(); ++k)
+    {
+      const t4c_shape& sh = G.shapes[kids[k]];
+      double c[3], h[3];
+      shapeLocalBox(sh, G.vertices.data(), c, h);
+      V3<double> mn, mx;
+      boxAabb(Xf<double>::from12(sh.pose), V3<double>(c[0], c[1], c[2]), V3<double>(h[0], h[1], h[2]), mn, mx);
+      const double pad = 1e-6;
+      kb[k].mn[0] = roundDown(mn.x - pad), kb[k].mn[1] = roundDown(mn.y - pad), kb[k].mn[2] = roundDown(mn.z - pad);
+      kb[k].mx[0] = roundUp(mx.x + pad), kb[k].mx[1] = roundUp(mx.y + pad), kb[k].mx[2] = roundUp(mx.z + pad);
+      for (int d = 0; d < 3; ++d)
+      {
+        lo[d] = std::min(lo[d], 0.5f * (kb[k].mn[d] + kb[k].mx[d]));
+        hi[d] = std::max(hi[d], 0.5f * (kb[k].mn[d] + kb[k].mx[d]));
+      }
+    }
+    std::vector<uint32_t> code(kids.size());
+    std::vector<int32_t> order(kids.size());
+    for (size_t k = 0; k < kids.size(); ++k)
+    {
+      uint32_t m = 0;
+      for (int d = 0; d < 3; ++d)
+      {
+        const float ext = std::max(hi[d] - lo[d], 1e-9f);
+        float t = (0.5f * (kb[k].mn[d] + kb[k].mx[d]) - lo[d]) / ext;
+        t = std::min(std::max(t * 1024.f, 0.f), 1023.f);
+        m |= expandBits10((uint32_t)t) << (2 - d);
+      }
+      code[k] = m;
+      order[k] = (int32_t)k;
+    }
+    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return code[x] < code[y]; });
+    std::vector<LbvhBuilder::Box> boxes(kids.size());
+    std::vector<uint32_t> codes(kids.size());
+    std::vector<int32_t> leaf(kids.size());
+    for (size_t k = 0; k < kids.size(); ++k)
+    {
+      boxes[k] = kb[order[k]];
+      codes[k] = code[order[k]];
+      leaf[k] = kids[order[k]];
+    }
+    C.link_root[a] = (int32_t)C.link_bvh.size();
+    if (kids.size() == 1)
+    {
+      DBvhNode n;
+      std::memset(&n, 0, sizeof(n));
+      for (int d = 0; d < 3; ++d)
+      {
+        n.lmn[d] = boxes[0].mn[d], n.lmx[d] = boxes[0].mx[d];
+        n.rmn[d] = 1e30f, n.rmx[d] = -1e30f;  // empty box: never overlaps
+      }
+      n.left = ~leaf[0];
+      n.right = ~leaf[0];
+      C.link_bvh.push_back(n);
+      continue;
+    }
+    // the builder numbers nodes from the size of the array it appends to: child references stay valid in the shared array
+    LbvhBuilder B{ boxes, codes, leaf, C.link_bvh, 0 };
+    LbvhBuilder::Box root;
+    B.build(0, (int)kids.size(), root);
+    if (B.max_depth > T4_BVH_STACK - 1)
+    {
+      err = "child tree of link '" + H.links[C.alinks[a]].name + "' too deep for the device traversal stack";
+      return false;
+    }
+  }
+  // ---- kinematic x kinematic items (links enabled, different, not allowed by the ACM): every child of the link with
+  //      FEWER shapes walks the child tree of the other link.  No cap on the number of shape pairs.
   for (int i = 0; i < na; ++i)
     for (int j = i + 1; j < na; ++j)
     {
@@ -473,18 +561,14 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
         continue;
       if (H.acm.count(hostPairKey(la, lb)))
         continue;
-      n_pairs += (long long)link_active_shapes[la].size() * (long long)link_active_shapes[lb].size();
-      if (n_pairs > T4_MAX_AA_PAIRS)
+      const bool walk_j = link_active_shapes[la].size() <= link_active_shapes[lb].size();
+      const std::vector<int32_t>& kids = walk_j ? link_active_shapes[la] : link_active_shapes[lb];
+      for (int sh : kids)
       {
-        err = "too many active-active shape pairs for the brute-force kinematic-kinematic broadphase";
-        return false;
+        C.aa_pairs.push_back(sh);
+        C.aa_pairs.push_back(walk_j ? j : i);
+        C.aa_pairs.push_back(walk_j ? 0 : 1);  // candidates are reported as (shape of the lower link, shape of the higher)
       }
-      for (int sa : link_active_shapes[la])
-        for (int sb : link_active_shapes[lb])
-        {
-          C.aa_pairs.push_back(sa);
-          C.aa_pairs.push_back(sb);
-        }
     }
   return true;
 }

@@ -102,8 +102,10 @@ struct KParams
   int32_t n_bvh_nodes;
   const int32_t* active_shapes;
   int32_t n_active_shapes;
-  const int32_t* aa_pairs;
+  const int32_t* aa_pairs;  // [3 * n_aa_pairs]: shape, active ordinal of the other link, swap flag (t4_host_scene.h)
   int32_t n_aa_pairs;
+  const DBvhNode* link_bvh;  // child trees of the kinematic links (boxes in the link frame)
+  const int32_t* link_root;  // [n_alinks]
   const uint32_t* acm_bits;  // [n_alinks][acm_words]
   int32_t acm_words;
   const double* pair_margin;  // [n_alinks][n_links] or null
@@ -633,32 +635,72 @@ T4_KD void broadStaticBody(int64_t item, const KParams& P)
     statAdd(P.stats, ST_BVH_OVERFLOW, overflow);
 }
 
-// item = pair * n + s ; pairs are (active shape, active shape) of two different links, ACM-filtered on the host
+// Kinematic x kinematic broadphase.  item = e * n + s ; entry e = (shape A of one kinematic link, the OTHER link of an
+// admissible link pair): the margin-grown world box of A is taken into the other link's frame and walks that link's
+// child tree -- what the reference's compound algorithms do with the compound's btDbvt
+// (tesseract_compound_collision_algorithm.cpp:323-338, ..._compound_compound_...:256-325).  Single-shape links have a
+// one-leaf tree, so robot self-collision pairs of convex hull links cost one box test as before.
 T4_KD void broadActiveBody(int64_t item, const KParams& P)
 {
-  const int pr = (int)(item / P.n);
-  const int64_t s = item - (int64_t)pr * P.n;
+  const int e = (int)(item / P.n);
+  const int64_t s = item - (int64_t)e * P.n;
   if (P.skip_hit && P.hit[s])
     return;
-  const int a = P.aa_pairs[2 * pr], b = P.aa_pairs[2 * pr + 1];
+  const int a = P.aa_pairs[3 * e], alb = P.aa_pairs[3 * e + 1], swap = P.aa_pairs[3 * e + 2];
   const DShape& Sa = P.shapes[a];
-  const DShape& Sb = P.shapes[b];
-  Xf<float> a0, a1, b0, b1;
+  Xf<float> a0, a1;
   shapePose<float>(P, Sa, a, s, a0, a1);
-  shapePose<float>(P, Sb, b, s, b0, b1);
-  V3<float> amn, amx, bmn, bmx;
-  shapeWorldBox(P, Sa, a0, a1, amn, amx);
-  shapeWorldBox(P, Sb, b0, b1, bmn, bmx);
+  V3<float> mn, mx;
+  shapeWorldBox(P, Sa, a0, a1, mn, mx);
+  // the narrowphase keeps a pair only when its distance is within the margin, and a box distance never exceeds the true
+  // distance: growing ONE side by the max margin loses nothing (the reference grows both, bullet_utils.h:170-177, which
+  // only adds candidates its narrowphase then rejects)
   const float grow = P.max_margin + T4_CULL_SLACK;
-  amn = amn - V3<float>(grow, grow, grow);
-  amx = amx + V3<float>(grow, grow, grow);
-  uint32_t cands = 0;
-  if (!(amn.x > bmx.x || amx.x < bmn.x || amn.y > bmx.y || amx.y < bmn.y || amn.z > bmx.z || amx.z < bmn.z))
+  const V3<float> cw = (mn + mx) * 0.5f;
+  const V3<float> hw = (mx - mn) * 0.5f + V3<float>(grow, grow, grow);
+  // the box in the other link's frame (conservative: box of the rotated box); cast: union over both poses of that link
+  V3<float> qmn(1e30f, 1e30f, 1e30f), qmx(-1e30f, -1e30f, -1e30f);
+  for (int pass = 0; pass < (P.cast ? 2 : 1); ++pass)
   {
-    cands = 1;
-    pushCandidate(P, s, a, b);
+    const Xf<float> xb = loadPose<float>((pass ? P.poses1 : P.poses0) + poseOffset(P, s, alb));
+    const V3<float> c = xb.invApply(cw);
+    const V3<float> h(t4abs(xb.r[0]) * hw.x + t4abs(xb.r[3]) * hw.y + t4abs(xb.r[6]) * hw.z,
+                      t4abs(xb.r[1]) * hw.x + t4abs(xb.r[4]) * hw.y + t4abs(xb.r[7]) * hw.z,
+                      t4abs(xb.r[2]) * hw.x + t4abs(xb.r[5]) * hw.y + t4abs(xb.r[8]) * hw.z);
+    const float pad = 1e-5f;  // FP32 rounding of the frame change
+    qmn = V3<float>(t4min(qmn.x, c.x - h.x - pad), t4min(qmn.y, c.y - h.y - pad), t4min(qmn.z, c.z - h.z - pad));
+    qmx = V3<float>(t4max(qmx.x, c.x + h.x + pad), t4max(qmx.y, c.y + h.y + pad), t4max(qmx.z, c.z + h.z + pad));
+  }
+  uint32_t cands = 0, overflow = 0;
+  int stack[T4_BVH_STACK];
+  int sp = 0;
+  stack[sp++] = P.link_root[alb];
+  while (sp > 0)
+  {
+    const DBvhNode& N = P.link_bvh[stack[--sp]];
+    for (int side = 0; side < 2; ++side)
+    {
+      if (!boxesOverlap(qmn, qmx, side ? N.rmn : N.lmn, side ? N.rmx : N.lmx))
+        continue;
+      const int child = side ? N.right : N.left;
+      if (child >= 0)
+      {
+        if (sp < T4_BVH_STACK)
+          stack[sp++] = child;
+        else
+          ++overflow;
+        continue;
+      }
+      ++cands;
+      if (swap)
+        pushCandidate(P, s, ~child, a);
+      else
+        pushCandidate(P, s, a, ~child);
+    }
   }
   statAdd(P.stats, ST_CANDIDATES, cands);
+  if (overflow)
+    statAdd(P.stats, ST_BVH_OVERFLOW, overflow);
 }
 
 }  // namespace t4

@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "t4_host_scene.h"
+#include "t4_jacobian.h"
 #include "t4_kernels2.h"
 
 #ifndef T4C_HOSTSIM
@@ -311,8 +312,11 @@ __global__ void __launch_bounds__(256) typeKeyKernel(KParams P, const uint32_t* 
     // (same hull vertices / support table inside a warp)
     const uint32_t a = P.cand_a[c];
     // minor (survivor queues only): the iteration count of the FP32 cull, a predictor of the exact pass's
-    const uint32_t cls = (!from_tasks && P.cand_class) ? (P.cand_class[c] & 63u) : 0u;
-    keys[i] = (uint16_t)(((((P.shapes[P.cand_b[c]].type & 7) << 5) | ((P.shapes[a].type & 3) << 3) | (a & 7u)) << 6) | cls);
+    // ... and, above it, whether phase 1 will be skipped (bit 7 of the class byte): a warp of certified pairs runs no
+    // boolean GJK at all, a mixed warp pays for it with the certified lanes idle
+    const uint32_t cb = (!from_tasks && P.cand_class) ? P.cand_class[c] : 0u;
+    const uint32_t cls = ((cb >> 7) << 6) | (cb & 63u);
+    keys[i] = (uint16_t)(((((P.shapes[P.cand_b[c]].type & 7) << 5) | ((P.shapes[a].type & 3) << 3) | (a & 7u)) << 7) | cls);
     if (from_tasks)
       idx[i] = (uint32_t)i;
   }
@@ -341,6 +345,18 @@ __global__ void dfmaPeakKernel(double* out, int iters)
     a4 = fma(a4, b, c), a5 = fma(a5, b, c), a6 = fma(a6, b, c), a7 = fma(a7, b, c);
   }
   out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+template <int MAXJ>
+__global__ void __launch_bounds__(128) jacobianKernel(JacParams Q, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    jacobianBody<MAXJ>(i, Q);
+}
+template <int MAXJ>
+__global__ void __launch_bounds__(128) contactGradKernel(JacParams Q, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    contactGradBody<MAXJ>(i, Q);
 }
 __global__ void sincosDebugKernel(const double* x, int64_t n, double* s, double* c)
 {
@@ -506,19 +522,28 @@ struct FkCache
   int n_joints = 0;
 };
 
+// Compiled scene + its device copy.  Immutable once built, so the clones of a scene share ONE image by reference count
+// (every consumer of an Environment takes a manager clone, tesseract_environment/src/core/environment.cpp:482-488: a clone
+// must not cost a compile and an upload); a scene that is modified afterwards builds a fresh image of its own and lets
+// go of the shared one.
+struct SceneImage
+{
+  CompiledScene comp;
+  DevBuf d_shapes, d_statics, d_verts, d_sup_cells, d_sup_cand, d_bvh, d_active, d_aa, d_acm, d_margin, d_shape_d, d_statics_d;
+  DevBuf d_link_bvh, d_link_root;
+};
+
 struct t4c_scene
 {
   int device = 0;
   HostScene host;
   unsigned long long rev = 1;       // bumped by every mutation
   unsigned long long uploaded = 0;  // rev of the device copy
-  CompiledScene comp;
+  std::shared_ptr<SceneImage> img = std::make_shared<SceneImage>();
   t4stream stream = nullptr;
   t4stream copy_stream = nullptr;  // progressive download of finished contact records (hostRun)
   t4stream aux_stream = nullptr;   // long-pair GJK pass, beside the deferred tiers / EPA on the main stream
   plat::t4event q_events[4] = { nullptr, nullptr, nullptr, nullptr };  // piecewise upload of q (hostRun)
-  // device scene
-  DevBuf d_shapes, d_statics, d_verts, d_sup_cells, d_sup_cand, d_bvh, d_active, d_aa, d_acm, d_margin, d_shape_d, d_statics_d;
   // per-call workspace
   DevBuf d_q0, d_q1, d_pin0, d_pin1, d_poses0, d_poses1, d_poses0d, d_poses1d;
   DevBuf d_cand_state, d_cand_a, d_cand_b, d_cand_class, d_long, d_tasks_long, d_surv, d_surv2, d_surv3, d_surv4, d_cull_claim, d_tasks;
@@ -566,41 +591,49 @@ static t4c_status syncScene(t4c_scene* s)
   if (s->uploaded == s->rev)
     return T4C_OK;
   std::string err;
-  if (!compileScene(s->host, s->comp, err))
+  // never rebuild in place: other clones may still be reading the old image
+  std::shared_ptr<SceneImage> img = std::make_shared<SceneImage>();
+  if (!compileScene(s->host, img->comp, err))
     return fail(T4C_ERR_UNSUPPORTED, "%s", err.c_str());
-  CompiledScene& C = s->comp;
+  CompiledScene& C = img->comp;
+  SceneImage& I = *img;
   t4stream st = s->stream;
-  bool ok = upload(s->d_shapes, C.shapes, st) && upload(s->d_statics, C.statics, st) && upload(s->d_verts, C.verts, st) &&
-            upload(s->d_sup_cells, C.sup_cells, st) && upload(s->d_sup_cand, C.sup_cand, st) &&
-            upload(s->d_bvh, C.bvh, st) && upload(s->d_active, C.active_shapes, st) && upload(s->d_aa, C.aa_pairs, st) &&
-            upload(s->d_acm, C.acm_bits, st) && upload(s->d_margin, C.pair_margin, st) &&
-            upload(s->d_shape_d, C.shape_d, st) && upload(s->d_statics_d, C.statics_d, st) && plat::sync(st);
+  bool ok = upload(I.d_shapes, C.shapes, st) && upload(I.d_statics, C.statics, st) && upload(I.d_verts, C.verts, st) &&
+            upload(I.d_sup_cells, C.sup_cells, st) && upload(I.d_sup_cand, C.sup_cand, st) &&
+            upload(I.d_bvh, C.bvh, st) && upload(I.d_active, C.active_shapes, st) && upload(I.d_aa, C.aa_pairs, st) &&
+            upload(I.d_acm, C.acm_bits, st) && upload(I.d_margin, C.pair_margin, st) &&
+            upload(I.d_shape_d, C.shape_d, st) && upload(I.d_statics_d, C.statics_d, st) &&
+            upload(I.d_link_bvh, C.link_bvh, st) && upload(I.d_link_root, C.link_root, st) && plat::sync(st);
   if (!ok)
     return fail(T4C_ERR_CUDA, "scene upload failed: %s", plat::lastError());
+  s->img = img;
   s->uploaded = s->rev;
   return T4C_OK;
 }
 
 static void fillSceneParams(const t4c_scene* s, KParams& P)
 {
-  const CompiledScene& C = s->comp;
+  const CompiledScene& C = s->img->comp;
+  const SceneImage& I = *s->img;
   std::memset(&P, 0, sizeof(P));
-  P.shapes = s->d_shapes.as<DShape>();
-  P.statics = s->d_statics.as<DStaticW>();
-  P.shape_d = s->d_shape_d.as<double>();
-  P.statics_d = s->d_statics_d.as<double>();
-  P.verts = s->d_verts.as<f4>();
-  P.sup_cells = C.sup_cells.empty() ? nullptr : s->d_sup_cells.as<uint32_t>();
-  P.sup_cand = s->d_sup_cand.as<uint16_t>();
-  P.bvh = s->d_bvh.as<DBvhNode>();
+  P.shapes = I.d_shapes.as<DShape>();
+  P.statics = I.d_statics.as<DStaticW>();
+  P.shape_d = I.d_shape_d.as<double>();
+  P.statics_d = I.d_statics_d.as<double>();
+  P.verts = I.d_verts.as<f4>();
+  P.sup_cells = C.sup_cells.empty() ? nullptr : I.d_sup_cells.as<uint32_t>();
+  P.sup_cand = I.d_sup_cand.as<uint16_t>();
+  P.bvh = I.d_bvh.as<DBvhNode>();
   P.n_bvh_nodes = (int)C.bvh.size();
-  P.active_shapes = s->d_active.as<int32_t>();
+  P.active_shapes = I.d_active.as<int32_t>();
   P.n_active_shapes = (int)C.active_shapes.size();
-  P.aa_pairs = s->d_aa.as<int32_t>();
-  P.n_aa_pairs = (int)(C.aa_pairs.size() / 2);
-  P.acm_bits = s->d_acm.as<uint32_t>();
+  P.aa_pairs = I.d_aa.as<int32_t>();
+  P.n_aa_pairs = (int)(C.aa_pairs.size() / 3);
+  P.link_bvh = I.d_link_bvh.as<DBvhNode>();
+  P.link_root = I.d_link_root.as<int32_t>();
+  P.acm_bits = I.d_acm.as<uint32_t>();
   P.acm_words = C.acm_words;
-  P.pair_margin = C.pair_margin.empty() ? nullptr : s->d_margin.as<double>();
+  P.pair_margin = C.pair_margin.empty() ? nullptr : I.d_margin.as<double>();
   P.n_links = (int)s->host.links.size();
   P.n_alinks = (int)C.alinks.size();
   P.default_margin = C.default_margin;
@@ -646,7 +679,7 @@ static t4c_status syncFk(t4c_scene* s, const t4c_fk_model* m, FkCache** out)
     std::memcpy(D.pre, J.parent_link < nl ? s->host.links[J.parent_link].pose : I12, sizeof(D.pre));
     child_joint[J.child_link] = j;
   }
-  const CompiledScene& C = s->comp;
+  const CompiledScene& C = s->img->comp;
   std::vector<int32_t> aj(std::max<size_t>(C.alinks.size(), 1), -1);
   std::vector<double> as(std::max<size_t>(C.alinks.size(), 1) * 12, 0.0);
   for (size_t a = 0; a < C.alinks.size(); ++a)
@@ -796,12 +829,12 @@ static const uint32_t* sortByType(t4c_scene* s, const KParams& P, const uint32_t
   const uint32_t* vals_in = from_tasks ? s->d_sort_idx.as<uint32_t>() : queue;
   size_t tmp = 0;
   // task queues and class-less runs have zero low bits: one 8-bit digit is enough for them
-  const int bit0 = (!from_tasks && P.cand_class) ? 0 : 6;
+  const int bit0 = (!from_tasks && P.cand_class) ? 0 : 7;
   if (cub::DeviceRadixSort::SortPairs(nullptr, tmp, s->d_sort_keys.as<uint16_t>(), s->d_sort_keys2.as<uint16_t>(), vals_in,
-                                      s->d_sort_vals.as<uint32_t>(), (int)n, bit0, 14, st) != cudaSuccess ||
+                                      s->d_sort_vals.as<uint32_t>(), (int)n, bit0, 15, st) != cudaSuccess ||
       !s->d_sort_tmp.ensure(tmp) ||
       cub::DeviceRadixSort::SortPairs(s->d_sort_tmp.p, tmp, s->d_sort_keys.as<uint16_t>(), s->d_sort_keys2.as<uint16_t>(),
-                                      vals_in, s->d_sort_vals.as<uint32_t>(), (int)n, bit0, 14, st) != cudaSuccess)
+                                      vals_in, s->d_sort_vals.as<uint32_t>(), (int)n, bit0, 15, st) != cudaSuccess)
     return nullptr;
   return s->d_sort_vals.as<uint32_t>();
 }
@@ -881,8 +914,9 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
   const size_t qelem = io.q_layout == T4C_Q_F64_ROWMAJOR ? sizeof(double) : sizeof(float);
   // records [0, upto) are final on the device (the compute stream has just been synchronised): send what is new to
   // the caller's page-locked buffer on the copy stream, under the kernels that follow
+  bool aux_busy = false;  // set while kernels of the long-pair pass run beside the main stream (they append records too)
   auto drain = [&](int64_t upto) -> bool {
-    if (!io.host_contacts || !io.contacts)
+    if (!io.host_contacts || !io.contacts || aux_busy)
       return true;
     upto = std::min<int64_t>(upto, io.capacity);
     const int64_t min_records = tuning().drain_min;
@@ -997,7 +1031,25 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
     }
     uint32_t cand_begin = 0, nsurv2 = 0, nsurv3 = 0, nsurv4 = 0;
     uint32_t long_cap_bound = 0, long_done = 0;
+    // kernels of the long-pair pass may be running on the auxiliary stream (see launchLongAsync below): they are joined
+    // before any queue they read is reallocated, and on EVERY way out of this function
+    struct AuxJoin
+    {
+      t4stream aux;
+      bool inflight = false;
+      void join()
+      {
+        if (inflight && aux)
+          plat::sync(aux);
+        inflight = false;
+      }
+      ~AuxJoin() { join(); }
+    } aux_join{ s->aux_stream };
+    uint32_t bound_cap = 0;
     auto bindQueues = [&]() -> bool {
+      if (aux_join.inflight && s->cand_cap != bound_cap)
+        aux_join.join();  // the queues are about to grow (and move)
+      bound_cap = s->cand_cap;
       const size_t cb = (size_t)s->cand_cap * sizeof(uint32_t), keep = (size_t)cand_begin * sizeof(uint32_t);
       if (!(s->d_cand_state.ensureKeep(cb, keep, st) && s->d_cand_a.ensureKeep(cb, keep, st) &&
             s->d_cand_b.ensureKeep(cb, keep, st) && s->d_surv.ensure(cb)))
@@ -1038,6 +1090,36 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
         P.surv4_w = s->d_surv4.as<uint32_t>();
       }
       return true;
+    };
+    uint32_t n_long_async = 0;  // long pairs whose GJK has been launched on the auxiliary stream
+    auto launchLongAsync = [&]() -> t4c_status {
+      if (!P.long_w || !s->aux_stream)
+        return T4C_OK;
+      const uint32_t nlong = std::min(qc[Q_LONG], P.long_cap);  // qc: read back by the exact pass just before
+      if (nlong <= long_done)
+        return T4C_OK;
+      const size_t need = (size_t)nlong * sizeof(EpaTask);
+      if (need > s->d_tasks_long.cap)
+      {
+        aux_join.join();  // the task queue of the running launches moves
+        T4_TRY(s->d_tasks_long.ensureKeep(std::max<size_t>(need, 4096 * sizeof(EpaTask)),
+                                          (size_t)n_long_async * sizeof(EpaTask), st),
+               "EPA task queue");
+      }
+      KParams PL = P;
+      PL.gjk_budget = 0;
+      PL.long_w = nullptr;
+      PL.surv = P.long_w + long_done;
+      PL.tasks = s->d_tasks_long.as<EpaTask>();
+      PL.task_cap = (uint32_t)(s->d_tasks_long.cap / sizeof(EpaTask));
+      PL.task_q = Q_TASK_LONG;
+      PL.task_order = nullptr;
+      launchGjk(PL, nlong - long_done, s->aux_stream);
+      aux_join.inflight = true;
+      aux_busy = true;  // slots below the record counter may still be unwritten: no progressive download meanwhile
+      n_long_async += nlong - long_done;
+      long_done = nlong;
+      return T4C_OK;
     };
     // one exact pass over a survivor queue: GJK kernel -> EPA task queue [-> EPA kernel].  With run_epa == false the
     // tasks stay queued (and the next pass appends to them): a launch of a few hundred EPA tasks lasts as long as its
@@ -1142,28 +1224,13 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
       rc = exactPass(s->d_surv.as<uint32_t>(), nsurv, round == n_rounds - 1 && !P.long_w);
       if (rc != T4C_OK)
         return rc;
-    }
-    // ---- long pairs of the rounds: their GJK (milliseconds with a handful of active lanes) starts now on its own
-    //      stream, beside the deferred tiers and the EPA launch of the main stream; joined below
-    uint32_t n_long_async = 0;
-    if (P.long_w)
-    {
-      T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (GJK)");
-      const uint32_t nlong = std::min(qc[Q_LONG], P.long_cap);
-      if (nlong > long_done)
-      {
-        n_long_async = nlong - long_done;
-        T4_TRY(s->d_tasks_long.ensure((size_t)n_long_async * sizeof(EpaTask)), "EPA task queue");
-        KParams PL = P;
-        PL.gjk_budget = 0;
-        PL.long_w = nullptr;
-        PL.surv = P.long_w + long_done;
-        PL.tasks = s->d_tasks_long.as<EpaTask>();
-        PL.task_cap = n_long_async;
-        PL.task_q = Q_TASK_LONG;
-        launchGjk(PL, n_long_async, s->aux_stream ? s->aux_stream : st);
-        long_done = nlong;
-      }
+      // ---- long pairs of this round: a pair that cycles towards the detector's 1000-iteration caps keeps one lane
+      //      busy for ~9 ms.  Its GJK starts NOW on the auxiliary stream, under the rounds that follow, the deferred
+      //      tiers and the EPA launch of the main stream (r3c: started only after the last round, the pass outlasted
+      //      its cover by 3 ms on the ranks whose batch holds such pairs -- the 0.90 scaling efficiency of round 1).
+      rc = launchLongAsync();
+      if (rc != T4C_OK)
+        return rc;
     }
     // ---- deferred tiers, for the states that are still without a contact
     rc = exactPass(s->d_surv2.as<uint32_t>(), nsurv2, true);
@@ -1178,9 +1245,9 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
     if (n_long_async > 0)
     {
       // join the long-pair pass; its penetrating pairs go through EPA now
-      T4_TRY(launchOk() && plat::sync(s->aux_stream ? s->aux_stream : st) &&
-                 plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st),
-             "narrowphase (long pairs)");
+      aux_join.join();
+      aux_busy = false;
+      T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (long pairs)");
       const uint32_t ntl = std::min(qc[Q_TASK_LONG], n_long_async);
       if (ntl > 0)
       {
@@ -1275,7 +1342,7 @@ static t4c_status hostRun(t4c_scene* s, BatchIO& io, const double* hq0, const do
   if (rc != T4C_OK)
     return rc;
   t4stream st = s->stream;
-  const int na = (int)s->comp.alinks.size();
+  const int na = (int)s->img->comp.alinks.size();
   if (io.model && !hq0 && io.q0)
   {
     // joint vectors already on the device (LVS expansion kernels)
@@ -1530,11 +1597,11 @@ t4c_status t4c_scene_create(const t4c_scene_desc* d, int32_t device, t4c_scene**
     H.links[i].active = d->links[i].active != 0;
     std::memcpy(H.links[i].pose, d->links[i].pose, sizeof(H.links[i].pose));
   }
-  H.shapes.assign(d->shapes, d->shapes + d->n_shapes);
-  for (auto& sh : H.shapes)
+  H.geom->shapes.assign(d->shapes, d->shapes + d->n_shapes);
+  for (auto& sh : H.geom->shapes)
     if (sh.type < T4C_SPHERE || sh.type > T4C_TRIANGLE || sh.link < 0 || sh.link >= d->n_links)
       return fail(T4C_ERR_INVALID, "bad shape record (type %d, link %d)", sh.type, sh.link);
-  H.vertices.assign(d->vertices, d->vertices + 3 * (size_t)d->n_vertices);
+  H.geom->vertices.assign(d->vertices, d->vertices + 3 * (size_t)d->n_vertices);
   for (int i = 0; i < d->n_acm_pairs; ++i)
     H.acm.insert(hostPairKey(d->acm_pairs[2 * i], d->acm_pairs[2 * i + 1]));
   H.default_margin = d->default_margin;
@@ -1558,7 +1625,7 @@ t4c_status t4c_scene_clone(const t4c_scene* src, t4c_scene** out)
     return fail(T4C_ERR_INVALID, "null argument");
   std::unique_ptr<t4c_scene> s(new t4c_scene());
   s->device = src->device;
-  s->host = src->host;
+  s->host = src->host;  // links, ACM, margins by value; geometry (shapes, vertices) by reference
   if (!plat::setDevice(s->device))
     return fail(T4C_ERR_CUDA, "cudaSetDevice(%d): %s", s->device, plat::lastError());
   s->stream = plat::newStream();
@@ -1566,9 +1633,19 @@ t4c_status t4c_scene_clone(const t4c_scene* src, t4c_scene** out)
   s->aux_stream = plat::newStream();
   for (auto& e : s->q_events)
     e = plat::newEvent();
-  t4c_status rc = syncScene(s.get());
-  if (rc != T4C_OK)
-    return rc;
+  if (src->uploaded == src->rev)
+  {
+    // the source's compiled image (host tables + device buffers) is current: share it, no compile, no upload
+    s->img = src->img;
+    s->rev = s->uploaded = 1;
+  }
+  else
+  {
+    t4c_status rc = syncScene(s.get());
+    if (rc != T4C_OK)
+      return rc;
+  }
+  s->chunk_hint = src->chunk_hint;
   *out = s.release();
   return T4C_OK;
 }
@@ -1709,6 +1786,131 @@ t4c_status t4c_fk(const t4c_fk_model* m, const t4c_scene* scene_c, const double*
     launchFk(P, 0, nc, st);
     T4_TRY(launchOk() && plat::d2h(link_poses + (size_t)base * nl * 12, P.fk_out, ob, st) && plat::sync(st), "FK");
   }
+  return T4C_OK;
+}
+
+static void launchJacobian(const JacParams& Q, int64_t n, bool grad, t4stream st)
+{
+  if (n <= 0)
+    return;
+#ifndef T4C_HOSTSIM
+  const int grid = gridFor(n, 128, 8);
+  if (Q.P.n_joints <= 16)
+  {
+    if (grad)
+      contactGradKernel<16><<<grid, 128, 0, st>>>(Q, n);
+    else
+      jacobianKernel<16><<<grid, 128, 0, st>>>(Q, n);
+  }
+  else if (grad)
+    contactGradKernel<T4_MAX_JOINTS><<<grid, 128, 0, st>>>(Q, n);
+  else
+    jacobianKernel<T4_MAX_JOINTS><<<grid, 128, 0, st>>>(Q, n);
+#else
+  (void)st;
+  for (int64_t i = 0; i < n; ++i)
+    if (grad)
+      contactGradBody<T4_MAX_JOINTS>(i, Q);
+    else
+      jacobianBody<T4_MAX_JOINTS>(i, Q);
+#endif
+  ++g_launches;
+}
+
+t4c_status t4c_jacobian(const t4c_fk_model* m, const t4c_scene* scene_c, const double* q, int64_t n, int32_t link,
+                        const double* point_local, double* J)
+{
+  t4c_scene* s = const_cast<t4c_scene*>(scene_c);
+  if (!m || !s || !q || !J || n < 0 || link < 0 || link >= (int)s->host.links.size())
+    return fail(T4C_ERR_INVALID, "bad argument");
+  t4c_status rc = syncScene(s);
+  if (rc != T4C_OK)
+    return rc;
+  FkCache* fc = nullptr;
+  rc = syncFk(s, m, &fc);
+  if (rc != T4C_OK)
+    return rc;
+  t4stream st = s->stream;
+  JacParams Q;
+  std::memset(&Q, 0, sizeof(Q));
+  fillSceneParams(s, Q.P);
+  fillFkParams(m, fc, Q.P);
+  int lj = -1;
+  for (size_t j = 0; j < m->joints.size(); ++j)
+    if (m->joints[j].child_link == link)
+      lj = (int)j;
+  Q.link_joint = lj;
+  Q.has_point = point_local ? 1 : 0;
+  if (point_local)
+    std::memcpy(Q.point, point_local, 3 * sizeof(double));
+  const size_t qb = (size_t)n * (size_t)m->n_q * sizeof(double), jb = (size_t)n * 6 * (size_t)m->n_q * sizeof(double);
+  T4_TRY(s->d_q0.ensure(std::max<size_t>(qb, 8)) && s->d_fk_out.ensure(std::max<size_t>(jb, 8)) &&
+             plat::h2d(s->d_q0.p, q, qb, st),
+         "Jacobian workspace");
+  Q.P.n = n, Q.P.q0 = s->d_q0.p, Q.P.q_layout = T4C_Q_F64_ROWMAJOR, Q.P.q_stride_n = n;
+  Q.J = s->d_fk_out.as<double>();
+  launchJacobian(Q, n, false, st);
+  T4_TRY(launchOk() && plat::d2h(J, Q.J, jb, st) && plat::sync(st), "Jacobian");
+  return T4C_OK;
+}
+
+static t4c_status contactGradients(t4c_scene* s, const t4c_fk_model* m, const void* q_dev, int32_t q_layout, int64_t n,
+                                   const t4c_contact* con_dev, int64_t nc, double* grad_dev)
+{
+  t4c_status rc = syncScene(s);
+  if (rc != T4C_OK)
+    return rc;
+  FkCache* fc = nullptr;
+  rc = syncFk(s, m, &fc);
+  if (rc != T4C_OK)
+    return rc;
+  JacParams Q;
+  std::memset(&Q, 0, sizeof(Q));
+  fillSceneParams(s, Q.P);
+  fillFkParams(m, fc, Q.P);
+  Q.P.n = n, Q.P.q0 = q_dev, Q.P.q_layout = q_layout, Q.P.q_stride_n = n;
+  Q.contacts = con_dev, Q.n_contacts = nc, Q.grad = grad_dev;
+  Q.link_to_joint = fc->link_joint.as<int32_t>();
+  launchJacobian(Q, nc, true, s->stream);
+  T4_TRY(launchOk(), "contact gradients");
+  return T4C_OK;
+}
+
+t4c_status t4c_contact_gradients_device(t4c_scene* s, const t4c_fk_model* m, const void* q, int32_t q_layout, int64_t n,
+                                        const t4c_contact* contacts, int64_t n_contacts, double* grad)
+{
+  if (!s || !m || !q || n < 0 || n_contacts < 0 || (n_contacts > 0 && (!contacts || !grad)))
+    return fail(T4C_ERR_INVALID, "bad argument");
+  const t4c_status rc = contactGradients(s, m, q, q_layout, n, contacts, n_contacts, grad);
+  if (rc != T4C_OK)
+    return rc;
+  T4_TRY(plat::sync(s->stream), "contact gradients");
+  return T4C_OK;
+}
+
+t4c_status t4c_contact_gradients(t4c_scene* s, const t4c_fk_model* m, const double* q, int64_t n,
+                                 const t4c_contact* contacts, int64_t n_contacts, double* grad)
+{
+  if (!s || !m || !q || n < 0 || n_contacts < 0 || (n_contacts > 0 && (!contacts || !grad)))
+    return fail(T4C_ERR_INVALID, "bad argument");
+  if (!bindDevice(s))
+    return fail(T4C_ERR_CUDA, "cudaSetDevice(%d): %s", s->device, plat::lastError());
+  for (int64_t i = 0; i < n_contacts; ++i)
+    if (contacts[i].state < 0 || contacts[i].state >= n || contacts[i].link[0] < 0 || contacts[i].link[1] < 0 ||
+        contacts[i].link[0] >= (int)s->host.links.size() || contacts[i].link[1] >= (int)s->host.links.size())
+      return fail(T4C_ERR_INVALID, "contact %lld refers to a state or link outside the batch", (long long)i);
+  t4stream st = s->stream;
+  const size_t qb = (size_t)n * (size_t)m->n_q * sizeof(double), cb = (size_t)n_contacts * sizeof(t4c_contact);
+  const size_t gb = (size_t)n_contacts * (size_t)m->n_q * sizeof(double);
+  T4_TRY(s->d_q0.ensure(std::max<size_t>(qb, 8)) && s->d_out.ensure(std::max<size_t>(cb, 8)) &&
+             s->d_fk_out.ensure(std::max<size_t>(gb, 8)) && plat::h2d(s->d_q0.p, q, qb, st) &&
+             plat::h2d(s->d_out.p, contacts, cb, st),
+         "gradient workspace");
+  const t4c_status rc = contactGradients(s, m, s->d_q0.p, T4C_Q_F64_ROWMAJOR, n, s->d_out.as<t4c_contact>(), n_contacts,
+                                         s->d_fk_out.as<double>());
+  if (rc != T4C_OK)
+    return rc;
+  T4_TRY(plat::d2h(grad, s->d_fk_out.p, gb, st) && plat::sync(st), "contact gradients");
   return T4C_OK;
 }
 
@@ -1954,9 +2156,9 @@ t4c_status t4c_check_cast_device(t4c_scene* s, const t4c_fk_model* m, int64_t n,
 t4c_status t4c_debug_hull_support(t4c_scene* s, int32_t shape, const double* dirs, int64_t n, int32_t* out,
                                   double* mean_candidates)
 {
-  if (!s || !dirs || !out || shape < 0 || shape >= (int)s->comp.shapes.size())
+  if (!s || !dirs || !out || shape < 0 || shape >= (int)s->img->comp.shapes.size())
     return fail(T4C_ERR_INVALID, "bad argument");
-  const CompiledScene& C = s->comp;
+  const CompiledScene& C = s->img->comp;
   const DShape& D = C.shapes[shape];
   if (D.type != SH_HULL)
     return fail(T4C_ERR_INVALID, "shape %d is not a hull", shape);

@@ -13,6 +13,13 @@ counts and the measured deviations (no silent allowance):
   NONUNIQUE   the closest pair is not unique (parallel faces / edges).  Required: same distance and normal (1e-5),
               pB - pA = d n on both sides (1e-5), and -- when link poses are supplied -- both device witnesses lie ON
               their own shapes (point-in-shape test in pure numpy / scipy, independent of oracle and device).
+  ORACLE_OFF_EXACT  the oracle -- the restated Bullet path -- is itself off the exact geometry: for barely penetrating
+              polytopes (depth < 1e-4) the restated btGjkEpaSolver2 can leave its GJK on a repeated support vertex and
+              report a small POSITIVE distance along an unrelated axis, and the answer then depends on the order of the
+              pair (observed: hull x box -6.4e-5 exact, oracle +2.06e-4 as (hull, box) and -6.4e-5 as (box, hull)).
+              Whether a real Bullet build does the same cannot be checked here (Bullet is not installed).  Accepted only
+              when the DEVICE agrees to 1e-5 with the exact Minkowski-hull value computed by scipy (tests/
+              second_opinion.py: no iteration, no tolerance); needs link poses and polytope / sphere shapes.
   CURVED_PEN  penetrating pair with a cylinder / cone core.  The reference's own penetration solver stops unconverged
               there (Bullet's 128-vertex polytope cap, tesseract_gjk_pair_detector.cpp:1024-1032 -> btGjkEpaSolver2):
               the depth bound agrees to 1e-5 but the face normal of a polytope that approximates a curved surface is
@@ -106,6 +113,27 @@ class ShapeTester:
         v = self.verts[s["vertex_offset"]:s["vertex_offset"] + 3]  # TRIANGLE: distance to the triangle
         return _point_triangle_distance(p, v[0], v[1], v[2])
 
+    def world_core(self, link, shape_id, sub, link_pose):
+        """(vertices of the core in the world frame, margin radius) for polytopes and spheres, else None"""
+        s = self.by_id[(link, shape_id, sub)]
+        t, par = s["type"], s["params"]
+        if t == SPHERE:
+            loc, r = np.zeros((1, 3)), par[0]
+        elif t == BOX:
+            h = np.asarray(par[:3])
+            loc, r = np.array([[sx * h[0], sy * h[1], sz * h[2]] for sx in (-1, 1) for sy in (-1, 1) for sz in (-1, 1)]), 0.0
+        elif t == HULL:
+            loc, r = self.verts[s["vertex_offset"]:s["vertex_offset"] + s["vertex_count"]], 0.0
+        elif t == TRIANGLE:
+            loc, r = self.verts[s["vertex_offset"]:s["vertex_offset"] + 3], 0.0
+        else:
+            return None
+        L = np.asarray(s["pose"], dtype=np.float64).reshape(3, 4)
+        T = np.asarray(link_pose, dtype=np.float64).reshape(3, 4)
+        R = T[:, :3] @ L[:, :3]
+        o = T[:, :3] @ L[:, 3] + T[:, 3]
+        return loc @ R.T + o, r
+
 
 def _point_triangle_distance(p, a, b, c):
     ab, ac, ap = b - a, c - a, p - a
@@ -146,7 +174,8 @@ def compare(builder, con_g, con_o, hit_g, hit_o, margin_of, per_shape=False, che
     tester = ShapeTester(builder)
     rep = dict(n_gpu=len(G), n_oracle=len(O), band_exempt=0, max_dd=0.0, max_dp=0.0, max_dn=0.0, nonunique=0,
                curved_pen=0, curved_dn_hist=[0] * (len(HIST_EDGES) + 1), curved_max_dn=0.0, curved_max_dp=0.0,
-               curved_max_witness_slack=0.0, max_dt=0.0, witness_checks=0, flag_mismatch=0, sentinel=0)
+               curved_max_witness_slack=0.0, max_dt=0.0, oracle_off_exact=0, oracle_off_exact_max=0.0,
+               witness_checks=0, flag_mismatch=0, sentinel=0)
     exempt_states = set()
     for k in set(G) ^ set(O):
         src = O if k in O else G
@@ -183,6 +212,23 @@ def compare(builder, con_g, con_o, hit_g, hit_o, margin_of, per_shape=False, che
             rep["sentinel"] += 1
             continue
         dd = abs(dg - do)
+        if dd > TOL + F32 and link_poses is not None:
+            # device and oracle disagree: let exact geometry decide (ORACLE_OFF_EXACT, see the module comment)
+            import second_opinion as so
+            st = k[0] - state_base
+            ca = tester.world_core(k[1], sidg[0], sidg[1], link_poses[st, k[1]])
+            cb = tester.world_core(k[2], sidg[2], sidg[3], link_poses[st, k[2]])
+            assert ca is not None and cb is not None, f"{k}: distance {dg} vs {do} (no exact value for this shape pair)"
+            d_exact, n_exact = so.exact_pair(ca[0], cb[0], ca[1], cb[1])
+            assert abs(dg - d_exact) <= TOL + F32, f"{k}: distance {dg} vs oracle {do}, exact {d_exact}"
+            # how far the ORACLE is off is recorded, not bounded: it is not a device tolerance (worst seen: 9 mm for two
+            # interpenetrating flat triangles of a mesh-mesh pair, where GJK / EPA on zero-volume shapes is ill-posed)
+            if n_exact is not None and abs(d_exact) > 1e-9:
+                # exact_pair's normal points from the second shape to the first; the record's from link 0 to link 1
+                assert np.linalg.norm(ng + n_exact) <= 1e-4, f"{k}: normal {ng} vs exact {-n_exact}"
+            rep["oracle_off_exact"] += 1
+            rep["oracle_off_exact_max"] = max(rep["oracle_off_exact_max"], abs(do - d_exact))
+            continue
         assert dd <= TOL + F32, f"{k}: distance {dg} vs {do}"
         rep["max_dd"] = max(rep["max_dd"], dd)
         dp = max(np.linalg.norm(pg[0] - po[0]), np.linalg.norm(pg[1] - po[1]))

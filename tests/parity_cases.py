@@ -148,3 +148,29 @@ def fk_parity(make_checker, robot="iiwa14", n=200):
     bad = int((Tg.view(np.uint64) != To.view(np.uint64)).sum())
     assert bad == 0, f"{bad} of {Tg.size} pose elements differ (max {float(np.abs(Tg - To).max())})"
     return 0.0
+
+
+def abb_mesh_config1(make_checker, n_states, threads=4, device_fk=True):
+    """SURVEY 8(d) config 1 / BASELINE configs[0]: ABB IRB2400 with its links loaded AS GIVEN -- triangle Mesh shapes, one
+    triangle shape per face (bullet_utils.cpp:111-132) -- self + environment check against one static 1 m box at
+    (1.0, 0, 0.5), ContactTestType::ALL, margin 0.05; the all-zeros state plus uniform-in-limits states.  The self check
+    of mesh links is compound x compound: every triangle of the smaller link walks the child tree of the other link
+    (t4_kernels.h broadActiveBody)."""
+    b = S.SceneBuilder()
+    root, moving = S.add_robot(b, S.load_robot("abb_irb2400"), convex=False)
+    b.add_collision_object("box", 0, [S.Box(1.0, 1.0, 1.0)], [S.identity()], pose_=S.pose((1.0, 0.0, 0.5)))
+    b.set_active(moving)
+    b.set_margin(0.05)
+    q = np.concatenate([np.zeros((1, 6)), S.random_states(b, n_states - 1, seed=1, dtype=np.float64)])
+    bc = make_checker(b)
+    hit_o, con_o, _ = pyoracle.check_discrete(b, q, capi.TEST_ALL, n_threads=threads)
+    T = pyoracle.fk(b, q)
+    if device_fk:
+        hit_g, con_g, stats = bc.check_discrete(q, capi.TEST_ALL)
+    else:
+        hit_g, con_g, _, stats = bc.check_link_poses(T, None, capi.TEST_ALL)
+    rep = compare_batch(b, con_g, con_o, hit_g, hit_o, 0.05, per_shape=True, link_poses=T,
+                        label=f"config1 ABB triangle-mesh links, self + box, ALL, n {n_states}")
+    rep["self_contacts"] = int(sum(1 for c in con_g if b.link_active[c["link"][0]] and b.link_active[c["link"][1]]))
+    rep["candidates"] = stats["candidates"]
+    return rep

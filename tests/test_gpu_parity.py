@@ -98,3 +98,10 @@ def test_config5_dual_arm():
     out = pc.config5_dual_arm(mk, 4000, 10000, threads=THREADS)
     print(out)
     assert out["self_or_cross"] > 0
+
+
+def test_config1_abb_mesh_links():
+    """configs[0]: ABB with triangle-mesh links as given, self + environment, ALL, zero state + 1000 random states"""
+    out = pc.abb_mesh_config1(mk, 1001, threads=THREADS)
+    print(out)
+    assert out["n_gpu"] > 0

@@ -49,6 +49,13 @@ def test_fk(robot):
     pc.fk_parity(mk, robot)
 
 
+def test_config1_abb_mesh_links():
+    """configs[0]: ABB with triangle-mesh links, self + environment, ALL (compound x compound through the child trees)"""
+    out = pc.abb_mesh_config1(mk, 12)
+    print(out)
+    assert out["n_gpu"] > 0
+
+
 def test_first_in_rounds():
     """FIRST queries in rounds over the robot's shapes (t4c.cu runBatch; on by default for >= 16384 states): same
     flags, one record per colliding state, each record a contact the oracle also reports"""
