@@ -220,7 +220,16 @@ t4c_status t4c_scene_set_acm(t4c_scene* scene, int32_t n_pairs, const int32_t* p
 t4c_status t4c_scene_set_margins(t4c_scene* scene, double default_margin, int32_t n_pairs,
                                  const int32_t* pairs, const double* values);
 t4c_status t4c_scene_set_link_pose(t4c_scene* scene, int32_t link, const double* pose12);
+/* several links at once (one BVH refit for all moved static objects); unchanged poses cost nothing */
+t4c_status t4c_scene_set_link_poses(t4c_scene* scene, int32_t n, const int32_t* links, const double* poses12);
 int32_t t4c_scene_num_active(const t4c_scene* scene); /* kinematic links, ascending link index */
+/* addCollisionObject / removeCollisionObject on a live scene (discrete_contact_manager.h:75-98).  Shape records: link
+ * field ignored, vertex offsets relative to `vertices`.  An existing link name is replaced.  A removed object keeps its
+ * link index (shapeless, disabled) so that the indices of the others do not move.  Moving a STATIC object with
+ * t4c_scene_set_link_pose refits the environment BVH (no rebuild); adding / removing rebuilds it at the next check. */
+t4c_status t4c_scene_add_object(t4c_scene* scene, const t4c_link* link, int32_t n_shapes, const t4c_shape* shapes,
+                                int32_t n_vertices, const double* vertices, int32_t* link_index);
+t4c_status t4c_scene_remove_object(t4c_scene* scene, int32_t link);
 
 t4c_status t4c_fk_model_create(const t4c_fk_model_desc* desc, const t4c_scene* scene, t4c_fk_model** out);
 void t4c_fk_model_destroy(t4c_fk_model* model);

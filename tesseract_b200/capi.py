@@ -114,7 +114,10 @@ def load_library(path=None):
     lib.t4c_scene_set_acm.argtypes = [VP, I32, C.POINTER(I32)]
     lib.t4c_scene_set_margins.argtypes = [VP, C.c_double, I32, C.POINTER(I32), DP]
     lib.t4c_scene_set_link_pose.argtypes = [VP, I32, DP]
+    lib.t4c_scene_set_link_poses.argtypes = [VP, I32, C.POINTER(I32), DP]
     lib.t4c_scene_num_active.argtypes = [VP]
+    lib.t4c_scene_add_object.argtypes = [VP, C.POINTER(Link), I32, C.POINTER(Shape), I32, DP, C.POINTER(I32)]
+    lib.t4c_scene_remove_object.argtypes = [VP, I32]
     lib.t4c_fk_model_create.argtypes = [C.POINTER(FkModelDesc), VP, C.POINTER(VP)]
     lib.t4c_fk_model_destroy.argtypes = [VP]
     lib.t4c_fk_model_destroy.restype = None
@@ -167,7 +170,8 @@ def load_library(path=None):
                  "t4c_debug_hull_support", "t4c_measure_fp64_peak", "t4c_debug_sincos", "t4c_comm_unique_id",
                  "t4c_comm_create", "t4c_comm_create_local", "t4c_check_discrete_sharded", "t4c_check_cast_sharded",
                  "t4c_check_discrete_multi", "t4c_jacobian", "t4c_contact_gradients",
-                 "t4c_contact_gradients_device"):
+                 "t4c_contact_gradients_device", "t4c_scene_add_object", "t4c_scene_remove_object",
+                 "t4c_scene_set_link_poses"):
         getattr(lib, name).restype = I32
     if path is None:
         _lib = lib

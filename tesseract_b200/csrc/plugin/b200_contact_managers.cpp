@@ -30,7 +30,10 @@ ManagerCore::~ManagerCore()
 }
 
 // clone(): identical objects, transforms, active set, margins, ACM function; geometries stay shared
-// (bullet_discrete_bvh_manager.cpp:81-105).  The device scene of the clone is built on its first query.
+// (bullet_discrete_bvh_manager.cpp:81-105).  Every consumer of an Environment takes a clone
+// (tesseract_environment/src/core/environment.cpp:482-488), so a clone must be cheap: when this manager's device scene
+// is built, the clone takes a reference to the same compiled image (t4c_scene_clone: no compile, no upload); otherwise
+// its scene is built on its first query.
 std::unique_ptr<ManagerCore> ManagerCore::clone() const
 {
   std::unique_ptr<ManagerCore> c(new ManagerCore(cast_, device_));
@@ -40,6 +43,13 @@ std::unique_ptr<ManagerCore> ManagerCore::clone() const
   c->active_ = active_;
   c->margins_ = margins_;
   c->fn_ = fn_;
+  if (scene_ && !dirty_structure_ && t4c_scene_clone(scene_, &c->scene_) == T4C_OK)
+  {
+    c->dirty_structure_ = false;
+    c->dirty_soft_ = true;  // settings are compared by the library: unchanged ones cost nothing
+    c->acm_uploaded_ = acm_uploaded_;
+    c->acm_valid_ = acm_valid_ && !dirty_soft_;
+  }
   return c;
 }
 
@@ -327,19 +337,26 @@ void ManagerCore::sync()
   if (dirty_soft_)
   {
     std::vector<int32_t> act((size_t)std::max(nl, 1), 0);
+    std::vector<int32_t> moved;
+    std::vector<double> moved_pose;
     for (int i = 0; i < nl; ++i)
     {
       act[i] = isActive(i) ? 1 : 0;
       check(t4c_scene_set_enabled(scene_, i, objects_[i].enabled ? 1 : 0), "t4c_scene_set_enabled");
       if (!act[i])
       {
-        double p[12];
-        toPose12(objects_[i].pose0, p);
-        check(t4c_scene_set_link_pose(scene_, i, p), "t4c_scene_set_link_pose");
+        moved.push_back(i);
+        moved_pose.resize(moved_pose.size() + 12);
+        toPose12(objects_[i].pose0, &moved_pose[moved_pose.size() - 12]);
       }
     }
     if (nl > 0)
       check(t4c_scene_set_active(scene_, act.data()), "t4c_scene_set_active");
+    // static objects that actually moved are refitted into the environment BVH in ONE pass (unchanged poses are
+    // recognised by the library and cost nothing)
+    if (!moved.empty())
+      check(t4c_scene_set_link_poses(scene_, (int32_t)moved.size(), moved.data(), moved_pose.data()),
+            "t4c_scene_set_link_poses");
     std::vector<int32_t> mp;
     std::vector<double> mv;
     for (const auto& kv : margins_.getPairCollisionMargins())

@@ -205,6 +205,27 @@ inline void shapeLocalBox(const t4c_shape& s, const double* vertices, double c[3
   }
 }
 
+// world-frame data of one STATIC shape (FP64, rounded once): pose, bounding sphere, padded box
+inline void staticShapeWorld(const t4c_shape& s, const double* vertices, const double* link_pose, DStaticW& w,
+                             double* pose_d12, float* box_mn, float* box_mx)
+{
+  double c[3], h[3];
+  shapeLocalBox(s, vertices, c, h);
+  const double rad = s.type == T4C_SPHERE ? s.params[0] : std::sqrt(h[0] * h[0] + h[1] * h[1] + h[2] * h[2]);
+  const Xf<double> xw = Xf<double>::from12(link_pose) * Xf<double>::from12(s.pose);
+  xw.to12(pose_d12);
+  Xf<float> xf = xw.cast<float>();
+  xf.to12(w.pose);
+  V3<double> mn, mx;
+  boxAabb(xw, V3<double>(c[0], c[1], c[2]), V3<double>(h[0], h[1], h[2]), mn, mx);
+  const V3<double> cw = xw(V3<double>(c[0], c[1], c[2]));
+  w.bs[0] = (float)cw.x, w.bs[1] = (float)cw.y, w.bs[2] = (float)cw.z;
+  w.bs[3] = roundUp(rad * (1.0 + 1e-6) + 1e-6);
+  const double pad = 1e-6;
+  box_mn[0] = roundDown(mn.x - pad), box_mn[1] = roundDown(mn.y - pad), box_mn[2] = roundDown(mn.z - pad);
+  box_mx[0] = roundUp(mx.x + pad), box_mx[1] = roundUp(mx.y + pad), box_mx[2] = roundUp(mx.z + pad);
+}
+
 inline bool isIdentity12(const double* p)
 {
   static const double I[12] = { 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0 };
@@ -337,20 +358,8 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
       continue;
     }
     // static shape: world pose + bounding data in FP64, rounded once
-    const Xf<double> xw = Xf<double>::from12(L.pose) * Xf<double>::from12(s.pose);
-    DStaticW& w = C.statics[i];
-    xw.to12(&C.statics_d[(size_t)i * 12]);
-    Xf<float> xf = xw.cast<float>();
-    xf.to12(w.pose);
-    V3<double> mn, mx;
-    boxAabb(xw, V3<double>(c[0], c[1], c[2]), V3<double>(h[0], h[1], h[2]), mn, mx);
-    const V3<double> cw = xw(V3<double>(c[0], c[1], c[2]));
-    w.bs[0] = (float)cw.x, w.bs[1] = (float)cw.y, w.bs[2] = (float)cw.z;
-    w.bs[3] = roundUp(rad * (1.0 + 1e-6) + 1e-6);
     LbvhBuilder::Box b;
-    const double pad = 1e-6;
-    b.mn[0] = roundDown(mn.x - pad), b.mn[1] = roundDown(mn.y - pad), b.mn[2] = roundDown(mn.z - pad);
-    b.mx[0] = roundUp(mx.x + pad), b.mx[1] = roundUp(mx.y + pad), b.mx[2] = roundUp(mx.z + pad);
+    staticShapeWorld(s, G.vertices.data(), L.pose, C.statics[i], &C.statics_d[(size_t)i * 12], b.mn, b.mx);
     sbox.push_back(b);
     sshape.push_back(i);
   }
@@ -571,6 +580,60 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
       }
     }
   return true;
+}
+
+// Refit of the environment BVH after static links moved (the topology stays, the boxes follow): recompute the world data
+// of the shapes of the moved links and every node box bottom-up.  Nodes are numbered in pre-order (a parent before its
+// children), so one sweep from the last node to the first sees every child before its parent.  The tree stays correct
+// whatever the motion; it only gets looser when objects travel far from where they were built -- a scene edit that adds
+// or removes shapes rebuilds it (compileScene).
+inline void refitStaticLinks(const HostScene& H, CompiledScene& C, const std::vector<char>& link_moved)
+{
+  const HostGeometry& G = *H.geom;
+  const int ns = (int)G.shapes.size();
+  std::vector<LbvhBuilder::Box> box((size_t)ns);
+  for (int i = 0; i < ns; ++i)
+  {
+    const t4c_shape& s = G.shapes[i];
+    const HostLink& L = H.links[s.link];
+    if (!L.enabled || L.active)
+      continue;
+    if (link_moved[s.link])
+      staticShapeWorld(s, G.vertices.data(), L.pose, C.statics[i], &C.statics_d[(size_t)i * 12], box[i].mn, box[i].mx);
+    else
+    {
+      // unchanged: its box is rebuilt from the stored world pose (cheap and keeps this function free of extra state)
+      DStaticW w;
+      double pd[12];
+      staticShapeWorld(s, G.vertices.data(), L.pose, w, pd, box[i].mn, box[i].mx);
+    }
+  }
+  for (int i = (int)C.bvh.size() - 1; i >= 0; --i)
+  {
+    DBvhNode& n = C.bvh[i];
+    for (int side = 0; side < 2; ++side)
+    {
+      const int child = side ? n.right : n.left;
+      float* mn = side ? n.rmn : n.lmn;
+      float* mx = side ? n.rmx : n.lmx;
+      if (side == 1 && C.bvh.size() == 1 && n.right == n.left)
+        continue;  // one-leaf tree: the right slot is the empty box
+      if (child < 0)
+      {
+        for (int k = 0; k < 3; ++k)
+          mn[k] = box[~child].mn[k], mx[k] = box[~child].mx[k];
+      }
+      else
+      {
+        const DBvhNode& c = C.bvh[child];
+        for (int k = 0; k < 3; ++k)
+        {
+          mn[k] = std::min(c.lmn[k], c.rmn[k]);
+          mx[k] = std::max(c.lmx[k], c.rmx[k]);
+        }
+      }
+    }
+  }
 }
 
 }  // namespace t4

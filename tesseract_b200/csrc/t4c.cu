@@ -584,6 +584,18 @@ static bool bindDevice(const t4c_scene* s)
   return plat::setDevice(s->device);
 }
 
+// upload of a scene image's device buffers (shared by the full build and the refit)
+static bool uploadImage(SceneImage& I, t4stream st)
+{
+  CompiledScene& C = I.comp;
+  return upload(I.d_shapes, C.shapes, st) && upload(I.d_statics, C.statics, st) && upload(I.d_verts, C.verts, st) &&
+         upload(I.d_sup_cells, C.sup_cells, st) && upload(I.d_sup_cand, C.sup_cand, st) && upload(I.d_bvh, C.bvh, st) &&
+         upload(I.d_active, C.active_shapes, st) && upload(I.d_aa, C.aa_pairs, st) && upload(I.d_acm, C.acm_bits, st) &&
+         upload(I.d_margin, C.pair_margin, st) && upload(I.d_shape_d, C.shape_d, st) &&
+         upload(I.d_statics_d, C.statics_d, st) && upload(I.d_link_bvh, C.link_bvh, st) &&
+         upload(I.d_link_root, C.link_root, st) && plat::sync(st);
+}
+
 static t4c_status syncScene(t4c_scene* s)
 {
   if (!bindDevice(s))
@@ -595,16 +607,7 @@ static t4c_status syncScene(t4c_scene* s)
   std::shared_ptr<SceneImage> img = std::make_shared<SceneImage>();
   if (!compileScene(s->host, img->comp, err))
     return fail(T4C_ERR_UNSUPPORTED, "%s", err.c_str());
-  CompiledScene& C = img->comp;
-  SceneImage& I = *img;
-  t4stream st = s->stream;
-  bool ok = upload(I.d_shapes, C.shapes, st) && upload(I.d_statics, C.statics, st) && upload(I.d_verts, C.verts, st) &&
-            upload(I.d_sup_cells, C.sup_cells, st) && upload(I.d_sup_cand, C.sup_cand, st) &&
-            upload(I.d_bvh, C.bvh, st) && upload(I.d_active, C.active_shapes, st) && upload(I.d_aa, C.aa_pairs, st) &&
-            upload(I.d_acm, C.acm_bits, st) && upload(I.d_margin, C.pair_margin, st) &&
-            upload(I.d_shape_d, C.shape_d, st) && upload(I.d_statics_d, C.statics_d, st) &&
-            upload(I.d_link_bvh, C.link_bvh, st) && upload(I.d_link_root, C.link_root, st) && plat::sync(st);
-  if (!ok)
+  if (!uploadImage(*img, s->stream))
     return fail(T4C_ERR_CUDA, "scene upload failed: %s", plat::lastError());
   s->img = img;
   s->uploaded = s->rev;
@@ -1662,15 +1665,22 @@ t4c_status t4c_scene_set_active(t4c_scene* s, const int32_t* flags)
 {
   if (!s || !flags)
     return fail(T4C_ERR_INVALID, "null argument");
+  bool changed = false;
   for (size_t i = 0; i < s->host.links.size(); ++i)
+  {
+    changed = changed || s->host.links[i].active != (flags[i] != 0);
     s->host.links[i].active = flags[i] != 0;
-  ++s->rev;
+  }
+  if (changed)  // an unchanged setting costs nothing: no recompile at the next check
+    ++s->rev;
   return T4C_OK;
 }
 t4c_status t4c_scene_set_enabled(t4c_scene* s, int32_t link, int32_t enabled)
 {
   if (!s || link < 0 || link >= (int)s->host.links.size())
     return fail(T4C_ERR_INVALID, "unknown link %d", link);
+  if (s->host.links[link].enabled == (enabled != 0))
+    return T4C_OK;
   s->host.links[link].enabled = enabled != 0;
   ++s->rev;
   return T4C_OK;
@@ -1679,9 +1689,12 @@ t4c_status t4c_scene_set_acm(t4c_scene* s, int32_t n, const int32_t* pairs)
 {
   if (!s || n < 0 || (n > 0 && !pairs))
     return fail(T4C_ERR_INVALID, "bad argument");
-  s->host.acm.clear();
+  std::unordered_set<uint64_t> acm;
   for (int i = 0; i < n; ++i)
-    s->host.acm.insert(hostPairKey(pairs[2 * i], pairs[2 * i + 1]));
+    acm.insert(hostPairKey(pairs[2 * i], pairs[2 * i + 1]));
+  if (acm == s->host.acm)
+    return T4C_OK;
+  s->host.acm.swap(acm);
   ++s->rev;
   return T4C_OK;
 }
@@ -1689,18 +1702,134 @@ t4c_status t4c_scene_set_margins(t4c_scene* s, double def, int32_t n, const int3
 {
   if (!s || n < 0 || (n > 0 && (!pairs || !values)))
     return fail(T4C_ERR_INVALID, "bad argument");
-  s->host.default_margin = def;
-  s->host.pair_margins.clear();
+  std::unordered_map<uint64_t, double> pm;
   for (int i = 0; i < n; ++i)
-    s->host.pair_margins[hostPairKey(pairs[2 * i], pairs[2 * i + 1])] = values[i];
+    pm[hostPairKey(pairs[2 * i], pairs[2 * i + 1])] = values[i];
+  if (def == s->host.default_margin && pm == s->host.pair_margins)
+    return T4C_OK;
+  s->host.default_margin = def;
+  s->host.pair_margins.swap(pm);
   ++s->rev;
   return T4C_OK;
 }
+t4c_status t4c_scene_set_link_poses(t4c_scene* s, int32_t n, const int32_t* links, const double* poses12)
+{
+  if (!s || n < 0 || (n > 0 && (!links || !poses12)))
+    return fail(T4C_ERR_INVALID, "bad argument");
+  std::vector<char> moved(s->host.links.size(), 0);
+  bool any = false, only_static = true;
+  for (int i = 0; i < n; ++i)
+  {
+    const int link = links[i];
+    if (link < 0 || link >= (int)s->host.links.size())
+      return fail(T4C_ERR_INVALID, "unknown link %d", link);
+    HostLink& L = s->host.links[link];
+    if (std::memcmp(L.pose, poses12 + 12 * (size_t)i, 12 * sizeof(double)) == 0)
+      continue;  // unchanged: nothing to do
+    std::memcpy(L.pose, poses12 + 12 * (size_t)i, 12 * sizeof(double));
+    moved[link] = 1;
+    any = true;
+    only_static = only_static && !L.active && L.enabled;
+  }
+  if (!any)
+    return T4C_OK;
+  if (s->uploaded == s->rev && only_static && bindDevice(s))
+  {
+    // Static objects moved and nothing else changed: REFIT the environment BVH (boxes follow, topology stays) instead of
+    // compiling the scene again.  The image may be shared with clones, so the refit goes into a copy.
+    std::shared_ptr<SceneImage> img = std::make_shared<SceneImage>();
+    img->comp = s->img->comp;
+    refitStaticLinks(s->host, img->comp, moved);
+    if (!uploadImage(*img, s->stream))
+      return fail(T4C_ERR_CUDA, "scene upload failed: %s", plat::lastError());
+    s->img = img;
+    s->uploaded = ++s->rev;
+    return T4C_OK;
+  }
+  ++s->rev;
+  return T4C_OK;
+}
+
 t4c_status t4c_scene_set_link_pose(t4c_scene* s, int32_t link, const double* pose12)
 {
-  if (!s || !pose12 || link < 0 || link >= (int)s->host.links.size())
+  if (!s || !pose12)
+    return fail(T4C_ERR_INVALID, "null argument");
+  return t4c_scene_set_link_poses(s, 1, &link, pose12);
+}
+
+// DiscreteContactManager::addCollisionObject / removeCollisionObject on an existing scene
+// (discrete_contact_manager.h:75-98; the Environment's add / remove link commands end here, environment.cpp:613-640).
+// The geometry may be shared with clones: it is copied before the first edit.  The next check compiles the scene again.
+static HostGeometry& ownGeometry(t4c_scene* s)
+{
+  if (s->host.geom.use_count() > 1)
+    s->host.geom = std::make_shared<HostGeometry>(*s->host.geom);
+  return *s->host.geom;
+}
+
+t4c_status t4c_scene_add_object(t4c_scene* s, const t4c_link* link, int32_t n_shapes, const t4c_shape* shapes,
+                                int32_t n_vertices, const double* vertices, int32_t* link_index)
+{
+  if (!s || !link || n_shapes < 0 || (n_shapes > 0 && !shapes) || n_vertices < 0 || (n_vertices > 0 && !vertices))
+    return fail(T4C_ERR_INVALID, "bad argument");
+  for (int i = 0; i < n_shapes; ++i)
+  {
+    const t4c_shape& sh = shapes[i];
+    const int need = sh.type == T4C_TRIANGLE ? 3 : sh.vertex_count;
+    if (sh.type < T4C_SPHERE || sh.type > T4C_TRIANGLE ||
+        ((sh.type == T4C_HULL || sh.type == T4C_TRIANGLE) && (sh.vertex_offset < 0 || sh.vertex_offset + need > n_vertices)))
+      return fail(T4C_ERR_INVALID, "bad shape record %d", i);
+  }
+  HostGeometry& G = ownGeometry(s);
+  const std::string name = link->name ? link->name : "";
+  int li = -1;
+  for (size_t i = 0; i < s->host.links.size(); ++i)
+    if (!name.empty() && s->host.links[i].name == name)
+      li = (int)i;
+  if (li >= 0)
+  {
+    // re-adding an existing name replaces the object (bullet_discrete_bvh_manager.cpp:113-114)
+    G.shapes.erase(std::remove_if(G.shapes.begin(), G.shapes.end(), [li](const t4c_shape& x) { return x.link == li; }),
+                   G.shapes.end());
+  }
+  else
+  {
+    li = (int)s->host.links.size();
+    s->host.links.emplace_back();
+  }
+  HostLink& L = s->host.links[li];
+  L.name = name;
+  L.type_id = link->type_id;
+  L.enabled = link->enabled != 0;
+  L.active = link->active != 0;
+  std::memcpy(L.pose, link->pose, sizeof(L.pose));
+  const int off = (int)(G.vertices.size() / 3);
+  G.vertices.insert(G.vertices.end(), vertices, vertices + 3 * (size_t)n_vertices);
+  for (int i = 0; i < n_shapes; ++i)
+  {
+    t4c_shape sh = shapes[i];
+    sh.link = li;
+    if (sh.type == T4C_HULL || sh.type == T4C_TRIANGLE)
+      sh.vertex_offset += off;
+    G.shapes.push_back(sh);
+  }
+  if (link_index)
+    *link_index = li;
+  ++s->rev;
+  return T4C_OK;
+}
+
+t4c_status t4c_scene_remove_object(t4c_scene* s, int32_t link)
+{
+  if (!s || link < 0 || link >= (int)s->host.links.size())
     return fail(T4C_ERR_INVALID, "unknown link %d", link);
-  std::memcpy(s->host.links[link].pose, pose12, 12 * sizeof(double));
+  HostGeometry& G = ownGeometry(s);
+  G.shapes.erase(std::remove_if(G.shapes.begin(), G.shapes.end(), [link](const t4c_shape& x) { return x.link == link; }),
+                 G.shapes.end());
+  // link indices of the other objects must not move (contact records and the ACM refer to them): the slot stays,
+  // shapeless and disabled
+  s->host.links[link].enabled = false;
+  s->host.links[link].active = false;
   ++s->rev;
   return T4C_OK;
 }

@@ -212,22 +212,35 @@ def compare(builder, con_g, con_o, hit_g, hit_o, margin_of, per_shape=False, che
             rep["sentinel"] += 1
             continue
         dd = abs(dg - do)
-        if dd > TOL + F32 and link_poses is not None:
-            # device and oracle disagree: let exact geometry decide (ORACLE_OFF_EXACT, see the module comment)
+        dn_pre = float(np.linalg.norm(ng - no)) if abs(do) > 1e-9 else 0.0
+
+        def device_matches_exact():
+            """ORACLE_OFF_EXACT (module comment): True when exact geometry confirms the DEVICE's distance and normal"""
+            if link_poses is None:
+                return False
             import second_opinion as so
             st = k[0] - state_base
-            ca = tester.world_core(k[1], sidg[0], sidg[1], link_poses[st, k[1]])
-            cb = tester.world_core(k[2], sidg[2], sidg[3], link_poses[st, k[2]])
-            assert ca is not None and cb is not None, f"{k}: distance {dg} vs {do} (no exact value for this shape pair)"
+            try:
+                ca = tester.world_core(k[1], sidg[0], sidg[1], link_poses[st, k[1]])
+                cb = tester.world_core(k[2], sidg[2], sidg[3], link_poses[st, k[2]])
+            except KeyError:
+                return False
+            if ca is None or cb is None:
+                return False
             d_exact, n_exact = so.exact_pair(ca[0], cb[0], ca[1], cb[1])
-            assert abs(dg - d_exact) <= TOL + F32, f"{k}: distance {dg} vs oracle {do}, exact {d_exact}"
-            # how far the ORACLE is off is recorded, not bounded: it is not a device tolerance (worst seen: 9 mm for two
-            # interpenetrating flat triangles of a mesh-mesh pair, where GJK / EPA on zero-volume shapes is ill-posed)
-            if n_exact is not None and abs(d_exact) > 1e-9:
-                # exact_pair's normal points from the second shape to the first; the record's from link 0 to link 1
-                assert np.linalg.norm(ng + n_exact) <= 1e-4, f"{k}: normal {ng} vs exact {-n_exact}"
+            if abs(dg - d_exact) > TOL + F32:
+                return False
+            # exact_pair's normal points from the second shape to the first; the record's from link 0 to link 1
+            if n_exact is not None and abs(d_exact) > 1e-9 and np.linalg.norm(ng + n_exact) > 1e-4:
+                return False
             rep["oracle_off_exact"] += 1
             rep["oracle_off_exact_max"] = max(rep["oracle_off_exact_max"], abs(do - d_exact))
+            return True
+
+        if (dd > TOL + F32 or dn_pre > 1e-3) and device_matches_exact():
+            # how far the ORACLE is off is recorded, not bounded: it is not a device tolerance (worst seen: 9 mm for two
+            # interpenetrating flat triangles of a mesh-mesh pair, where GJK / EPA on zero-volume shapes is ill-posed;
+            # sign and normal of a 3 um triangle-triangle contact)
             continue
         assert dd <= TOL + F32, f"{k}: distance {dg} vs {do}"
         rep["max_dd"] = max(rep["max_dd"], dd)
