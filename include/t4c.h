@@ -176,7 +176,8 @@ typedef struct t4c_stats {
   uint64_t phase1_skipped;    /* exact pairs whose boolean GJK outcome was already certified by the cull */
   uint64_t support_vertices_epa;  /* part of support_vertices_fp64 evaluated in the EPA kernel */
   uint64_t phase1_skip_violations; /* T4C_VERIFY_SKIP test hook: certified pairs whose boolean GJK disagreed (must be 0) */
-  uint64_t reserved[1];
+  uint64_t closest_pruned;    /* CLOSEST: cull survivors whose bounds show they cannot be the minimum of their (state,
+                                 link pair) key -- compound links (octomaps, meshes) -- and that skip the exact pass */
 } t4c_stats;
 
 typedef struct t4c_scene t4c_scene;

@@ -60,11 +60,11 @@ class Stats(C.Structure):
                                           "colliding_states", "cull_iterations", "exact_pairs", "phase1_iterations",
                                           "phase2_iterations", "epa_gjk_iterations", "support_vertices",
                                           "support_vertices_fp64", "bvh_stack_overflows", "phase1_skipped",
-                                          "support_vertices_epa", "phase1_skip_violations")] + \
-               [("reserved", C.c_uint64 * 1)]
+                                          "support_vertices_epa", "phase1_skip_violations",
+                                          "closest_pruned")]
 
     def as_dict(self):
-        return {n: int(getattr(self, n)) for n, _ in self._fields_ if n != "reserved"}
+        return {n: int(getattr(self, n)) for n, _ in self._fields_}
 
 
 class Result(C.Structure):

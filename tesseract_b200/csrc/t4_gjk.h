@@ -315,6 +315,7 @@ struct GjkOut
   V3<T> pA;    // witness on core A (WITNESS only)
   int iters;
   bool separated_by_1mm;  // some support plane proved the cores more than 1e-3 apart (a lower bound, not the distance)
+  T lower2;               // best proven lower bound of the core distance, squared (0: none)
   Simplex<T, WITNESS> sx;
 };
 
@@ -338,6 +339,7 @@ T4_HD int gjkDistance(const ShapeW<T>& A, const ShapeW<T>& B, V3<T> axis, bool w
   int status = GJK_SEPARATED;
   int it = 0;
   out.separated_by_1mm = false;
+  out.lower2 = T(0);
   for (; it < max_iter; ++it)
   {
     const V3<T> p = supportW(A, -v, with_margin);
@@ -348,6 +350,8 @@ T4_HD int gjkDistance(const ShapeW<T>& A, const ShapeW<T>& B, V3<T> axis, bool w
     // v.x >= delta for every point x of A - B: the cores are at least delta / |v| apart
     if (delta > T(0) && delta * delta > vv * T(1e-6))
       out.separated_by_1mm = true;
+    if (delta > T(0) && vv > T(0))
+      out.lower2 = t4max(out.lower2, delta * delta / vv);
     if (delta > T(0) && delta * delta > vv * cutoff * cutoff)
     {
       status = GJK_FAR;

@@ -57,6 +57,8 @@ struct CompiledScene
   std::vector<int32_t> aa_pairs;   // [3 * items]: shape, active ordinal of the other link, 1 if the shape's link is the higher one
   std::vector<DBvhNode> link_bvh;  // child trees of all kinematic links, boxes in the link frame
   std::vector<int32_t> link_root;  // [n_alinks] root node in link_bvh, -1: the link has no shapes
+  std::vector<int32_t> link_group; // [n_links] dense id of enabled links with more than one shape (CLOSEST pruning), else -1
+  int n_groups = 0;
   std::vector<uint32_t> acm_bits;
   int acm_words = 0;
   std::vector<double> pair_margin;  // empty: default only
@@ -482,6 +484,17 @@ inline bool compileScene(const HostScene& H, CompiledScene& C, std::string& err)
       if (C.link_alink[b] >= 0)
         C.pair_margin[(size_t)C.link_alink[b] * nl + a] = kv.second;
     }
+  }
+  // ---- links that are compounds of several shapes (octomaps, meshes): the keys CLOSEST pruning works on
+  {
+    std::vector<int> count((size_t)std::max(nl, 1), 0);
+    for (int i = 0; i < ns; ++i)
+      if (H.links[G.shapes[i].link].enabled)
+        ++count[G.shapes[i].link];
+    C.link_group.assign((size_t)std::max(nl, 1), -1);
+    for (int l = 0; l < nl; ++l)
+      if (count[l] > 1)
+        C.link_group[l] = C.n_groups++;
   }
   // ---- child trees of the kinematic links (TesseractCompoundCollisionAlgorithm walks the compound's btDbvt with the
   //      other shape's box, tesseract_compound_collision_algorithm.cpp:323-338; compound x compound is a dual-tree walk,

@@ -148,6 +148,12 @@ struct KParams
   int gjk_budget;         // support pairs a pair may spend in phases 1-2 before it is deferred (0: unlimited)
   int verify_skip;        // test hook: run phase 1 for certified pairs too and count contradictions
   uint8_t* cand_class;    // per candidate: iterations the FP32 cull needed (sort key of the exact queues) or null
+  // CLOSEST pruning for compound links (octomaps, meshes): only the minimum per (state, link pair) is reported, so the
+  // FP32 bounds of the cull decide which pairs of a key can still be that minimum (t4_kernels2.h pruneBody)
+  const int32_t* link_group;  // [n_links] dense id of links with more than one shape, else -1; null: pruning off
+  int32_t n_groups;
+  uint32_t* key_min_ub;       // [n][n_alinks][n_groups] ordered bits of the smallest distance UPPER bound of the key
+  float* cand_lb;             // [cand_cap] distance LOWER bound of every surviving candidate
   uint32_t cand_cap;
   uint32_t cull_base;  // first candidate of the range the cull kernel works on (FIRST in rounds: candidates append)
   uint32_t* surv;      // queue read by the GJK kernel in this launch

@@ -54,6 +54,8 @@ T4_KD bool analyticPair(int ta, int tb)
   return false;
 }
 
+T4_KD uint32_t orderedBits(float f);
+
 T4_KD void pushSurvivor(const KParams& P, uint32_t c, int tier)
 {
   uint32_t* q = tier == 0 ? P.surv_w : (tier == 1 ? P.surv2_w : (tier == 2 ? P.surv3_w : P.surv4_w));
@@ -88,6 +90,8 @@ T4_KD void cullBody(int64_t item, const KParams& P)
   {
     if (P.cand_class)
       P.cand_class[c] = 0;
+    if (P.key_min_ub)
+      P.cand_lb[c] = -1e30f;  // analytic pairs carry no bounds: never pruned
     pushSurvivor(P, (uint32_t)c, first_rec ? 3 : 0);
     return;
   }
@@ -126,6 +130,26 @@ T4_KD void cullBody(int64_t item, const KParams& P)
     P.cand_class[c] = (uint8_t)((g.iters < 63 ? g.iters : 63) | (g.separated_by_1mm ? 0x80 : 0));
   if (st == GJK_SEPARATED && !P.calc_dist)
     return;
+  if (P.key_min_ub)
+  {
+    // distance bounds of this pair from the FP32 iteration: the closest point of the last simplex is a point of A - B
+    // (upper bound of the core distance), the best support plane a lower bound; intersecting cores: both zero
+    const bool sep = st == GJK_SEPARATED || st == GJK_NEAR;
+    const float ub = (sep ? t4sqrt(g.v.len2()) : 0.f) - msum;
+    const float lb = (sep ? t4sqrt(g.lower2) : 0.f) - msum;
+    P.cand_lb[c] = lb;
+    const int grp = P.link_group[P.shapes[b].link];
+    if (grp >= 0)
+    {
+      const size_t slot = ((size_t)s * P.n_alinks + P.shapes[a].alink) * P.n_groups + grp;
+#ifdef T4_DEVICE_BUILD
+      atomicMin(&P.key_min_ub[slot], orderedBits(ub));
+#else
+      if (orderedBits(ub) < P.key_min_ub[slot])
+        P.key_min_ub[slot] = orderedBits(ub);
+#endif
+    }
+  }
   if (P.hit_only)
   {
     // simplex encloses the origin (cores overlap), or |v| <= margins + pair margin - slack: certainly a contact
@@ -157,6 +181,36 @@ T4_KD void cullBody(int64_t item, const KParams& P)
   pushSurvivor(P, (uint32_t)c, 0);
 }
 
+// ContactTestType::CLOSEST keeps ONE record per (state, link pair): the minimum distance (core/common.h:151-157).  When
+// link B is a compound of many shapes (an octomap of a million voxels, a mesh), hundreds of its shapes are inside the
+// margin of a robot link, and all but one of their exact results are thrown away.  item = survivor of the cull: it stays
+// in the exact queue only if its distance LOWER bound does not exceed the smallest UPPER bound seen for its key by more
+// than the slack -- what the exact pass (which may stop up to ~1e-4 above the true distance, t4_bullet.h) and the FP32
+// arithmetic of the bounds can differ by.  The reported minimum is unchanged: the pair the reference would report has
+// lower bound <= its reference distance <= every other pair's reference distance <= that pair's upper bound + 1e-4.
+#define T4_PRUNE_SLACK 5e-4f
+T4_KD float orderedFloat(uint32_t u);
+T4_KD void pruneBody(int64_t i, const KParams& P)
+{
+  const uint32_t c = P.surv[i];
+  const int b = (int)P.cand_b[c];
+  const int grp = P.link_group[P.shapes[b].link];
+  bool keep = true;
+  if (grp >= 0)
+  {
+    const int64_t s = P.cand_state[c];
+    const int a = (int)P.cand_a[c];
+    const size_t slot = ((size_t)s * P.n_alinks + P.shapes[a].alink) * P.n_groups + grp;
+    const uint32_t m = P.key_min_ub[slot];  // 0xffffffff: no pair of this key has published a bound (analytic pairs)
+    keep = m == 0xffffffffu || P.cand_lb[c] <= orderedFloat(m) + T4_PRUNE_SLACK;
+  }
+  if (keep)
+  {
+    const uint32_t k = qAppend(&P.qcount[Q_SURV2]);
+    P.surv2_w[k] = c;  // at most as many as came in
+  }
+}
+
 T4_KD uint32_t orderedBits(float f)
 {
   uint32_t u;
@@ -172,6 +226,21 @@ T4_KD uint32_t orderedBits(float f)
   u = cv.u;
 #endif
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+T4_KD float orderedFloat(uint32_t u)
+{
+  const uint32_t v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+#ifdef T4_DEVICE_BUILD
+  return __uint_as_float(v);
+#else
+  union
+  {
+    float f;
+    uint32_t u;
+  } cv;
+  cv.u = v;
+  return cv.f;
+#endif
 }
 T4_KD unsigned long long orderedBits64(double d)
 {

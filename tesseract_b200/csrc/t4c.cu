@@ -280,6 +280,11 @@ __global__ void __launch_bounds__(256, T4_CULL_MIN_CTAS) cullKernel(KParams P, i
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     cullBody(i, P);
 }
+__global__ void __launch_bounds__(256) pruneKernel(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    pruneBody(i, P);
+}
 void t4LaunchGjk(const KParams& P, int64_t n, int grid, int block, cudaStream_t st);  // t4c_exact.cu (-fmad=false)
 void t4LaunchLvsCount(const LvsParams& L, int64_t n, int grid, cudaStream_t st);
 void t4LaunchLvsExpand(const LvsParams& L, int64_t n, int grid, cudaStream_t st);
@@ -466,6 +471,7 @@ static void launchEpa(const KParams& P, int64_t n, t4stream st)
   profEnd(st);
   ++g_launches;
 }
+static void launchPrune(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(pruneKernel, PK_CULL, 256, 8, P, n, st); }
 static void launchClosestInsert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestInsertKernel, PK_CLOSEST_INSERT, 256, 8, P, n, st); }
 static void launchClosestEmit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestEmitKernel, PK_CLOSEST_EMIT, 256, 8, P, n, st); }
 static void launchCountHit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(countHitKernel, PK_COUNT_HIT, 256, 8, P, n, st); }
@@ -497,6 +503,7 @@ static void launchEpa(const KParams& P, int64_t n, t4stream)
   if (n > 0)
     ++g_launches;
 }
+static void launchPrune(const KParams& P, int64_t n, t4stream) { T4_SERIAL(pruneBody, P, n); }
 static void launchClosestInsert(const KParams& P, int64_t n, t4stream) { T4_SERIAL(closestInsertBody, P, n); }
 static void launchClosestEmit(const KParams& P, int64_t n, t4stream) { T4_SERIAL(closestEmitBody, P, n); }
 static void launchCountHit(const KParams& P, int64_t n, t4stream)
@@ -530,7 +537,7 @@ struct SceneImage
 {
   CompiledScene comp;
   DevBuf d_shapes, d_statics, d_verts, d_sup_cells, d_sup_cand, d_bvh, d_active, d_aa, d_acm, d_margin, d_shape_d, d_statics_d;
-  DevBuf d_link_bvh, d_link_root;
+  DevBuf d_link_bvh, d_link_root, d_link_group;
 };
 
 struct t4c_scene
@@ -552,6 +559,7 @@ struct t4c_scene
   DevBuf d_hit_send, d_shard_out, d_gather_hit, d_gather_out;  // multi-GPU entries (t4_multi.h)
   DevBuf d_traj, d_lvs_counts, d_lvs_offsets, d_lvs_tmp;
   DevBuf d_sort_keys, d_sort_keys2, d_sort_vals, d_sort_idx, d_sort_tmp;
+  DevBuf d_key_min, d_cand_lb;
   uint32_t cand_cap = 0;
   int64_t chunk_hint = 0;  // states per chunk that fitted the device memory (0: the default)
   std::unordered_map<const t4c_fk_model*, std::unique_ptr<FkCache>> fk;
@@ -562,7 +570,7 @@ struct t4c_scene
     DevBuf* bufs[] = { &d_poses0, &d_poses1, &d_poses0d, &d_poses1d, &d_cand_state, &d_cand_a, &d_cand_b, &d_cand_class,
                        &d_long, &d_tasks_long, &d_surv, &d_surv2, &d_surv3, &d_surv4, &d_cull_claim, &d_tasks, &d_hit,
                        &d_claim, &d_raw, &d_raw_local, &d_raw_d64, &d_ht_rep, &d_ht_best, &d_sort_keys, &d_sort_keys2,
-                       &d_sort_vals, &d_sort_idx, &d_sort_tmp };
+                       &d_sort_vals, &d_sort_idx, &d_sort_tmp, &d_key_min, &d_cand_lb };
     for (DevBuf* b : bufs)
       b->reset();
     cand_cap = 0;
@@ -593,7 +601,7 @@ static bool uploadImage(SceneImage& I, t4stream st)
          upload(I.d_active, C.active_shapes, st) && upload(I.d_aa, C.aa_pairs, st) && upload(I.d_acm, C.acm_bits, st) &&
          upload(I.d_margin, C.pair_margin, st) && upload(I.d_shape_d, C.shape_d, st) &&
          upload(I.d_statics_d, C.statics_d, st) && upload(I.d_link_bvh, C.link_bvh, st) &&
-         upload(I.d_link_root, C.link_root, st) && plat::sync(st);
+         upload(I.d_link_root, C.link_root, st) && upload(I.d_link_group, C.link_group, st) && plat::sync(st);
 }
 
 static t4c_status syncScene(t4c_scene* s)
@@ -912,6 +920,7 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
   T4_TRY(plat::zero(P.stats, ST_COUNT * sizeof(unsigned long long), st), "memset");
   unsigned long long stats_host[ST_COUNT];
   std::memset(stats_host, 0, sizeof(stats_host));
+  unsigned long long stats_pruned = 0;  // survivors of the cull that the CLOSEST pruning kept out of the exact pass
   const int na = P.n_alinks;
   int64_t total = 0;
   const size_t qelem = io.q_layout == T4C_Q_F64_ROWMAJOR ? sizeof(double) : sizeof(float);
@@ -1034,6 +1043,18 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
     }
     uint32_t cand_begin = 0, nsurv2 = 0, nsurv3 = 0, nsurv4 = 0;
     uint32_t long_cap_bound = 0, long_done = 0;
+    // CLOSEST against links that are compounds of many shapes: prune the exact queue with the cull's bounds (pruneBody)
+    const int n_groups = s->img->comp.n_groups;
+    const bool prune = closest && n_groups > 0 && (int64_t)na * n_groups <= 4096;
+    P.link_group = nullptr, P.n_groups = 0, P.key_min_ub = nullptr, P.cand_lb = nullptr;
+    if (prune)
+    {
+      const size_t kb = (size_t)nc * (size_t)na * (size_t)n_groups * sizeof(uint32_t);
+      T4_TRY(s->d_key_min.ensure(kb) && plat::fill(s->d_key_min.p, 0xff, kb, st), "pruning table");
+      P.link_group = s->img->d_link_group.as<int32_t>();
+      P.n_groups = n_groups;
+      P.key_min_ub = s->d_key_min.as<uint32_t>();
+    }
     // kernels of the long-pair pass may be running on the auxiliary stream (see launchLongAsync below): they are joined
     // before any queue they read is reallocated, and on EVERY way out of this function
     struct AuxJoin
@@ -1071,6 +1092,14 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
         P.cand_class = s->d_cand_class.as<uint8_t>();
       }
       P.cand_cap = s->cand_cap;
+      if (prune)
+      {
+        if (!(s->d_cand_lb.ensureKeep((size_t)s->cand_cap * sizeof(float), (size_t)cand_begin * sizeof(float), st) &&
+              s->d_surv2.ensure(cb)))
+          return false;
+        P.cand_lb = s->d_cand_lb.as<float>();
+        P.surv2_w = s->d_surv2.as<uint32_t>();
+      }
       P.long_w = nullptr;
       P.long_cap = 0;
       P.task_q = Q_TASK;
@@ -1209,6 +1238,19 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
       cand_begin = ncand;
       const uint32_t nsurv = qc[Q_SURV];
       nsurv2 = qc[Q_SURV2], nsurv3 = qc[Q_SURV3], nsurv4 = qc[Q_SURV4];
+      // ---- CLOSEST pruning: the survivors that can still be the minimum of their key
+      uint32_t* exact_queue = s->d_surv.as<uint32_t>();
+      uint32_t n_exact = nsurv;
+      if (prune && nsurv > 0)
+      {
+        T4_TRY(plat::zero(P.qcount + Q_SURV2, sizeof(uint32_t), st), "memset");
+        P.surv = s->d_surv.as<uint32_t>();
+        launchPrune(P, nsurv, st);
+        T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "prune");
+        exact_queue = s->d_surv2.as<uint32_t>();
+        n_exact = qc[Q_SURV2];
+        stats_pruned += nsurv - n_exact;
+      }
       // ---- FP64 exact pass over the first tier
       if (closest)
       {
@@ -1224,7 +1266,7 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
         }
       }
       // with a long-pair queue the EPA launch waits until the long pairs' GJK has been started beside it
-      rc = exactPass(s->d_surv.as<uint32_t>(), nsurv, round == n_rounds - 1 && !P.long_w);
+      rc = exactPass(exact_queue, n_exact, round == n_rounds - 1 && !P.long_w);
       if (rc != T4C_OK)
         return rc;
       // ---- long pairs of this round: a pair that cycles towards the detector's 1000-iteration caps keeps one lane
@@ -1322,6 +1364,7 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
   io.stats.phase1_skipped = stats_host[ST_P1_SKIPPED];
   io.stats.support_vertices_epa = stats_host[ST_SUPV_EPA];
   io.stats.phase1_skip_violations = stats_host[ST_P1_VIOLATIONS];
+  io.stats.closest_pruned = stats_pruned;
   if (stats_host[ST_BVH_OVERFLOW])
     return fail(T4C_ERR_UNSUPPORTED, "environment BVH traversal overflowed its stack %llu times: results incomplete",
                 stats_host[ST_BVH_OVERFLOW]);

@@ -65,3 +65,25 @@ def test_closest_vs_first_and_all(setup):
     assert len(con_c) == len(kc), "CLOSEST must hold one record per key"
     assert np.array_equal(kc, ka)
     assert np.array_equal(dc, da)
+
+
+def test_phase1_certificate_never_contradicted():
+    """The exact pass skips its boolean GJK (phase 1) for pairs the FP32 cull certified as more than 1 mm apart.  Under
+    the T4C_VERIFY_SKIP hook the phase runs anyway and every certified pair whose boolean GJK says "intersect" is
+    counted: 1 Mi states of configs[1] in FIRST and 256 Ki in CLOSEST mode, zero contradictions allowed."""
+    import subprocess, sys
+    code = ("import numpy as np; from tesseract_b200 import capi, scene as S; "
+            "from tesseract_b200.managers import BatchChecker; "
+            "b = S.build_config2(n_prims=10000, margin=0.05); bc = BatchChecker(b); "
+            "q = S.random_states(b, 1 << 20, seed=1234, dtype=np.float64); "
+            "h, c, st = bc.check_discrete(q, capi.TEST_FIRST, capacity=1 << 20); "
+            "print('FIRST', st['phase1_skipped'], st['phase1_skip_violations']); "
+            "assert st['phase1_skipped'] > 100000 and st['phase1_skip_violations'] == 0, st; "
+            "h, c, st = bc.check_discrete(q[:1 << 18], capi.TEST_CLOSEST); "
+            "print('CLOSEST', st['phase1_skipped'], st['phase1_skip_violations']); "
+            "assert st['phase1_skipped'] > 100000 and st['phase1_skip_violations'] == 0, st")
+    env = dict(os.environ, T4C_VERIFY_SKIP="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=1200)
+    print(r.stdout[-1000:])
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]

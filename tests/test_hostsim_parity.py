@@ -111,3 +111,18 @@ def test_chunked_batches_with_rounds():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+def test_phase1_certificate_never_contradicted():
+    """T4C_VERIFY_SKIP: phase 1 runs for certified pairs too and contradictions are counted (see test_gpu_fullsize)"""
+    import subprocess, sys, os
+    code = ("import sys; sys.path.insert(0, 'tests'); import numpy as np; from hostsim import build as h; "
+            "from tesseract_b200 import capi, scene as S; from tesseract_b200.managers import BatchChecker; "
+            "b = S.build_config2(n_prims=10000, margin=0.05); bc = BatchChecker(b, lib=h.lib()); "
+            "q = S.random_states(b, 1500, seed=5, dtype=np.float64); "
+            "hh, c, st = bc.check_discrete(q, capi.TEST_CLOSEST); print(st['phase1_skipped'], st['phase1_skip_violations']); "
+            "assert st['phase1_skipped'] > 1000 and st['phase1_skip_violations'] == 0, st")
+    env = dict(os.environ, T4C_VERIFY_SKIP="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout + r.stderr
