@@ -34,16 +34,17 @@ ManagerCore::~ManagerCore()
 // (tesseract_environment/src/core/environment.cpp:482-488), so a clone must be cheap: when this manager's device scene
 // is built, the clone takes a reference to the same compiled image (t4c_scene_clone: no compile, no upload); otherwise
 // its scene is built on its first query.
-std::unique_ptr<ManagerCore> ManagerCore::clone() const
+std::unique_ptr<ManagerCore> ManagerCore::clone(int device) const
 {
-  std::unique_ptr<ManagerCore> c(new ManagerCore(cast_, device_));
+  const bool same = device < 0 || device == device_;
+  std::unique_ptr<ManagerCore> c(new ManagerCore(cast_, same ? device_ : device));
   c->objects_ = objects_;
   c->names_ = names_;
   c->index_ = index_;
   c->active_ = active_;
   c->margins_ = margins_;
   c->fn_ = fn_;
-  if (scene_ && !dirty_structure_ && t4c_scene_clone(scene_, &c->scene_) == T4C_OK)
+  if (same && scene_ && !dirty_structure_ && t4c_scene_clone(scene_, &c->scene_) == T4C_OK)
   {
     c->dirty_structure_ = false;
     c->dirty_soft_ = true;  // settings are compared by the library: unchanged ones cost nothing

@@ -36,7 +36,9 @@ public:
   ~ManagerCore();
   ManagerCore(const ManagerCore&) = delete;
   ManagerCore& operator=(const ManagerCore&) = delete;
-  std::unique_ptr<ManagerCore> clone() const;
+  // device < 0: same device, sharing the compiled scene image; otherwise a replica of this manager on that device
+  std::unique_ptr<ManagerCore> clone(int device = -1) const;
+  int device() const { return device_; }
 
   bool addCollisionObject(const std::string& name, int mask_id, const CollisionShapesConst& shapes,
                           const tesseract_common::VectorIsometry3d& shape_poses, bool enabled);

@@ -241,4 +241,99 @@ void isValid(std::vector<uint8_t>& valid, B200DiscreteManager& manager, const B2
   for (int64_t i = 0; i < n; ++i)
     valid[(size_t)i] = hit[(size_t)i] ? 0 : 1;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// several GPUs
+// ---------------------------------------------------------------------------------------------------------------
+B200MultiDeviceChecker::B200MultiDeviceChecker(B200DiscreteManager& manager, const std::vector<int>& devices)
+{
+  if (devices.empty())
+    throw std::runtime_error("B200MultiDeviceChecker: empty device list");
+  for (int d : devices)
+    cores_.push_back(manager.core().clone(d));
+  std::vector<int32_t> devs(devices.begin(), devices.end());
+  comms_.assign(devices.size(), nullptr);
+  if (t4c_comm_create_local(devs.data(), (int32_t)devs.size(), comms_.data()) != T4C_OK)
+    throw std::runtime_error(std::string("tesseract_b200: t4c_comm_create_local: ") + t4c_last_error());
+}
+
+B200MultiDeviceChecker::~B200MultiDeviceChecker()
+{
+  for (t4c_comm* c : comms_)
+    t4c_comm_destroy(c);
+}
+
+void B200MultiDeviceChecker::checkStates(const B200StateSolver& state_solver, const std::vector<std::string>& joint_names,
+                                         const TrajArray& states, const tesseract_collision::ContactRequest& request,
+                                         std::vector<uint8_t>& hit, std::vector<t4c_contact>& contacts)
+{
+  if (states.cols() != (long)joint_names.size())
+    throw std::runtime_error("checkStates: states have " + std::to_string(states.cols()) + " columns for " +
+                             std::to_string(joint_names.size()) + " joint names");
+  const int64_t n = states.rows();
+  hit.assign((size_t)n, 0);
+  contacts.clear();
+  if (n == 0)
+    return;
+  // the joint table does not depend on the device: one FK model, built against the first replica
+  const t4c_fk_model* model = state_solver.model(*cores_[0], joint_names);
+  std::vector<t4c_scene*> scenes;
+  for (auto& c : cores_)
+    scenes.push_back(c->scene());
+  t4c_request rq;
+  rq.type = request.type == tesseract_collision::ContactTestType::FIRST ?
+                T4C_TEST_FIRST :
+                (request.type == tesseract_collision::ContactTestType::CLOSEST ? T4C_TEST_CLOSEST : T4C_TEST_ALL);
+  rq.calculate_penetration = request.calculate_penetration ? 1 : 0;
+  rq.calculate_distance = request.calculate_distance ? 1 : 0;
+  int64_t cap = std::max<int64_t>(256, 4 * n);
+  for (;;)
+  {
+    contacts.resize((size_t)cap);
+    t4c_result r;
+    std::memset(&r, 0, sizeof(r));
+    r.hit = hit.data();
+    r.contacts = contacts.data();
+    r.capacity = cap;
+    const t4c_status st = t4c_check_discrete_multi(scenes.data(), model, comms_.data(), (int32_t)scenes.size(),
+                                                   states.data(), n, &rq, &r);
+    stats_ = r.stats;
+    if (st == T4C_ERR_CAPACITY)
+    {
+      cap = r.n_contacts;
+      continue;
+    }
+    if (st != T4C_OK)
+      throw std::runtime_error(std::string("tesseract_b200: t4c_check_discrete_multi: ") + t4c_last_error());
+    contacts.resize((size_t)r.n_contacts);
+    return;
+  }
+}
+
+void B200MultiDeviceChecker::isValid(std::vector<uint8_t>& valid, const B200StateSolver& state_solver,
+                                     const std::vector<std::string>& joint_names, const TrajArray& states)
+{
+  const int64_t n = states.rows();
+  valid.assign((size_t)n, 1);
+  if (n == 0)
+    return;
+  const t4c_fk_model* model = state_solver.model(*cores_[0], joint_names);
+  std::vector<t4c_scene*> scenes;
+  for (auto& c : cores_)
+    scenes.push_back(c->scene());
+  t4c_request rq;
+  rq.type = T4C_TEST_FIRST;
+  rq.calculate_penetration = 1;
+  rq.calculate_distance = 1;
+  std::vector<uint8_t> hit((size_t)n, 0);
+  t4c_result r;
+  std::memset(&r, 0, sizeof(r));
+  r.hit = hit.data();
+  if (t4c_check_discrete_multi(scenes.data(), model, comms_.data(), (int32_t)scenes.size(), states.data(), n, &rq, &r) !=
+      T4C_OK)
+    throw std::runtime_error(std::string("tesseract_b200: t4c_check_discrete_multi: ") + t4c_last_error());
+  stats_ = r.stats;
+  for (int64_t i = 0; i < n; ++i)
+    valid[(size_t)i] = hit[(size_t)i] ? 0 : 1;
+}
 }  // namespace tesseract_b200

@@ -91,5 +91,35 @@ std::vector<uint8_t> checkTrajectories(std::vector<std::vector<tesseract_collisi
 // the manager); flags only, no contact records leave the device
 void isValid(std::vector<uint8_t>& valid, B200DiscreteManager& manager, const B200StateSolver& state_solver,
              const std::vector<std::string>& joint_names, const TrajArray& states);
+
+// The same validators over SEVERAL GPUs of one box: the manager is replicated on every device (the
+// reference's "one clone per thread", discrete_contact_manager.h:59-65, with a device per clone), a batch is cut into
+// contiguous shards, and flags + contact records + counters come back to the first device in one grouped NCCL exchange
+// (t4c_check_discrete_multi, include/t4c.h).
+class B200MultiDeviceChecker
+{
+public:
+  // devices: CUDA device indices, devices[0] receives the gathered results.  The manager's current objects, transforms
+  // of static links, active set, margins and ACM function are copied; later changes of `manager` are not followed.
+  B200MultiDeviceChecker(B200DiscreteManager& manager, const std::vector<int>& devices);
+  ~B200MultiDeviceChecker();
+  B200MultiDeviceChecker(const B200MultiDeviceChecker&) = delete;
+  B200MultiDeviceChecker& operator=(const B200MultiDeviceChecker&) = delete;
+
+  // isValid() over all devices
+  void isValid(std::vector<uint8_t>& valid, const B200StateSolver& state_solver,
+               const std::vector<std::string>& joint_names, const TrajArray& states);
+  // per-state flags and raw records (t4c_contact::state = row of `states`) of a discrete check over all devices
+  void checkStates(const B200StateSolver& state_solver, const std::vector<std::string>& joint_names,
+                   const TrajArray& states, const tesseract_collision::ContactRequest& request,
+                   std::vector<uint8_t>& hit, std::vector<t4c_contact>& contacts);
+  const t4c_stats& lastStats() const { return stats_; }
+  int devices() const { return (int)cores_.size(); }
+
+private:
+  std::vector<std::unique_ptr<ManagerCore>> cores_;
+  std::vector<t4c_comm*> comms_;
+  t4c_stats stats_{};
+};
 }  // namespace tesseract_b200
 #endif

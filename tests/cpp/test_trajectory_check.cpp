@@ -398,6 +398,34 @@ static void discreteOnly()
       n_invalid += m.empty() ? 0 : 1;
     }
     EXPECT_TRUE(n_invalid > 3 && n_invalid < 64);
+    // the same batch over every GPU of the box (contiguous shards, one NCCL gather to the first device): identical
+    // flags, and the gathered records carry global state indices.  Needs two devices: skipped elsewhere.
+    if (t4c_device_count() >= 2)
+    {
+      std::vector<int> devs;
+      for (int d = 0; d < std::min(t4c_device_count(), 4); ++d)
+        devs.push_back(d);
+      B200MultiDeviceChecker multi(batched, devs);
+      const tesseract_common::TrajArray many = sweep(1001, 1);
+      std::vector<uint8_t> v1, vm;
+      isValid(v1, batched, solver, names, many);
+      multi.isValid(vm, solver, names, many);
+      EXPECT_TRUE(v1 == vm);
+      std::vector<uint8_t> hit;
+      std::vector<t4c_contact> recs;
+      multi.checkStates(solver, names, many, ContactRequest(ContactTestType::FIRST), hit, recs);
+      size_t colliding = 0;
+      for (size_t r = 0; r < hit.size(); ++r)
+      {
+        EXPECT_TRUE((hit[r] != 0) == (v1[r] == 0));
+        colliding += hit[r] ? 1 : 0;
+      }
+      EXPECT_TRUE(recs.size() == colliding);
+      for (const t4c_contact& c : recs)
+        EXPECT_TRUE(c.state >= 0 && c.state < 1001 && hit[(size_t)c.state]);
+      EXPECT_TRUE(multi.lastStats().states == 1001);
+      std::printf("multi-device validator: %d devices, %zu of 1001 states colliding\n", multi.devices(), colliding);
+    }
   }
   {
     // a commanded subset: the other joints stay at zero (StateSolver::getState(joint_names, values))

@@ -11,6 +11,9 @@ ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpuru
     python bench.py --steps 1 --warmup 1 --no-secondary --no-cpu-baseline > gpurun_out/ncu_launch.log 2>&1
 echo "ncu list exit $?"
 ncu --set full --clock-control none --import-source on -k regex:"gjkKernelR128|epaKernelR128|cullKernel|broadStaticKernel|fkKernelT|pruneKernel|broadActiveKernel" \
-    -s 26 -c 30 -o gpurun_out/prof python bench.py --steps 1 --warmup 1 --no-secondary --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
+    -s 26 -c 30 -f -o gpurun_out/prof python bench.py --steps 1 --warmup 1 --no-secondary --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
 echo "ncu full exit $?"
-ls -la gpurun_out/*.ncu-rep
+# the report itself is too large to travel back (64 MiB limit on gpurun_out/): keep its raw page as CSV
+ncu -i gpurun_out/prof.ncu-rep --page raw --csv > gpurun_out/full_raw.csv 2> gpurun_out/ncu_export.err
+ls -la gpurun_out/prof.ncu-rep gpurun_out/full_raw.csv
+rm -f gpurun_out/prof.ncu-rep
