@@ -77,6 +77,9 @@ struct alignas(16) DJoint
   double axis[3];  // normalised
   int32_t type, parent_joint, q_index, pad;
   double pre[12];  // world pose of the parent link when parent_joint < 0
+  int32_t alink;   // active-link ordinal whose pose this joint's frame is, or -1
+  int32_t keep;    // 1: a joint other than the next one has this joint as its parent (tree branch): keep the frame
+  int32_t pad2[2];
 };
 
 // one pair handed from the GJK kernel (phases 1-2) to the EPA kernel (phases 3-4)
@@ -336,6 +339,31 @@ T4_KD double loadQ(const KParams& P, const void* q, int64_t s, int j)
   if (P.q_layout == T4C_Q_F64_ROWMAJOR)
     return ((const double*)q)[(size_t)s * P.n_q + j];
   return (double)((const float*)q)[(size_t)s * P.n_q + j];
+}
+
+// frame of joint j relative to its parent: T_origin * motion(q_j)
+T4_KD Xf<double> fkLocal(const KParams& P, const DJoint& J, const void* q, int64_t s)
+{
+  Xf<double> local = Xf<double>::from12(J.origin);
+  if (J.type == T4C_JOINT_REVOLUTE)
+  {
+    const double a = loadQ(P, q, s, J.q_index);
+    const double sn = t4sin(a), cs = t4cos(a);
+    const double t = 1.0 - cs, x = J.axis[0], y = J.axis[1], z = J.axis[2];
+    Xf<double> rot;
+    rot.r[0] = t * x * x + cs, rot.r[1] = t * x * y - sn * z, rot.r[2] = t * x * z + sn * y;
+    rot.r[3] = t * x * y + sn * z, rot.r[4] = t * y * y + cs, rot.r[5] = t * y * z - sn * x;
+    rot.r[6] = t * x * z - sn * y, rot.r[7] = t * y * z + sn * x, rot.r[8] = t * z * z + cs;
+    local = local * rot;
+  }
+  else if (J.type == T4C_JOINT_PRISMATIC)
+  {
+    const double a = loadQ(P, q, s, J.q_index);
+    Xf<double> tr;
+    tr.p = V3<double>(J.axis[0] * a, J.axis[1] * a, J.axis[2] * a);
+    local = local * tr;
+  }
+  return local;
 }
 
 T4_KD void fkOne(const KParams& P, const void* q, int64_t s, Xf<double>* Tj)

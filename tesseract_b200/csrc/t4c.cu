@@ -689,7 +689,13 @@ static t4c_status syncFk(t4c_scene* s, const t4c_fk_model* m, FkCache** out)
     static const double I12[12] = { 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0 };
     std::memcpy(D.pre, J.parent_link < nl ? s->host.links[J.parent_link].pose : I12, sizeof(D.pre));
     child_joint[J.child_link] = j;
+    D.alink = (J.child_link < (int)s->img->comp.link_alink.size()) ? s->img->comp.link_alink[J.child_link] : -1;
+    D.keep = 0;
   }
+  // a frame has to outlive the next joint only when a LATER joint hangs on it (tree branch): serial chains keep nothing
+  for (int j = 0; j < nj; ++j)
+    if (dj[j].parent_joint >= 0 && dj[j].parent_joint != j - 1)
+      dj[dj[j].parent_joint].keep = 1;
   const CompiledScene& C = s->img->comp;
   std::vector<int32_t> aj(std::max<size_t>(C.alinks.size(), 1), -1);
   std::vector<double> as(std::max<size_t>(C.alinks.size(), 1) * 12, 0.0);
@@ -1467,8 +1473,11 @@ static t4c_status hostRun(t4c_scene* s, BatchIO& io, const double* hq0, const do
   r->stats = io.stats;
   if (rc != T4C_OK && rc != T4C_ERR_CAPACITY)
   {
-    if (io.host_copied > 0)
-      plat::sync(s->copy_stream);  // nothing may still be writing into the caller's buffer after the return
+    // nothing may still be reading from or writing into the caller's buffers after the return: the progressive record
+    // download AND the piecewise q upload both run on the copy stream
+    if ((io.host_copied > 0 || io.q_pieces > 0) && s->copy_stream)
+      plat::sync(s->copy_stream);
+    plat::sync(st);
     return rc;
   }
   const int64_t ncopy = std::min<int64_t>(io.n_contacts, r->capacity);

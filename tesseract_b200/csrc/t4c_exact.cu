@@ -47,7 +47,6 @@ __global__ void __launch_bounds__(128) fkKernelT(KParams P, int64_t first, int64
   __shared__ double stage[4][32 * STRIDE];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double* sm = stage[warp];
-  Xf<double> Tj[MAXJ];
   for (int64_t base = blockIdx.x * (int64_t)blockDim.x; base < n; base += (int64_t)gridDim.x * blockDim.x)
   {
     const int64_t i = base + threadIdx.x;
@@ -57,6 +56,7 @@ __global__ void __launch_bounds__(128) fkKernelT(KParams P, int64_t first, int64
     {
       if (valid)
       {
+        Xf<double> Tj[MAXJ];
         fkOne(P, P.q0, s, Tj);
         fkStoreAllLinks(P, Tj, s);
       }
@@ -64,42 +64,68 @@ __global__ void __launch_bounds__(128) fkKernelT(KParams P, int64_t first, int64
     }
     const int64_t s0 = first + base + warp * 32;                     // first state of this warp
     const int cnt = (int)t4min<int64_t>(32, n - (base + warp * 32));  // states of this warp inside the range
+    // the warp writes the 32 poses of one link as one contiguous run of full 128-bit lanes
+    auto writeLink = [&](int a, const Xf<double>& x, float* dst, double* dstd) {
+      if (valid)
+      {
+        double* r = sm + lane * STRIDE;
+        r[0] = x.r[0], r[1] = x.r[1], r[2] = x.r[2], r[3] = x.p.x;
+        r[4] = x.r[3], r[5] = x.r[4], r[6] = x.r[5], r[7] = x.p.y;
+        r[8] = x.r[6], r[9] = x.r[7], r[10] = x.r[8], r[11] = x.p.z;
+      }
+      __syncwarp();
+      if (cnt > 0)
+      {
+        const size_t off = poseOffset(P, s0, a);  // 96 B (48 B) per state: 16-byte aligned for any s0
+        double2* o64 = reinterpret_cast<double2*>(dstd + off);
+        for (int e = lane; e < cnt * 6; e += 32)  // 6 x 128 bit per FP64 record
+        {
+          const int st = e / 6, k = (e - st * 6) * 2;
+          o64[e] = make_double2(sm[st * STRIDE + k], sm[st * STRIDE + k + 1]);
+        }
+        float4* o32 = reinterpret_cast<float4*>(dst + off);
+        for (int e = lane; e < cnt * 3; e += 32)  // 3 x 128 bit per FP32 record
+        {
+          const int st = e / 3, k = (e - st * 3) * 4;
+          const double* r = sm + st * STRIDE + k;
+          o32[e] = make_float4((float)r[0], (float)r[1], (float)r[2], (float)r[3]);
+        }
+      }
+      __syncwarp();
+    };
     for (int pass = 0; pass < (P.cast ? 2 : 1); ++pass)
     {
-      if (valid)
-        fkOne(P, pass ? P.q1 : P.q0, s, Tj);
+      const void* q = pass ? P.q1 : P.q0;
       float* dst = pass ? P.poses1 : P.poses0;
       double* dstd = pass ? P.poses1d : P.poses0d;
-      for (int a = 0; a < P.n_alinks; ++a)
+      // Joint frames are consumed as they are produced: the frame of joint j is the pose of the link it drives and the
+      // parent of joint j + 1.  Only frames that a LATER joint hangs on (tree branches, DJoint::keep) go to the
+      // thread-local array -- for a serial arm nothing does.  Round 1 kept all MAXJ frames in local memory: 1.5 KB per
+      // state written and read back through L2, three times the traffic of the poses themselves (ncu r3e: 0.85 GB of
+      // DRAM writes per 256 Ki states for 0.26 GB of poses).
+      Xf<double> kept[MAXJ];
+      Xf<double> prev;
+      for (int j = 0; j < P.n_joints; ++j)  // uniform across the warp: the joint table is the same for every state
       {
+        const DJoint& J = P.joints[j];
+        Xf<double> cur;
         if (valid)
         {
-          const Xf<double> x = fkAlinkPose(P, Tj, a);
-          double* r = sm + lane * STRIDE;
-          r[0] = x.r[0], r[1] = x.r[1], r[2] = x.r[2], r[3] = x.p.x;
-          r[4] = x.r[3], r[5] = x.r[4], r[6] = x.r[5], r[7] = x.p.y;
-          r[8] = x.r[6], r[9] = x.r[7], r[10] = x.r[8], r[11] = x.p.z;
+          const Xf<double> local = fkLocal(P, J, q, s);
+          const Xf<double> parent = J.parent_joint < 0 ? Xf<double>::from12(J.pre) :
+                                                         (J.parent_joint == j - 1 ? prev : kept[J.parent_joint]);
+          cur = parent * local;
+          if (J.keep)
+            kept[j] = cur;
+          prev = cur;
         }
-        __syncwarp();
-        if (cnt > 0)
-        {
-          const size_t off = poseOffset(P, s0, a);  // 96 B (48 B) per state: 16-byte aligned for any s0
-          double2* o64 = reinterpret_cast<double2*>(dstd + off);
-          for (int e = lane; e < cnt * 6; e += 32)  // 6 x 128 bit per FP64 record
-          {
-            const int st = e / 6, k = (e - st * 6) * 2;
-            o64[e] = make_double2(sm[st * STRIDE + k], sm[st * STRIDE + k + 1]);
-          }
-          float4* o32 = reinterpret_cast<float4*>(dst + off);
-          for (int e = lane; e < cnt * 3; e += 32)  // 3 x 128 bit per FP32 record
-          {
-            const int st = e / 3, k = (e - st * 3) * 4;
-            const double* r = sm + st * STRIDE + k;
-            o32[e] = make_float4((float)r[0], (float)r[1], (float)r[2], (float)r[3]);
-          }
-        }
-        __syncwarp();
+        if (J.alink >= 0)
+          writeLink(J.alink, cur, dst, dstd);
       }
+      // kinematic links that no joint of the model drives keep their scene pose
+      for (int a = 0; a < P.n_alinks; ++a)
+        if (P.alink_joint[a] < 0)
+          writeLink(a, Xf<double>::from12(P.alink_static + (size_t)a * 12), dst, dstd);
     }
   }
 }
