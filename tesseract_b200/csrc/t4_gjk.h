@@ -324,12 +324,17 @@ struct GjkOut
  *          (tesseract_gjk_pair_detector.cpp:855-861, exit code 10; here with the true |v| instead of the running
  *          squared distance so that it can already fire on the first support)
  * accept : (cull mode, accept >= 0) stop with GJK_NEAR once |v| <= accept -- the pair is certainly within range
+ * certify: (with accept) a pair that is within range keeps iterating, for at most `certify` more support pairs, until a
+ *          support plane shows that the cores are more than 1 mm apart (out.separated_by_1mm), the simplex encloses
+ *          the origin (GJK_INTERSECT) or the iteration converges: |v| <= accept is an UPPER bound of the distance, it
+ *          does not tell a pair with separated cores (phases 1-2 of the detector) from a penetrating one (EPA)
  */
 template <class T, bool WITNESS>
 T4_HD int gjkDistance(const ShapeW<T>& A, const ShapeW<T>& B, V3<T> axis, bool with_margin, T cutoff, T accept,
-                      GjkOut<T, WITNESS>& out, int max_iter)
+                      GjkOut<T, WITNESS>& out, int max_iter, int certify = 0)
 {
   Simplex<T, WITNESS>& sx = out.sx;
+  bool near = false;
   sx.reset();
   V3<T> v = axis;
   if (v.len2() < Eps<T>::eps())
@@ -352,6 +357,8 @@ T4_HD int gjkDistance(const ShapeW<T>& A, const ShapeW<T>& B, V3<T> axis, bool w
       out.separated_by_1mm = true;
     if (delta > T(0) && vv > T(0))
       out.lower2 = t4max(out.lower2, delta * delta / vv);
+    if (near && (out.separated_by_1mm || --certify < 0))
+      break;
     if (delta > T(0) && delta * delta > vv * cutoff * cutoff)
     {
       status = GJK_FAR;
@@ -402,10 +409,16 @@ T4_HD int gjkDistance(const ShapeW<T>& A, const ShapeW<T>& B, V3<T> axis, bool w
     have_v = true;
     if (accept >= T(0) && sqd <= accept * accept)
     {
-      status = GJK_NEAR;
-      break;
+      near = true;
+      if (certify <= 0 || out.separated_by_1mm)
+      {
+        status = GJK_NEAR;
+        break;
+      }
     }
   }
+  if (near && status == GJK_SEPARATED)
+    status = GJK_NEAR;  // within range whatever else the extra iterations found out
   out.v = v;
   out.iters = it + 1;
   if (WITNESS && (status == GJK_SEPARATED))

@@ -118,7 +118,9 @@ T4_KD void cullBody(int64_t item, const KParams& P)
   if (!P.calc_dist)
     accept = -1.f;  // separated cores are never reported (tesseract_gjk_pair_detector.cpp:830-834)
   GjkOut<float, false> g;
-  const int st = gjkDistance<float, false>(A, B, axis0, false, cutoff, accept, g, 48);
+  // FIRST with records: a pair that is certainly within range iterates on (a few support pairs at most) until it is
+  // also known whether its cores are apart -- the difference between one cheap GJK and an EPA run in the exact pass
+  const int st = gjkDistance<float, false>(A, B, axis0, false, cutoff, accept, g, 48, (first_rec && bool_mode) ? 8 : 0);
   statAdd(P.stats, ST_GJK_PAIRS, 1);
   statAdd(P.stats, ST_CULL_ITERS, (uint32_t)g.iters);
   statAdd(P.stats, ST_SUPV, A.evals + B.evals);
@@ -161,11 +163,12 @@ T4_KD void cullBody(int64_t item, const KParams& P)
   }
   if (first_rec)
   {
-    // tier 0: one certainly-in-contact, separated pair per state (GJK only); tiers 1 / 2: one certainly penetrating
+    // tier 0: one pair per state that is certainly in contact AND whose cores are certainly apart (phase 2 of the
+    // detector only: no EPA, phase 1 skipped under the same certificate); tiers 1 / 2: one certainly penetrating
     // pair per state (needs EPA; only looked at when the earlier tiers left the state without a contact) -- against a
     // flat-faced or point-core shape (median 7 EPA iterations) before one against a cylinder / cone (15-75 iterations:
     // the polytope has to approximate the curved surface); tier 3: the rest.
-    const bool certain = st == GJK_NEAR && bool_mode && g.v.len2() > 1e-8f;
+    const bool certain = st == GJK_NEAR && bool_mode && g.separated_by_1mm;
     const bool deep = st == GJK_INTERSECT && g.v.len2() == 0.f && P.calc_pen;
     const bool curved = A.curvedCore() || B.curvedCore();
     int tier = 3;

@@ -783,6 +783,7 @@ struct Tuning
   int64_t upload_piece_min = 65536;  // T4C_UPLOAD_PIECE_MIN: states per piece of the piecewise q upload
   int max_rounds = 8;
   int verify_skip = 0;               // T4C_VERIFY_SKIP: run phase 1 for certified pairs too, count contradictions
+  int trace = 0;                     // T4C_TRACE_PASSES: queue sizes of every exact pass on stderr
   Tuning()
   {
     auto env = [](const char* name, long long dflt, long long lo) {
@@ -795,6 +796,7 @@ struct Tuning
     drain_min = env("T4C_DRAIN_MIN", drain_min, 1);
     upload_piece_min = env("T4C_UPLOAD_PIECE_MIN", upload_piece_min, 1);
     verify_skip = (int)env("T4C_VERIFY_SKIP", 0, 0);
+    trace = (int)env("T4C_TRACE_PASSES", 0, 0);
   }
 };
 static const Tuning& tuning()
@@ -1181,6 +1183,9 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
           P.surv = const_cast<uint32_t*>(sorted);
         launchGjk(P, nq, st);
         T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (GJK)");
+        if (tuning().trace)
+          std::fprintf(stderr, "[t4c] exact pass: %u pairs, EPA tasks %u -> %u, long %u, records %u\n", nq, ntask_pending,
+                       std::min(qc[Q_TASK], P.task_cap), qc[Q_LONG], qc[Q_RAW]);
         ntask_pending = std::min(qc[Q_TASK], P.task_cap);
       }
       if (run_epa && ntask_pending > 0)
@@ -1283,14 +1288,18 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
       if (rc != T4C_OK)
         return rc;
     }
-    // ---- deferred tiers, for the states that are still without a contact
-    rc = exactPass(s->d_surv2.as<uint32_t>(), nsurv2, true);
+    // ---- deferred tiers, for the states that are still without a contact (no pair of theirs is certainly in contact
+    //      with its cores certainly apart): the rest first -- a pair that turns out to be separated and within the
+    //      margin settles the state without EPA -- then the certainly penetrating ones.  Their EPA tasks share ONE
+    //      launch at the end (longPass below): a launch of a few thousand tasks lasts as long as its slowest task
+    //      (~1 ms against a cylinder), and tasks of states that were settled meanwhile leave at once.
+    rc = exactPass(s->d_surv4.as<uint32_t>(), nsurv4, false);
     if (rc != T4C_OK)
       return rc;
-    rc = exactPass(s->d_surv3.as<uint32_t>(), nsurv3, true);
+    rc = exactPass(s->d_surv2.as<uint32_t>(), nsurv2, false);
     if (rc != T4C_OK)
       return rc;
-    rc = exactPass(s->d_surv4.as<uint32_t>(), nsurv4, true);
+    rc = exactPass(s->d_surv3.as<uint32_t>(), nsurv3, false);
     if (rc != T4C_OK)
       return rc;
     if (n_long_async > 0)
