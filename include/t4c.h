@@ -238,6 +238,18 @@ void t4c_fk_model_destroy(t4c_fk_model* model);
 /* Batched forward kinematics: q is n x n_q row-major doubles (host); out is n x n_links x 12 doubles
  * (every scene link; links no joint reaches keep their scene pose). */
 t4c_status t4c_fk(const t4c_fk_model* model, const t4c_scene* scene, const double* q, int64_t n, double* link_poses);
+/* t4c_fk for callers that may not allocate device memory (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments
+ * and results as t4c_fk (bit for bit: the same kernel); q and the poses are staged in a fixed 8 MiB array of device
+ * memory that belongs to the library image (T4C_FK_NOALLOC_SCRATCH_BYTES; every GPU that loads the library holds it
+ * until exit), so n * (n_q * 8 + n_links * 96) + 256 bytes must fit: T4C_ERR_CAPACITY otherwise.  The scene and the
+ * model must already be resident on the device (one earlier t4c_fk / check call after the last edit): this entry never
+ * uploads or allocates, it returns T4C_ERR_INVALID instead.  All calls on a device share the array (contents of the
+ * previous call are overwritten, nothing needs clearing); overlapping use on one GPU would race, so calls of one
+ * process are serialised per device inside the entry. */
+#define T4C_FK_NOALLOC_SCRATCH_BYTES (8u << 20)
+t4c_status t4c_fk_noalloc(const t4c_fk_model* model, const t4c_scene* scene, const double* q, int64_t n,
+                          double* link_poses);
 
 /* Geometric Jacobian of `link` for n joint vectors (host buffers): J is n x 6 x n_q row-major, rows 0-2 linear and 3-5
  * angular velocity of the link per unit joint velocity, world frame, taken at the link origin or at point_local (a

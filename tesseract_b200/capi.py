@@ -82,6 +82,8 @@ class Gathered(C.Structure):
                 ("n_states", C.c_int64), ("stats", Stats)]
 
 
+FK_NOALLOC_SCRATCH_BYTES = 8 << 20  # include/t4c.h T4C_FK_NOALLOC_SCRATCH_BYTES
+
 # numpy view of t4c_contact (80 bytes)
 CONTACT_DTYPE = np.dtype([("state", "<i4"), ("link", "<i4", 2), ("subshape_id", "<i4", 2), ("shape_id", "<i2", 2),
                           ("distance", "<f4"), ("point", "<f4", (2, 3)), ("normal", "<f4", 3), ("cc_time", "<f4", 2),
@@ -122,6 +124,7 @@ def load_library(path=None):
     lib.t4c_fk_model_destroy.argtypes = [VP]
     lib.t4c_fk_model_destroy.restype = None
     lib.t4c_fk.argtypes = [VP, VP, DP, I64, DP]
+    lib.t4c_fk_noalloc.argtypes = [VP, VP, DP, I64, DP]
     lib.t4c_lvs_count.argtypes = [DP, I64, I32, I32, C.c_double, I32, C.POINTER(I64)]
     lib.t4c_lvs_items.argtypes = [DP, I64, I32, I32, C.c_double, I32, I64, C.POINTER(I32), C.POINTER(I32),
                                   C.POINTER(I32), C.POINTER(I64)]
@@ -163,7 +166,7 @@ def load_library(path=None):
     lib.t4c_debug_hull_support.argtypes = [VP, I32, DP, I64, C.POINTER(I32), DP]
     for name in ("t4c_scene_create", "t4c_scene_clone", "t4c_scene_set_active", "t4c_scene_set_enabled",
                  "t4c_scene_set_acm", "t4c_scene_set_margins", "t4c_scene_set_link_pose", "t4c_scene_num_active",
-                 "t4c_fk_model_create", "t4c_fk", "t4c_check_discrete", "t4c_check_link_poses_discrete",
+                 "t4c_fk_model_create", "t4c_fk", "t4c_fk_noalloc", "t4c_check_discrete", "t4c_check_link_poses_discrete",
                  "t4c_check_cast", "t4c_check_link_poses_cast", "t4c_check_trajectories_discrete",
                  "t4c_check_trajectories_cast", "t4c_check_discrete_device", "t4c_check_cast_device",
                  "t4c_measure_fp32_peak", "t4c_lvs_count", "t4c_lvs_items", "t4c_lvs_item_states",

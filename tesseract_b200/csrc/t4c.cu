@@ -6,6 +6,7 @@
  * tests/hostsim/libt4c_hostsim.so, a TEST-ONLY simulator that runs the identical kernel bodies serially on the host
  * so numerics can be debugged without a GPU; it is never loaded by the tesseract_b200 package.
  */
+#include <mutex>
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
@@ -2001,6 +2002,100 @@ static void launchJacobian(const JacParams& Q, int64_t n, bool grad, t4stream st
   for (int64_t i = 0; i < n; ++i)
     if (grad)
       contactGradBody<T4_MAX_JOINTS>(i, Q);
+// ---------------------------------------------------------------------------------------------------------------------
+// t4c_fk_noalloc: t4c_fk for callers that may not allocate device memory (code under CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// t4c_fk stages q and the poses in growable device buffers (s->d_q0, s->d_fk_out: cudaMalloc when they
+// grow); this entry stages them in ONE fixed array of device memory that is part of the library image:
+//   - every GPU that loads the library holds T4C_NOALLOC_SCRATCH_BYTES (8 MiB) of it until the process exits;
+//   - n * (n_q * 8 + n_links * 96) bytes (+ 256 of padding) have to fit, larger requests are refused (T4C_ERR_CAPACITY);
+//   - the scene image and the FK model must already be resident (any earlier t4c_fk / check call after the last edit):
+//     this entry never uploads them, it refuses instead (T4C_ERR_INVALID);
+//   - every call on a device shares the array and finds the previous call's bytes in it.  Nothing has to start at
+//     zero: the upload overwrites the q region and the kernel writes every link of every state (fkStoreAllLinks)
+//     before the download reads it.  Calls that overlap on one GPU would race on it; inside one process they cannot
+//     (the entry is synchronous and holds a per-device lock from upload to download), two PROCESSES have separate
+//     copies of the array.
+// In host code `g_noalloc_scratch` is a stand-in for the symbol, not a device address: the pointer the kernel gets
+// comes from cudaGetSymbolAddress, taken once per device with that device current.
+// ---------------------------------------------------------------------------------------------------------------------
+#define T4C_NOALLOC_SCRATCH_BYTES (8u << 20)
+#define T4C_NOALLOC_MAX_DEVICES 64
+#ifndef T4C_HOSTSIM
+static __device__ __align__(256) unsigned char g_noalloc_scratch[T4C_NOALLOC_SCRATCH_BYTES];
+#else
+alignas(256) static unsigned char g_noalloc_scratch[T4C_NOALLOC_SCRATCH_BYTES];
+#endif
+static std::mutex g_noalloc_lock[T4C_NOALLOC_MAX_DEVICES];
+static void* g_noalloc_addr[T4C_NOALLOC_MAX_DEVICES] = {};
+
+// device address of the scratch array on `device` (current); looked up once per device
+static t4c_status noallocScratch(int device, unsigned char** out)
+{
+  if (device < 0 || device >= T4C_NOALLOC_MAX_DEVICES)
+    return fail(T4C_ERR_INVALID, "device %d outside [0, %d)", device, T4C_NOALLOC_MAX_DEVICES);
+  if (!g_noalloc_addr[device])
+  {
+#ifndef T4C_HOSTSIM
+    void* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || !ptr)
+    {
+      cudaGetLastError();
+      return fail(T4C_ERR_CUDA, "cudaGetSymbolAddress(scratch) on device %d: %s", device, cudaGetErrorString(e));
+    }
+    g_noalloc_addr[device] = ptr;
+#else
+    g_noalloc_addr[device] = g_noalloc_scratch;
+#endif
+  }
+  *out = static_cast<unsigned char*>(g_noalloc_addr[device]);
+  return T4C_OK;
+}
+
+t4c_status t4c_fk_noalloc(const t4c_fk_model* m, const t4c_scene* scene_c, const double* q, int64_t n, double* link_poses)
+{
+  t4c_scene* s = const_cast<t4c_scene*>(scene_c);
+  if (!m || !s || !q || !link_poses || n < 0)
+    return fail(T4C_ERR_INVALID, "null argument");
+  if (!bindDevice(s))
+    return fail(T4C_ERR_CUDA, "cudaSetDevice(%d): %s", s->device, plat::lastError());
+  const auto it = s->fk.find(m);
+  if (s->uploaded != s->rev || !s->img || it == s->fk.end() || !it->second || it->second->scene_rev != s->rev)
+    return fail(T4C_ERR_INVALID, "t4c_fk_noalloc never uploads: the scene or the FK model is not resident on the device "
+                                 "(run t4c_fk or a check once after creating / editing them)");
+  const int nl = (int)s->host.links.size();
+  const size_t qb = (size_t)n * (size_t)m->n_q * sizeof(double);
+  const size_t q_region = (qb + 255) & ~(size_t)255;
+  const size_t ob = (size_t)n * (size_t)nl * 12 * sizeof(double);
+  if (q_region + ob > T4C_NOALLOC_SCRATCH_BYTES)
+    return fail(T4C_ERR_CAPACITY, "t4c_fk_noalloc: %lld states x (%d joint values + %d link poses) need %zu bytes of "
+                                  "scratch, the fixed array holds %u (at most %lld states of this model)",
+                (long long)n, m->n_q, nl, q_region + ob, (unsigned)T4C_NOALLOC_SCRATCH_BYTES,
+                (long long)((T4C_NOALLOC_SCRATCH_BYTES - 256) / ((size_t)m->n_q * 8 + (size_t)nl * 96)));
+  if (n == 0)
+    return T4C_OK;
+  std::lock_guard<std::mutex> guard(g_noalloc_lock[s->device < T4C_NOALLOC_MAX_DEVICES && s->device >= 0 ? s->device : 0]);
+  unsigned char* scratch = nullptr;
+  const t4c_status rc = noallocScratch(s->device, &scratch);
+  if (rc != T4C_OK)
+    return rc;
+  t4stream st = s->stream;
+  KParams P;
+  fillSceneParams(s, P);
+  fillFkParams(m, it->second.get(), P);
+  T4_TRY(plat::h2d(scratch, q, qb, st), "FK upload");
+  P.n = n;
+  P.q0 = scratch;
+  P.q_layout = T4C_Q_F64_ROWMAJOR;
+  P.q_stride_n = n;
+  P.cast = 0;
+  P.fk_out = reinterpret_cast<double*>(scratch + q_region);
+  launchFk(P, 0, n, st);
+  T4_TRY(launchOk() && plat::d2h(link_poses, P.fk_out, ob, st) && plat::sync(st), "FK");
+  return T4C_OK;
+}
+
     else
       jacobianBody<T4_MAX_JOINTS>(i, Q);
 #endif
