@@ -63,6 +63,7 @@ enum
   Q_OUT,        // final contacts emitted by the CLOSEST reduction
   Q_LONG,       // survivors whose GJK ran out of its iteration budget: run again, without one, beside the later passes
   Q_TASK_LONG,  // EPA tasks of the long-pair pass (it runs on its own stream: own task queue)
+  Q_LIVE,       // FIRST in rounds: states still without a contact at the start of the round (liveKeyBody)
   Q_COUNT
 };
 
@@ -141,6 +142,14 @@ struct KParams
   // ---- request
   int32_t test_type, calc_pen, calc_dist, hit_only;
   int32_t skip_hit;  // FIRST in rounds: states that already have a contact take no further part (ContactTestData::done)
+  // FIRST in rounds: the states of this round's broadphase, in Morton order of the round's first shape, states that
+  // already have a contact last (marked T4_DEAD_STATE); null: all states in index order
+  const uint32_t* live;
+  uint32_t n_live;         // entries of `live` the broadphase is launched over
+  const uint32_t* live_prev;  // liveKeyBody: the previous round's list (null: identity)
+  uint32_t* live_key;      // liveKeyBody out: sort key per entry
+  uint32_t* live_val;      // liveKeyBody out: state per entry
+  float live_org[3], live_scale[3];  // scene box -> Morton grid
   // ---- queues / outputs
   uint32_t* cand_state;
   uint32_t* cand_a;
@@ -590,10 +599,59 @@ T4_KD void pushCandidate(const KParams& P, int64_t s, int a, int b)
 #define T4_CULL_SLACK 2e-5f
 
 // item = a_ord * n + s  (shape-major, so that a warp works on 32 states of the SAME robot shape)
+#define T4_DEAD_STATE 0xffffffffu
+#define T4_LIVE_BITS 7 /* Morton grid: 2^7 cells per axis; key = 21 bits + the dead flag */
+
+T4_KD uint32_t spread3(uint32_t v)
+{
+  // bit i of the low 10 bits -> bit 3 i
+  v = (v | (v << 16)) & 0x030000ffu;
+  v = (v | (v << 8)) & 0x0300f00fu;
+  v = (v | (v << 4)) & 0x030c30c3u;
+  v = (v | (v << 2)) & 0x09249249u;
+  return v;
+}
+
+// item = entry of the previous round's state list.  Key of a state for this round's broadphase: dead flag (the state
+// has its contact) above the Morton code of the world position of the round's first shape.  After the radix sort the
+// 32 states of a warp have that shape in the same 3 cm cell of the scene: they walk the same nodes of the
+// environment tree, and the states that are done sit at the end of the list where whole warps leave at once.
+// (Before: a warp took 32 consecutive states of a random batch -- 8 of 32 lanes active in the traversal, and in the
+// later rounds most lanes belonged to states that were done.)
+T4_KD void liveKeyBody(int64_t i, const KParams& P)
+{
+  const uint32_t s = P.live_prev ? P.live_prev[i] : (uint32_t)i;
+  uint32_t key = 1u << (3 * T4_LIVE_BITS);
+  if (s != T4_DEAD_STATE && !(P.skip_hit && P.hit[s]))
+  {
+    const int sh = P.active_shapes[0];
+    const DShape& S = P.shapes[sh];
+    Xf<float> x0, x1;
+    shapePose<float>(P, S, sh, (int64_t)s, x0, x1);
+    const V3<float> c = x0(V3<float>(S.bc[0], S.bc[1], S.bc[2]));
+    const float hi = (float)((1 << T4_LIVE_BITS) - 1);
+    const float gx = t4min(t4max((c.x - P.live_org[0]) * P.live_scale[0], 0.f), hi);
+    const float gy = t4min(t4max((c.y - P.live_org[1]) * P.live_scale[1], 0.f), hi);
+    const float gz = t4min(t4max((c.z - P.live_org[2]) * P.live_scale[2], 0.f), hi);
+    key = spread3((uint32_t)gx) | (spread3((uint32_t)gy) << 1) | (spread3((uint32_t)gz) << 2);
+    qAppend(&P.qcount[Q_LIVE]);
+  }
+  P.live_key[i] = key;
+  P.live_val[i] = key >> (3 * T4_LIVE_BITS) ? T4_DEAD_STATE : s;
+}
+
 T4_KD void broadStaticBody(int64_t item, const KParams& P)
 {
-  const int a_ord = (int)(item / P.n);
-  const int64_t s = item - (int64_t)a_ord * P.n;
+  const int64_t per_shape = P.live ? (int64_t)P.n_live : P.n;
+  const int a_ord = (int)(item / per_shape);
+  int64_t s = item - (int64_t)a_ord * per_shape;
+  if (P.live)
+  {
+    const uint32_t ls = P.live[s];
+    if (ls == T4_DEAD_STATE)
+      return;
+    s = (int64_t)ls;
+  }
   if (P.skip_hit && P.hit[s])
     return;
   const int sh = P.active_shapes[a_ord];

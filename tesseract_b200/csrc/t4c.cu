@@ -58,6 +58,7 @@ static void* alloc(size_t n) { return std::malloc(n ? n : 1); }
 static void release(void* p) { std::free(p); }
 static bool h2d(void* d, const void* s, size_t n, t4stream) { std::memcpy(d, s, n); return true; }
 static bool d2h(void* d, const void* s, size_t n, t4stream) { std::memcpy(d, s, n); return true; }
+static bool d2d(void* d, const void* s, size_t n, t4stream) { std::memcpy(d, s, n); return true; }
 static bool zero(void* d, size_t n, t4stream) { std::memset(d, 0, n); return true; }
 static bool fill(void* d, int v, size_t n, t4stream) { std::memset(d, v, n); return true; }
 static bool sync(t4stream) { return true; }
@@ -112,6 +113,11 @@ static bool h2d(void* d, const void* s, size_t n, t4stream st)
 static bool d2h(void* d, const void* s, size_t n, t4stream st)
 {
   return n == 0 || chk(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, st));
+}
+// device to device, also into a peer's memory (an IPC-mapped or peer-enabled pointer: the copy goes over NVLink)
+static bool d2d(void* d, const void* s, size_t n, t4stream st)
+{
+  return n == 0 || chk(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToDevice, st));
 }
 static bool zero(void* d, size_t n, t4stream st) { return n == 0 || chk(cudaMemsetAsync(d, 0, n, st)); }
 static bool fill(void* d, int v, size_t n, t4stream st) { return n == 0 || chk(cudaMemsetAsync(d, v, n, st)); }
@@ -280,6 +286,11 @@ __global__ void __launch_bounds__(256, T4_CULL_MIN_CTAS) cullKernel(KParams P, i
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     cullBody(i, P);
+}
+__global__ void __launch_bounds__(256) liveKeyKernel(KParams P, int64_t n)
+{
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    liveKeyBody(i, P);
 }
 __global__ void __launch_bounds__(256) pruneKernel(KParams P, int64_t n)
 {
@@ -473,6 +484,7 @@ static void launchEpa(const KParams& P, int64_t n, t4stream st)
   ++g_launches;
 }
 static void launchPrune(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(pruneKernel, PK_CULL, 256, 8, P, n, st); }
+static void launchLiveKey(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(liveKeyKernel, PK_BROAD_STATIC, 256, 8, P, n, st); }
 static void launchClosestInsert(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestInsertKernel, PK_CLOSEST_INSERT, 256, 8, P, n, st); }
 static void launchClosestEmit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(closestEmitKernel, PK_CLOSEST_EMIT, 256, 8, P, n, st); }
 static void launchCountHit(const KParams& P, int64_t n, t4stream st) { T4_LAUNCH(countHitKernel, PK_COUNT_HIT, 256, 8, P, n, st); }
@@ -505,6 +517,7 @@ static void launchEpa(const KParams& P, int64_t n, t4stream)
     ++g_launches;
 }
 static void launchPrune(const KParams& P, int64_t n, t4stream) { T4_SERIAL(pruneBody, P, n); }
+static void launchLiveKey(const KParams& P, int64_t n, t4stream) { T4_SERIAL(liveKeyBody, P, n); }
 static void launchClosestInsert(const KParams& P, int64_t n, t4stream) { T4_SERIAL(closestInsertBody, P, n); }
 static void launchClosestEmit(const KParams& P, int64_t n, t4stream) { T4_SERIAL(closestEmitBody, P, n); }
 static void launchCountHit(const KParams& P, int64_t n, t4stream)
@@ -561,6 +574,7 @@ struct t4c_scene
   DevBuf d_traj, d_lvs_counts, d_lvs_offsets, d_lvs_tmp;
   DevBuf d_sort_keys, d_sort_keys2, d_sort_vals, d_sort_idx, d_sort_tmp;
   DevBuf d_key_min, d_cand_lb;
+  DevBuf d_live_a, d_live_b, d_live_key, d_live_key2, d_live_val;  // FIRST in rounds: ordered state lists
   uint32_t cand_cap = 0;
   int64_t chunk_hint = 0;  // states per chunk that fitted the device memory (0: the default)
   std::unordered_map<const t4c_fk_model*, std::unique_ptr<FkCache>> fk;
@@ -571,7 +585,8 @@ struct t4c_scene
     DevBuf* bufs[] = { &d_poses0, &d_poses1, &d_poses0d, &d_poses1d, &d_cand_state, &d_cand_a, &d_cand_b, &d_cand_class,
                        &d_long, &d_tasks_long, &d_surv, &d_surv2, &d_surv3, &d_surv4, &d_cull_claim, &d_tasks, &d_hit,
                        &d_claim, &d_raw, &d_raw_local, &d_raw_d64, &d_ht_rep, &d_ht_best, &d_sort_keys, &d_sort_keys2,
-                       &d_sort_vals, &d_sort_idx, &d_sort_tmp, &d_key_min, &d_cand_lb };
+                       &d_sort_vals, &d_sort_idx, &d_sort_tmp, &d_key_min, &d_cand_lb, &d_live_a, &d_live_b,
+                       &d_live_key, &d_live_key2, &d_live_val };
     for (DevBuf* b : bufs)
       b->reset();
     cand_cap = 0;
@@ -758,6 +773,11 @@ struct BatchIO
   // as they are final, while later rounds / chunks compute; host_copied = records already on their way
   t4c_contact* host_contacts = nullptr;
   int64_t host_copied = 0;
+  // sharded entries (t4_multi.h): records are ALSO pushed, as soon as they are final, into this rank's region of the
+  // root's gather slab -- peer memory, the copy engine writes it over NVLink on the copy stream while the later rounds
+  // compute; pushed = records already on their way (the final exchange sends only what is left)
+  t4c_contact* push_dst = nullptr;
+  int64_t push_cap = 0, pushed = 0;
   // q arrives in q_pieces uploads of q_piece_states states each on the copy stream (event k = piece k is resident):
   // FK runs piece by piece under the rest of the upload
   int q_pieces = 0;
@@ -785,6 +805,8 @@ struct Tuning
   int max_rounds = 8;
   int verify_skip = 0;               // T4C_VERIFY_SKIP: run phase 1 for certified pairs too, count contradictions
   int trace = 0;                     // T4C_TRACE_PASSES: queue sizes of every exact pass on stderr
+  int peer_push = 1;                 // T4C_PEER_PUSH=0: sharded entries move every record in the final exchange
+  int live_order = 1;                // T4C_LIVE_ORDER=0: rounds walk all states in index order (r3j behaviour)
   Tuning()
   {
     auto env = [](const char* name, long long dflt, long long lo) {
@@ -798,6 +820,8 @@ struct Tuning
     upload_piece_min = env("T4C_UPLOAD_PIECE_MIN", upload_piece_min, 1);
     verify_skip = (int)env("T4C_VERIFY_SKIP", 0, 0);
     trace = (int)env("T4C_TRACE_PASSES", 0, 0);
+    peer_push = (int)env("T4C_PEER_PUSH", 1, 0);
+    live_order = (int)env("T4C_LIVE_ORDER", 1, 0);
   }
 };
 static const Tuning& tuning()
@@ -861,6 +885,31 @@ static const uint32_t* sortByType(t4c_scene* s, const KParams& P, const uint32_t
 #else
 static const uint32_t* sortByType(t4c_scene*, const KParams&, const uint32_t*, int, uint32_t) { return nullptr; }
 #endif
+
+// stable radix sort of the round's state list by (done flag, Morton cell): keys / values of liveKeyBody -> `out`
+static bool sortLive(t4c_scene* s, const KParams& P, uint32_t n, uint32_t* out)
+{
+#ifndef T4C_HOSTSIM
+  t4stream st = s->stream;
+  size_t tmp = 0;
+  const int bits = 3 * T4_LIVE_BITS + 1;
+  return s->d_live_key2.ensure((size_t)n * 4) &&
+         cub::DeviceRadixSort::SortPairs(nullptr, tmp, P.live_key, s->d_live_key2.as<uint32_t>(), P.live_val, out, (int)n, 0,
+                                         bits, st) == cudaSuccess &&
+         s->d_sort_tmp.ensure(tmp) &&
+         cub::DeviceRadixSort::SortPairs(s->d_sort_tmp.p, tmp, P.live_key, s->d_live_key2.as<uint32_t>(), P.live_val, out,
+                                         (int)n, 0, bits, st) == cudaSuccess;
+#else
+  (void)s;
+  std::vector<uint32_t> idx(n);
+  for (uint32_t i = 0; i < n; ++i)
+    idx[i] = i;
+  std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return P.live_key[a] < P.live_key[b]; });
+  for (uint32_t i = 0; i < n; ++i)
+    out[i] = P.live_val[idx[i]];
+  return true;
+#endif
+}
 
 static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH);
 
@@ -937,15 +986,24 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
   // the caller's page-locked buffer on the copy stream, under the kernels that follow
   bool aux_busy = false;  // set while kernels of the long-pair pass run beside the main stream (they append records too)
   auto drain = [&](int64_t upto) -> bool {
-    if (!io.host_contacts || !io.contacts || aux_busy)
+    if (!io.contacts || aux_busy)
       return true;
     upto = std::min<int64_t>(upto, io.capacity);
     const int64_t min_records = tuning().drain_min;
-    if (upto - io.host_copied < min_records)
-      return true;
-    const bool ok = plat::d2h(io.host_contacts + io.host_copied, io.contacts + io.host_copied,
-                              (size_t)(upto - io.host_copied) * sizeof(t4c_contact), s->copy_stream);
-    io.host_copied = upto;
+    bool ok = true;
+    if (io.host_contacts && upto - io.host_copied >= min_records)
+    {
+      ok = plat::d2h(io.host_contacts + io.host_copied, io.contacts + io.host_copied,
+                     (size_t)(upto - io.host_copied) * sizeof(t4c_contact), s->copy_stream);
+      io.host_copied = upto;
+    }
+    const int64_t to = std::min<int64_t>(upto, io.push_cap);
+    if (io.push_dst && to - io.pushed >= min_records)
+    {
+      ok = ok && plat::d2d(io.push_dst + io.pushed, io.contacts + io.pushed,
+                           (size_t)(to - io.pushed) * sizeof(t4c_contact), s->copy_stream);
+      io.pushed = to;
+    }
     return ok;
   };
   for (int64_t base = 0; base < io.n; base += CH)
@@ -1022,6 +1080,26 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
     if (io.req.type == T4C_TEST_FIRST && nc >= roundMinStates() && n_all_active > 1 && P.n_bvh_nodes > 0)
       n_rounds = std::min(n_all_active, maxRounds());
     P.skip_hit = n_rounds > 1 ? 1 : 0;
+    // rounds walk an ordered list of the states that are still without a contact (Morton grid over the scene box)
+    bool use_live = n_rounds > 1 && P.n_bvh_nodes > 0 && tuning().live_order;
+    const uint32_t* live_cur = nullptr;
+    uint32_t live_n = 0;
+    if (use_live)
+    {
+      const size_t lb = (size_t)nc * sizeof(uint32_t);
+      if (!(s->d_live_a.ensure(lb) && s->d_live_b.ensure(lb) && s->d_live_key.ensure(lb) && s->d_live_val.ensure(lb)))
+      {
+        g_alloc_failed = false;
+        use_live = false;
+      }
+      const DBvhNode& R = s->img->comp.bvh[0];
+      for (int k = 0; k < 3; ++k)
+      {
+        const float mn = std::min(R.lmn[k], R.rmn[k]) - 0.5f, mx = std::max(R.lmx[k], R.rmx[k]) + 0.5f;
+        P.live_org[k] = mn;
+        P.live_scale[k] = (float)(1 << T4_LIVE_BITS) / std::max(mx - mn, 1e-3f);
+      }
+    }
     // Candidates APPEND across the rounds (survivor queues hold candidate indices).  Per round only the first tier of
     // survivors is resolved: pairs that are certainly in contact without penetrating -- one cheap GJK each.  The
     // other tiers (one certainly penetrating pair per state, then the rest) accumulate and are resolved after the
@@ -1222,12 +1300,45 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
       P.active_shapes = all_active + lo;
       P.n_active_shapes = hi - lo;
       P.n_aa_pairs = round == 0 ? n_all_aa : 0;
+      // ---- this round's states in Morton order of the round's first shape, the states that are done last
+      //      (liveKeyBody).  The list of the previous round is the input: it shrinks as the states settle.
+      P.live = nullptr;
+      P.n_live = 0;
+      if (use_live)
+      {
+        const uint32_t n_prev = live_cur ? live_n : (uint32_t)nc;
+        uint32_t* const out = (live_cur == s->d_live_a.as<uint32_t>()) ? s->d_live_b.as<uint32_t>() : s->d_live_a.as<uint32_t>();
+        if (n_prev > 0)
+        {
+          T4_TRY(plat::zero(P.qcount + Q_LIVE, sizeof(uint32_t), st), "memset");
+          P.live_prev = live_cur;
+          P.live_key = s->d_live_key.as<uint32_t>();
+          P.live_val = s->d_live_val.as<uint32_t>();
+          launchLiveKey(P, n_prev, st);
+          if (sortLive(s, P, n_prev, out))
+          {
+            P.live = out;
+            P.n_live = n_prev;
+          }
+          else
+          {
+            g_alloc_failed = false;  // no room for the sort: this round walks every state in index order
+            use_live = false;
+          }
+        }
+        else
+        {
+          P.live = out;  // every state is done: nothing to traverse
+          P.n_live = 0;
+        }
+      }
+      const int64_t per_shape = P.live ? (int64_t)P.n_live : nc;
       // ---- broadphase (retried with a larger queue when it overflows)
       for (int attempt = 0;; ++attempt)
       {
         T4_TRY(bindQueues(), "candidate queue");
         if (P.n_bvh_nodes > 0)
-          launchBroadStatic(P, nc * (int64_t)P.n_active_shapes, st);
+          launchBroadStatic(P, per_shape * (int64_t)P.n_active_shapes, st);
         launchBroadActive(P, nc * (int64_t)P.n_aa_pairs, st);
         T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "broadphase");
         if (qc[Q_CAND] <= s->cand_cap)
@@ -1240,6 +1351,11 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
         T4_TRY(plat::h2d(P.qcount + Q_CAND, &cand_begin, sizeof(uint32_t), st) && plat::sync(st), "queue rewind");
       }
       const uint32_t ncand = qc[Q_CAND];
+      if (P.live)
+      {
+        live_cur = P.live;
+        live_n = std::min(qc[Q_LIVE], P.n_live);
+      }
       // ---- FP32 cull of this round's candidates
       T4_TRY(plat::zero(P.qcount + Q_SURV, sizeof(uint32_t), st), "memset");
       P.cull_base = cand_begin;
@@ -1980,28 +2096,6 @@ t4c_status t4c_fk(const t4c_fk_model* m, const t4c_scene* scene_c, const double*
   return T4C_OK;
 }
 
-static void launchJacobian(const JacParams& Q, int64_t n, bool grad, t4stream st)
-{
-  if (n <= 0)
-    return;
-#ifndef T4C_HOSTSIM
-  const int grid = gridFor(n, 128, 8);
-  if (Q.P.n_joints <= 16)
-  {
-    if (grad)
-      contactGradKernel<16><<<grid, 128, 0, st>>>(Q, n);
-    else
-      jacobianKernel<16><<<grid, 128, 0, st>>>(Q, n);
-  }
-  else if (grad)
-    contactGradKernel<T4_MAX_JOINTS><<<grid, 128, 0, st>>>(Q, n);
-  else
-    jacobianKernel<T4_MAX_JOINTS><<<grid, 128, 0, st>>>(Q, n);
-#else
-  (void)st;
-  for (int64_t i = 0; i < n; ++i)
-    if (grad)
-      contactGradBody<T4_MAX_JOINTS>(i, Q);
 // ---------------------------------------------------------------------------------------------------------------------
 // t4c_fk_noalloc: t4c_fk for callers that may not allocate device memory (code under CUDA graph capture, tight serving
 // loops, harnesses that forbid cudaMalloc).  No counterpart in the reference; added
@@ -2096,6 +2190,28 @@ t4c_status t4c_fk_noalloc(const t4c_fk_model* m, const t4c_scene* scene_c, const
   return T4C_OK;
 }
 
+static void launchJacobian(const JacParams& Q, int64_t n, bool grad, t4stream st)
+{
+  if (n <= 0)
+    return;
+#ifndef T4C_HOSTSIM
+  const int grid = gridFor(n, 128, 8);
+  if (Q.P.n_joints <= 16)
+  {
+    if (grad)
+      contactGradKernel<16><<<grid, 128, 0, st>>>(Q, n);
+    else
+      jacobianKernel<16><<<grid, 128, 0, st>>>(Q, n);
+  }
+  else if (grad)
+    contactGradKernel<T4_MAX_JOINTS><<<grid, 128, 0, st>>>(Q, n);
+  else
+    jacobianKernel<T4_MAX_JOINTS><<<grid, 128, 0, st>>>(Q, n);
+#else
+  (void)st;
+  for (int64_t i = 0; i < n; ++i)
+    if (grad)
+      contactGradBody<T4_MAX_JOINTS>(i, Q);
     else
       jacobianBody<T4_MAX_JOINTS>(i, Q);
 #endif

@@ -84,6 +84,48 @@ def test_multi_matches_single_device_and_oracle(rig, tt):
         print(rep)
     else:
         assert np.array_equal(np.sort(con_m["state"]), np.flatnonzero(hit_m))
+        # every gathered record (most of them reach the root through the progressive peer-memory push) is, field for
+        # field, the record the single-device ALL query holds for the same (state, link pair, shapes)
+        hit_a, con_a, _ = bc.check_discrete(q, capi.TEST_ALL)
+        Ga = parity.index(con_a, True)
+        Gm = parity.index(con_m, True)
+        missing = [k for k in Gm if k not in Ga]
+        assert not missing, f"{len(missing)} gathered FIRST records have no counterpart in the ALL result"
+        assert max(abs(Gm[k][0] - Ga[k][0]) for k in Gm) == 0.0
+        assert max(float(np.abs(np.asarray(Gm[k][1]) - np.asarray(Ga[k][1])).max()) for k in Gm) == 0.0
         idx = np.sort(np.random.default_rng(5).choice(n, 3000, replace=False))
         hit_o, _, _ = pyoracle.check_discrete(b, q[idx], tt, want_contacts=False, n_threads=os.cpu_count() or 4)
         assert np.array_equal(hit_m[idx], hit_o)
+
+
+def test_sharded_processes_push_records_over_peer_memory(tmp_path):
+    """One PROCESS per device (the torchrun layout of bench.py): t4c_check_discrete_sharded with the root's gather slab
+    mapped into the peers through CUDA IPC; records are pushed while the rounds compute (test hooks make the small
+    shards run in rounds and push in small pieces).  tests/sharded_worker.py holds the comparison."""
+    import subprocess
+    import sys
+    nd = min(n_devices(), 2)
+    if nd < 2:
+        pytest.skip("needs at least two CUDA devices")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, T4C_ROUND_MIN_STATES="1", T4C_DRAIN_MIN="256", T4C_TRACE_PASSES="1")
+    idfile = str(tmp_path / "comm_id")
+    procs = [subprocess.Popen([sys.executable, os.path.join(root, "tests", "sharded_worker.py"), str(r), str(nd), idfile,
+                               "20000"], cwd=root, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+             for r in range(nd)]
+    outs = []
+    try:
+        for p in procs:
+            outs.append(p.communicate(timeout=900)[0])
+    finally:
+        for p in procs:
+            if p.poll() is None:
+                p.kill()
+    for r, (p, o) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0, f"rank {r}:\n{o[-3000:]}"
+    assert "SHARDED OK" in outs[0], outs[0][-3000:]
+    # the records did travel through the slab (a rank that could not map it would still pass: it sends everything)
+    import re
+    pushed = [int(m.group(1)) for m in re.finditer(r"pushed (\d+) of \d+ records", outs[0])]
+    assert pushed and max(pushed) > 0, "no record reached the root through the peer-memory push"
+    print(outs[0][-400:])
