@@ -474,12 +474,22 @@ static void launchGjk(const KParams& P, int64_t n, t4stream st)
   profEnd(st);
   ++g_launches;
 }
+static int epaBlockOverride();  // Tuning::epa_block (defined with the tuning parameters below)
 static void launchEpa(const KParams& P, int64_t n, t4stream st)
 {
   if (n <= 0)
     return;
   profBegin(PK_EPA, st);
-  t4LaunchEpa(P, n, gridFor(n, 128, 4, true), 128, st);
+  // a launch of a few thousand tasks lasts as long as its slowest task (124 iterations against a cylinder): small
+  // launches use small CTAs so that the tasks spread over all SMs and each SM's L1 holds fewer polytope pools
+  int block = 128;
+  if (epaBlockOverride() > 0)
+    block = epaBlockOverride();
+  else if (n <= (int64_t)smCount() * 4 * 32)
+    block = 32;
+  else if (n <= (int64_t)smCount() * 4 * 64)
+    block = 64;
+  t4LaunchEpa(P, n, gridFor(n, block, 4 * (128 / block), true), block, st);
   profEnd(st);
   ++g_launches;
 }
@@ -807,6 +817,11 @@ struct Tuning
   int trace = 0;                     // T4C_TRACE_PASSES: queue sizes of every exact pass on stderr
   int peer_push = 1;                 // T4C_PEER_PUSH=0: sharded entries move every record in the final exchange
   int live_order = 1;                // T4C_LIVE_ORDER=0: rounds walk all states in index order (r3j behaviour)
+  // a round takes unit * (this % * n / live states) shapes; 0 = off, -1 = the measured choice (profiles/r3l): 35 for
+  // queries with records, 70 for flags-only queries
+  int round_merge = -1;              // T4C_ROUND_MERGE
+  int epa_block = 0;                 // T4C_EPA_BLOCK: threads per CTA of the EPA launch (0: by task count)
+  int round_order = -1;              // T4C_ROUND_ORDER: 0 distal shapes first, 1 proximal first, -1 the measured choice
   Tuning()
   {
     auto env = [](const char* name, long long dflt, long long lo) {
@@ -822,6 +837,9 @@ struct Tuning
     trace = (int)env("T4C_TRACE_PASSES", 0, 0);
     peer_push = (int)env("T4C_PEER_PUSH", 1, 0);
     live_order = (int)env("T4C_LIVE_ORDER", 1, 0);
+    round_merge = (int)env("T4C_ROUND_MERGE", round_merge, -1);
+    round_order = (int)env("T4C_ROUND_ORDER", -1, -1);
+    epa_block = (int)env("T4C_EPA_BLOCK", 0, 0);
   }
 };
 static const Tuning& tuning()
@@ -830,16 +848,19 @@ static const Tuning& tuning()
   return t;
 }
 static int64_t roundMinStates() { return tuning().round_min_states; }
+static int epaBlockOverride() { return tuning().epa_block; }
 static int gjkBudget() { return tuning().gjk_budget; }
 static int maxRounds() { return tuning().max_rounds; }
 static int64_t chunkStates() { return tuning().chunk_states; }
 // survivor queues are sorted by (types, iteration count of the FP32 cull): the exact pass of a pair needs about as many
 // iterations as its cull did, so a warp's lanes finish together (GJK -6 %, r2g)
 static bool sortClass() { return true; }
-// 0: last active shapes first (distal links of a serial arm), 1: first shapes first.  Measured on configs[1] (r1v):
-// flags-only queries are fastest distal-first (157 M vs 138 M states/s), queries with records proximal-first
-// (38.0 M vs 36.1 M: fewer states end up needing EPA iterations)
-static int roundOrder(bool with_records) { return with_records ? 1 : 0; }
+// 0: last active shapes first (distal links of a serial arm), 1: first shapes first.  Distal-first settles most
+// states in the first rounds (the end of the arm sweeps the largest volume): 85 M instead of 208 M tree nodes per 1 Mi
+// states on configs[1].  Round 1 measured queries WITH records faster proximal-first (fewer EPA runs); since tier 0
+// holds only certified pairs EPA hardly runs, and distal-first wins for both (profiles/r3l: 79.9 M vs 75.7 M states/s
+// with records, 239.6 M vs 195.6 M flags-only).
+static int roundOrder(bool) { return 0; }
 
 static uint32_t nextPow2(uint64_t x)
 {
@@ -1291,12 +1312,32 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
       long_done = nlong;
       return r;
     };
-    for (int round = 0; round < n_rounds; ++round)
+    // Slices of the robot's shapes, one per round.  A round has a fixed cost (five host round trips, a dozen
+    // launches: ~0.15 ms) and pays by what the states it settles do not have to do in the later rounds, so the slices
+    // grow as the live states get fewer: `unit` shapes while most states are live, then unit * (merge * n / live).
+    const int unit = n_rounds > 1 ? (n_all_active + maxRounds() - 1) / maxRounds() : n_all_active;
+    const int order = tuning().round_order >= 0 ? tuning().round_order : roundOrder(first_rec);
+    int cursor = 0;  // shapes taken so far
+    for (int round = 0; cursor < n_all_active; ++round)
     {
-      // slices from the far end of the kinematic chain first (distal links sweep the largest volume)
-      const int slice = roundOrder(first_rec) ? round : n_rounds - 1 - round;
-      const int lo = (int)((int64_t)n_all_active * slice / n_rounds);
-      const int hi = (int)((int64_t)n_all_active * (slice + 1) / n_rounds);
+      const int remaining = n_all_active - cursor;
+      int take = std::min(unit, remaining);
+      const int merge = tuning().round_merge >= 0 ? tuning().round_merge : (first_rec ? 35 : 70);
+      if (n_rounds > 1 && round > 0 && merge > 0)
+      {
+        int64_t est_live = first_rec ? nc - (int64_t)std::min<uint32_t>(qc[Q_RAW], (uint32_t)nc) : nc;
+        if (live_cur)
+          est_live = std::min<int64_t>(est_live, live_n);  // counted at the start of the previous round
+        const int64_t mult = (int64_t)merge * nc / (100 * std::max<int64_t>(est_live, 1));
+        take = (int)std::min<int64_t>(remaining, (int64_t)unit * std::max<int64_t>(mult, 1));
+      }
+      if (n_rounds > 1 && round >= maxRounds() - 1)
+        take = remaining;
+      const bool last_round = cursor + take == n_all_active;
+      // order 0: from the far end of the kinematic chain (distal links sweep the largest volume), 1: from the base
+      const int lo = order ? cursor : n_all_active - cursor - take;
+      const int hi = lo + take;
+      cursor += take;
       P.active_shapes = all_active + lo;
       P.n_active_shapes = hi - lo;
       P.n_aa_pairs = round == 0 ? n_all_aa : 0;
@@ -1394,7 +1435,7 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
         }
       }
       // with a long-pair queue the EPA launch waits until the long pairs' GJK has been started beside it
-      rc = exactPass(exact_queue, n_exact, round == n_rounds - 1 && !P.long_w);
+      rc = exactPass(exact_queue, n_exact, last_round && !P.long_w);
       if (rc != T4C_OK)
         return rc;
       // ---- long pairs of this round: a pair that cycles towards the detector's 1000-iteration caps keeps one lane
