@@ -820,6 +820,7 @@ struct Tuning
   // a round takes unit * (this % * n / live states) shapes; 0 = off, -1 = the measured choice (profiles/r3l): 35 for
   // queries with records, 70 for flags-only queries
   int round_merge = -1;              // T4C_ROUND_MERGE
+  int64_t sort_min = 4096;           // T4C_SORT_MIN: exact-pass queues shorter than this are not sorted by type
   int epa_block = 0;                 // T4C_EPA_BLOCK: threads per CTA of the EPA launch (0: by task count)
   int round_order = -1;              // T4C_ROUND_ORDER: 0 distal shapes first, 1 proximal first, -1 the measured choice
   Tuning()
@@ -840,6 +841,7 @@ struct Tuning
     round_merge = (int)env("T4C_ROUND_MERGE", round_merge, -1);
     round_order = (int)env("T4C_ROUND_ORDER", -1, -1);
     epa_block = (int)env("T4C_EPA_BLOCK", 0, 0);
+    sort_min = env("T4C_SORT_MIN", sort_min, 0);
   }
 };
 static const Tuning& tuning()
@@ -849,6 +851,7 @@ static const Tuning& tuning()
 }
 static int64_t roundMinStates() { return tuning().round_min_states; }
 static int epaBlockOverride() { return tuning().epa_block; }
+static int64_t sortMin() { return tuning().sort_min; }
 static int gjkBudget() { return tuning().gjk_budget; }
 static int maxRounds() { return tuning().max_rounds; }
 static int64_t chunkStates() { return tuning().chunk_states; }
@@ -882,7 +885,7 @@ static uint32_t nextPow2(uint64_t x)
 // from_tasks == 0, task indices otherwise) or null when sorting is off / not worthwhile
 static const uint32_t* sortByType(t4c_scene* s, const KParams& P, const uint32_t* queue, int from_tasks, uint32_t n)
 {
-  if (n < 4096)
+  if (n < (uint32_t)sortMin())
     return nullptr;
   t4stream st = s->stream;
   if (!(s->d_sort_keys.ensure((size_t)n * 2) && s->d_sort_keys2.ensure((size_t)n * 2) && s->d_sort_vals.ensure((size_t)n * 4) &&
