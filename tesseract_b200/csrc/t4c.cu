@@ -1437,6 +1437,17 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
           P.raw_local = s->d_raw_local.as<float>();
         }
       }
+      // A launch of the exact kernel lasts at least as long as one pair (~0.15 ms on an otherwise idle GPU): the few
+      // tier-0 pairs of the last round (the links next to the base) join the first deferred pass instead of paying
+      // that latency for a launch of their own.
+      if (first_rec && last_round && n_rounds > 1 && n_exact > 0 && n_exact < 4096 &&
+          (uint64_t)nsurv4 + n_exact <= (uint64_t)P.surv_cap)
+      {
+        T4_TRY(plat::d2d(s->d_surv4.as<uint32_t>() + nsurv4, exact_queue, (size_t)n_exact * sizeof(uint32_t), st),
+               "survivor queue");
+        nsurv4 += n_exact;
+        n_exact = 0;
+      }
       // with a long-pair queue the EPA launch waits until the long pairs' GJK has been started beside it
       rc = exactPass(exact_queue, n_exact, last_round && !P.long_w);
       if (rc != T4C_OK)
