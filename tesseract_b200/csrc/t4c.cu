@@ -474,7 +474,6 @@ static void launchGjk(const KParams& P, int64_t n, t4stream st)
   profEnd(st);
   ++g_launches;
 }
-static int epaBlockOverride();  // Tuning::epa_block (defined with the tuning parameters below)
 static void launchEpa(const KParams& P, int64_t n, t4stream st)
 {
   if (n <= 0)
@@ -482,10 +481,10 @@ static void launchEpa(const KParams& P, int64_t n, t4stream st)
   profBegin(PK_EPA, st);
   // a launch of a few thousand tasks lasts as long as its slowest task (124 iterations against a cylinder): small
   // launches use small CTAs so that the tasks spread over all SMs and each SM's L1 holds fewer polytope pools
+  // (7.6 k tasks: 1.97 -> 1.47 ms, profiles/r3m).  Keeping the polytopes of such launches in a dense global pool
+  // instead of thread-local memory changed nothing (profiles/r3q): the tail is a serial FP64 dependency chain.
   int block = 128;
-  if (epaBlockOverride() > 0)
-    block = epaBlockOverride();
-  else if (n <= (int64_t)smCount() * 4 * 32)
+  if (n <= (int64_t)smCount() * 4 * 32)
     block = 32;
   else if (n <= (int64_t)smCount() * 4 * 64)
     block = 64;
@@ -797,9 +796,11 @@ struct BatchIO
   t4c_stats stats{};
 };
 
-// Pipeline parameters.  The values are the measured choices (profiles/README.md); the six environment variables are
-// TEST HOOKS that let small test batches reach the code paths of the million-state runs (rounds, budgets, chunking,
-// progressive copies) -- nothing else in the library reads the environment.
+// Pipeline parameters.  The values are the measured choices (profiles/README.md).  The environment variables are read
+// ONCE, here: six TEST HOOKS that let small test batches reach the code paths of the million-state runs (rounds,
+// budgets, chunking, progressive copies, the phase-1 certificate check), a trace of the exact passes, and three
+// A/B switches (peer push, live ordering, slice growth) that the profiles' on / off comparisons use.  Nothing else in
+// the library reads the environment.
 struct Tuning
 {
   // FIRST queries of at least this many states (per chunk) run in rounds over the robot's shapes (runBatch)
@@ -820,9 +821,6 @@ struct Tuning
   // a round takes unit * (this % * n / live states) shapes; 0 = off, -1 = the measured choice (profiles/r3l): 35 for
   // queries with records, 70 for flags-only queries
   int round_merge = -1;              // T4C_ROUND_MERGE
-  int64_t sort_min = 4096;           // T4C_SORT_MIN: exact-pass queues shorter than this are not sorted by type
-  int epa_block = 0;                 // T4C_EPA_BLOCK: threads per CTA of the EPA launch (0: by task count)
-  int round_order = -1;              // T4C_ROUND_ORDER: 0 distal shapes first, 1 proximal first, -1 the measured choice
   Tuning()
   {
     auto env = [](const char* name, long long dflt, long long lo) {
@@ -839,9 +837,6 @@ struct Tuning
     peer_push = (int)env("T4C_PEER_PUSH", 1, 0);
     live_order = (int)env("T4C_LIVE_ORDER", 1, 0);
     round_merge = (int)env("T4C_ROUND_MERGE", round_merge, -1);
-    round_order = (int)env("T4C_ROUND_ORDER", -1, -1);
-    epa_block = (int)env("T4C_EPA_BLOCK", 0, 0);
-    sort_min = env("T4C_SORT_MIN", sort_min, 0);
   }
 };
 static const Tuning& tuning()
@@ -850,8 +845,6 @@ static const Tuning& tuning()
   return t;
 }
 static int64_t roundMinStates() { return tuning().round_min_states; }
-static int epaBlockOverride() { return tuning().epa_block; }
-static int64_t sortMin() { return tuning().sort_min; }
 static int gjkBudget() { return tuning().gjk_budget; }
 static int maxRounds() { return tuning().max_rounds; }
 static int64_t chunkStates() { return tuning().chunk_states; }
@@ -885,7 +878,7 @@ static uint32_t nextPow2(uint64_t x)
 // from_tasks == 0, task indices otherwise) or null when sorting is off / not worthwhile
 static const uint32_t* sortByType(t4c_scene* s, const KParams& P, const uint32_t* queue, int from_tasks, uint32_t n)
 {
-  if (n < (uint32_t)sortMin())
+  if (n < 4096)
     return nullptr;
   t4stream st = s->stream;
   if (!(s->d_sort_keys.ensure((size_t)n * 2) && s->d_sort_keys2.ensure((size_t)n * 2) && s->d_sort_vals.ensure((size_t)n * 4) &&
@@ -1319,7 +1312,7 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
     // launches: ~0.15 ms) and pays by what the states it settles do not have to do in the later rounds, so the slices
     // grow as the live states get fewer: `unit` shapes while most states are live, then unit * (merge * n / live).
     const int unit = n_rounds > 1 ? (n_all_active + maxRounds() - 1) / maxRounds() : n_all_active;
-    const int order = tuning().round_order >= 0 ? tuning().round_order : roundOrder(first_rec);
+    const int order = roundOrder(first_rec);
     int cursor = 0;  // shapes taken so far
     for (int round = 0; cursor < n_all_active; ++round)
     {
