@@ -481,7 +481,7 @@ static void launchEpa(const KParams& P, int64_t n, t4stream st)
   profBegin(PK_EPA, st);
   // a launch of a few thousand tasks lasts as long as its slowest task (124 iterations against a cylinder): small
   // launches use small CTAs so that the tasks spread over all SMs and each SM's L1 holds fewer polytope pools
-  // (7.6 k tasks: 1.97 -> 1.47 ms, profiles/r3m).  Keeping the polytopes of such launches in a dense global pool
+  // (16 k tasks: 1.97 -> 1.47 ms, profiles/r3m).  Keeping the polytopes of such launches in a dense global pool
   // instead of thread-local memory changed nothing (profiles/r3q): the tail is a serial FP64 dependency chain.
   int block = 128;
   if (n <= (int64_t)smCount() * 4 * 32)
@@ -573,6 +573,7 @@ struct t4c_scene
   t4stream stream = nullptr;
   t4stream copy_stream = nullptr;  // progressive download of finished contact records (hostRun)
   t4stream aux_stream = nullptr;   // long-pair GJK pass, beside the deferred tiers / EPA on the main stream
+  t4stream epa_stream = nullptr;   // EPA tasks of the first deferred pass, beside the other deferred passes
   plat::t4event q_events[4] = { nullptr, nullptr, nullptr, nullptr };  // piecewise upload of q (hostRun)
   // per-call workspace
   DevBuf d_q0, d_q1, d_pin0, d_pin1, d_poses0, d_poses1, d_poses0d, d_poses1d;
@@ -583,6 +584,7 @@ struct t4c_scene
   DevBuf d_traj, d_lvs_counts, d_lvs_offsets, d_lvs_tmp;
   DevBuf d_sort_keys, d_sort_keys2, d_sort_vals, d_sort_idx, d_sort_tmp;
   DevBuf d_key_min, d_cand_lb;
+  DevBuf d_epa_order;  // type order of the EPA tasks that start early (private copy: the sort buffers are reused)
   DevBuf d_live_a, d_live_b, d_live_key, d_live_key2, d_live_val;  // FIRST in rounds: ordered state lists
   uint32_t cand_cap = 0;
   int64_t chunk_hint = 0;  // states per chunk that fitted the device memory (0: the default)
@@ -595,7 +597,7 @@ struct t4c_scene
                        &d_long, &d_tasks_long, &d_surv, &d_surv2, &d_surv3, &d_surv4, &d_cull_claim, &d_tasks, &d_hit,
                        &d_claim, &d_raw, &d_raw_local, &d_raw_d64, &d_ht_rep, &d_ht_best, &d_sort_keys, &d_sort_keys2,
                        &d_sort_vals, &d_sort_idx, &d_sort_tmp, &d_key_min, &d_cand_lb, &d_live_a, &d_live_b,
-                       &d_live_key, &d_live_key2, &d_live_val };
+                       &d_live_key, &d_live_key2, &d_live_val, &d_epa_order };
     for (DevBuf* b : bufs)
       b->reset();
     cand_cap = 0;
@@ -607,6 +609,7 @@ struct t4c_scene
     plat::freeStream(stream);
     plat::freeStream(copy_stream);
     plat::freeStream(aux_stream);
+    plat::freeStream(epa_stream);
     for (auto& e : q_events)
       plat::freeEvent(e);
   }
@@ -817,6 +820,7 @@ struct Tuning
   int verify_skip = 0;               // T4C_VERIFY_SKIP: run phase 1 for certified pairs too, count contradictions
   int trace = 0;                     // T4C_TRACE_PASSES: queue sizes of every exact pass on stderr
   int peer_push = 1;                 // T4C_PEER_PUSH=0: sharded entries move every record in the final exchange
+  int epa_early = 1;                 // T4C_EPA_EARLY=0: one EPA launch after all deferred passes (r3o behaviour)
   int live_order = 1;                // T4C_LIVE_ORDER=0: rounds walk all states in index order (r3j behaviour)
   // a round takes unit * (this % * n / live states) shapes; 0 = off, -1 = the measured choice (profiles/r3l): 35 for
   // queries with records, 70 for flags-only queries
@@ -836,6 +840,7 @@ struct Tuning
     trace = (int)env("T4C_TRACE_PASSES", 0, 0);
     peer_push = (int)env("T4C_PEER_PUSH", 1, 0);
     live_order = (int)env("T4C_LIVE_ORDER", 1, 0);
+    epa_early = (int)env("T4C_EPA_EARLY", 1, 0);
     round_merge = (int)env("T4C_ROUND_MERGE", round_merge, -1);
   }
 };
@@ -954,6 +959,8 @@ static t4c_status runBatch(t4c_scene* s, BatchIO& io)
     plat::sync(s->stream);
     if (s->aux_stream)
       plat::sync(s->aux_stream);
+    if (s->epa_stream)
+      plat::sync(s->epa_stream);
     if (s->copy_stream)
       plat::sync(s->copy_stream);
     s->releaseWorkspace();
@@ -1261,6 +1268,19 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
     // tasks stay queued (and the next pass appends to them): a launch of a few hundred EPA tasks lasts as long as its
     // slowest task, so the rounds share ONE EPA launch instead of paying that tail once per round.
     uint32_t ntask_pending = 0;
+    size_t task_seg = 0;  // tasks in front of the pending ones that have been handed to an EPA launch already
+    struct EpaJoin
+    {
+      t4stream stream;
+      bool inflight = false;
+      void join()
+      {
+        if (inflight && stream)
+          plat::sync(stream);
+        inflight = false;
+      }
+      ~EpaJoin() { join(); }
+    } epa_join{ s->epa_stream };
     auto runEpa = [&](uint32_t ntask) -> t4c_status {
       launchEpa(P, ntask, st);
       return T4C_OK;
@@ -1268,10 +1288,11 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
     auto exactPass = [&](uint32_t* queue, uint32_t nq, bool run_epa) -> t4c_status {
       if (nq > 0)
       {
-        T4_TRY(s->d_tasks.ensureKeep(((size_t)ntask_pending + nq) * sizeof(EpaTask),
-                                     (size_t)ntask_pending * sizeof(EpaTask), st),
-               "EPA task queue");
-        P.tasks = s->d_tasks.as<EpaTask>();
+        const size_t need = (task_seg + ntask_pending + nq) * sizeof(EpaTask);
+        if (need > s->d_tasks.cap)
+          epa_join.join();  // the queue is about to move under the launch that reads its first segment
+        T4_TRY(s->d_tasks.ensureKeep(need, (task_seg + ntask_pending) * sizeof(EpaTask), st), "EPA task queue");
+        P.tasks = s->d_tasks.as<EpaTask>() + task_seg;
         P.task_cap = ntask_pending + nq;
         P.surv = queue;
         P.task_order = nullptr;
@@ -1293,6 +1314,34 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
         ntask_pending = 0;
         T4_TRY(plat::zero(P.qcount + Q_TASK, sizeof(uint32_t), st), "memset");
       }
+      return T4C_OK;
+    };
+    // The pending EPA tasks start NOW on their own stream while the main stream goes on with the next exact passes;
+    // tasks queued from here on form a new segment of the queue.  An EPA launch of a few thousand tasks lasts as long
+    // as its slowest task (1.5 - 2 ms) with a tenth of the GPU's thread slots busy: it costs the passes beside it
+    // next to nothing, and they no longer wait in front of it.
+    auto startEpaEarly = [&]() -> t4c_status {
+      if (!s->epa_stream || !tuning().epa_early || ntask_pending < 256 || epa_join.inflight)
+        return T4C_OK;
+      KParams PE = P;
+      const uint32_t* order = sortByType(s, P, nullptr, 1, ntask_pending);
+      if (order)
+      {
+        if (!s->d_epa_order.ensure((size_t)ntask_pending * sizeof(uint32_t)))
+        {
+          g_alloc_failed = false;
+          return T4C_OK;  // no room for the private order: the tasks stay pending for the launch at the end
+        }
+        T4_TRY(plat::d2d(s->d_epa_order.p, order, (size_t)ntask_pending * sizeof(uint32_t), st), "EPA task order");
+        PE.task_order = s->d_epa_order.as<uint32_t>();
+      }
+      else
+        PE.task_order = nullptr;
+      T4_TRY(plat::zero(P.qcount + Q_TASK, sizeof(uint32_t), st) && plat::sync(st), "EPA task queue");
+      launchEpa(PE, ntask_pending, s->epa_stream);
+      epa_join.inflight = true;
+      task_seg += ntask_pending;
+      ntask_pending = 0;
       return T4C_OK;
     };
     // pairs whose GJK ran out of its iteration budget (Q_LONG): all of them together, without a budget
@@ -1461,6 +1510,12 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
     rc = exactPass(s->d_surv4.as<uint32_t>(), nsurv4, false);
     if (rc != T4C_OK)
       return rc;
+    if (first_rec && n_rounds > 1)
+    {
+      rc = startEpaEarly();  // most EPA tasks come out of this pass (two thirds on configs[1])
+      if (rc != T4C_OK)
+        return rc;
+    }
     rc = exactPass(s->d_surv2.as<uint32_t>(), nsurv2, false);
     if (rc != T4C_OK)
       return rc;
@@ -1491,6 +1546,7 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
     P.active_shapes = all_active;
     P.n_active_shapes = n_all_active;
     P.n_aa_pairs = n_all_aa;
+    epa_join.join();
     T4_TRY(launchOk() && plat::d2h(qc, P.qcount, sizeof(qc), st) && plat::sync(st), "narrowphase (EPA)");
     const uint32_t nraw = qc[Q_RAW];
     if (closest)
@@ -1839,6 +1895,7 @@ t4c_status t4c_scene_create(const t4c_scene_desc* d, int32_t device, t4c_scene**
   s->stream = plat::newStream();
   s->copy_stream = plat::newStream();
   s->aux_stream = plat::newStream();
+  s->epa_stream = plat::newStream();
   for (auto& e : s->q_events)
     e = plat::newEvent();
   t4c_status rc = syncScene(s.get());
@@ -1860,6 +1917,7 @@ t4c_status t4c_scene_clone(const t4c_scene* src, t4c_scene** out)
   s->stream = plat::newStream();
   s->copy_stream = plat::newStream();
   s->aux_stream = plat::newStream();
+  s->epa_stream = plat::newStream();
   for (auto& e : s->q_events)
     e = plat::newEvent();
   if (src->uploaded == src->rev)

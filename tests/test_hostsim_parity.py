@@ -72,6 +72,22 @@ def test_first_in_rounds():
     assert r.returncode == 0, r.stdout + r.stderr
 
 
+@pytest.mark.parametrize("hooks", [dict(T4C_LIVE_ORDER="0"), dict(T4C_ROUND_MERGE="0"), dict(T4C_ROUND_MERGE="300")])
+def test_first_in_rounds_ab_switches(hooks):
+    """the A/B switches of the round scheduler (ordered live-state lists off, slice growth off / extreme): same flags
+    as the oracle, one record per colliding state"""
+    import subprocess, sys, os
+    code = ("import sys; sys.path.insert(0, 'tests'); import parity_cases as pc; from hostsim import build as h; "
+            "from tesseract_b200.managers import BatchChecker; from tesseract_b200 import capi; "
+            "mk = lambda b: BatchChecker(b, lib=h.lib()); "
+            "print(pc.discrete_config2(mk, 300, 10000, capi.TEST_FIRST)); "
+            "print(pc.flags_only(mk, 400, 10000))")
+    env = dict(os.environ, T4C_ROUND_MIN_STATES="1", **hooks)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout + r.stderr
+
+
 def test_config4_voxels_and_mesh():
     """configs[3] style: ABB hull links vs octomap voxels (fixture box_2m.bt) + the plane_4m.stl triangle mesh"""
     import os
