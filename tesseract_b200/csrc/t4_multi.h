@@ -102,6 +102,7 @@ struct t4c_comm
   DevBuf d_header;  // [world] headers (root receives into it; every rank stages its own in slot `rank`)
   // root side: the gather slab, [world] regions of slab_region records
   DevBuf d_slab;
+  std::vector<std::unique_ptr<DevBuf>> retired;  // earlier, smaller slabs (see pushHandshake)
   int64_t slab_region = 0;
   uint64_t slab_gen = 0;
   cudaIpcMemHandle_t slab_handle;
@@ -170,6 +171,14 @@ static t4c_status pushHandshake(t4c_scene* s, t4c_comm* c, int root, const t4c_g
       bool ok = true;
       if (bytes > c->d_slab.cap)
       {
+        // a slab that peers may still have mapped is never freed under them (freeing exported memory before the
+        // importers have closed it is undefined): it is retired until the communicator goes away
+        if (c->d_slab.p)
+        {
+          c->retired.emplace_back(new DevBuf());
+          std::swap(c->retired.back()->p, c->d_slab.p);
+          std::swap(c->retired.back()->cap, c->d_slab.cap);
+        }
         ok = c->d_slab.ensure(bytes);
         c->slab_handle_ok = ok && cudaIpcGetMemHandle(&c->slab_handle, c->d_slab.p) == cudaSuccess;
         ++c->slab_gen;
@@ -379,6 +388,8 @@ static t4c_status checkSharded(t4c_scene* s, const t4c_fk_model* m, t4c_comm* c,
     return fail(T4C_ERR_CUDA, "libnccl.so.2 could not be loaded");
   if (s->device != c->device)
     return fail(T4C_ERR_INVALID, "scene is on device %d, communicator on device %d", s->device, c->device);
+  if (!bindDevice(s))
+    return fail(T4C_ERR_CUDA, "cudaSetDevice(%d): %s", s->device, plat::lastError());
   BatchIO io;
   io.n = n_local;
   io.cast = cast;
