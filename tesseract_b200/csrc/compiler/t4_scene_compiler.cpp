@@ -688,6 +688,26 @@ std::string resolve(const std::string& uri, const std::string& package_root)
   return uri;
 }
 
+// occupied leaves of an octomap -> one box / sphere per leaf, leaf-iterator order, child index = subshape_id
+// (createShapePrimitive(Octree), bullet_utils.cpp:160-243: box half = size / 2, sphere inside r = size / 2, sphere
+// outside r = sqrt(2) size / 2); `base` = pose of the octree in the link frame
+void addOctomapLeaves(t4c_compiled& C, int li, int shape_id, const std::vector<double>& leaves, int sub_type, const Pose& base)
+{
+  for (size_t v = 0; v < leaves.size() / 4; ++v)
+  {
+    Pose L;
+    L.m[3] = leaves[4 * v], L.m[7] = leaves[4 * v + 1], L.m[11] = leaves[4 * v + 2];
+    const Pose P = base.identity() ? L : base * L;
+    const double h = leaves[4 * v + 3] / 2;
+    if (sub_type == 0)
+      C.shape(T4C_BOX, li, shape_id, (int)v, h, h, h, P);
+    else if (sub_type == 1)
+      C.shape(T4C_SPHERE, li, shape_id, (int)v, h, 0, 0, P);
+    else
+      C.shape(T4C_SPHERE, li, shape_id, (int)v, std::sqrt(2 * (h * h)), 0, 0, P);
+  }
+}
+
 // geometry of one <collision> -> shape records of link `li` (shape_id = index in the link's geometry list)
 t4c_status addGeometry(t4c_compiled& C, int li, int shape_id, bool single, const Xml* geom, const Pose& P,
                        const std::string& package_root, bool convex)
@@ -719,6 +739,29 @@ t4c_status addGeometry(t4c_compiled& C, int li, int shape_id, bool single, const
   if (const Xml* c = geom->child("cone"))
   {
     C.shape(T4C_CONE, li, shape_id, sub, std::atof(c->get("radius").c_str()), std::atof(c->get("length").c_str()), 0, P);
+    return T4C_OK;
+  }
+  if (const Xml* o = geom->child("octomap"))
+  {
+    // <octomap shape_type="box|sphere_inside|sphere_outside" [prune]><octree filename=".bt"/></octomap>
+    // (tesseract_urdf/src/octomap.cpp:44-96, octree.cpp:33-59).  `prune` (merging of equal children after loading) is
+    // not applied: a .bt file stores the tree as it was pruned when written.  <point_cloud> is not read.
+    const std::string st = o->get("shape_type");
+    const int sub_type = st == "box" ? 0 : (st == "sphere_inside" ? 1 : (st == "sphere_outside" ? 2 : -1));
+    if (sub_type < 0)
+      return cfail(T4C_ERR_INVALID, "octomap: shape_type must be 'box', 'sphere_inside' or 'sphere_outside'");
+    const Xml* ot = o->child("octree");
+    if (!ot)
+      return cfail(o->child("point_cloud") ? T4C_ERR_UNSUPPORTED : T4C_ERR_INVALID,
+                   "octomap: missing element 'octree' (point clouds are not read)");
+    std::string data, err;
+    const std::string path = resolve(ot->get("filename"), package_root);
+    if (!readFile(path, data))
+      return cfail(T4C_ERR_INVALID, "octree: cannot read " + path);
+    std::vector<double> leaves;
+    if (!loadBt(data, leaves, err))
+      return cfail(T4C_ERR_INVALID, err);
+    addOctomapLeaves(C, li, shape_id, leaves, sub_type, P);
     return T4C_OK;
   }
   const Xml* m = geom->child("mesh");
@@ -926,19 +969,7 @@ t4c_status t4c_compiled_add_octomap(t4c_compiled* c, const char* link_name, cons
   if (pose12)
     std::memcpy(c->links[li].pose, pose12, 12 * sizeof(double));
   const int shape_id = c->shapes_of_link[li]++;
-  for (size_t v = 0; v < leaves.size() / 4; ++v)
-  {
-    Pose P;
-    P.m[3] = leaves[4 * v], P.m[7] = leaves[4 * v + 1], P.m[11] = leaves[4 * v + 2];
-    const double h = leaves[4 * v + 3] / 2;
-    // bullet_utils.cpp:182-183,205,228: box of half = size / 2, sphere inside r = size / 2, sphere outside r = sqrt(2) size / 2
-    if (sub_type == 0)
-      c->shape(T4C_BOX, li, shape_id, (int)v, h, h, h, P);
-    else if (sub_type == 1)
-      c->shape(T4C_SPHERE, li, shape_id, (int)v, h, 0, 0, P);
-    else
-      c->shape(T4C_SPHERE, li, shape_id, (int)v, std::sqrt(2 * (h * h)), 0, 0, P);
-  }
+  addOctomapLeaves(*c, li, shape_id, leaves, sub_type == 0 ? 0 : (sub_type == 1 ? 1 : 2), Pose());
   c->refresh();
   return T4C_OK;
 }

@@ -143,3 +143,71 @@ def test_compiled_scene_gives_the_same_contacts():
     assert max(abs(mine[k] - ref[k]) for k in mine) <= 1e-6  # hull vertex ORDER may differ (support ties), not the hull
     lib.t4c_fk_model_destroy(model)
     lib.t4c_scene_destroy(scene)
+
+
+def _write_bt(path, occupied, res=0.1, depth=16):
+    """minimal writer of the octomap binary format: a tree with the given occupied depth-16 voxels
+    (integer keys per axis, 0 .. 2^16 - 1), everything else unknown; children of a node in index order 0..7,
+    two bits per child at (2c, 2c + 1): (0, 1) occupied leaf, (1, 1) inner node, (0, 0) unknown"""
+    tree = {}
+    for k in occupied:
+        node = tree
+        for d in range(depth - 1, -1, -1):
+            c = (((k[0] >> d) & 1) << 0) | (((k[1] >> d) & 1) << 1) | (((k[2] >> d) & 1) << 2)
+            node = node.setdefault(c, {})
+    out = bytearray()
+    n_nodes = [1]
+
+    def emit(node):
+        bits = 0
+        for c in range(8):
+            if c in node:
+                bits |= (0b11 if node[c] else 0b10) << (2 * c)
+                n_nodes[0] += 1
+        out.extend(int(bits).to_bytes(2, "little"))
+        for c in range(8):
+            if c in node and node[c]:
+                emit(node[c])
+
+    emit(tree)
+    with open(path, "wb") as f:
+        f.write(b"# Octomap OcTree binary file\nid OcTree\nsize %d\nres %g\ndata\n" % (n_nodes[0], res))
+        f.write(bytes(out))
+
+
+def test_urdf_octomap_element(tmp_path):
+    """<octomap shape_type=...><octree filename=.bt/></octomap> in a URDF collision (tesseract_urdf/src/octomap.cpp):
+    one box / sphere per occupied leaf in the collision's frame; self-contained (writes its own .bt)"""
+    half = 1 << 15
+    keys = [(half + 3, half + 1, half), (half - 2, half + 7, half + 4), (half, half, half), (half + 3, half + 1, half + 1)]
+    bt = tmp_path / "tiny.bt"
+    _write_bt(str(bt), keys, res=0.1)
+    leaves = compiler.read_octomap_bt(str(bt))
+    assert leaves.shape == (4, 4)
+    want = sorted(tuple((np.array(k) - half + 0.5) * 0.1) for k in keys)
+    assert np.abs(np.array(sorted(map(tuple, leaves[:, :3]))) - np.array(want)).max() < 1e-9
+    assert np.allclose(leaves[:, 3], 0.1)
+    for shape_type, t4_type, r in (("box", capi.BOX, 0.05), ("sphere_inside", capi.SPHERE, 0.05),
+                                   ("sphere_outside", capi.SPHERE, np.sqrt(2 * 0.05 ** 2))):
+        urdf = tmp_path / f"map_{shape_type}.urdf"
+        urdf.write_text(f"""<robot name="m"><link name="world"/><link name="map">
+  <collision><origin xyz="1 2 3" rpy="0 0 1.5707963267948966"/>
+    <geometry><octomap shape_type="{shape_type}"><octree filename="{bt}"/></octomap></geometry></collision></link>
+  <joint name="j" type="fixed"><parent link="world"/><child link="map"/></joint></robot>""")
+        cs = compiler.CompiledScene(str(urdf), None, convex=True)
+        sd = cs.scene_desc()
+        assert sd.n_shapes == 4
+        li = cs.link_index("map")
+        for i in range(4):
+            sh = sd.shapes[i]
+            assert sh.link == li and sh.type == t4_type and sh.subshape_id == i
+            assert abs(sh.params[0] - r) < 1e-12
+            # leaf centre (x, y, z) in the collision frame, rotated by 90 degrees about z and shifted by (1, 2, 3)
+            x, y, z = leaves[i, :3]
+            p = np.array([sh.pose[3], sh.pose[7], sh.pose[11]])
+            assert np.abs(p - np.array([1 - y, 2 + x, 3 + z])).max() < 1e-9
+    bad = tmp_path / "bad.urdf"
+    bad.write_text(f"""<robot name="m"><link name="map"><collision><geometry><octomap shape_type="cube">
+      <octree filename="{bt}"/></octomap></geometry></collision></link></robot>""")
+    with pytest.raises(compiler.CompilerError):
+        compiler.CompiledScene(str(bad), None)
