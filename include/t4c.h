@@ -210,6 +210,9 @@ typedef struct t4c_device_io {
 
 const char* t4c_last_error(void);
 int32_t t4c_abi_version(void);
+/* "cuda sm_100a" for the product library; "hostsim" for the host simulation of the kernel bodies that the CPU test
+ * tier builds (tests/hostsim) -- the Python binding refuses to load the latter as the product library */
+const char* t4c_build_info(void);
 int32_t t4c_device_count(void);
 
 t4c_status t4c_scene_create(const t4c_scene_desc* desc, int32_t device, t4c_scene** out);

@@ -106,6 +106,11 @@ def load_library(path=None):
     VP, I32, I64, DP = C.c_void_p, C.c_int32, C.c_int64, C.POINTER(C.c_double)
     lib.t4c_last_error.restype = C.c_char_p
     lib.t4c_abi_version.restype = I32
+    lib.t4c_build_info.restype = C.c_char_p
+    if path is None and lib.t4c_build_info() != b"cuda sm_100a":
+        # only the tests hand over the host simulator, and they do it explicitly (path=...): never through T4C_LIB
+        raise RuntimeError(f"{p} is not the CUDA build of libt4c.so ({lib.t4c_build_info().decode()}); "
+                           "there is no CPU fallback")
     lib.t4c_device_count.restype = I32
     lib.t4c_scene_create.argtypes = [C.POINTER(SceneDesc), I32, C.POINTER(VP)]
     lib.t4c_scene_clone.argtypes = [VP, C.POINTER(VP)]

@@ -1825,6 +1825,14 @@ static t4c_status measurePeak(int32_t device, double* tflops, K kernel, int iter
 extern "C" {
 const char* t4c_last_error(void) { return g_err.c_str(); }
 int32_t t4c_abi_version(void) { return T4C_ABI_VERSION; }
+const char* t4c_build_info(void)
+{
+#ifdef T4C_HOSTSIM
+  return "hostsim";
+#else
+  return "cuda sm_100a";
+#endif
+}
 int32_t t4c_device_count(void) { return plat::deviceCount(); }
 uint64_t t4c_kernel_launch_count(void) { return g_launches.load(); }
 void t4c_profile_enable(int32_t on)

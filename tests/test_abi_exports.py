@@ -4,6 +4,8 @@ import ctypes as C
 import os
 import re
 
+import pytest
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
@@ -39,3 +41,17 @@ def test_no_cpu_fallback_without_device():
     st = lib.t4c_scene_create(C.byref(desc), 0, C.byref(h))
     assert st == capi.T4C_ERR_CUDA
     assert b"no CPU path" in lib.t4c_last_error()
+
+
+def test_product_binding_refuses_the_host_simulator(monkeypatch):
+    """T4C_LIB may point the binding at another CUDA build of the library, never at the CPU-tier host simulator"""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from hostsim import build as hostsim
+    from tesseract_b200 import capi
+    assert capi.load_library().t4c_build_info() == b"cuda sm_100a"
+    assert hostsim.lib().t4c_build_info() == b"hostsim"  # explicit path: the tests' own use
+    monkeypatch.setenv("T4C_LIB", hostsim.LIB)
+    monkeypatch.setattr(capi, "_lib", None)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        capi.load_library()
