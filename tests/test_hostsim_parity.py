@@ -142,3 +142,42 @@ def test_phase1_certificate_never_contradicted():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+def test_round_scheduler_edge_cases():
+    """FIRST in rounds on the corner inputs: a scene without static shapes (no environment tree: self-collision only),
+    batches of 0 / 1 / 2 states, cast segments, flags without distance and penetration"""
+    import subprocess, sys, os
+    code = r'''
+import sys; sys.path.insert(0, "tests")
+import numpy as np
+from hostsim import build as h
+from tesseract_b200.managers import BatchChecker
+from tesseract_b200 import capi, scene as S
+from oracle import pyoracle
+lib = h.lib()
+b = S.SceneBuilder(); S.add_robot(b, S.load_robot("abb_irb2400")); b.set_margin(0.05)
+q = S.random_states(b, 300, seed=3, dtype=np.float64)
+hit, con, st = BatchChecker(b, lib=lib).check_discrete(q, capi.TEST_FIRST)
+assert np.array_equal(hit, pyoracle.check_discrete(b, q, capi.TEST_FIRST)[0]) and len(con) == int(hit.sum())
+b2 = S.build_config2(n_prims=500, margin=0.05)
+bc2 = BatchChecker(b2, lib=lib)
+for n in (1, 2, 0):
+    q2 = S.random_states(b2, max(n, 1), seed=5, dtype=np.float64)[:n]
+    hit, con, st = bc2.check_discrete(q2, capi.TEST_FIRST)
+    want = pyoracle.check_discrete(b2, q2, capi.TEST_FIRST)[0] if n else np.zeros(0, np.uint8)
+    assert np.array_equal(hit, want) and len(con) == int(hit.sum())
+q0 = S.random_states(b2, 200, seed=6, dtype=np.float64)
+q1 = q0 + 0.05 * np.random.default_rng(1).standard_normal(q0.shape)
+hit, con, loc, st = bc2.check_cast(q0, q1, capi.TEST_FIRST)
+assert np.array_equal(hit, pyoracle.check_cast(b2, q0, q1, capi.TEST_FIRST)[0]) and len(con) == int(hit.sum())
+hit, con, st = bc2.check_discrete(q0, capi.TEST_FIRST, calculate_penetration=False, calculate_distance=False,
+                                  want_contacts=False)
+assert np.array_equal(hit, pyoracle.check_discrete(b2, q0, capi.TEST_FIRST, calculate_penetration=False,
+                                                   calculate_distance=False)[0])
+print("edge cases ok")
+'''
+    env = dict(os.environ, T4C_ROUND_MIN_STATES="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0 and "edge cases ok" in r.stdout, r.stdout + r.stderr
