@@ -15,7 +15,10 @@ using namespace t4;
 
 // 128-register budget (four 128-thread CTAs per SM): measured faster on B200 than the unconstrained build (r1d); tighter
 // budgets (96 / 80 registers) made no difference (r2a sweep)
-__global__ void __launch_bounds__(128, 4) gjkKernelR128(KParams P, int64_t n)
+#ifndef T4_GJK_MIN_CTAS
+#define T4_GJK_MIN_CTAS 4
+#endif
+__global__ void __launch_bounds__(128, T4_GJK_MIN_CTAS) gjkKernelR128(KParams P, int64_t n)
 {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     gjkBody(i, P);
