@@ -1504,9 +1504,10 @@ static t4c_status runBatchChunked(t4c_scene* s, BatchIO& io, int64_t CH)
     }
     // ---- deferred tiers, for the states that are still without a contact (no pair of theirs is certainly in contact
     //      with its cores certainly apart): the rest first -- a pair that turns out to be separated and within the
-    //      margin settles the state without EPA -- then the certainly penetrating ones.  Their EPA tasks share ONE
-    //      launch at the end (longPass below): a launch of a few thousand tasks lasts as long as its slowest task
-    //      (~1 ms against a cylinder), and tasks of states that were settled meanwhile leave at once.
+    //      margin settles the state without EPA -- then the certainly penetrating ones.  A launch of a few thousand
+    //      EPA tasks lasts as long as its slowest task (1.5 - 2 ms against a cylinder): the tasks of the first pass
+    //      start at once on their own stream (startEpaEarly), the others share ONE launch at the end (longPass
+    //      below), and tasks of states that were settled meanwhile leave at once.
     rc = exactPass(s->d_surv4.as<uint32_t>(), nsurv4, false);
     if (rc != T4C_OK)
       return rc;
