@@ -599,6 +599,10 @@ T4_KD void pushCandidate(const KParams& P, int64_t s, int a, int b)
 #define T4_CULL_SLACK 2e-5f
 
 // item = a_ord * n + s  (shape-major, so that a warp works on 32 states of the SAME robot shape)
+// resident 128-thread CTAs per SM of the EPA kernel (register budget 65536 / (128 * this)); sweeps: profiles/r2a, r3z
+#ifndef T4_EPA_MIN_CTAS
+#define T4_EPA_MIN_CTAS 4
+#endif
 #define T4_DEAD_STATE 0xffffffffu
 #define T4_LIVE_BITS 7 /* Morton grid: 2^7 cells per axis; key = 21 bits + the dead flag */
 

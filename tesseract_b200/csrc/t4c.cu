@@ -488,7 +488,7 @@ static void launchEpa(const KParams& P, int64_t n, t4stream st)
     block = 32;
   else if (n <= (int64_t)smCount() * 4 * 64)
     block = 64;
-  t4LaunchEpa(P, n, gridFor(n, block, 4 * (128 / block), true), block, st);
+  t4LaunchEpa(P, n, gridFor(n, block, T4_EPA_MIN_CTAS * (128 / block), true), block, st);
   profEnd(st);
   ++g_launches;
 }

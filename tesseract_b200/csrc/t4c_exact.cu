@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(128, T4_GJK_MIN_CTAS) gjkKernelR128(KParams P,
 // of a task -- seed GJK, support mapping, phase 4 -- is most of its instructions, a warp instruction costs the same
 // issue slot for one active lane as for 32, and shared memory holds 64 tasks per SM where this kernel keeps 512 in
 // flight to hide the FP64 dependency latency.
-__global__ void __launch_bounds__(128, 4) epaKernelR128(KParams P, int64_t n)
+__global__ void __launch_bounds__(128, T4_EPA_MIN_CTAS) epaKernelR128(KParams P, int64_t n)
 {
   Epa<double> epa;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
