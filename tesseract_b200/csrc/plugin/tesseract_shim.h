@@ -175,6 +175,21 @@ public:
   }
   const PairsCollisionMarginData& getPairCollisionMargins() const { return lookup_table_; }
   double getMaxCollisionMargin() const { return max_collision_margin_; }
+  // collision_margin_data.h:163-181: every margin moves, so the maximum moves with them
+  void incrementMargins(const double& increment)
+  {
+    default_collision_margin_ += increment;
+    max_collision_margin_ += increment;
+    for (auto& p : lookup_table_)
+      p.second += increment;
+  }
+  void scaleMargins(const double& scale)
+  {
+    default_collision_margin_ *= scale;
+    max_collision_margin_ *= scale;
+    for (auto& p : lookup_table_)
+      p.second *= scale;
+  }
   void apply(const CollisionMarginData& d, CollisionMarginOverrideType t)
   {
     switch (t)

@@ -59,3 +59,14 @@ def test_plugin_library_exports():
     lib = ctypes.CDLL(os.path.join(ROOT, "tesseract_b200", "csrc", "libtesseract_b200_managers.so"))
     for sym in ("tesseract_b200_create_discrete_manager", "tesseract_b200_create_cast_manager"):
         assert hasattr(lib, sym)
+
+
+def test_cpp_margin_data():
+    """CollisionMarginData (a14) with the numbers of the reference's collision_margin_data_unit.cpp; host only"""
+    out = os.path.join(ROOT, "tests", "cpp", "test_margin_data.bin")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-Wall", "-Wextra", "-Werror",
+                           os.path.join(ROOT, "tests", "cpp", "test_margin_data.cpp"), "-I" + os.path.join(ROOT, "include"),
+                           "-o", out])
+    r = subprocess.run([out], capture_output=True, text=True, timeout=60)
+    print(r.stdout, r.stderr)
+    assert r.returncode == 0 and "0 failures" in r.stdout, r.stdout + r.stderr
