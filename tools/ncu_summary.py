@@ -11,7 +11,7 @@ import json
 import sys
 from collections import OrderedDict
 
-NAMES = OrderedDict([("fkKernelT", "fk"), ("broadStaticKernel", "broad_static"), ("broadActiveKernel", "broad_active"),
+NAMES = OrderedDict([("fkKernelT", "fk"), ("broadStaticKernel", "broad_static"), ("liveKeyKernel", "broad_static"), ("broadActiveKernel", "broad_active"),
                      ("cullKernel", "cull_fp32"), ("pruneKernel", "cull_fp32"), ("gjkKernelR128", "gjk_fp64"),
                      ("epaKernelR128", "epa_fp64")])
 
